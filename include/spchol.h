@@ -1,0 +1,115 @@
+/*
+ * spchol.h -- C-ABI of the B200-native sparse Cholesky (libspchol.so).
+ *
+ * This is the drop-in boundary for the reference's numeric hot path.  The reference
+ * (evanwporter/SparseCholesky) has no FFI of its own; its boundary is the public C++ header
+ * API.  Each entry point below names the reference interface it replaces (file:line relative
+ * to the reference tree).  The C++23 host header include/chol.hpp (same public names as the
+ * reference's include/chol.hpp) and the Python binding sparsecholesky_b200/api.py are thin
+ * wrappers over exactly these symbols.  INTEGRATION.md shows the reference-side binding.
+ *
+ * Conventions: plain pointers and sizes only; A is the upper triangle in CSC (row <= col,
+ * rows ascending per column) exactly as triplet_to_csc_matrix produces it; L is lower CSC,
+ * diagonal first, rows ascending (reference include/chol.hpp:844-855).  All functions return
+ * 0 on success, a negative code on error (text via spchol_last_error()).  There is NO CPU
+ * fallback: numeric entry points fail with SPCHOL_ENOGPU when no CUDA device is usable.
+ */
+#ifndef SPCHOL_H
+#define SPCHOL_H
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SPCHOL_OK        0
+#define SPCHOL_EINVAL   -1   /* malformed argument / pattern */
+#define SPCHOL_ENOMEM   -2
+#define SPCHOL_ENOGPU   -3   /* no CUDA device: the product path never falls back to the CPU */
+#define SPCHOL_ECUDA    -4   /* CUDA runtime error */
+#define SPCHOL_ERANGE   -5   /* nnz(L) does not fit the 32-bit CSC the reference API uses */
+#define SPCHOL_EIO      -6
+
+typedef struct spchol_symbolic spchol_symbolic;  /* host symbolic analysis == reference SChol + supernodes */
+typedef struct spchol_plan     spchol_plan;      /* device-resident numeric plan for one pattern */
+
+const char* spchol_last_error(void);
+const char* spchol_version(void);
+int spchol_device_count(void);   /* 0 when no usable GPU */
+
+/* ---- ingest ------------------------------------------------------------------------------ */
+/* replaces triplet_to_csc_matrix<T> (include/chol.hpp:309-369). Ap[n+1], Ai/Ax[nz] caller
+ * allocated; *nnz_out = merged entry count. */
+int spchol_triplet_to_csc(int64_t nz, const int* ti, const int* tj, const double* tx, int n,
+                          int* Ap, int* Ai, double* Ax, int64_t* nnz_out);
+/* replaces load_matrix_market_to_csc<T> (include/mtx_reader.hpp:17-62): same parsing rules
+ * (skip '%' lines, "rows cols nnz", 1-based triples mirrored to the upper triangle).
+ * Two-call protocol: with ti == NULL only *n_out / *nz_out are written. */
+int spchol_mtx_read(const char* path, int* n_out, int64_t* nz_out, int* ti, int* tj, double* tx);
+
+/* ---- symbolic helpers (integer only, host) ------------------------------------------------ */
+int spchol_etree(int n, const int* Ap, const int* Ai, int* parent);                 /* chol.hpp:378  */
+int spchol_post_order(int n, const int* parent, int* post);                          /* chol.hpp:466  */
+int spchol_col_count(int n, const int* Ap, const int* Ai, const int* parent,
+                     const int* post, int* colcount);                               /* chol.hpp:567  */
+int spchol_ereach(int n, const int* Ap, const int* Ai, const double* Ax, int k,
+                  const int* parent, int* s, int* w, double* x, int top);           /* chol.hpp:725/:737, returns new top */
+int spchol_compute_levels(int n, const int* parent, int* level_ptr, int* level_nodes); /* src/chol.cpp:7, returns #levels */
+int spchol_compute_supernodes(int n, const int* parent, const int64_t* Lp,
+                              int* sn_id, int* sn_start);                           /* src/chol.cpp:42, returns #supernodes */
+int spchol_atree(int n, const int* parent, const int* sn_id, int ns, const int* sn_start,
+                 int* super_parent);                                                /* src/chol.cpp:102 */
+
+/* ---- symbolic phase: replaces schol<T>(A) (include/chol.hpp:874-946) ---------------------- */
+int     spchol_symbolic_create(int n, const int* Ap, const int* Ai, spchol_symbolic** out);
+/* same, with explicit amalgamation control: relax = 0 keeps the reference's fundamental supernodes */
+int     spchol_symbolic_create_ex(int n, const int* Ap, const int* Ai, int relax, spchol_symbolic** out);
+void    spchol_symbolic_destroy(spchol_symbolic*);
+int     spchol_symbolic_n(const spchol_symbolic*);
+int64_t spchol_symbolic_nnzL(const spchol_symbolic*);
+double  spchol_symbolic_flops(const spchol_symbolic*);          /* sum_j colcount_j^2 */
+int     spchol_symbolic_parent(const spchol_symbolic*, int* parent);          /* SChol::parent */
+int     spchol_symbolic_colcount(const spchol_symbolic*, int* colcount);
+int     spchol_symbolic_Lp64(const spchol_symbolic*, int64_t* Lp);            /* n+1 */
+int     spchol_symbolic_Lp(const spchol_symbolic*, int* Lp);                  /* SChol::p(); SPCHOL_ERANGE if > INT_MAX */
+int     spchol_symbolic_Li(const spchol_symbolic*, int* Li);                  /* SChol::i() */
+/* supernode partition: which = 0 fundamental (reference rule), 1 = relaxed fronts actually factored */
+int     spchol_symbolic_supernodes(const spchol_symbolic*, int which, int* ns_out,
+                                   int* sn_start /* n+1 slots */, int* sn_parent /* n slots */);
+/* stats[0..7] = ns_fund, ns_relaxed, sum_m, panel_entries, padded_zeros, max_w, max_m, nlevels(relaxed) */
+int     spchol_symbolic_stats(const spchol_symbolic*, int64_t* stats);
+
+/* ---- numeric plan + factorization: replaces chol<T>(A) (include/chol.hpp:750-863) --------- */
+/* device: CUDA ordinal. The plan owns the device L buffer and contribution workspace. */
+int  spchol_plan_create(const spchol_symbolic*, int device, spchol_plan** out);
+void spchol_plan_destroy(spchol_plan*);
+/* plan_stats[0..9] = ns, nlevels, n_small, n_large, lbuf_entries, ws_entries, n_ops, max_m, max_w, device_bytes */
+int  spchol_plan_stats(const spchol_plan*, int64_t* stats);
+
+/* Host-buffer call (what chol(A,S) binds): H2D of Ax, factor, CSC gather, D2H of Lx.
+ * info = 0, or (1-based) a column whose pivot was <= 0 -> "A is not positive definite." (chol.hpp:849-850). */
+int  spchol_factor(spchol_plan*, const double* Ax_host, double* Lx_host, int* info);
+/* Device-resident call: dAx is a device pointer (nnzA doubles); L stays on the device in
+ * supernodal panels.  Asynchronous on the plan's stream; *info is valid after spchol_sync. */
+int  spchol_factor_device(spchol_plan*, const double* dAx);
+int  spchol_export_csc_device(spchol_plan*, double* dLx);      /* gather panels -> CSC order (device ptr) */
+int  spchol_sync(spchol_plan*, int* info);
+/* pointer to the device L buffer (supernodal panels), for callers that keep L resident */
+int  spchol_lbuf(spchol_plan*, double** dL, int64_t* entries);
+/* copy the supernodal L buffer to host (entries doubles) */
+int  spchol_lbuf_to_host(spchol_plan*, double* L_host);
+/* timing of the last spchol_factor call, milliseconds: [h2d, numeric, export, d2h] */
+int  spchol_last_timing(const spchol_plan*, double* ms4);
+/* stream handle (cudaStream_t) the plan launches on, for CUDA-event timing by the caller */
+void* spchol_stream(spchol_plan*);
+/* number of kernel launches the last factorization issued */
+int64_t spchol_last_launches(const spchol_plan*);
+
+/* ||A - L L^T||_F / ||A||_F evaluated on the device over the pattern of L (exact, not sampled):
+ * uses the CSC L of the last spchol_factor / export. Only for nnz(L) <= INT_MAX. */
+int  spchol_residual(spchol_plan*, const double* Ax_host, double* rel_fro);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* SPCHOL_H */

@@ -1,0 +1,7 @@
+"""spchol-b200: B200-native multifrontal sparse Cholesky behind the reference's host API."""
+from .api import (  # noqa: F401
+    CscMatrix, SChol, Expected, Sym,
+    triplet_to_csc_matrix, load_matrix_market_to_csc, build_csc_matrix_from_pattern,
+    etree, post_order, col_count, ereach, compute_levels, compute_supernodes, atree,
+    schol, chol, csc_to_dense, device_count,
+)

@@ -1,0 +1,158 @@
+// Host-only part of the C-ABI (ingest + symbolic); see include/spchol.h for the contract and
+// the reference interfaces each entry point replaces.
+#include <climits>
+#include <cstdio>
+#include <cstring>
+#include <fstream>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/spchol.h"
+#include "capi_internal.h"
+
+namespace spchol {
+static thread_local std::string g_error;
+void set_error(const std::string& msg) { g_error = msg; }
+}  // namespace spchol
+using namespace spchol;
+
+extern "C" {
+
+const char* spchol_last_error(void) { return g_error.c_str(); }
+const char* spchol_version(void) { return "spchol-b200 0.1 (sm_100a)"; }
+
+int spchol_triplet_to_csc(int64_t nz, const int* ti, const int* tj, const double* tx, int n,
+                          int* Ap, int* Ai, double* Ax, int64_t* nnz_out) {
+    if (n <= 0 || nz < 0 || !Ap || (nz > 0 && (!ti || !tj || !tx || !Ai || !Ax))) {
+        set_error("spchol_triplet_to_csc: bad argument"); return SPCHOL_EINVAL;
+    }
+    const int64_t m = triplet_to_csc(nz, ti, tj, tx, n, Ap, Ai, Ax);
+    if (m < 0) { set_error("spchol_triplet_to_csc: index out of range"); return SPCHOL_EINVAL; }
+    if (m > INT_MAX) { set_error("spchol_triplet_to_csc: nnz exceeds int"); return SPCHOL_ERANGE; }
+    if (nnz_out) *nnz_out = m;
+    return SPCHOL_OK;
+}
+
+// Matrix Market coordinate reader with the reference's rules (include/mtx_reader.hpp:17-62):
+// leading '%' lines skipped, then "rows cols nnz", then nnz 1-based (row col value) triples,
+// each mirrored into the upper triangle.  The banner is not interpreted.
+int spchol_mtx_read(const char* path, int* n_out, int64_t* nz_out, int* ti, int* tj, double* tx) {
+    if (!path || !n_out || !nz_out) { set_error("spchol_mtx_read: null argument"); return SPCHOL_EINVAL; }
+    std::ifstream f(path);
+    if (!f) { set_error(std::string("Could not open file ") + path); return SPCHOL_EIO; }
+    while (f.peek() == '%') f.ignore(1 << 20, '\n');
+    long long nr = 0, nc = 0, nl = 0;
+    if (!(f >> nr >> nc >> nl) || nr <= 0 || nr != nc || nl < 0 || nr > INT_MAX) {
+        set_error("spchol_mtx_read: bad size line (matrix must be square)"); return SPCHOL_EINVAL;
+    }
+    *n_out = static_cast<int>(nr);
+    *nz_out = nl;
+    if (!ti) return SPCHOL_OK;
+    for (long long l = 0; l < nl; ++l) {
+        long long r, c; double v;
+        if (!(f >> r >> c >> v)) { set_error("spchol_mtx_read: truncated file"); return SPCHOL_EIO; }
+        --r; --c;
+        if (c < r) std::swap(r, c);
+        ti[l] = static_cast<int>(r); tj[l] = static_cast<int>(c); tx[l] = v;
+    }
+    return SPCHOL_OK;
+}
+
+int spchol_etree(int n, const int* Ap, const int* Ai, int* parent) {
+    if (n <= 0 || !Ap || !Ai || !parent) return SPCHOL_EINVAL;
+    etree(n, Ap, Ai, parent); return 0;
+}
+int spchol_post_order(int n, const int* parent, int* post) {
+    if (n <= 0 || !parent || !post) return SPCHOL_EINVAL;
+    post_order(n, parent, post); return 0;
+}
+int spchol_col_count(int n, const int* Ap, const int* Ai, const int* parent, const int* post, int* cc) {
+    if (n <= 0 || !Ap || !Ai || !parent || !post || !cc) return SPCHOL_EINVAL;
+    col_count(n, Ap, Ai, parent, post, cc); return 0;
+}
+int spchol_ereach(int n, const int* Ap, const int* Ai, const double* Ax, int k, const int* parent,
+                  int* s, int* w, double* x, int top) {
+    return ereach(n, Ap, Ai, Ax, k, parent, s, w, x, top);
+}
+int spchol_compute_levels(int n, const int* parent, int* level_ptr, int* level_nodes) {
+    return compute_levels(n, parent, level_ptr, level_nodes);
+}
+int spchol_compute_supernodes(int n, const int* parent, const int64_t* Lp, int* sn_id, int* sn_start) {
+    return compute_supernodes(n, parent, Lp, sn_id, sn_start);
+}
+int spchol_atree(int n, const int* parent, const int* sn_id, int ns, const int* sn_start, int* sp) {
+    atree_from_etree(n, parent, sn_id, ns, sn_start, sp); return 0;
+}
+
+int spchol_symbolic_create_ex(int n, const int* Ap, const int* Ai, int relax, spchol_symbolic** out) {
+    if (!out || !Ap || !Ai) { set_error("spchol_symbolic_create: null argument"); return SPCHOL_EINVAL; }
+    *out = nullptr;
+    spchol_symbolic* s = new (std::nothrow) spchol_symbolic();
+    if (!s) return SPCHOL_ENOMEM;
+    try {
+        RelaxParams rp; rp.enable = relax != 0;
+        analyze(n, Ap, Ai, rp, s->S);
+    } catch (const std::bad_alloc&) { delete s; set_error("out of host memory"); return SPCHOL_ENOMEM;
+    } catch (const std::exception& e) { delete s; set_error(e.what()); return SPCHOL_EINVAL; }
+    *out = s;
+    return SPCHOL_OK;
+}
+int spchol_symbolic_create(int n, const int* Ap, const int* Ai, spchol_symbolic** out) {
+    return spchol_symbolic_create_ex(n, Ap, Ai, 1, out);
+}
+void spchol_symbolic_destroy(spchol_symbolic* s) { delete s; }
+int spchol_symbolic_n(const spchol_symbolic* s) { return s ? s->S.n : 0; }
+int64_t spchol_symbolic_nnzL(const spchol_symbolic* s) { return s ? s->S.nnzL : 0; }
+double spchol_symbolic_flops(const spchol_symbolic* s) { return s ? s->S.flops : 0; }
+int spchol_symbolic_parent(const spchol_symbolic* s, int* parent) {
+    if (!s || !parent) return SPCHOL_EINVAL;
+    std::memcpy(parent, s->S.parent.data(), sizeof(int) * s->S.n); return 0;
+}
+int spchol_symbolic_colcount(const spchol_symbolic* s, int* cc) {
+    if (!s || !cc) return SPCHOL_EINVAL;
+    std::memcpy(cc, s->S.colcount.data(), sizeof(int) * s->S.n); return 0;
+}
+int spchol_symbolic_Lp64(const spchol_symbolic* s, int64_t* Lp) {
+    if (!s || !Lp) return SPCHOL_EINVAL;
+    std::memcpy(Lp, s->S.Lp.data(), sizeof(int64_t) * (s->S.n + 1)); return 0;
+}
+int spchol_symbolic_Lp(const spchol_symbolic* s, int* Lp) {
+    if (!s || !Lp) return SPCHOL_EINVAL;
+    if (s->S.nnzL > INT_MAX) { set_error("nnz(L) exceeds the 32-bit CSC of the reference API"); return SPCHOL_ERANGE; }
+    for (int j = 0; j <= s->S.n; ++j) Lp[j] = static_cast<int>(s->S.Lp[j]);
+    return 0;
+}
+int spchol_symbolic_Li(const spchol_symbolic* s, int* Li) {
+    if (!s || !Li) return SPCHOL_EINVAL;
+    if (s->S.nnzL > INT_MAX) { set_error("nnz(L) exceeds the 32-bit CSC of the reference API"); return SPCHOL_ERANGE; }
+    s->S.fill_Li(Li); return 0;
+}
+int spchol_symbolic_supernodes(const spchol_symbolic* s, int which, int* ns_out, int* sn_start, int* sn_parent) {
+    if (!s || !ns_out) return SPCHOL_EINVAL;
+    const Symbolic& S = s->S;
+    const int ns = which ? S.ns : S.nsf;
+    *ns_out = ns;
+    const std::vector<int>& st = which ? S.sn_start : S.fsn_start;
+    const std::vector<int>& pa = which ? S.sn_parent : S.fsn_parent;
+    if (sn_start) std::memcpy(sn_start, st.data(), sizeof(int) * (ns + 1));
+    if (sn_parent) std::memcpy(sn_parent, pa.data(), sizeof(int) * ns);
+    return 0;
+}
+int spchol_symbolic_stats(const spchol_symbolic* s, int64_t* st) {
+    if (!s || !st) return SPCHOL_EINVAL;
+    const Symbolic& S = s->S;
+    int maxw = 0, maxm = 0;
+    std::vector<int> lvl(S.ns, 0);
+    int nlev = 0;
+    for (int k = 0; k < S.ns; ++k) {
+        maxw = std::max(maxw, S.w(k)); maxm = std::max(maxm, S.m(k));
+        if (S.sn_parent[k] >= 0) lvl[S.sn_parent[k]] = std::max(lvl[S.sn_parent[k]], lvl[k] + 1);
+        nlev = std::max(nlev, lvl[k] + 1);
+    }
+    st[0] = S.nsf; st[1] = S.ns; st[2] = S.sum_m; st[3] = S.panel_entries; st[4] = S.padded_zeros;
+    st[5] = maxw; st[6] = maxm; st[7] = nlev;
+    return 0;
+}
+
+}  // extern "C"

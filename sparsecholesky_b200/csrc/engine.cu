@@ -1,0 +1,300 @@
+// Device engine + numeric C-ABI (see include/spchol.h).  No CPU fallback: every numeric entry
+// point returns SPCHOL_ENOGPU when no CUDA device is usable.
+#include <climits>
+#include <cstdio>
+#include <cstring>
+#include <new>
+#include <string>
+#include <vector>
+
+#include "../../include/spchol.h"
+#include "capi_internal.h"
+#include "kernels.cuh"
+
+using namespace spchol;
+
+#define CK(call)                                                                          \
+    do {                                                                                  \
+        cudaError_t e_ = (call);                                                          \
+        if (e_ != cudaSuccess) {                                                          \
+            set_error(std::string(#call) + ": " + cudaGetErrorString(e_));                \
+            return SPCHOL_ECUDA;                                                          \
+        }                                                                                 \
+    } while (0)
+
+struct spchol_plan {
+    int device = 0;
+    HostPlan H;
+    cudaStream_t stream = nullptr;
+    cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
+    // device buffers
+    double* dL = nullptr; double* dW = nullptr; double* dAx = nullptr; double* dLx = nullptr;
+    int* dinfo = nullptr;
+    int *d_first = nullptr, *d_w = nullptr, *d_m = nullptr, *d_ld = nullptr, *d_parent = nullptr;
+    int64_t *d_panel_off = nullptr, *d_cb_off = nullptr, *d_rel_off = nullptr;
+    int *d_rel = nullptr, *d_child_ptr = nullptr, *d_child_idx = nullptr;
+    int64_t *d_a_dest = nullptr, *d_l_src = nullptr;
+    int *d_small_list = nullptr, *d_extadd_list = nullptr;
+    ZeroTask* d_zero = nullptr; PotrfTask* d_potrf = nullptr; TrsmTask* d_trsm = nullptr; GemmTask* d_gemm = nullptr;
+    int64_t device_bytes = 0;
+    int64_t last_launches = 0;
+    double last_ms[4] = {0, 0, 0, 0};
+    std::vector<void*> allocs;
+    FrontArrays fa{};
+};
+
+namespace {
+
+template <class T>
+int upload(spchol_plan* p, const std::vector<T>& v, T** out) {
+    *out = nullptr;
+    const size_t bytes = std::max<size_t>(v.size(), 1) * sizeof(T);
+    void* d = nullptr;
+    CK(cudaMalloc(&d, bytes));
+    p->allocs.push_back(d);
+    p->device_bytes += static_cast<int64_t>(bytes);
+    if (!v.empty()) CK(cudaMemcpy(d, v.data(), v.size() * sizeof(T), cudaMemcpyHostToDevice));
+    *out = static_cast<T*>(d);
+    return 0;
+}
+template <class T>
+int dalloc(spchol_plan* p, int64_t count, T** out) {
+    void* d = nullptr;
+    const size_t bytes = static_cast<size_t>(std::max<int64_t>(count, 1)) * sizeof(T);
+    CK(cudaMalloc(&d, bytes));
+    p->allocs.push_back(d);
+    p->device_bytes += static_cast<int64_t>(bytes);
+    *out = static_cast<T*>(d);
+    return 0;
+}
+
+template <int T>
+int set_small_attr() {
+    CK(cudaFuncSetAttribute(k_front_small<T>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024));
+    return 0;
+}
+
+// issue the whole numeric factorization on the plan's stream
+int run_numeric(spchol_plan* p, const double* dAx) {
+    const HostPlan& H = p->H;
+    cudaStream_t st = p->stream;
+    int64_t launches = 0;
+    CK(cudaMemsetAsync(p->dL, 0, static_cast<size_t>(H.lbuf_entries) * sizeof(double), st));
+    CK(cudaMemsetAsync(p->dinfo, 0x7f, sizeof(int), st));
+    {
+        const int64_t nb = (H.nnzA + 255) / 256;
+        k_assemble<<<static_cast<unsigned>(nb), 256, 0, st>>>(H.nnzA, p->d_a_dest, dAx, p->dL);
+        ++launches;
+    }
+    for (const Op& op : H.ops) {
+        switch (op.kind) {
+        case OP_SMALL: {
+            const int* list = p->d_small_list + op.begin;
+            const unsigned g = static_cast<unsigned>(op.count);
+            switch (op.threads) {
+            case 32:  k_front_small<32><<<g, 32, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo); break;
+            case 64:  k_front_small<64><<<g, 64, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo); break;
+            case 128: k_front_small<128><<<g, 128, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo); break;
+            default:  k_front_small<256><<<g, 256, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo); break;
+            }
+            ++launches;
+        } break;
+        case OP_ZERO:
+            for (int b = 0; b < op.count; b += 65535) {
+                const int c = std::min(op.count - b, 65535);
+                k_zero<<<dim3(256, c), 256, 0, st>>>(p->d_zero + op.begin + b, p->dW);
+                ++launches;
+            }
+            break;
+        case OP_EXTADD:
+            k_extend_add<<<dim3(op.count, std::min(op.gx, 2048)), 128, 0, st>>>(p->d_extadd_list + op.begin, p->fa, p->dL, p->dW);
+            ++launches;
+            break;
+        case OP_POTRF:
+            k_potrf_diag<<<op.count, 256, 0, st>>>(p->d_potrf + op.begin, p->dL, p->dinfo);
+            ++launches;
+            break;
+        case OP_TRSM:
+            k_trsm<<<dim3(op.count, (op.gx + 127) / 128), 128, 0, st>>>(p->d_trsm + op.begin, p->dL);
+            ++launches;
+            break;
+        case OP_GEMM:
+            for (int b = 0; b < op.count; b += 65535) {
+                const int c = std::min(op.count - b, 65535);
+                k_gemm_dmma<<<dim3((op.gx + G_BM - 1) / G_BM, (op.gy + G_BN - 1) / G_BN, c), 256, G_SMEM, st>>>(
+                    p->d_gemm + op.begin + b, p->dL, p->dW);
+                ++launches;
+            }
+            break;
+        default: break;
+        }
+    }
+    CK(cudaGetLastError());
+    p->last_launches = launches;
+    return 0;
+}
+
+int read_info(spchol_plan* p, int* info) {
+    int v = 0;
+    CK(cudaMemcpyAsync(&v, p->dinfo, sizeof(int), cudaMemcpyDeviceToHost, p->stream));
+    CK(cudaStreamSynchronize(p->stream));
+    if (info) *info = (v == 0x7f7f7f7f) ? 0 : v;
+    return 0;
+}
+
+}  // namespace
+
+extern "C" {
+
+int spchol_device_count(void) {
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int spchol_plan_create(const spchol_symbolic* sym, int device, spchol_plan** out) {
+    if (!sym || !out) { set_error("spchol_plan_create: null argument"); return SPCHOL_EINVAL; }
+    *out = nullptr;
+    if (spchol_device_count() <= 0) {
+        set_error("spchol: no CUDA device available (the numeric path has no CPU fallback)");
+        return SPCHOL_ENOGPU;
+    }
+    spchol_plan* p = new (std::nothrow) spchol_plan();
+    if (!p) return SPCHOL_ENOMEM;
+    p->device = device;
+    try {
+        PlanOptions opt;
+        const Symbolic& S = symbolic_of(sym);
+        opt.want_csc = S.nnzL <= INT_MAX ? 1 : 0;
+        build_plan(S, opt, p->H);
+    } catch (const std::exception& e) {
+        set_error(e.what()); delete p; return SPCHOL_EINVAL;
+    }
+    int rc = 0;
+    auto fail = [&](int code) { spchol_plan_destroy(p); return code; };
+    if (cudaSetDevice(device) != cudaSuccess) { set_error("cudaSetDevice failed"); return fail(SPCHOL_ECUDA); }
+    if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); return fail(SPCHOL_ECUDA); }
+    for (auto& e : p->ev) if (cudaEventCreate(&e) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(SPCHOL_ECUDA); }
+    HostPlan& H = p->H;
+#define UP(vec, ptr) if ((rc = upload(p, vec, &ptr))) return fail(rc)
+    UP(H.first, p->d_first); UP(H.w, p->d_w); UP(H.m, p->d_m); UP(H.ld, p->d_ld); UP(H.parent, p->d_parent);
+    UP(H.panel_off, p->d_panel_off); UP(H.cb_off, p->d_cb_off); UP(H.rel_off, p->d_rel_off);
+    UP(H.rel, p->d_rel); UP(H.child_ptr, p->d_child_ptr); UP(H.child_idx, p->d_child_idx);
+    UP(H.a_dest, p->d_a_dest); UP(H.l_src, p->d_l_src);
+    UP(H.small_list, p->d_small_list); UP(H.extadd_list, p->d_extadd_list);
+    UP(H.zero_tasks, p->d_zero); UP(H.potrf_tasks, p->d_potrf); UP(H.trsm_tasks, p->d_trsm); UP(H.gemm_tasks, p->d_gemm);
+#undef UP
+    // the big host-side maps are only needed on the device from here on
+    std::vector<int64_t>().swap(H.a_dest);
+    std::vector<int64_t>().swap(H.l_src);
+    std::vector<int>().swap(H.rel);
+    if ((rc = dalloc(p, H.lbuf_entries, &p->dL))) return fail(rc);
+    if ((rc = dalloc(p, H.ws_entries, &p->dW))) return fail(rc);
+    if ((rc = dalloc(p, 1, &p->dinfo))) return fail(rc);
+    p->fa = FrontArrays{p->d_first, p->d_w, p->d_m, p->d_ld, p->d_parent, p->d_panel_off, p->d_cb_off,
+                        p->d_rel_off, p->d_rel, p->d_child_ptr, p->d_child_idx};
+    if ((rc = set_small_attr<32>()) || (rc = set_small_attr<64>()) || (rc = set_small_attr<128>()) ||
+        (rc = set_small_attr<256>())) return fail(rc);
+    if (cudaFuncSetAttribute(k_gemm_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM) != cudaSuccess) {
+        set_error("cudaFuncSetAttribute(k_gemm_dmma) failed"); return fail(SPCHOL_ECUDA);
+    }
+    *out = p;
+    return SPCHOL_OK;
+}
+
+void spchol_plan_destroy(spchol_plan* p) {
+    if (!p) return;
+    cudaSetDevice(p->device);
+    for (void* d : p->allocs) cudaFree(d);
+    for (auto& e : p->ev) if (e) cudaEventDestroy(e);
+    if (p->stream) cudaStreamDestroy(p->stream);
+    delete p;
+}
+
+int spchol_plan_stats(const spchol_plan* p, int64_t* st) {
+    if (!p || !st) return SPCHOL_EINVAL;
+    const HostPlan& H = p->H;
+    st[0] = H.ns; st[1] = H.nlevels; st[2] = H.n_small; st[3] = H.n_large; st[4] = H.lbuf_entries;
+    st[5] = H.ws_entries; st[6] = static_cast<int64_t>(H.ops.size()); st[7] = H.max_m; st[8] = H.max_w;
+    st[9] = p->device_bytes;
+    return 0;
+}
+
+int spchol_factor_device(spchol_plan* p, const double* dAx) {
+    if (!p || !dAx) { set_error("spchol_factor_device: null argument"); return SPCHOL_EINVAL; }
+    CK(cudaSetDevice(p->device));
+    return run_numeric(p, dAx);
+}
+
+int spchol_export_csc_device(spchol_plan* p, double* dLx) {
+    if (!p || !dLx) { set_error("spchol_export_csc_device: null argument"); return SPCHOL_EINVAL; }
+    if (p->H.nnzL > INT_MAX) { set_error("nnz(L) exceeds the 32-bit CSC of the reference API"); return SPCHOL_ERANGE; }
+    CK(cudaSetDevice(p->device));
+    const int64_t nb = (p->H.nnzL + 255) / 256;
+    k_export<<<static_cast<unsigned>(nb), 256, 0, p->stream>>>(p->H.nnzL, p->d_l_src, p->dL, dLx);
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int spchol_sync(spchol_plan* p, int* info) {
+    if (!p) return SPCHOL_EINVAL;
+    CK(cudaSetDevice(p->device));
+    return read_info(p, info);
+}
+
+int spchol_factor(spchol_plan* p, const double* Ax, double* Lx, int* info) {
+    if (!p || !Ax || !Lx) { set_error("spchol_factor: null argument"); return SPCHOL_EINVAL; }
+    if (p->H.nnzL > INT_MAX) { set_error("nnz(L) exceeds the 32-bit CSC of the reference API"); return SPCHOL_ERANGE; }
+    CK(cudaSetDevice(p->device));
+    int rc;
+    if (!p->dAx && (rc = dalloc(p, p->H.nnzA, &p->dAx))) return rc;
+    if (!p->dLx && (rc = dalloc(p, p->H.nnzL, &p->dLx))) return rc;
+    cudaStream_t st = p->stream;
+    CK(cudaEventRecord(p->ev[0], st));
+    CK(cudaMemcpyAsync(p->dAx, Ax, static_cast<size_t>(p->H.nnzA) * sizeof(double), cudaMemcpyHostToDevice, st));
+    CK(cudaEventRecord(p->ev[1], st));
+    if ((rc = run_numeric(p, p->dAx))) return rc;
+    CK(cudaEventRecord(p->ev[2], st));
+    if ((rc = spchol_export_csc_device(p, p->dLx))) return rc;
+    CK(cudaEventRecord(p->ev[3], st));
+    CK(cudaMemcpyAsync(Lx, p->dLx, static_cast<size_t>(p->H.nnzL) * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(p->ev[4], st));
+    if ((rc = read_info(p, info))) return rc;
+    for (int i = 0; i < 4; ++i) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, p->ev[i], p->ev[i + 1]));
+        p->last_ms[i] = ms;
+    }
+    return SPCHOL_OK;
+}
+
+int spchol_lbuf(spchol_plan* p, double** dL, int64_t* entries) {
+    if (!p) return SPCHOL_EINVAL;
+    if (dL) *dL = p->dL;
+    if (entries) *entries = p->H.lbuf_entries;
+    return 0;
+}
+
+int spchol_lbuf_to_host(spchol_plan* p, double* L_host) {
+    if (!p || !L_host) return SPCHOL_EINVAL;
+    CK(cudaSetDevice(p->device));
+    CK(cudaMemcpyAsync(L_host, p->dL, static_cast<size_t>(p->H.lbuf_entries) * sizeof(double), cudaMemcpyDeviceToHost, p->stream));
+    CK(cudaStreamSynchronize(p->stream));
+    return 0;
+}
+
+int spchol_last_timing(const spchol_plan* p, double* ms4) {
+    if (!p || !ms4) return SPCHOL_EINVAL;
+    for (int i = 0; i < 4; ++i) ms4[i] = p->last_ms[i];
+    return 0;
+}
+
+void* spchol_stream(spchol_plan* p) { return p ? static_cast<void*>(p->stream) : nullptr; }
+int64_t spchol_last_launches(const spchol_plan* p) { return p ? p->last_launches : 0; }
+
+int spchol_residual(spchol_plan*, const double*, double*) {
+    set_error("spchol_residual: not implemented yet");
+    return SPCHOL_EINVAL;
+}
+
+}  // extern "C"

@@ -1,0 +1,152 @@
+"""Parity tests proper (GPU, through the C-ABI): L from the sm_100a multifrontal path vs the
+oracle / the reference's golden vectors.  Bar (BASELINE.json north_star): pattern bit-exact,
+values within 1e-10 relative, ||A - L L^T||_F / ||A||_F <= 1e-12."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+import sparsecholesky_b200 as sc
+from oracle import pyoracle as po
+from sparsecholesky_b200 import synth
+
+pytestmark = pytest.mark.gpu
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+REL_TOL = 1e-10      # per-entry relative tolerance (north_star)
+RES_TOL = 1e-12      # Frobenius residual tolerance (north_star)
+
+
+def rel_err(Lx, ref):
+    den = np.abs(ref)
+    ok = den > 0
+    e = np.zeros_like(ref)
+    e[ok] = np.abs(Lx[ok] - ref[ok]) / den[ok]
+    e[~ok] = np.abs(Lx[~ok])
+    return float(e.max()) if e.size else 0.0
+
+
+def residual(A, L):
+    """||A - L L^T||_F / ||A||_F with scipy sparse products (exact, host side, test only)."""
+    import scipy.sparse as sp
+    Ls = sp.csc_matrix((L.x, L.i, L.p), shape=(A.n, A.n))
+    Au = sp.csc_matrix((A.x, A.i, A.p), shape=(A.n, A.n))
+    Af = Au + sp.triu(Au, 1).T
+    R = (Af - Ls @ Ls.T).tocsc()
+    return float(np.sqrt((R.data ** 2).sum()) / np.sqrt((Af.data ** 2).sum()))
+
+
+GOLD_NUMERIC = ["test3", "bcsstk01", "1138_bus", "lap2d_24", "lap3d_10", "lap2d_7x5"]
+
+
+@pytest.mark.parametrize("name", GOLD_NUMERIC)
+@pytest.mark.parametrize("relax", [False, True])
+def test_chol_matches_reference_golden(name, relax):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    A = sc.CscMatrix(int(g["n"]), g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A, relax=relax)
+    L = sc.chol(A, S).value()
+    assert (L.p == g["Lp"]).all() and (L.i == g["Li"]).all()          # pattern bit-exact
+    assert rel_err(L.x, g["Lx"]) <= REL_TOL
+    assert residual(A, L) <= RES_TOL
+
+
+def test_chol_without_S_and_reference_test3():
+    # tests/test_chol.cpp:59-97: chol(A) lower triangle vs dense Cholesky within 1e-9
+    A = sc.triplet_to_csc_matrix([0, 0, 0, 1, 1, 2], [0, 1, 2, 1, 2, 2], [4.0, 1.0, 1.0, 3.0, 0.0, 2.0], 3)
+    L = sc.chol(A)
+    assert L.has_value()
+    D = sc.csc_to_dense(L.value())
+    ref = np.linalg.cholesky(np.array([[4.0, 1, 1], [1, 3, 0], [1, 0, 2]]))
+    assert np.abs(np.tril(D) - ref).max() < 1e-9
+
+
+def test_not_positive_definite_message():
+    A = sc.triplet_to_csc_matrix([0, 0, 1], [0, 1, 1], [1.0, 2.0, 1.0], 2)
+    r = sc.chol(A)
+    assert not r.has_value() and r.error() == "A is not positive definite."     # chol.hpp:850
+    # indefinite deep inside a larger matrix, large-front path included
+    perm = synth.nd_perm(40, 40, 1)
+    ti, tj, tx, n = synth.laplacian_triplets(40, 40, 1, perm)
+    tx = tx.copy(); tx[n - 1] = -1.0          # last diagonal (root separator) made negative
+    r = sc.chol(sc.triplet_to_csc_matrix(ti, tj, tx, n))
+    assert not r.has_value() and r.error() == "A is not positive definite."
+
+
+@pytest.mark.parametrize("dims", [(33, 31, 1), (64, 64, 1), (16, 16, 16), (40, 7, 5), (1, 1, 1), (2, 1, 1), (200, 1, 1)])
+def test_laplacians_vs_oracle(dims):
+    perm = synth.nd_perm(*dims)
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
+    if n == 1:
+        tx = np.array([2.0])
+    A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
+    S = sc.schol(A)
+    L = sc.chol(A, S).value()
+    rc, Lp, Li, Lx = po.chol(n, A.p, A.i, A.x)
+    assert rc == 0
+    assert (L.p == Lp).all() and (L.i == Li).all()
+    assert rel_err(L.x, Lx) <= REL_TOL
+    assert residual(A, L) <= RES_TOL
+
+
+@pytest.mark.parametrize("seed", [0, 1, 2, 3])
+def test_random_spd_vs_oracle(seed):
+    rng = np.random.default_rng(seed)
+    n = [37, 150, 400, 900][seed]
+    dens = [0.2, 0.05, 0.02, 0.01][seed]
+    iu = np.triu_indices(n, 1)
+    sel = rng.random(iu[0].size) < dens
+    ti = np.concatenate([np.arange(n), iu[0][sel]]); tj = np.concatenate([np.arange(n), iu[1][sel]])
+    off = rng.standard_normal(sel.sum())
+    rowsum = np.zeros(n); np.add.at(rowsum, iu[0][sel], np.abs(off)); np.add.at(rowsum, iu[1][sel], np.abs(off))
+    tx = np.concatenate([rowsum + 1.0 + rng.random(n), off])
+    A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
+    S = sc.schol(A)
+    L = sc.chol(A, S).value()
+    rc, Lp, Li, Lx = po.chol(n, A.p, A.i, A.x)
+    assert rc == 0 and (L.p == Lp).all() and (L.i == Li).all()
+    assert rel_err(L.x, Lx) <= REL_TOL
+    assert residual(A, L) <= RES_TOL
+
+
+def test_plan_reuse_many_values():
+    # chol(A, S) with one S and several value sets (config 5's usage pattern), batch family D A D
+    g = np.load(os.path.join(GOLD, "1138_bus.npz"))
+    n = int(g["n"])
+    A = sc.CscMatrix(n, g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A)
+    for b in (0, 1, 7):
+        Ab = sc.CscMatrix(n, A.p, A.i, synth.batch_values(A.p, A.i, A.x, b))
+        L = sc.chol(Ab, S).value()
+        rc, Lp, Li, Lx = po.chol(n, A.p, A.i, Ab.x)
+        assert rc == 0 and (L.i == Li).all()
+        assert rel_err(L.x, Lx) <= REL_TOL
+
+
+def test_midsize_2d_large_front_path():
+    # 2D 256^2: root separator w = 256+, exercises blocked POTRF/TRSM/DMMA path; oracle takes ~1 s
+    dims = (256, 256, 1)
+    perm = synth.nd_perm(*dims)
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
+    A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
+    S = sc.schol(A)
+    assert S.nnz == 2332245
+    L = sc.chol(A, S).value()
+    rc, Lp, Li, Lx = po.chol(n, A.p, A.i, A.x)
+    assert rc == 0 and (L.p == Lp).all() and (L.i == Li).all()
+    assert rel_err(L.x, Lx) <= REL_TOL
+    assert residual(A, L) <= RES_TOL
+
+
+def test_midsize_3d_large_front_path():
+    dims = (24, 24, 24)
+    perm = synth.nd_perm(*dims)
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
+    A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
+    S = sc.schol(A)
+    L = sc.chol(A, S).value()
+    rc, Lp, Li, Lx = po.chol(n, A.p, A.i, A.x)
+    assert rc == 0 and (L.p == Lp).all() and (L.i == Li).all()
+    assert rel_err(L.x, Lx) <= REL_TOL
+    assert residual(A, L) <= RES_TOL

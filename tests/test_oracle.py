@@ -1,0 +1,111 @@
+"""Pins the plain-C oracle (oracle/oracle.c): against the golden vectors produced by the
+reference's own code (tests/golden/*.npz) and, where oracle/_ref/libref.so is present,
+bit-for-bit against the reference itself on fresh seeded inputs."""
+import glob
+import os
+
+import numpy as np
+import pytest
+
+from oracle import pyoracle as po
+from sparsecholesky_b200 import synth
+
+GOLD = os.path.join(os.path.dirname(__file__), "golden")
+NAMES = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLD, "*.npz")))
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_oracle_matches_reference_golden(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    n = int(g["n"]); Ap, Ai, Ax = g["Ap"], g["Ai"], g["Ax"]
+    parent = po.etree(n, Ap, Ai)
+    assert (parent == g["parent"]).all()
+    post = po.post_order(parent)
+    assert (post == g["post"]).all()
+    assert (po.col_count(n, Ap, Ai, parent, post) == g["colcount"]).all()
+    p2, Lp, Li = po.schol(n, Ap, Ai)
+    assert (p2 == g["parent"]).all() and (Lp == g["Lp"]).all() and (Li == g["Li"]).all()
+    sn_id, st = po.compute_supernodes(parent, Lp)
+    assert (sn_id == g["sn_id"]).all() and (st == g["sn_start"]).all()
+    assert (po.atree(Lp, Li, sn_id, st) == g["atree"]).all()
+    lv = po.compute_levels(parent)
+    glv = [g["level_nodes"][g["level_ptr"][l]:g["level_ptr"][l + 1]].tolist() for l in range(len(g["level_ptr"]) - 1)]
+    assert lv == glv
+    if "chol_rc" in g:
+        rc, _, Li2, Lx = po.chol(n, Ap, Ai, Ax)
+        assert (rc != 0) == (int(g["chol_rc"]) != 0)
+        if rc == 0:
+            assert (Li2 == g["Li"]).all()
+            assert np.array_equal(Lx, g["Lx"])        # bit-exact: same operations in the same order
+
+
+def test_known_answers_from_reference_tests():
+    # reference tests/test_chol.cpp:6-25 (etree) and SURVEY.md §4 golden list
+    g = np.load(os.path.join(GOLD, "thesis7.npz"))
+    assert g["parent"].tolist() == [2, 5, 4, 5, 5, 6, -1]
+    assert g["colcount"].tolist() == [5, 2, 4, 2, 3, 2, 1]
+    g9 = np.load(os.path.join(GOLD, "thesis9.npz"))
+    assert g9["parent"].tolist() == [1, 7, 3, 6, 5, 6, 7, 8, -1]
+    assert g9["sn_start"].tolist() == [0, 2, 3, 4, 5, 9]
+    # tests/test_chol.cpp:27-57: ereach(A,5) without presetting w[5]
+    n = 7; Ap, Ai, Ax = g["Ap"], g["Ai"], g["Ax"]
+    s = np.zeros(n, np.int32); w = np.full(n, -1, np.int32); x = np.zeros(n)
+    path = np.zeros(n, np.int32)
+    po.oracle().orc_ereach(n, Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data, 5, g["parent"].ctypes.data,
+                           s.ctypes.data, w.ctypes.data, x.ctypes.data, n, path.ctypes.data)
+    assert s.tolist() == [3, 1, 0, 2, 4, 5, 6]
+    # tests/test_chol.cpp:59-97: 3x3 against dense Cholesky within 1e-9
+    g3 = np.load(os.path.join(GOLD, "test3.npz"))
+    Ld = np.linalg.cholesky(np.array([[4.0, 1, 1], [1, 3, 0], [1, 0, 2]]))
+    rc, Lp, Li, Lx = po.chol(3, g3["Ap"], g3["Ai"], g3["Ax"])
+    assert rc == 0
+    for j in range(3):
+        for k in range(Lp[j], Lp[j + 1]):
+            assert abs(Lx[k] - Ld[Li[k], j]) < 1e-9
+    # bcsstk01 / 1138_bus first values
+    gb = np.load(os.path.join(GOLD, "bcsstk01.npz"))
+    assert np.allclose(gb["Lx"][:4], [1682.9344962059574, 594.20019154305817, 1237.9170657127238, -1.9806673051415467], rtol=0, atol=0)
+    g1 = np.load(os.path.join(GOLD, "1138_bus.npz"))
+    assert int(g1["Lp"][-1]) == 38312 and len(g1["sn_start"]) - 1 == 804
+
+
+def test_not_positive_definite():
+    g = np.load(os.path.join(GOLD, "notpd2.npz"))
+    assert int(g["chol_rc"]) == 1 and str(g["chol_err"]) == "A is not positive definite."
+    rc, *_ = po.chol(2, g["Ap"], g["Ai"], g["Ax"])
+    assert rc == 2          # pivot of column 1 (0-based) is <= 0
+
+
+@pytest.mark.skipif(not po.have_ref(), reason="oracle/_ref/libref.so not built (reference tree absent)")
+@pytest.mark.parametrize("seed", [0, 1, 2])
+def test_oracle_bitexact_vs_reference_random(seed):
+    rng = np.random.default_rng(seed)
+    n = 120
+    dens = 0.04
+    mask = rng.random((n, n)) < dens
+    iu = np.triu_indices(n, 1)
+    sel = mask[iu]
+    ti = np.concatenate([np.arange(n), iu[0][sel]]); tj = np.concatenate([np.arange(n), iu[1][sel]])
+    tx = np.concatenate([n + rng.random(n), rng.standard_normal(sel.sum())])
+    # duplicates and lower-triangle entries exercise the ingest rules
+    ti = np.concatenate([ti, tj[n:n + 5]]); tj = np.concatenate([tj, ti[n:n + 5]]); tx = np.concatenate([tx, np.full(5, 0.25)])
+    Ap, Ai, Ax = po.triplet_to_csc(ti, tj, tx, n)
+    rAp, rAi, rAx = po.ref_triplet_to_csc(ti, tj, tx, n)
+    assert (Ap == rAp).all() and (Ai == rAi).all() and np.array_equal(Ax, rAx)
+    parent, Lp, Li = po.schol(n, Ap, Ai)
+    rparent, rLp, rLi, _ = po.ref_schol(n, Ap, Ai)
+    assert (parent == rparent).all() and (Lp == rLp).all() and (Li == rLi).all()
+    rc, _, Li2, Lx = po.chol(n, Ap, Ai, Ax, parent, Lp)
+    rrc, _, rLi2, rLx, _, _ = po.ref_chol(n, Ap, Ai, Ax, int(Lp[n]))
+    assert rc == 0 and rrc == 0 and (Li2 == rLi2).all() and np.array_equal(Lx, rLx)
+
+
+@pytest.mark.skipif(not po.have_ref(), reason="oracle/_ref/libref.so not built (reference tree absent)")
+def test_oracle_bitexact_vs_reference_laplacian():
+    perm = synth.nd_perm(12, 9, 5)
+    ti, tj, tx, n = synth.laplacian_triplets(12, 9, 5, perm)
+    Ap, Ai, Ax = po.triplet_to_csc(ti, tj, tx, n)
+    parent, Lp, Li = po.schol(n, Ap, Ai)
+    rc, _, _, Lx = po.chol(n, Ap, Ai, Ax, parent, Lp)
+    rrc, _, rLi, rLx, _, _ = po.ref_chol(n, Ap, Ai, Ax, int(Lp[n]))
+    assert rc == 0 and rrc == 0 and (Li == rLi).all() and np.array_equal(Lx, rLx)

@@ -1,0 +1,118 @@
+"""Host logic of the product (C-ABI, no GPU): ingest + symbolic phase must reproduce the
+reference's S.p / S.i / S.parent / supernodes / atree / levels bit-exactly (golden vectors made by
+the reference's own code), and the library must export every symbol include/spchol.h declares."""
+import ctypes
+import glob
+import os
+import re
+
+import numpy as np
+import pytest
+
+import sparsecholesky_b200 as sc
+from sparsecholesky_b200 import _lib, synth
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+GOLD = os.path.join(ROOT, "tests", "golden")
+NAMES = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLD, "*.npz")))
+
+
+def test_library_exports_every_declared_symbol():
+    hdr = open(os.path.join(ROOT, "include", "spchol.h")).read()
+    declared = set(re.findall(r"\b(spchol_[A-Za-z0-9_]+)\s*\(", hdr))
+    assert len(declared) > 30
+    L = ctypes.CDLL(_lib.LIB_PATH)
+    for name in declared:
+        assert hasattr(L, name), name
+    assert declared == set(_lib.SIGNATURES), declared ^ set(_lib.SIGNATURES)
+
+
+@pytest.mark.parametrize("name", NAMES)
+def test_symbolic_matches_reference_golden(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    n = int(g["n"])
+    A = sc.CscMatrix(n, g["Ap"], g["Ai"], g["Ax"])
+    parent = sc.etree(A)
+    assert (parent == g["parent"]).all()
+    post = sc.post_order(parent)
+    assert (post == g["post"]).all()
+    assert (sc.col_count(A, parent, post) == g["colcount"]).all()
+    for relax in (False, True):
+        S = sc.schol(A, relax=relax)
+        assert (S.parent == g["parent"]).all()
+        assert (S.p == g["Lp"]).all() and (S.i == g["Li"]).all()
+        assert S.flops == float((g["colcount"].astype(np.float64) ** 2).sum())
+        sn_id, st = sc.compute_supernodes(S)
+        assert (sn_id == g["sn_id"]).all() and (st == g["sn_start"]).all()
+        assert (sc.atree(S, sn_id, st) == g["atree"]).all()
+        fst, fpa = S.supernodes(relaxed=False)
+        assert (fst == g["sn_start"]).all() and (fpa == g["atree"]).all()
+    lv = sc.compute_levels(parent)
+    glv = [g["level_nodes"][g["level_ptr"][l]:g["level_ptr"][l + 1]].tolist() for l in range(len(g["level_ptr"]) - 1)]
+    assert lv == glv
+    alv = sc.compute_levels(g["atree"])
+    galv = [g["alevel_nodes"][g["alevel_ptr"][l]:g["alevel_ptr"][l + 1]].tolist() for l in range(len(g["alevel_ptr"]) - 1)]
+    assert alv == galv
+
+
+def test_reference_unit_tests_restated():
+    # tests/test_chol.cpp:6-25 EliminationTree
+    pattern = [[0], [1], [0, 2], [3], [0, 2, 4], [0, 1, 3, 5], [0, 2, 5, 6]]
+    A = sc.build_csc_matrix_from_pattern(pattern)
+    parent = sc.etree(A)
+    assert parent.tolist() == [2, 5, 4, 5, 5, 6, -1]
+    # tests/test_chol.cpp:27-57 ColumnReach (both overloads)
+    n = A.size()
+    w = np.full(n, -1, np.int32); s = np.zeros(n, np.int32); x = np.zeros(n)
+    sc.ereach(A, 5, parent, s, w, x, n)
+    assert s.tolist() == [3, 1, 0, 2, 4, 5, 6]
+    w[:] = -1                      # the reference re-runs on the already-marked w; same s stays
+    sc.ereach(A, 5, parent, s, w, None, n)
+    assert s.tolist() == [3, 1, 0, 2, 4, 5, 6]
+
+
+def test_triplet_rules():
+    # mirror to upper, sum duplicates, keep explicit zeros (chol.hpp:321-346; tests/test_chol.cpp:79)
+    A = sc.triplet_to_csc_matrix([0, 1, 2, 2, 1, 0, 2], [0, 1, 2, 0, 0, 1, 1], [4.0, 3.0, 2.0, 1.0, 0.5, 0.5, 0.0], 3)
+    assert A.p.tolist() == [0, 1, 3, 6]
+    assert A.i.tolist() == [0, 0, 1, 0, 1, 2]
+    assert A.x.tolist() == [4.0, 1.0, 3.0, 1.0, 0.0, 2.0]
+    assert A[1, 0] == 1.0 and A[0, 1] == 1.0 and A[2, 1] == 0.0
+    with pytest.raises(sc.api.SpcholError):
+        sc.triplet_to_csc_matrix([0, 5], [0, 0], [1.0, 1.0], 3)
+
+
+def test_mtx_reader():
+    A = sc.load_matrix_market_to_csc(os.path.join(ROOT, "tests", "data", "bcsstk01.mtx"))
+    g = np.load(os.path.join(GOLD, "bcsstk01.npz"))
+    assert A.n == 48 and (A.p == g["Ap"]).all() and (A.i == g["Ai"]).all() and np.array_equal(A.x, g["Ax"])
+    with pytest.raises(RuntimeError, match="Could not open file"):
+        sc.load_matrix_market_to_csc("/nonexistent/file.mtx")
+
+
+def test_survey_check_values_large():
+    # SURVEY.md §8(d) check values for the generator + symbolic at a size the reference needs minutes for
+    perm = synth.nd_perm(4, 4, 1)
+    assert perm[-4:].tolist() == [2, 6, 10, 14]
+    ti, tj, tx, n = synth.laplacian_triplets(4, 4, 1, perm)
+    S = sc.schol(sc.triplet_to_csc_matrix(ti, tj, tx, n), relax=False)
+    assert S.nnz == 64 and S.flops == 282 and S.stats()["ns_fund"] == 11
+    perm = synth.nd_perm(256, 256, 1)
+    ti, tj, tx, n = synth.laplacian_triplets(256, 256, 1, perm)
+    S = sc.schol(sc.triplet_to_csc_matrix(ti, tj, tx, n))
+    assert S.nnz == 2332245                      # BASELINE.md §2, 2D 256^2 ND
+    perm = synth.nd_perm(32, 32, 32)
+    ti, tj, tx, n = synth.laplacian_triplets(32, 32, 32, perm)
+    S = sc.schol(sc.triplet_to_csc_matrix(ti, tj, tx, n))
+    assert S.nnz == 8130857 and S.flops == 5708347727.0     # BASELINE.md §2, 3D 32^3 ND
+    st = S.stats()
+    # relaxed fronts: fewer, never lose a column, padded storage accounted
+    assert st["ns_relaxed"] < st["ns_fund"] and st["panel_entries"] >= S.nnz
+
+
+def test_numeric_path_fails_loudly_without_gpu():
+    if sc.device_count() > 0:
+        pytest.skip("GPU present")
+    A = sc.triplet_to_csc_matrix([0, 0, 1], [0, 1, 1], [4.0, 1.0, 3.0], 2)
+    with pytest.raises(sc.api.SpcholError, match="no CUDA device"):
+        sc.chol(A)
