@@ -86,6 +86,10 @@ void spchol_plan_destroy(spchol_plan*);
 /* plan_stats[0..9] = ns, nlevels, n_small, n_large, lbuf_entries, ws_entries, n_ops, max_m, max_w, device_bytes */
 int  spchol_plan_stats(const spchol_plan*, int64_t* stats);
 
+/* host-only dry run of the planner (no GPU needed): same stats layout, device_bytes = bytes the
+ * plan would allocate; extra[0..5] = #small ops, #extadd ops, #potrf ops, #trsm ops, #gemm ops, gemm flops (as int64) */
+int  spchol_plan_dryrun(const spchol_symbolic*, int64_t* stats, int64_t* extra);
+
 /* Host-buffer call (what chol(A,S) binds): H2D of Ax, factor, CSC gather, D2H of Lx.
  * info = 0, or (1-based) a column whose pivot was <= 0 -> "A is not positive definite." (chol.hpp:849-850). */
 int  spchol_factor(spchol_plan*, const double* Ax_host, double* Lx_host, int* info);
@@ -100,6 +104,12 @@ int  spchol_lbuf(spchol_plan*, double** dL, int64_t* entries);
 int  spchol_lbuf_to_host(spchol_plan*, double* L_host);
 /* timing of the last spchol_factor call, milliseconds: [h2d, numeric, export, d2h] */
 int  spchol_last_timing(const spchol_plan*, double* ms4);
+/* per-op-kind device timing (CUDA events around every launch group; adds a sync, so use it on an
+ * extra untimed step): kinds 0 small fronts, 1 zero, 2 extend-add, 3 potrf, 4 trsm, 5 gemm/syrk (DMMA),
+ * 6 memset+assemble.  flops2[0] = algorithmic flops of the kind-5 launches (lower trapezoids only),
+ * flops2[1] = flops of their full rectangles. */
+int  spchol_set_profile(spchol_plan*, int on);
+int  spchol_get_profile(const spchol_plan*, double* kind_ms8, int64_t* kind_launches8, double* flops2);
 /* stream handle (cudaStream_t) the plan launches on, for CUDA-event timing by the caller */
 void* spchol_stream(spchol_plan*);
 /* number of kernel launches the last factorization issued */

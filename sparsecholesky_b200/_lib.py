@@ -42,6 +42,7 @@ SIGNATURES = {
     "spchol_plan_create": (C.c_int, [_VP, C.c_int, C.POINTER(_VP)]),
     "spchol_plan_destroy": (None, [_VP]),
     "spchol_plan_stats": (C.c_int, [_VP, _VP]),
+    "spchol_plan_dryrun": (C.c_int, [_VP, _VP, _VP]),
     "spchol_factor": (C.c_int, [_VP, _VP, _VP, C.POINTER(C.c_int)]),
     "spchol_factor_device": (C.c_int, [_VP, _VP]),
     "spchol_export_csc_device": (C.c_int, [_VP, _VP]),
@@ -49,6 +50,8 @@ SIGNATURES = {
     "spchol_lbuf": (C.c_int, [_VP, C.POINTER(_VP), C.POINTER(C.c_int64)]),
     "spchol_lbuf_to_host": (C.c_int, [_VP, _VP]),
     "spchol_last_timing": (C.c_int, [_VP, _VP]),
+    "spchol_set_profile": (C.c_int, [_VP, C.c_int]),
+    "spchol_get_profile": (C.c_int, [_VP, _VP, _VP, _VP]),
     "spchol_stream": (_VP, [_VP]),
     "spchol_last_launches": (C.c_int64, [_VP]),
     "spchol_residual": (C.c_int, [_VP, _VP, C.POINTER(C.c_double)]),

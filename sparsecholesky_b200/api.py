@@ -146,6 +146,15 @@ class SChol:
             self._plans[device] = _Handle(h, lib().spchol_plan_destroy)
         return self._plans[device]
 
+    def plan_dryrun(self):
+        """planner statistics without a GPU (host-only)"""
+        st = np.zeros(10, np.int64); ex = np.zeros(6, np.int64)
+        check(lib().spchol_plan_dryrun(self._sym.h, ptr(st), ptr(ex)))
+        keys = ["ns", "nlevels", "n_small", "n_large", "lbuf_entries", "ws_entries", "n_ops", "max_m", "max_w", "device_bytes"]
+        d = dict(zip(keys, (int(v) for v in st)))
+        d.update(dict(zip(["ops_small", "ops_extadd", "ops_potrf", "ops_trsm", "ops_gemm", "gemm_flops"], (int(v) for v in ex))))
+        return d
+
     def plan_stats(self, device=0):
         st = np.zeros(10, np.int64)
         check(lib().spchol_plan_stats(self.plan(device).h, ptr(st)))

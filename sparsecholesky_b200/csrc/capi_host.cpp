@@ -10,6 +10,7 @@
 
 #include "../../include/spchol.h"
 #include "capi_internal.h"
+#include "plan.h"
 
 namespace spchol {
 static thread_local std::string g_error;
@@ -152,6 +153,31 @@ int spchol_symbolic_stats(const spchol_symbolic* s, int64_t* st) {
     }
     st[0] = S.nsf; st[1] = S.ns; st[2] = S.sum_m; st[3] = S.panel_entries; st[4] = S.padded_zeros;
     st[5] = maxw; st[6] = maxm; st[7] = nlev;
+    return 0;
+}
+
+int spchol_plan_dryrun(const spchol_symbolic* s, int64_t* st, int64_t* extra) {
+    if (!s || !st) return SPCHOL_EINVAL;
+    try {
+        HostPlan H; PlanOptions opt;
+        opt.want_csc = s->S.nnzL <= INT_MAX ? 1 : 0;
+        build_plan(s->S, opt, H);
+        st[0] = H.ns; st[1] = H.nlevels; st[2] = H.n_small; st[3] = H.n_large; st[4] = H.lbuf_entries;
+        st[5] = H.ws_entries; st[6] = static_cast<int64_t>(H.ops.size()); st[7] = H.max_m; st[8] = H.max_w;
+        st[9] = 8 * (H.lbuf_entries + H.ws_entries) + 8 * static_cast<int64_t>(H.a_dest.size() + H.l_src.size()) +
+                4 * static_cast<int64_t>(H.rel.size()) + 60 * static_cast<int64_t>(H.ns);
+        if (extra) {
+            for (int k = 0; k < 6; ++k) extra[k] = 0;
+            for (const Op& op : H.ops) {
+                if (op.kind == OP_SMALL) ++extra[0];
+                else if (op.kind == OP_EXTADD) ++extra[1];
+                else if (op.kind == OP_POTRF) ++extra[2];
+                else if (op.kind == OP_TRSM) ++extra[3];
+                else if (op.kind == OP_GEMM) ++extra[4];
+            }
+            extra[5] = static_cast<int64_t>(H.gemm_flops);
+        }
+    } catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
     return 0;
 }
 

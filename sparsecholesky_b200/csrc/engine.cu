@@ -41,6 +41,11 @@ struct spchol_plan {
     double last_ms[4] = {0, 0, 0, 0};
     std::vector<void*> allocs;
     FrontArrays fa{};
+    // optional per-op-kind timing (spchol_set_profile): events around every launch group
+    int profile = 0;
+    std::vector<cudaEvent_t> prof_ev;
+    double kind_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    int64_t kind_launches[8] = {0, 0, 0, 0, 0, 0, 0, 0};
 };
 
 namespace {
@@ -79,6 +84,21 @@ int run_numeric(spchol_plan* p, const double* dAx) {
     const HostPlan& H = p->H;
     cudaStream_t st = p->stream;
     int64_t launches = 0;
+    const bool prof = p->profile != 0;
+    size_t pe = 0;
+    std::vector<int> pkind;
+    auto mark = [&](int kind) -> int {     // record an event; kind = op kind that FOLLOWS (or -1 at the end)
+        if (!prof) return 0;
+        if (pe >= p->prof_ev.size()) {
+            cudaEvent_t e;
+            if (cudaEventCreate(&e) != cudaSuccess) return -1;
+            p->prof_ev.push_back(e);
+        }
+        cudaEventRecord(p->prof_ev[pe++], st);
+        pkind.push_back(kind);
+        return 0;
+    };
+    mark(6);
     CK(cudaMemsetAsync(p->dL, 0, static_cast<size_t>(H.lbuf_entries) * sizeof(double), st));
     CK(cudaMemsetAsync(p->dinfo, 0x7f, sizeof(int), st));
     {
@@ -87,6 +107,8 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         ++launches;
     }
     for (const Op& op : H.ops) {
+        mark(op.kind);
+        const int64_t before = launches;
         switch (op.kind) {
         case OP_SMALL: {
             const int* list = p->d_small_list + op.begin;
@@ -128,9 +150,19 @@ int run_numeric(spchol_plan* p, const double* dAx) {
             break;
         default: break;
         }
+        if (prof) p->kind_launches[op.kind] += launches - before;
     }
+    mark(-1);
     CK(cudaGetLastError());
     p->last_launches = launches;
+    if (prof) {
+        CK(cudaStreamSynchronize(st));
+        for (size_t i = 0; i + 1 < pe; ++i) {
+            float ms = 0;
+            CK(cudaEventElapsedTime(&ms, p->prof_ev[i], p->prof_ev[i + 1]));
+            if (pkind[i] >= 0 && pkind[i] < 8) p->kind_ms[pkind[i]] += ms;
+        }
+    }
     return 0;
 }
 
@@ -207,6 +239,7 @@ void spchol_plan_destroy(spchol_plan* p) {
     cudaSetDevice(p->device);
     for (void* d : p->allocs) cudaFree(d);
     for (auto& e : p->ev) if (e) cudaEventDestroy(e);
+    for (auto& e : p->prof_ev) cudaEventDestroy(e);
     if (p->stream) cudaStreamDestroy(p->stream);
     delete p;
 }
@@ -286,6 +319,19 @@ int spchol_lbuf_to_host(spchol_plan* p, double* L_host) {
 int spchol_last_timing(const spchol_plan* p, double* ms4) {
     if (!p || !ms4) return SPCHOL_EINVAL;
     for (int i = 0; i < 4; ++i) ms4[i] = p->last_ms[i];
+    return 0;
+}
+
+int spchol_set_profile(spchol_plan* p, int on) {
+    if (!p) return SPCHOL_EINVAL;
+    p->profile = on;
+    for (int k = 0; k < 8; ++k) { p->kind_ms[k] = 0; p->kind_launches[k] = 0; }
+    return 0;
+}
+int spchol_get_profile(const spchol_plan* p, double* kind_ms8, int64_t* kind_launches8, double* flops2) {
+    if (!p) return SPCHOL_EINVAL;
+    for (int k = 0; k < 8; ++k) { if (kind_ms8) kind_ms8[k] = p->kind_ms[k]; if (kind_launches8) kind_launches8[k] = p->kind_launches[k]; }
+    if (flops2) { flops2[0] = p->H.gemm_flops_alg; flops2[1] = p->H.gemm_flops; }
     return 0;
 }
 

@@ -305,6 +305,18 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                         P.gemm_tasks.push_back(st.ge);
                         c.gx = std::max(c.gx, st.ge.M); c.gy = std::max(c.gy, st.ge.N);
                         P.gemm_flops += 2.0 * st.ge.M * st.ge.N * st.ge.K;
+                        {   // wanted entries: column j holds rows i >= j - diag
+                            double cnt = 0;
+                            const int Mq = st.ge.M, Nq = st.ge.N, dg = st.ge.diag;
+                            const int jfull = std::min(Nq, std::max(0, dg + 1));      // columns with all M rows
+                            cnt += static_cast<double>(jfull) * Mq;
+                            const int jlast = std::min(Nq, Mq + dg);                    // beyond this: empty
+                            if (jlast > jfull) {
+                                const double a = Mq - (jfull - dg), b = Mq - (jlast - 1 - dg);
+                                cnt += (a + b) * (jlast - jfull) / 2.0;
+                            }
+                            P.gemm_flops_alg += 2.0 * cnt * st.ge.K;
+                        }
                     }
                 }
                 a.count = static_cast<int>(P.potrf_tasks.size()) - a.begin;

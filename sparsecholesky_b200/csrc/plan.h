@@ -68,7 +68,8 @@ struct HostPlan {
     // statistics
     int64_t n_small = 0, n_large = 0;
     int max_m = 0, max_w = 0;
-    double gemm_flops = 0;           // flops issued through OP_GEMM (incl. masked-tile waste)
+    double gemm_flops = 0;           // flops of the full M x N x K rectangles of OP_GEMM tasks
+    double gemm_flops_alg = 0;       // flops of the wanted (lower-trapezoid) part only
 };
 
 void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P);
