@@ -1,0 +1,306 @@
+#!/usr/bin/env python
+"""bench.py -- fp64 factor GFLOP/s + chol() ms of the B200 numeric sparse Cholesky (BASELINE.json metric).
+
+    python bench.py --gpus 1 --steps K --warmup W [--workload lap3d_128]
+    python -m torch.distributed.run --nproc-per-node N ... bench.py --gpus N --steps K --warmup W
+    python bench.py --impl reference ...        # the reference's own CPU chol() on a bounded sample
+
+A step = one numeric factorization chol(A, S) of the workload with the symbolic plan resident
+(the plan is what `S` carries between calls).  `value` = sum_j colcount_j^2 / device time with the
+values of A already in HBM; `e2e` = the same through the host-buffer C-ABI call (pinned host A in,
+L back to pinned host memory inside the timed region).  Prints ONE JSON line on rank 0.
+"""
+import argparse
+import ctypes as C
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+WORKLOADS = {
+    # name: (dims, description, cpu sample dims)
+    "lap3d_128": ((128, 128, 128), "3D 7-point Laplacian 128^3 (2.1M rows), geometric ND", (32, 32, 32)),
+    "lap3d_96": ((96, 96, 96), "3D 7-point Laplacian 96^3, geometric ND", (32, 32, 32)),
+    "lap3d_64": ((64, 64, 64), "3D 7-point Laplacian 64^3, geometric ND", (32, 32, 32)),
+    "lap3d_32": ((32, 32, 32), "3D 7-point Laplacian 32^3, geometric ND", (32, 32, 32)),
+    "lap2d_1024": ((1024, 1024, 1), "2D 5-point Laplacian 1024^2 (1.05M rows), geometric ND", (256, 256, 1)),
+    "lap2d_256": ((256, 256, 1), "2D 5-point Laplacian 256^2, geometric ND", (256, 256, 1)),
+}
+METRIC = "fp64_factor_gflops"
+UNIT = "GFLOP/s"
+
+
+def make_matrix(dims):
+    import sparsecholesky_b200 as sc
+    from sparsecholesky_b200 import synth
+    perm = synth.nd_perm(*dims)
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
+    return sc.triplet_to_csc_matrix(ti, tj, tx, n)
+
+
+class ClockSampler:
+    """nvidia-smi clocks + throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,power.draw,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index, self.rows, self._stop, self._t = index, [], threading.Event(), None
+
+    def _run(self):
+        while not self._stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), f"--query-gpu={self.Q}",
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([v.strip() for v in out.strip().split(",")])
+            except Exception:
+                pass
+            self._stop.wait(0.1)
+
+    def start(self):
+        self._t = threading.Thread(target=self._run, daemon=True); self._t.start()
+
+    def stop(self):
+        self._stop.set()
+        if self._t:
+            self._t.join(timeout=6)
+        sm, mx, reasons = [], [], set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 7:
+                continue
+            try:
+                sm.append(float(r[0])); mx.append(float(r[1]))
+            except ValueError:
+                continue
+            for k, nm in enumerate(names):
+                if r[3 + k].lower().startswith("active"):
+                    reasons.add(nm)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": max(mx) if mx else None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def cpu_reference_time(dims, repeats=1):
+    """The reference's own chol() (oracle/_ref/libref.so when it was built from /root/reference,
+    else the plain-C port) on one host core.  Returns (kind, seconds_best, flops, n, nnzL)."""
+    from oracle import pyoracle as po
+    A = make_matrix(dims)
+    n = A.n
+    parent, Lp, _ = po.schol(n, A.p, A.i, want_Li=False)
+    nnzL = int(Lp[n])
+    cc = np.diff(Lp).astype(np.float64)
+    flops = float((cc * cc).sum())
+    best = None
+    if po.have_ref():
+        kind = "reference"
+        for _ in range(repeats):
+            rc, _, _, _, sec, err = po.ref_chol(n, A.p, A.i, A.x, nnzL)
+            assert rc == 0, err
+            best = sec if best is None else min(best, sec)
+    else:
+        kind = "port"
+        for _ in range(repeats):
+            t0 = time.perf_counter()
+            rc, _, _, _ = po.chol(n, A.p, A.i, A.x, parent, Lp)
+            sec = time.perf_counter() - t0
+            assert rc == 0
+            best = sec if best is None else min(best, sec)
+    return kind, best, flops, n, nnzL
+
+
+def run_reference(args, rank):
+    if rank != 0:
+        return
+    dims, desc, sample = WORKLOADS[args.workload]
+    from oracle import pyoracle as po
+    A = make_matrix(sample)
+    n = A.n
+    parent, Lp, _ = po.schol(n, A.p, A.i, want_Li=False)
+    nnzL = int(Lp[n])
+    cc = np.diff(Lp).astype(np.float64)
+    flops = float((cc * cc).sum())
+    use_ref = po.have_ref()
+
+    def step():
+        if use_ref:
+            rc, _, _, _, sec, err = po.ref_chol(n, A.p, A.i, A.x, nnzL)
+            assert rc == 0, err
+            return sec
+        t0 = time.perf_counter()
+        rc, _, _, _ = po.chol(n, A.p, A.i, A.x, parent, Lp)
+        assert rc == 0
+        return time.perf_counter() - t0
+
+    for _ in range(args.warmup):
+        step()
+    t = [step() for _ in range(args.steps)]
+    sec = float(np.mean(t))
+    gf = flops / sec * 1e-9
+    smp = f"{'x'.join(map(str, sample))} Laplacian (same generator/ND ordering), chol() only, symbolic excluded"
+    line = {
+        "impl": "reference", "metric": METRIC, "value": gf, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+        "warmup": args.warmup, "ms_per_step": sec * 1e3, "higher_is_better": True, "scaling": "strong",
+        "vs_baseline": None, "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "description": desc, "reference_sample": smp,
+                   "note": "the reference cannot run 128^3 (32-bit nnz overflow) and needs ~10 min for 64^3; "
+                           "its GFLOP/s falls with n (O(n^2) workspace), so this sample flatters it"},
+        "cpu_baseline": {"value": gf, "unit": UNIT, "cores": 1, "kind": "reference" if use_ref else "port", "sample": smp},
+        "e2e": {"value": gf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
+        "gpu_launches": 0,
+    }
+    print(json.dumps(line), flush=True)
+
+
+def main():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--workload", default="lap3d_128", choices=sorted(WORKLOADS))
+    ap.add_argument("--no-cpu-baseline", action="store_true")
+    ap.add_argument("--no-e2e", action="store_true")
+    args = ap.parse_args()
+    args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
+    rank = int(os.environ.get("RANK", "0"))
+    world = int(os.environ.get("WORLD_SIZE", "1"))
+    local_rank = int(os.environ.get("LOCAL_RANK", "0"))
+
+    if args.impl == "reference":
+        run_reference(args, rank)
+        return
+
+    import torch
+    import sparsecholesky_b200 as sc
+    from sparsecholesky_b200._lib import check, lib, ptr
+    L = lib()
+    if sc.device_count() <= 0:
+        raise SystemExit("bench.py: no CUDA device (the numeric path has no CPU fallback)")
+    torch.cuda.set_device(local_rank)
+    dist = None
+    if world > 1:
+        import torch.distributed as dist
+        dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
+        from sparsecholesky_b200 import multigpu
+        multigpu.run_bench(args, rank, world, local_rank, dist, WORKLOADS, METRIC, UNIT, ClockSampler, cpu_reference_time)
+        dist.destroy_process_group()
+        return
+
+    dims, desc, sample = WORKLOADS[args.workload]
+    t0 = time.time()
+    A = make_matrix(dims)
+    t_gen = time.time() - t0
+    t0 = time.time()
+    S = sc.schol(A)
+    t_sym = time.time() - t0
+    t0 = time.time()
+    plan = S.plan(local_rank)
+    t_plan = time.time() - t0
+    ps = S.plan_stats(local_rank)
+    stream = torch.cuda.ExternalStream(L.spchol_stream(plan.h), device=local_rank)
+    dAx = torch.from_numpy(A.x).to(f"cuda:{local_rank}")
+    info = C.c_int(0)
+
+    def step():
+        check(L.spchol_factor_device(plan.h, dAx.data_ptr()), "spchol_factor_device")
+
+    for _ in range(args.warmup):
+        step()
+    check(L.spchol_sync(plan.h, C.byref(info)))
+    assert info.value == 0, f"factorization failed: info={info.value}"
+    torch.cuda.synchronize()
+    sampler = ClockSampler(local_rank)
+    sampler.start()
+    e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
+    torch.cuda.synchronize()
+    e0.record(stream)
+    for _ in range(args.steps):
+        step()
+    e1.record(stream)
+    check(L.spchol_sync(plan.h, C.byref(info)))
+    torch.cuda.synchronize()
+    clocks = sampler.stop()
+    ms = e0.elapsed_time(e1) / args.steps
+    launches = int(L.spchol_last_launches(plan.h)) * args.steps
+    gflops = S.flops / ms * 1e-6
+
+    # roofline of the dominant kernel (DMMA SYRK/GEMM): one extra profiled step, CUDA events per launch group
+    check(L.spchol_set_profile(plan.h, 1))
+    step()
+    check(L.spchol_sync(plan.h, C.byref(info)))
+    kms = np.zeros(8); kl = np.zeros(8, np.int64); fl2 = np.zeros(2)
+    check(L.spchol_get_profile(plan.h, ptr(kms), ptr(kl), ptr(fl2)))
+    check(L.spchol_set_profile(plan.h, 0))
+    peak = C.c_double(0)
+    check(L.spchol_fp64_peak(local_rank, C.byref(peak)))
+    names = ["small_fronts", "zero", "extend_add", "potrf", "trsm", "gemm_dmma", "memset_assemble"]
+    kind_ms = {nm: round(float(kms[i]), 3) for i, nm in enumerate(names)}
+    gemm_ms = float(kms[5]); gemm_launches = int(kl[5])
+    achieved = fl2[0] / gemm_ms * 1e-9 if gemm_ms > 0 else 0.0
+    roofline = {
+        "kernel": "k_gemm_dmma", "bound": "tensor", "achieved": round(achieved, 3), "peak": round(peak.value, 3),
+        "unit": "TFLOP/s", "frac": round(achieved / peak.value, 4) if peak.value else None, "traffic": None,
+        "peak_source": "measured live: register-resident mma.sync.m8n8k4.f64 chains on this GPU (MEASURED_PEAKS.json has no FP64 entry)",
+        "launches": gemm_launches, "avg_launch_ms": round(gemm_ms / max(gemm_launches, 1), 4),
+        "algorithmic_flops_per_step": fl2[0], "share_of_step": round(gemm_ms / max(float(kms.sum()), 1e-9), 3),
+        "whole_factor_frac_of_peak": round(gflops * 1e-3 / peak.value, 4) if peak.value else None,
+    }
+
+    # e2e: host-buffer C-ABI call, pinned host memory, H2D + D2H inside the timed region
+    e2e = None
+    if not args.no_e2e:
+        nA = A.capacity()
+        use_csc = S.nnz <= 2**31 - 1
+        out_entries = S.nnz if use_csc else ps["lbuf_entries"]
+        hA = C.c_void_p(); hL = C.c_void_p()
+        check(L.spchol_host_alloc(nA * 8, C.byref(hA)), "host_alloc")
+        check(L.spchol_host_alloc(out_entries * 8, C.byref(hL)), "host_alloc")
+        C.memmove(hA.value, A.x.ctypes.data, nA * 8)
+        fn = L.spchol_factor if use_csc else L.spchol_factor_lbuf
+        e2e_steps = max(1, min(args.steps, 3))
+        check(fn(plan.h, hA.value, hL.value, C.byref(info)), "e2e warmup")
+        torch.cuda.synchronize()
+        t0 = time.perf_counter()
+        for _ in range(e2e_steps):
+            check(fn(plan.h, hA.value, hL.value, C.byref(info)), "e2e")
+        torch.cuda.synchronize()
+        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        tm = np.zeros(4)
+        L.spchol_last_timing(plan.h, ptr(tm))
+        e2e = {"value": S.flops / e2e_ms * 1e-6, "unit": UNIT, "ms_per_step": e2e_ms, "steps": e2e_steps,
+               "h2d_bytes_per_step": nA * 8, "d2h_bytes_per_step": out_entries * 8 + 4,
+               "result": "CSC L values (reference layout)" if use_csc else "supernodal L panels (nnz(L) > INT_MAX: no 32-bit CSC)",
+               "last_step_ms": {"h2d": tm[0], "numeric": tm[1], "export": tm[2], "d2h": tm[3]}}
+        L.spchol_host_free(hA); L.spchol_host_free(hL)
+
+    cpu = None
+    if not args.no_cpu_baseline:
+        kind, sec, fl, n_s, nnz_s = cpu_reference_time(sample)
+        cpu = {"value": fl / sec * 1e-9, "unit": UNIT, "cores": 1, "kind": kind, "seconds": sec,
+               "sample": f"{'x'.join(map(str, sample))} Laplacian, same generator + ND ordering (n={n_s}, nnz(L)={nnz_s}); "
+                         f"chol() only; the reference is single-threaded and cannot run the full workload "
+                         f"({'32-bit nnz overflow' if S.nnz > 2**31 - 1 else 'O(n^2) workspace: minutes to hours'})",
+               "host_cores_available": os.cpu_count()}
+
+    line = {
+        "metric": METRIC, "value": gflops, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
+        "ms_per_step": ms, "chol_ms": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+        "dtype": "f64", "data": "synthetic",
+        "config": {"workload": args.workload, "description": desc, "n": A.n, "nnz_A": A.capacity(), "nnz_L": S.nnz,
+                   "flops": S.flops, "fronts": ps["ns"], "levels": ps["nlevels"], "l2": "inputs larger than L2 "
+                   f"(L buffer {ps['lbuf_entries'] * 8 / 1e9:.2f} GB + workspace {ps['ws_entries'] * 8 / 1e9:.2f} GB rewritten every step)",
+                   "host_seconds": {"generate": round(t_gen, 2), "schol": round(t_sym, 2), "plan_upload": round(t_plan, 2)}},
+        "roofline": roofline, "kernel_ms": kind_ms, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+        "clocks": clocks,
+    }
+    print(json.dumps(line), flush=True)
+
+
+if __name__ == "__main__":
+    main()

@@ -98,6 +98,14 @@ int  spchol_factor(spchol_plan*, const double* Ax_host, double* Lx_host, int* in
 int  spchol_factor_device(spchol_plan*, const double* dAx);
 int  spchol_export_csc_device(spchol_plan*, double* dLx);      /* gather panels -> CSC order (device ptr) */
 int  spchol_sync(spchol_plan*, int* info);
+/* Host-buffer call for patterns with nnz(L) > INT_MAX: L is returned as the supernodal panel
+ * buffer (lbuf_entries doubles, layout described by spchol_plan_stats / DESIGN.md) */
+int  spchol_factor_lbuf(spchol_plan*, const double* Ax_host, double* Lbuf_host, int* info);
+/* pinned host memory for the host-buffer calls (cudaHostAlloc / cudaFreeHost) */
+int  spchol_host_alloc(int64_t bytes, void** out);
+int  spchol_host_free(void* ptr);
+/* measured FP64 tensor-pipe (DMMA) peak of the device in TFLOP/s: the roofline denominator */
+int  spchol_fp64_peak(int device, double* tflops);
 /* pointer to the device L buffer (supernodal panels), for callers that keep L resident */
 int  spchol_lbuf(spchol_plan*, double** dL, int64_t* entries);
 /* copy the supernodal L buffer to host (entries doubles) */

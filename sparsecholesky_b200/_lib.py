@@ -47,6 +47,10 @@ SIGNATURES = {
     "spchol_factor_device": (C.c_int, [_VP, _VP]),
     "spchol_export_csc_device": (C.c_int, [_VP, _VP]),
     "spchol_sync": (C.c_int, [_VP, C.POINTER(C.c_int)]),
+    "spchol_factor_lbuf": (C.c_int, [_VP, _VP, _VP, C.POINTER(C.c_int)]),
+    "spchol_host_alloc": (C.c_int, [C.c_int64, C.POINTER(_VP)]),
+    "spchol_host_free": (C.c_int, [_VP]),
+    "spchol_fp64_peak": (C.c_int, [C.c_int, C.POINTER(C.c_double)]),
     "spchol_lbuf": (C.c_int, [_VP, C.POINTER(_VP), C.POINTER(C.c_int64)]),
     "spchol_lbuf_to_host": (C.c_int, [_VP, _VP]),
     "spchol_last_timing": (C.c_int, [_VP, _VP]),

@@ -301,6 +301,88 @@ int spchol_factor(spchol_plan* p, const double* Ax, double* Lx, int* info) {
     return SPCHOL_OK;
 }
 
+// H2D of Ax, numeric, D2H of the whole supernodal L buffer (for patterns whose CSC L exceeds
+// the reference's 32-bit indices, e.g. the 128^3 Laplacian).
+int spchol_factor_lbuf(spchol_plan* p, const double* Ax, double* Lbuf_host, int* info) {
+    if (!p || !Ax || !Lbuf_host) { set_error("spchol_factor_lbuf: null argument"); return SPCHOL_EINVAL; }
+    CK(cudaSetDevice(p->device));
+    int rc;
+    if (!p->dAx && (rc = dalloc(p, p->H.nnzA, &p->dAx))) return rc;
+    cudaStream_t st = p->stream;
+    CK(cudaEventRecord(p->ev[0], st));
+    CK(cudaMemcpyAsync(p->dAx, Ax, static_cast<size_t>(p->H.nnzA) * sizeof(double), cudaMemcpyHostToDevice, st));
+    CK(cudaEventRecord(p->ev[1], st));
+    if ((rc = run_numeric(p, p->dAx))) return rc;
+    CK(cudaEventRecord(p->ev[2], st));
+    CK(cudaEventRecord(p->ev[3], st));
+    CK(cudaMemcpyAsync(Lbuf_host, p->dL, static_cast<size_t>(p->H.lbuf_entries) * sizeof(double), cudaMemcpyDeviceToHost, st));
+    CK(cudaEventRecord(p->ev[4], st));
+    if ((rc = read_info(p, info))) return rc;
+    for (int i = 0; i < 4; ++i) {
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, p->ev[i], p->ev[i + 1]));
+        p->last_ms[i] = ms;
+    }
+    return SPCHOL_OK;
+}
+
+int spchol_host_alloc(int64_t bytes, void** out) {
+    if (!out || bytes <= 0) return SPCHOL_EINVAL;
+    *out = nullptr;
+    if (spchol_device_count() <= 0) { set_error("spchol_host_alloc: no CUDA device"); return SPCHOL_ENOGPU; }
+    CK(cudaHostAlloc(out, static_cast<size_t>(bytes), cudaHostAllocDefault));
+    return 0;
+}
+int spchol_host_free(void* ptr) {
+    if (!ptr) return 0;
+    CK(cudaFreeHost(ptr));
+    return 0;
+}
+
+namespace {
+__global__ void k_dmma_probe(double* out, int iters) {
+    double c[8][2];
+#pragma unroll
+    for (int i = 0; i < 8; ++i) { c[i][0] = 0; c[i][1] = 0; }
+    const double a = 1.0 + threadIdx.x * 1e-9, b = 1.0 - threadIdx.x * 1e-9;
+    for (int it = 0; it < iters; ++it) {
+#pragma unroll
+        for (int i = 0; i < 8; ++i) dmma884(c[i][0], c[i][1], a, b);
+    }
+    double s = 0;
+#pragma unroll
+    for (int i = 0; i < 8; ++i) s += c[i][0] + c[i][1];
+    out[blockIdx.x * blockDim.x + threadIdx.x] = s;
+}
+}  // namespace
+
+// FP64 tensor-pipe peak of this GPU: register-resident DMMA chains, best of 5 (TFLOP/s).
+int spchol_fp64_peak(int device, double* tflops) {
+    if (!tflops) return SPCHOL_EINVAL;
+    if (spchol_device_count() <= 0) { set_error("spchol_fp64_peak: no CUDA device"); return SPCHOL_ENOGPU; }
+    CK(cudaSetDevice(device));
+    cudaDeviceProp prop;
+    CK(cudaGetDeviceProperties(&prop, device));
+    const int blocks = prop.multiProcessorCount * 2, threads = 256, iters = 20000;
+    double* out = nullptr;
+    CK(cudaMalloc(&out, sizeof(double) * blocks * threads));
+    cudaEvent_t e0, e1;
+    CK(cudaEventCreate(&e0)); CK(cudaEventCreate(&e1));
+    float best = 1e30f;
+    for (int r = 0; r < 7; ++r) {
+        CK(cudaEventRecord(e0));
+        k_dmma_probe<<<blocks, threads>>>(out, iters);
+        CK(cudaEventRecord(e1));
+        CK(cudaEventSynchronize(e1));
+        float ms = 0;
+        CK(cudaEventElapsedTime(&ms, e0, e1));
+        if (r >= 2 && ms < best) best = ms;
+    }
+    cudaEventDestroy(e0); cudaEventDestroy(e1); cudaFree(out);
+    *tflops = 2.0 * 8 * 8 * 4 * 8 * iters * static_cast<double>(threads / 32) * blocks / best * 1e-9;
+    return 0;
+}
+
 int spchol_lbuf(spchol_plan* p, double** dL, int64_t* entries) {
     if (!p) return SPCHOL_EINVAL;
     if (dL) *dL = p->dL;
