@@ -1,0 +1,90 @@
+// The reference's tests/test_chol.cpp restated as plain asserts (GoogleTest is not available
+// offline) against the drop-in header.  Usage: test_dropin <data dir> [gpu]
+// Without "gpu" only the host-side cases run (the CPU container); with it chol() runs on the GPU.
+#include <cmath>
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+
+#include "chol.hpp"
+#include "mtx_reader.hpp"
+
+#define CHECK(c) do { if (!(c)) { std::printf("FAILED %s:%d: %s\n", __FILE__, __LINE__, #c); std::exit(1); } } while (0)
+
+static void dense_cholesky(std::vector<double>& a, int n) {      // stand-in for the test's dpotrf_ call
+    for (int k = 0; k < n; ++k) {
+        a[k + k * n] = std::sqrt(a[k + k * n]);
+        for (int i = k + 1; i < n; ++i) a[i + k * n] /= a[k + k * n];
+        for (int j = k + 1; j < n; ++j) for (int i = j; i < n; ++i) a[i + j * n] -= a[i + k * n] * a[j + k * n];
+    }
+}
+
+int main(int argc, char** argv) {
+    const std::string data = argc > 1 ? argv[1] : "tests/data";
+    const bool gpu = argc > 2 && !std::strcmp(argv[2], "gpu");
+    const std::vector<std::vector<int>> pattern = {{0}, {1}, {0, 2}, {3}, {0, 2, 4}, {0, 1, 3, 5}, {0, 2, 5, 6}};
+    {   // CholeskyTest.EliminationTree (reference tests/test_chol.cpp:6-25)
+        auto A = build_csc_matrix_from_pattern<double>(pattern);
+        auto parent = etree(A);
+        CHECK(parent.size() == A.size());
+        CHECK((parent == std::vector<int>{2, 5, 4, 5, 5, 6, -1}));
+    }
+    {   // CholeskyTest.ColumnReach (:27-57)
+        auto A = build_csc_matrix_from_pattern<double>(pattern);
+        const auto n = A.size();
+        std::vector<int> w(n, -1), s(n);
+        std::vector<double> x(n);
+        auto parent = etree(A);
+        auto t = ereach(A, 5, parent, s, w, x, n); (void)t;
+        CHECK((s == std::vector<int>{3, 1, 0, 2, 4, 5, 6}));
+        t = ereach(A, 5, parent, s, w, n);
+        CHECK((s == std::vector<int>{3, 1, 0, 2, 4, 5, 6}));
+    }
+    {   // symbolic known answers: bcsstk01 through the reader
+        auto A = load_matrix_market_to_csc<double>(data + "/bcsstk01.mtx");
+        CHECK(A.size() == 48 && A.p()[48] == 224);
+        auto S = schol(A);
+        CHECK(S.capacity() == 877 && S.size() == 48);
+        std::vector<std::size_t> sn;
+        auto id = compute_supernodes(S, sn);
+        CHECK(sn.size() == 16 && sn.back() == 48);
+        auto at = atree(S, id, sn);
+        CHECK(compute_levels(at).size() == 13 && compute_levels(S.parent).size() == 46);
+        bool threw = false;
+        try { load_matrix_market_to_csc<double>("/nonexistent.mtx"); } catch (const std::runtime_error&) { threw = true; }
+        CHECK(threw);
+    }
+    if (gpu) {
+        {   // CholeskyTest.SimplicialCholesky (:59-97)
+            std::vector<double> expected = {4.0, 1.0, 1.0, 1.0, 3.0, 0.0, 1.0, 0.0, 2.0};
+            dense_cholesky(expected, 3);
+            std::vector<int> ti = {0, 0, 0, 1, 1, 2}, tj = {0, 1, 2, 1, 2, 2};
+            std::vector<double> tx = {4.0, 1.0, 1.0, 3.0, 0.0, 2.0};
+            auto A = triplet_to_csc_matrix(ti, tj, tx, 3);
+            auto L = chol(A);
+            CHECK(L.has_value());
+            auto result = csc_to_dense(*L);
+            for (int j = 0; j < 3; ++j) for (int i = j; i < 3; ++i) CHECK(std::fabs(result[i + j * 3] - expected[i + j * 3]) < 1e-9);
+        }
+        {   // README usage: S reused across numeric calls; known first values of L
+            auto A = load_matrix_market_to_csc<double>(data + "/bcsstk01.mtx");
+            auto S = schol(A);
+            auto L = chol(A, S).value();
+            CHECK(L.p() == S.p() && L.i() == S.i());
+            CHECK(std::fabs(L.x()[0] - 1682.9344962059574) < 1e-9 && std::fabs(L.x()[3] - (-1.9806673051415467)) < 1e-9);
+            auto L2 = chol(A, S).value();
+            CHECK(L2.x() == L.x());
+        }
+        {   // error path (reference chol.hpp:850)
+            auto A = triplet_to_csc_matrix<double>({0, 0, 1}, {0, 1, 1}, {1.0, 2.0, 1.0}, 2);
+            auto L = chol(A);
+            CHECK(!L.has_value() && L.error() == "A is not positive definite.");
+        }
+    } else {
+        auto A = triplet_to_csc_matrix<double>({0, 0, 1}, {0, 1, 1}, {4.0, 1.0, 3.0}, 2);
+        auto L = chol(A);
+        if (spchol_device_count() == 0) CHECK(!L.has_value() && L.error().find("no CUDA device") != std::string::npos);
+    }
+    std::printf("test_dropin OK (%s)\n", gpu ? "gpu" : "host only");
+    return 0;
+}
