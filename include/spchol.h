@@ -29,9 +29,11 @@ extern "C" {
 #define SPCHOL_ECUDA    -4   /* CUDA runtime error */
 #define SPCHOL_ERANGE   -5   /* nnz(L) does not fit the 32-bit CSC the reference API uses */
 #define SPCHOL_EIO      -6
+#define SPCHOL_ENCCL    -7   /* NCCL missing or failed (multi-GPU entry points only) */
 
 typedef struct spchol_symbolic spchol_symbolic;  /* host symbolic analysis == reference SChol + supernodes */
 typedef struct spchol_plan     spchol_plan;      /* device-resident numeric plan for one pattern */
+typedef struct spchol_comm     spchol_comm;      /* multi-GPU communicator: one rank per process per GPU */
 
 const char* spchol_last_error(void);
 const char* spchol_version(void);
@@ -89,6 +91,35 @@ int  spchol_plan_stats(const spchol_plan*, int64_t* stats);
 /* host-only dry run of the planner (no GPU needed): same stats layout, device_bytes = bytes the
  * plan would allocate; extra[0..5] = #small ops, #extadd ops, #potrf ops, #trsm ops, #gemm ops, gemm flops (as int64) */
 int  spchol_plan_dryrun(const spchol_symbolic*, int64_t* stats, int64_t* extra);
+/* same for rank `rank` of a `world`-rank plan; extra[6] = #transfers, extra[7] = doubles moved;
+ * comm_sig (may be NULL, 4 slots): order-sensitive hashes of this rank's transfer sequence, used by the
+ * tests to check that the ranks' programs match: [0] #broadcasts, [1] #sends, [2] #recvs, [3] hash */
+int  spchol_plan_dryrun_dist(const spchol_symbolic*, int rank, int world, const int* dist_opts,
+                             int64_t* stats, int64_t* extra, int64_t* comm_sig);
+
+/* ---- multi-GPU: one matrix factored by `world` ranks, one process per GPU ------------------ */
+/* No reference counterpart (the reference is single-threaded).  The host binding
+ * moves the 128-byte NCCL unique id from rank 0 to the others (torch.distributed / MPI / a file);
+ * libnccl.so.2 is dlopen()ed here, single-GPU callers never need it. */
+int  spchol_comm_unique_id(void* id128);
+int  spchol_comm_create(int rank, int world, const void* id128, int device, spchol_comm** out);
+void spchol_comm_destroy(spchol_comm*);
+int  spchol_comm_rank(const spchol_comm*);
+int  spchol_comm_world(const spchol_comm*);
+/* Collective over the communicator: every rank passes the same symbolic analysis.  The assembly
+ * tree is mapped proportionally (subtrees -> ranks, split subtrees -> rank groups); fronts of a
+ * rank group are factored block-column cyclic with in-place NCCL broadcasts of factored block
+ * columns; contribution blocks move up with NCCL broadcast / send / recv.  dist_opts (may be NULL):
+ * [0] block-column width (default 256), [1] narrowest front that is factored by a group (default 1024).
+ * spchol_factor_device / _sync / _export_csc_device / _lbuf work as for a single-GPU plan; every
+ * rank must call them in the same order.  Exported CSC values are 0 where another rank holds the
+ * entry (sum the ranks' vectors); info is already the minimum over all ranks. */
+int  spchol_plan_create_dist(const spchol_symbolic*, spchol_comm*, const int* dist_opts, spchol_plan** out);
+/* dist_stats[0..7] = rank, world, fronts held, fronts factored by a group, #transfers, doubles moved
+ * per factorization by this rank, block-column width, 0; rank_load[world] = estimated flops per rank */
+int  spchol_plan_dist_stats(const spchol_plan*, int64_t* dist_stats, double* rank_load);
+/* host-only: the mapping a `world`-rank plan would use (no GPU, no NCCL): own_lo/own_n per relaxed front */
+int  spchol_map_fronts(const spchol_symbolic*, int world, int dist_min_w, int* own_lo, int* own_n, double* rank_load);
 
 /* Host-buffer call (what chol(A,S) binds): H2D of Ax, factor, CSC gather, D2H of Lx.
  * info = 0, or (1-based) a column whose pivot was <= 0 -> "A is not positive definite." (chol.hpp:849-850). */
@@ -114,7 +145,7 @@ int  spchol_lbuf_to_host(spchol_plan*, double* L_host);
 int  spchol_last_timing(const spchol_plan*, double* ms4);
 /* per-op-kind device timing (CUDA events around every launch group; adds a sync, so use it on an
  * extra untimed step): kinds 0 small fronts, 1 zero, 2 extend-add, 3 potrf, 4 trsm, 5 gemm/syrk (DMMA),
- * 6 memset+assemble.  flops2[0] = algorithmic flops of the kind-5 launches (lower trapezoids only),
+ * 6 inter-GPU transfers (NCCL), 7 memset+assemble (+ the info all-reduce of a multi-GPU plan).  flops2[0] = algorithmic flops of the kind-5 launches (lower trapezoids only),
  * flops2[1] = flops of their full rectangles. */
 int  spchol_set_profile(spchol_plan*, int on);
 int  spchol_get_profile(const spchol_plan*, double* kind_ms8, int64_t* kind_launches8, double* flops2);

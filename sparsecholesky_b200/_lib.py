@@ -43,6 +43,15 @@ SIGNATURES = {
     "spchol_plan_destroy": (None, [_VP]),
     "spchol_plan_stats": (C.c_int, [_VP, _VP]),
     "spchol_plan_dryrun": (C.c_int, [_VP, _VP, _VP]),
+    "spchol_plan_dryrun_dist": (C.c_int, [_VP, C.c_int, C.c_int, _VP, _VP, _VP, _VP]),
+    "spchol_comm_unique_id": (C.c_int, [_VP]),
+    "spchol_comm_create": (C.c_int, [C.c_int, C.c_int, _VP, C.c_int, C.POINTER(_VP)]),
+    "spchol_comm_destroy": (None, [_VP]),
+    "spchol_comm_rank": (C.c_int, [_VP]),
+    "spchol_comm_world": (C.c_int, [_VP]),
+    "spchol_plan_create_dist": (C.c_int, [_VP, _VP, _VP, C.POINTER(_VP)]),
+    "spchol_plan_dist_stats": (C.c_int, [_VP, _VP, _VP]),
+    "spchol_map_fronts": (C.c_int, [_VP, C.c_int, C.c_int, _VP, _VP, _VP]),
     "spchol_factor": (C.c_int, [_VP, _VP, _VP, C.POINTER(C.c_int)]),
     "spchol_factor_device": (C.c_int, [_VP, _VP]),
     "spchol_export_csc_device": (C.c_int, [_VP, _VP]),

@@ -27,7 +27,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     if verbose:
         cmd += ["-Xptxas", "-v"]
     cmd += [os.path.join(CSRC, s) for s in SOURCES]
-    cmd += ["-o", OUT, "-lcudart"]
+    cmd += ["-o", OUT, "-lcudart", "-ldl"]
     r = subprocess.run(cmd, capture_output=True, text=True)
     if r.returncode != 0:
         sys.stderr.write(r.stdout + r.stderr)

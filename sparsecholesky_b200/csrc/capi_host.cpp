@@ -156,18 +156,24 @@ int spchol_symbolic_stats(const spchol_symbolic* s, int64_t* st) {
     return 0;
 }
 
-int spchol_plan_dryrun(const spchol_symbolic* s, int64_t* st, int64_t* extra) {
+static int dryrun_impl(const spchol_symbolic* s, int rank, int world, const int* dist_opts, int64_t* st,
+                       int64_t* extra, int nextra, int64_t* comm_sig) {
     if (!s || !st) return SPCHOL_EINVAL;
     try {
         HostPlan H; PlanOptions opt;
         opt.want_csc = s->S.nnzL <= INT_MAX ? 1 : 0;
+        opt.rank = rank; opt.world = world;
+        if (dist_opts) {
+            if (dist_opts[0] > 0) opt.dist_NB = dist_opts[0];
+            if (dist_opts[1] > 0) opt.dist_min_w = dist_opts[1];
+        }
         build_plan(s->S, opt, H);
         st[0] = H.ns; st[1] = H.nlevels; st[2] = H.n_small; st[3] = H.n_large; st[4] = H.lbuf_entries;
         st[5] = H.ws_entries; st[6] = static_cast<int64_t>(H.ops.size()); st[7] = H.max_m; st[8] = H.max_w;
         st[9] = 8 * (H.lbuf_entries + H.ws_entries) + 8 * static_cast<int64_t>(H.a_dest.size() + H.l_src.size()) +
                 4 * static_cast<int64_t>(H.rel.size()) + 60 * static_cast<int64_t>(H.ns);
         if (extra) {
-            for (int k = 0; k < 6; ++k) extra[k] = 0;
+            for (int k = 0; k < nextra; ++k) extra[k] = 0;
             for (const Op& op : H.ops) {
                 if (op.kind == OP_SMALL) ++extra[0];
                 else if (op.kind == OP_EXTADD) ++extra[1];
@@ -176,8 +182,45 @@ int spchol_plan_dryrun(const spchol_symbolic* s, int64_t* st, int64_t* extra) {
                 else if (op.kind == OP_GEMM) ++extra[4];
             }
             extra[5] = static_cast<int64_t>(H.gemm_flops);
+            if (nextra > 7) { extra[6] = static_cast<int64_t>(H.comm_tasks.size()); extra[7] = H.comm_doubles; }
+        }
+        if (comm_sig) {
+            comm_sig[0] = comm_sig[1] = comm_sig[2] = 0;
+            uint64_t h = 1469598103934665603ull;
+            auto mix = [&](uint64_t v) { h ^= v; h *= 1099511628211ull; };
+            for (const CommTask& t : H.comm_tasks) {
+                ++comm_sig[t.kind];
+                // what every participant must agree on: kind of exchange, group/pair, root, length
+                if (t.kind == COMM_BCAST) { mix(1); mix(t.lo); mix(t.n); mix(t.root); }
+                else { mix(2); mix(std::min(t.root, rank)); mix(std::max(t.root, rank)); }
+                mix(static_cast<uint64_t>(t.count));
+            }
+            comm_sig[3] = static_cast<int64_t>(h & 0x7fffffffffffffffull);
         }
     } catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
+    return 0;
+}
+
+int spchol_plan_dryrun(const spchol_symbolic* s, int64_t* st, int64_t* extra) {
+    return dryrun_impl(s, 0, 1, nullptr, st, extra, 6, nullptr);
+}
+
+int spchol_plan_dryrun_dist(const spchol_symbolic* s, int rank, int world, const int* dist_opts, int64_t* st,
+                            int64_t* extra, int64_t* comm_sig) {
+    if (world < 1 || rank < 0 || rank >= world) { set_error("spchol_plan_dryrun_dist: bad rank/world"); return SPCHOL_EINVAL; }
+    return dryrun_impl(s, rank, world, dist_opts, st, extra, 8, comm_sig);
+}
+
+int spchol_map_fronts(const spchol_symbolic* s, int world, int dist_min_w, int* own_lo, int* own_n, double* rank_load) {
+    if (!s || world < 1) return SPCHOL_EINVAL;
+    const Symbolic& S = s->S;
+    std::vector<int> w(S.ns), m(S.ns), lo, cnt;
+    std::vector<double> load;
+    for (int k = 0; k < S.ns; ++k) { w[k] = S.w(k); m[k] = S.m(k); }
+    map_fronts(S.ns, S.sn_parent.data(), w.data(), m.data(), world, dist_min_w > 0 ? dist_min_w : PlanOptions().dist_min_w,
+               lo, cnt, load);
+    for (int k = 0; k < S.ns; ++k) { if (own_lo) own_lo[k] = lo[k]; if (own_n) own_n[k] = cnt[k]; }
+    if (rank_load) for (int r = 0; r < world; ++r) rank_load[r] = load[r];
     return 0;
 }
 

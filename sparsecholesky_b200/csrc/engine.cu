@@ -2,9 +2,14 @@
 // point returns SPCHOL_ENOGPU when no CUDA device is usable.
 #include <climits>
 #include <cstdio>
+#include <cstdlib>
 #include <cstring>
+#include <dlfcn.h>
+#include <map>
 #include <new>
+#include <set>
 #include <string>
+#include <utility>
 #include <vector>
 
 #include "../../include/spchol.h"
@@ -22,7 +27,73 @@ using namespace spchol;
         }                                                                                 \
     } while (0)
 
+// ---- NCCL, bound at run time (dlopen) so that single-GPU users need no NCCL at all -----------
+namespace {
+struct NcclId { char internal[128]; };
+struct NcclApi {
+    void* h = nullptr;
+    int (*GetUniqueId)(NcclId*) = nullptr;
+    int (*CommInitRank)(void**, int, NcclId, int) = nullptr;
+    int (*CommSplit)(void*, int, int, void**, void*) = nullptr;
+    int (*CommDestroy)(void*) = nullptr;
+    int (*Broadcast)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Send)(const void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*Recv)(void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*AllReduce)(const void*, void*, size_t, int, int, void*, cudaStream_t) = nullptr;
+    int (*GroupStart)() = nullptr;
+    int (*GroupEnd)() = nullptr;
+    const char* (*GetErrorString)(int) = nullptr;
+};
+constexpr int kNcclInt32 = 2, kNcclFloat64 = 8, kNcclMin = 3, kNcclSplitNoColor = -1;
+
+NcclApi* nccl_api() {
+    static NcclApi api;
+    static bool tried = false;
+    if (tried) return api.h ? &api : nullptr;
+    tried = true;
+    const char* names[] = {getenv("SPCHOL_NCCL_LIB"), "libnccl.so.2", "libnccl.so"};
+    for (const char* nm : names) {
+        if (!nm || !*nm) continue;
+        api.h = dlopen(nm, RTLD_NOW | RTLD_GLOBAL);
+        if (api.h) break;
+    }
+    if (!api.h) return nullptr;
+    bool ok = true;
+    auto sym = [&](const char* nm) { void* f = dlsym(api.h, nm); if (!f) ok = false; return f; };
+    api.GetUniqueId = reinterpret_cast<decltype(api.GetUniqueId)>(sym("ncclGetUniqueId"));
+    api.CommInitRank = reinterpret_cast<decltype(api.CommInitRank)>(sym("ncclCommInitRank"));
+    api.CommSplit = reinterpret_cast<decltype(api.CommSplit)>(sym("ncclCommSplit"));
+    api.CommDestroy = reinterpret_cast<decltype(api.CommDestroy)>(sym("ncclCommDestroy"));
+    api.Broadcast = reinterpret_cast<decltype(api.Broadcast)>(sym("ncclBroadcast"));
+    api.Send = reinterpret_cast<decltype(api.Send)>(sym("ncclSend"));
+    api.Recv = reinterpret_cast<decltype(api.Recv)>(sym("ncclRecv"));
+    api.AllReduce = reinterpret_cast<decltype(api.AllReduce)>(sym("ncclAllReduce"));
+    api.GroupStart = reinterpret_cast<decltype(api.GroupStart)>(sym("ncclGroupStart"));
+    api.GroupEnd = reinterpret_cast<decltype(api.GroupEnd)>(sym("ncclGroupEnd"));
+    api.GetErrorString = reinterpret_cast<decltype(api.GetErrorString)>(sym("ncclGetErrorString"));
+    if (!ok) { dlclose(api.h); api.h = nullptr; return nullptr; }
+    return &api;
+}
+}  // namespace
+
+#define NCK(call)                                                                         \
+    do {                                                                                  \
+        int e_ = (call);                                                                  \
+        if (e_ != 0) {                                                                    \
+            set_error(std::string(#call) + ": " + nccl_api()->GetErrorString(e_));        \
+            return SPCHOL_ENCCL;                                                          \
+        }                                                                                 \
+    } while (0)
+
+struct spchol_comm {
+    int rank = 0, world = 1, device = 0;
+    void* world_comm = nullptr;
+    std::map<std::pair<int, int>, void*> groups;      // (lo, n) -> sub-communicator (nullptr: not a member)
+};
+
 struct spchol_plan {
+    spchol_comm* comm = nullptr;
+    int *d_own_n = nullptr, *d_own_idx = nullptr;
     int device = 0;
     HostPlan H;
     cudaStream_t stream = nullptr;
@@ -98,7 +169,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         pkind.push_back(kind);
         return 0;
     };
-    mark(6);
+    mark(7);
     CK(cudaMemsetAsync(p->dL, 0, static_cast<size_t>(H.lbuf_entries) * sizeof(double), st));
     CK(cudaMemsetAsync(p->dinfo, 0x7f, sizeof(int), st));
     {
@@ -148,9 +219,31 @@ int run_numeric(spchol_plan* p, const double* dAx) {
                 ++launches;
             }
             break;
+        case OP_COMM: {
+            NcclApi* nc = nccl_api();
+            if (!p->comm || !nc) { set_error("spchol: plan has transfers but no communicator"); return SPCHOL_EINVAL; }
+            for (int b = 0; b < op.count; ++b) {
+                const CommTask& t = H.comm_tasks[op.begin + b];
+                double* buf = (t.space ? p->dW : p->dL) + t.off;
+                if (t.kind == COMM_BCAST) {
+                    void* c = t.n == p->comm->world ? p->comm->world_comm : p->comm->groups[{t.lo, t.n}];
+                    if (!c) { set_error("spchol: broadcast on a rank group this rank is not part of"); return SPCHOL_EINVAL; }
+                    NCK(nc->Broadcast(buf, buf, static_cast<size_t>(t.count), kNcclFloat64, t.root - t.lo, c, st));
+                } else if (t.kind == COMM_SEND) {
+                    NCK(nc->Send(buf, static_cast<size_t>(t.count), kNcclFloat64, t.root, p->comm->world_comm, st));
+                } else {
+                    NCK(nc->Recv(buf, static_cast<size_t>(t.count), kNcclFloat64, t.root, p->comm->world_comm, st));
+                }
+                ++launches;
+            }
+        } break;
         default: break;
         }
         if (prof) p->kind_launches[op.kind] += launches - before;
+    }
+    if (p->comm && p->comm->world > 1) {      // first failing column over all ranks
+        mark(7);
+        NCK(nccl_api()->AllReduce(p->dinfo, p->dinfo, 1, kNcclInt32, kNcclMin, p->comm->world_comm, st));
     }
     mark(-1);
     CK(cudaGetLastError());
@@ -184,7 +277,8 @@ int spchol_device_count(void) {
     return n;
 }
 
-int spchol_plan_create(const spchol_symbolic* sym, int device, spchol_plan** out) {
+static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm* comm, const int* dist_opts,
+                            spchol_plan** out) {
     if (!sym || !out) { set_error("spchol_plan_create: null argument"); return SPCHOL_EINVAL; }
     *out = nullptr;
     if (spchol_device_count() <= 0) {
@@ -194,16 +288,38 @@ int spchol_plan_create(const spchol_symbolic* sym, int device, spchol_plan** out
     spchol_plan* p = new (std::nothrow) spchol_plan();
     if (!p) return SPCHOL_ENOMEM;
     p->device = device;
+    p->comm = comm;
     try {
         PlanOptions opt;
         const Symbolic& S = symbolic_of(sym);
         opt.want_csc = S.nnzL <= INT_MAX ? 1 : 0;
+        if (comm) { opt.rank = comm->rank; opt.world = comm->world; }
+        if (dist_opts) {
+            if (dist_opts[0] > 0) opt.dist_NB = dist_opts[0];
+            if (dist_opts[1] > 0) opt.dist_min_w = dist_opts[1];
+        }
         build_plan(S, opt, p->H);
     } catch (const std::exception& e) {
         set_error(e.what()); delete p; return SPCHOL_EINVAL;
     }
     int rc = 0;
     auto fail = [&](int code) { spchol_plan_destroy(p); return code; };
+    if (comm && comm->world > 1) {
+        // one sub-communicator per distinct rank group of the (global) mapping; every rank walks the
+        // same sorted list, so the collective ncclCommSplit calls line up
+        NcclApi* nc = nccl_api();
+        std::set<std::pair<int, int>> need;
+        for (int s2 = 0; s2 < p->H.ns; ++s2)
+            if (p->H.own_n[s2] > 1 && p->H.own_n[s2] < comm->world) need.insert({p->H.own_lo[s2], p->H.own_n[s2]});
+        for (const auto& g : need) {
+            if (comm->groups.count(g)) continue;
+            const bool in = comm->rank >= g.first && comm->rank < g.first + g.second;
+            void* sub = nullptr;
+            const int e = nc->CommSplit(comm->world_comm, in ? 0 : kNcclSplitNoColor, comm->rank, &sub, nullptr);
+            if (e != 0) { set_error(std::string("ncclCommSplit: ") + nc->GetErrorString(e)); return fail(SPCHOL_ENCCL); }
+            comm->groups[g] = in ? sub : nullptr;
+        }
+    }
     if (cudaSetDevice(device) != cudaSuccess) { set_error("cudaSetDevice failed"); return fail(SPCHOL_ECUDA); }
     if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); return fail(SPCHOL_ECUDA); }
     for (auto& e : p->ev) if (cudaEventCreate(&e) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(SPCHOL_ECUDA); }
@@ -212,6 +328,7 @@ int spchol_plan_create(const spchol_symbolic* sym, int device, spchol_plan** out
     UP(H.first, p->d_first); UP(H.w, p->d_w); UP(H.m, p->d_m); UP(H.ld, p->d_ld); UP(H.parent, p->d_parent);
     UP(H.panel_off, p->d_panel_off); UP(H.cb_off, p->d_cb_off); UP(H.rel_off, p->d_rel_off);
     UP(H.rel, p->d_rel); UP(H.child_ptr, p->d_child_ptr); UP(H.child_idx, p->d_child_idx);
+    UP(H.own_n, p->d_own_n); UP(H.own_idx, p->d_own_idx);
     UP(H.a_dest, p->d_a_dest); UP(H.l_src, p->d_l_src);
     UP(H.small_list, p->d_small_list); UP(H.extadd_list, p->d_extadd_list);
     UP(H.zero_tasks, p->d_zero); UP(H.potrf_tasks, p->d_potrf); UP(H.trsm_tasks, p->d_trsm); UP(H.gemm_tasks, p->d_gemm);
@@ -224,7 +341,7 @@ int spchol_plan_create(const spchol_symbolic* sym, int device, spchol_plan** out
     if ((rc = dalloc(p, H.ws_entries, &p->dW))) return fail(rc);
     if ((rc = dalloc(p, 1, &p->dinfo))) return fail(rc);
     p->fa = FrontArrays{p->d_first, p->d_w, p->d_m, p->d_ld, p->d_parent, p->d_panel_off, p->d_cb_off,
-                        p->d_rel_off, p->d_rel, p->d_child_ptr, p->d_child_idx};
+                        p->d_rel_off, p->d_rel, p->d_child_ptr, p->d_child_idx, p->d_own_n, p->d_own_idx, H.dist_NB};
     if ((rc = set_small_attr<32>()) || (rc = set_small_attr<64>()) || (rc = set_small_attr<128>()) ||
         (rc = set_small_attr<256>())) return fail(rc);
     if (cudaFuncSetAttribute(k_gemm_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM) != cudaSuccess) {
@@ -233,6 +350,54 @@ int spchol_plan_create(const spchol_symbolic* sym, int device, spchol_plan** out
     *out = p;
     return SPCHOL_OK;
 }
+
+int spchol_plan_create(const spchol_symbolic* sym, int device, spchol_plan** out) {
+    return plan_create_impl(sym, device, nullptr, nullptr, out);
+}
+
+int spchol_plan_create_dist(const spchol_symbolic* sym, spchol_comm* comm, const int* dist_opts, spchol_plan** out) {
+    if (!comm) { set_error("spchol_plan_create_dist: null communicator"); return SPCHOL_EINVAL; }
+    return plan_create_impl(sym, comm->device, comm, dist_opts, out);
+}
+
+int spchol_comm_unique_id(void* id128) {
+    NcclApi* nc = nccl_api();
+    if (!nc) { set_error("spchol: libnccl.so.2 could not be loaded (set SPCHOL_NCCL_LIB)"); return SPCHOL_ENCCL; }
+    if (!id128) return SPCHOL_EINVAL;
+    NCK(nc->GetUniqueId(static_cast<NcclId*>(id128)));
+    return 0;
+}
+
+int spchol_comm_create(int rank, int world, const void* id128, int device, spchol_comm** out) {
+    if (!out || !id128 || world < 1 || rank < 0 || rank >= world) { set_error("spchol_comm_create: bad argument"); return SPCHOL_EINVAL; }
+    *out = nullptr;
+    if (spchol_device_count() <= 0) { set_error("spchol_comm_create: no CUDA device"); return SPCHOL_ENOGPU; }
+    NcclApi* nc = nccl_api();
+    if (!nc) { set_error("spchol: libnccl.so.2 could not be loaded (set SPCHOL_NCCL_LIB)"); return SPCHOL_ENCCL; }
+    CK(cudaSetDevice(device));
+    spchol_comm* c = new (std::nothrow) spchol_comm();
+    if (!c) return SPCHOL_ENOMEM;
+    c->rank = rank; c->world = world; c->device = device;
+    NcclId id;
+    std::memcpy(&id, id128, sizeof(id));
+    const int e = nc->CommInitRank(&c->world_comm, world, id, rank);
+    if (e != 0) { set_error(std::string("ncclCommInitRank: ") + nc->GetErrorString(e)); delete c; return SPCHOL_ENCCL; }
+    *out = c;
+    return 0;
+}
+
+void spchol_comm_destroy(spchol_comm* c) {
+    if (!c) return;
+    NcclApi* nc = nccl_api();
+    if (nc) {
+        for (auto& g : c->groups) if (g.second) nc->CommDestroy(g.second);
+        if (c->world_comm) nc->CommDestroy(c->world_comm);
+    }
+    delete c;
+}
+
+int spchol_comm_rank(const spchol_comm* c) { return c ? c->rank : 0; }
+int spchol_comm_world(const spchol_comm* c) { return c ? c->world : 1; }
 
 void spchol_plan_destroy(spchol_plan* p) {
     if (!p) return;
@@ -250,6 +415,17 @@ int spchol_plan_stats(const spchol_plan* p, int64_t* st) {
     st[0] = H.ns; st[1] = H.nlevels; st[2] = H.n_small; st[3] = H.n_large; st[4] = H.lbuf_entries;
     st[5] = H.ws_entries; st[6] = static_cast<int64_t>(H.ops.size()); st[7] = H.max_m; st[8] = H.max_w;
     st[9] = p->device_bytes;
+    return 0;
+}
+
+int spchol_plan_dist_stats(const spchol_plan* p, int64_t* st, double* rank_load) {
+    if (!p || !st) return SPCHOL_EINVAL;
+    const HostPlan& H = p->H;
+    int64_t held = 0;
+    for (int s = 0; s < H.ns; ++s) held += H.holds(s) ? 1 : 0;
+    st[0] = H.rank; st[1] = H.world; st[2] = held; st[3] = H.n_dist;
+    st[4] = static_cast<int64_t>(H.comm_tasks.size()); st[5] = H.comm_doubles; st[6] = H.dist_NB; st[7] = 0;
+    if (rank_load) for (int r = 0; r < H.world; ++r) rank_load[r] = H.rank_load[r];
     return 0;
 }
 

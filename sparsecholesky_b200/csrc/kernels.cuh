@@ -16,6 +16,9 @@ struct FrontArrays {          // device pointers, one entry per front
     const int* first; const int* w; const int* m; const int* ld; const int* parent;
     const int64_t* panel_off; const int64_t* cb_off; const int64_t* rel_off;
     const int* rel; const int* child_ptr; const int* child_idx;
+    // multi-GPU: size of the rank group that factors the front (1 = this rank alone), this rank's
+    // index in it, and the block-column width the group deals round-robin (see plan.h)
+    const int* own_n; const int* own_idx; int dist_NB;
 };
 
 __device__ __forceinline__ int even_up_d(int v) { return (v + 1) & ~1; }
@@ -28,7 +31,7 @@ __device__ __forceinline__ int even_up_d(int v) { return (v + 1) & ~1; }
 __global__ void k_assemble(int64_t nnzA, const int64_t* __restrict__ a_dest,
                            const double* __restrict__ Ax, double* __restrict__ L) {
     const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
-    if (i < nnzA) L[a_dest[i]] = Ax[i];
+    if (i < nnzA) { const int64_t d = a_dest[i]; if (d >= 0) L[d] = Ax[i]; }   // d < 0: front held by another rank
 }
 
 // gather the CSC values of L out of the supernodal panels (replaces
@@ -36,7 +39,7 @@ __global__ void k_assemble(int64_t nnzA, const int64_t* __restrict__ a_dest,
 __global__ void k_export(int64_t nnzL, const int64_t* __restrict__ l_src,
                          const double* __restrict__ L, double* __restrict__ Lx) {
     const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
-    if (i < nnzL) Lx[i] = L[l_src[i]];
+    if (i < nnzL) { const int64_t q = l_src[i]; Lx[i] = q >= 0 ? L[q] : 0.0; }   // q < 0: exported by another rank
 }
 
 __global__ void k_zero(const ZeroTask* __restrict__ tasks, double* __restrict__ W) {
@@ -145,8 +148,15 @@ __global__ void __launch_bounds__(128) k_extend_add(const int* __restrict__ list
     const int* __restrict__ r = fa.rel + fa.rel_off[c];
     double* __restrict__ Pp = L + fa.panel_off[p];
     double* __restrict__ Cp = (fa.cb_off[p] >= 0) ? W + fa.cb_off[p] : nullptr;
+    // parent factored by a rank group: only the block columns this rank owns are assembled here
+    const int G = fa.own_n[p], me = fa.own_idx[p], DNB = fa.dist_NB;
+    const int nbp = (wp + DNB - 1) / DNB;
     for (int jj = blockIdx.y; jj < mc; jj += gridDim.y) {
         const int cj = r[jj];
+        if (G > 1) {
+            const int blk = cj < wp ? cj / DNB : nbp + (cj - wp) / DNB;
+            if (blk % G != me) continue;
+        }
         const double* src = C + static_cast<int64_t>(jj) * ldc;
         if (cj < wp) {
             double* dst = Pp + static_cast<int64_t>(cj) * ldp;

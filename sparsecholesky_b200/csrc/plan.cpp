@@ -71,28 +71,119 @@ private:
 
 }  // namespace
 
+// ---------------------------------------------------------------------------------------------
+// Proportional mapping of the assembly tree onto `world` ranks.  Top-down: a front that owns a
+// rank group [lo, lo+n) with n > 1 deals the group out to its children -- the largest children
+// are seeded with one rank each, spare ranks go one by one to the child with the highest load per
+// rank, children that got no rank of their own are packed onto the least loaded rank (LPT).  A
+// front whose group has one rank pins its whole subtree there.  Fronts with a multi-rank group are
+// factored by the group when they are at least dist_min_w columns wide, otherwise by rank `lo`.
+// ---------------------------------------------------------------------------------------------
+void map_fronts(int ns, const int* parent, const int* w, const int* m, int world, int dist_min_w,
+                std::vector<int>& own_lo, std::vector<int>& own_n, std::vector<double>& rank_load) {
+    own_lo.assign(ns, 0); own_n.assign(ns, 1); rank_load.assign(std::max(world, 1), 0.0);
+    std::vector<double> work(ns), sub(ns);
+    for (int s = 0; s < ns; ++s) {
+        const double mm = m[s], ww = w[s];
+        // sum_{k=0}^{w-1} (m-k)^2
+        work[s] = ww * mm * mm - mm * ww * (ww - 1) + (ww - 1) * ww * (2 * ww - 1) / 6.0;
+        sub[s] = work[s];
+    }
+    for (int s = 0; s < ns; ++s) if (parent[s] >= 0) sub[parent[s]] += sub[s];
+    if (world <= 1) { for (int s = 0; s < ns; ++s) rank_load[0] += work[s]; return; }
+
+    std::vector<int> cptr(ns + 2, 0), cidx;
+    // slot ns = virtual root holding the roots of the forest
+    for (int s = 0; s < ns; ++s) ++cptr[(parent[s] >= 0 ? parent[s] : ns) + 1];
+    for (int s = 0; s <= ns; ++s) cptr[s + 1] += cptr[s];
+    cidx.resize(cptr[ns + 1]);
+    {
+        std::vector<int> cur(cptr.begin(), cptr.end() - 1);
+        for (int s = 0; s < ns; ++s) cidx[cur[parent[s] >= 0 ? parent[s] : ns]++] = s;
+    }
+    std::vector<int> glo(ns + 1, 0), gn(ns + 1, 1);     // group handed to each front by its parent
+    glo[ns] = 0; gn[ns] = world;
+    std::vector<int> kids, cnt;
+    std::vector<double> bin;
+    for (int s = ns; s >= 0; --s) {                       // parents before children
+        const int lo = glo[s], n = gn[s];
+        if (s < ns) {
+            if (n > 1 && w[s] >= dist_min_w) {
+                own_lo[s] = lo; own_n[s] = n;
+                for (int r = 0; r < n; ++r) rank_load[lo + r] += work[s] / n;
+            } else {
+                own_lo[s] = lo; own_n[s] = 1;
+                rank_load[lo] += work[s];
+            }
+        }
+        const int kb = cptr[s], ke = cptr[s + 1];
+        if (kb == ke) continue;
+        if (n == 1) { for (int q = kb; q < ke; ++q) { glo[cidx[q]] = lo; gn[cidx[q]] = 1; } continue; }
+        kids.assign(cidx.begin() + kb, cidx.begin() + ke);
+        std::stable_sort(kids.begin(), kids.end(), [&](int a, int b) { return sub[a] > sub[b]; });
+        const int k = static_cast<int>(kids.size()), seeds = std::min(n, k);
+        cnt.assign(k, 0);
+        for (int i = 0; i < seeds; ++i) cnt[i] = 1;
+        for (int spare = n - seeds; spare > 0; --spare) {
+            int best = 0;
+            for (int i = 1; i < seeds; ++i) if (sub[kids[i]] / cnt[i] > sub[kids[best]] / cnt[best]) best = i;
+            ++cnt[best];
+        }
+        bin.assign(n, 0.0);
+        int cur = lo;
+        for (int i = 0; i < seeds; ++i) {
+            glo[kids[i]] = cur; gn[kids[i]] = cnt[i];
+            for (int r = 0; r < cnt[i]; ++r) bin[cur - lo + r] += sub[kids[i]] / cnt[i];
+            cur += cnt[i];
+        }
+        for (int i = seeds; i < k; ++i) {
+            int best = 0;
+            for (int r = 1; r < n; ++r) if (bin[r] < bin[best]) best = r;
+            glo[kids[i]] = lo + best; gn[kids[i]] = 1;
+            bin[best] += sub[kids[i]];
+        }
+    }
+}
+
 void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     P = HostPlan();
     const int ns = S.ns, n = S.n;
+    const int rank = opt.rank, world = std::max(opt.world, 1);
+    if (rank < 0 || rank >= world) throw std::runtime_error("spchol: rank outside [0, world)");
+    const int nb = opt.nb, NB = std::max(opt.NB, opt.nb);
+    const int DNB = std::max(opt.dist_NB, 1);
     P.n = n; P.ns = ns; P.nnzA = S.nnzA; P.nnzL = S.nnzL; P.flops = S.flops;
+    P.rank = rank; P.world = world; P.dist_NB = DNB;
     P.first.resize(ns); P.w.resize(ns); P.m.resize(ns); P.ld.resize(ns);
     P.parent = S.sn_parent;
-    P.panel_off.resize(ns); P.cb_off.assign(ns, -1); P.rel_off.resize(ns + 1);
-    int64_t off = 0, roff = 0;
+    P.panel_off.assign(ns, -1); P.cb_off.assign(ns, -1); P.rel_off.resize(ns + 1);
     for (int s = 0; s < ns; ++s) {
         P.first[s] = S.sn_start[s];
         P.w[s] = S.w(s);
         P.m[s] = S.m(s);
         P.ld[s] = even_up(P.m[s]);
-        P.panel_off[s] = off;
-        off += static_cast<int64_t>(P.ld[s]) * P.w[s];
-        P.rel_off[s] = roff;
-        roff += P.m[s] - P.w[s];
         P.max_m = std::max(P.max_m, P.m[s]);
         P.max_w = std::max(P.max_w, P.w[s]);
     }
-    P.rel_off[ns] = roff;
+    map_fronts(ns, P.parent.data(), P.w.data(), P.m.data(), world, opt.dist_min_w, P.own_lo, P.own_n, P.rank_load);
+    P.own_idx.assign(ns, -1);
+    int64_t off = 0, roff = 0;
+    for (int s = 0; s < ns; ++s) {
+        if (rank >= P.own_lo[s] && rank < P.own_lo[s] + P.own_n[s]) {
+            P.own_idx[s] = rank - P.own_lo[s];
+            P.panel_off[s] = off;
+            off += static_cast<int64_t>(P.ld[s]) * P.w[s];
+            if (P.own_n[s] > 1) ++P.n_dist;
+        }
+    }
     P.lbuf_entries = off;
+    // relative indices are needed where the parent is assembled, i.e. on the parent's holders
+    for (int s = 0; s < ns; ++s) {
+        P.rel_off[s] = roff;
+        const int p = P.parent[s];
+        if (p >= 0 && P.holds(p)) roff += P.m[s] - P.w[s];
+    }
+    P.rel_off[ns] = roff;
 
     // children (ascending) and height-based levels
     P.child_ptr.assign(ns + 1, 0);
@@ -121,16 +212,17 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     P.rel.resize(roff);
     for (int s = 0; s < ns; ++s) {
         const int p = P.parent[s];
-        const int nb = P.m[s] - P.w[s];
-        if (nb == 0) continue;
+        const int nbr = P.m[s] - P.w[s];
+        if (nbr == 0) continue;
         if (p < 0) throw std::runtime_error("spchol: root front with below rows");
+        if (!P.holds(p)) continue;
         const int* rs = S.below(s);
         const int* rp = S.below(p);
         const int nbp = P.m[p] - P.w[p];
         const int pend = P.first[p] + P.w[p];
         int* out = P.rel.data() + P.rel_off[s];
         int q = 0;
-        for (int t = 0; t < nb; ++t) {
+        for (int t = 0; t < nbr; ++t) {
             const int r = rs[t];
             if (r < pend) { out[t] = r - P.first[p]; continue; }
             while (q < nbp && rp[q] < r) ++q;
@@ -139,7 +231,8 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         }
     }
 
-    // A scatter map (A is upper CSC: entry (i,j), i <= j, lands at L(j,i))
+    // A scatter map (A is upper CSC: entry (i,j), i <= j, lands at L(j,i)); -1 where the front
+    // of column i is not held by this rank
     P.a_dest.resize(S.nnzA);
     for (int j = 0; j < n; ++j) {
         for (int p = S.Ap[j]; p < S.Ap[j + 1]; ++p) {
@@ -150,23 +243,27 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             if (j < P.first[s] + P.w[s]) pos = j - P.first[s];
             else {
                 const int* b = S.below(s);
-                const int nb = P.m[s] - P.w[s];
-                const int* it = std::lower_bound(b, b + nb, j);
-                if (it == b + nb || *it != j) throw std::runtime_error("spchol: A entry outside the symbolic pattern");
+                const int nbr = P.m[s] - P.w[s];
+                const int* it = std::lower_bound(b, b + nbr, j);
+                if (it == b + nbr || *it != j) throw std::runtime_error("spchol: A entry outside the symbolic pattern");
                 pos = P.w[s] + static_cast<int>(it - b);
             }
-            P.a_dest[p] = P.panel_off[s] + static_cast<int64_t>(c) * P.ld[s] + pos;
+            P.a_dest[p] = P.holds(s) ? P.panel_off[s] + static_cast<int64_t>(c) * P.ld[s] + pos : -1;
         }
     }
 
-    // CSC export map
+    // CSC export map; a panel replicated over a rank group is exported by the group's first rank
     if (opt.want_csc) {
         P.l_src.resize(S.nnzL);
         for (int j = 0; j < n; ++j) {
             const int s = S.sn_id[j], f = S.fsn_id[j];
+            int64_t q = S.Lp[j];
+            if (!P.holds(s) || (P.own_n[s] > 1 && P.own_idx[s] != 0)) {
+                for (; q < S.Lp[j + 1]; ++q) P.l_src[q] = -1;
+                continue;
+            }
             const int c = j - P.first[s];
             const int64_t colbase = P.panel_off[s] + static_cast<int64_t>(c) * P.ld[s];
-            int64_t q = S.Lp[j];
             const int fend = S.fsn_start[f + 1];
             for (int r = j; r < fend; ++r) P.l_src[q++] = colbase + (r - P.first[s]);
             const int* fb = S.fbelow.data() + S.fbelow_ptr[f];
@@ -175,43 +272,66 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                 for (int t = 0; t < nfb; ++t) P.l_src[q++] = colbase + P.w[s] + t;
             } else {
                 const int* b = S.below(s);
-                const int nb = P.m[s] - P.w[s];
+                const int nbr = P.m[s] - P.w[s];
                 const int send = P.first[s] + P.w[s];
                 int k = 0;
                 for (int t = 0; t < nfb; ++t) {
                     const int r = fb[t];
                     if (r < send) { P.l_src[q++] = colbase + (r - P.first[s]); continue; }
-                    while (k < nb && b[k] < r) ++k;
-                    if (k >= nb || b[k] != r) throw std::runtime_error("spchol: export map row missing");
+                    while (k < nbr && b[k] < r) ++k;
+                    if (k >= nbr || b[k] != r) throw std::runtime_error("spchol: export map row missing");
                     P.l_src[q++] = colbase + P.w[s] + k;
                 }
             }
         }
     }
 
-    // contribution-block workspace + launch program, level by level
+    // ---- contribution-block workspace + launch program, level by level ----------------------
     Arena arena;
-    std::vector<int64_t> cb_size(ns, 0);
-    const int nb = opt.nb, NB = std::max(opt.NB, opt.nb);
+    std::vector<int64_t> ws_size(ns, 0);      // what this rank has allocated for front s's cb (own or staged copy)
+    auto cb_entries = [&](int s) { const int mb = P.m[s] - P.w[s]; return static_cast<int64_t>(even_up(mb)) * mb; };
+    auto ws_alloc = [&](int s) {
+        ws_size[s] = even_up64(cb_entries(s));
+        P.cb_off[s] = arena.alloc(ws_size[s]);
+    };
+    auto add_gemm = [&](Op& op, const GemmTask& ge) {
+        P.gemm_tasks.push_back(ge);
+        op.gx = std::max(op.gx, ge.M); op.gy = std::max(op.gy, ge.N);
+        P.gemm_flops += 2.0 * ge.M * ge.N * ge.K;
+        // wanted entries: column j holds rows i >= j - diag
+        double cnt = 0;
+        const int Mq = ge.M, Nq = ge.N, dg = ge.diag;
+        const int jfull = std::min(Nq, std::max(0, dg + 1));      // columns with all M rows
+        cnt += static_cast<double>(jfull) * Mq;
+        const int jlast = std::min(Nq, Mq + dg);                    // beyond this: empty
+        if (jlast > jfull) {
+            const double a = Mq - (jfull - dg), b = Mq - (jlast - 1 - dg);
+            cnt += (a + b) * (jlast - jfull) / 2.0;
+        }
+        P.gemm_flops_alg += 2.0 * cnt * ge.K;
+    };
+    auto add_comm = [&](int kind, int lo, int cn, int root, int space, int64_t coff, int64_t count, int lv) {
+        Op op{}; op.kind = OP_COMM; op.begin = static_cast<int>(P.comm_tasks.size()); op.count = 1; op.level = lv;
+        P.comm_tasks.push_back({kind, lo, cn, root, space, coff, count});
+        P.ops.push_back(op);
+        P.comm_doubles += count;
+    };
+
     static const int cls_m[] = {16, 24, 32, 48, 64, 96, 128, 1 << 30};
     static const int cls_thr[] = {32, 32, 64, 64, 128, 128, 256, 256};
     const int ncls = 8;
-    for (int lv = 0; lv < nlev; ++lv) {
+
+    // fronts of one level that live on this rank only: small ones one CTA each, large ones in
+    // lockstep (zero cb, extend-add rounds, blocked panel factorization, Schur complement)
+    auto emit_local = [&](const std::vector<int>& fronts, int lv) {
         std::vector<int> small[8], large;
-        for (int s : by_level[lv]) {
-            if (opt.owner && opt.owner[s] != opt.rank) continue;
-            const int mb = P.m[s] - P.w[s];
-            if (mb > 0) {
-                cb_size[s] = static_cast<int64_t>(even_up(mb)) * mb;
-                P.cb_off[s] = arena.alloc(even_up64(cb_size[s]));
-            }
+        for (int s : fronts) {
             if (P.m[s] <= opt.small_max_m) {
                 int c = 0;
                 while (P.m[s] > cls_m[c]) ++c;
                 small[c].push_back(s);
             } else large.push_back(s);
         }
-        // --- small fronts: one CTA per front, bucketed by size class -------------------------
         for (int c = 0; c < ncls; ++c) {
             if (small[c].empty()) continue;
             int mm = 0;
@@ -226,113 +346,223 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             P.ops.push_back(op);
             P.n_small += op.count;
         }
-        // --- large fronts: zero cb, extend-add rounds, blocked panel factorization, SYRK ----
-        if (!large.empty()) {
-            P.n_large += static_cast<int64_t>(large.size());
-            P.max_potrf_slots = std::max(P.max_potrf_slots, static_cast<int>(large.size()));
-            {
-                Op op{}; op.kind = OP_ZERO; op.begin = static_cast<int>(P.zero_tasks.size()); op.level = lv;
-                for (int s : large) if (P.cb_off[s] >= 0) P.zero_tasks.push_back({P.cb_off[s], cb_size[s]});
-                op.count = static_cast<int>(P.zero_tasks.size()) - op.begin;
-                if (op.count) P.ops.push_back(op);
+        if (large.empty()) return;
+        P.n_large += static_cast<int64_t>(large.size());
+        P.max_potrf_slots = std::max(P.max_potrf_slots, static_cast<int>(large.size()));
+        {
+            Op op{}; op.kind = OP_ZERO; op.begin = static_cast<int>(P.zero_tasks.size()); op.level = lv;
+            for (int s : large) if (P.cb_off[s] >= 0) P.zero_tasks.push_back({P.cb_off[s], cb_entries(s)});
+            op.count = static_cast<int>(P.zero_tasks.size()) - op.begin;
+            if (op.count) P.ops.push_back(op);
+        }
+        int max_children = 0;
+        for (int s : large) max_children = std::max(max_children, P.child_ptr[s + 1] - P.child_ptr[s]);
+        for (int r = 0; r < max_children; ++r) {
+            Op op{}; op.kind = OP_EXTADD; op.begin = static_cast<int>(P.extadd_list.size()); op.level = lv;
+            int maxmb = 0;
+            for (int s : large) {
+                if (P.child_ptr[s] + r >= P.child_ptr[s + 1]) continue;
+                const int c = P.child_idx[P.child_ptr[s] + r];
+                if (P.m[c] == P.w[c]) continue;
+                P.extadd_list.push_back(c);
+                maxmb = std::max(maxmb, P.m[c] - P.w[c]);
             }
-            int max_children = 0;
-            for (int s : large) max_children = std::max(max_children, P.child_ptr[s + 1] - P.child_ptr[s]);
-            for (int r = 0; r < max_children; ++r) {
-                Op op{}; op.kind = OP_EXTADD; op.begin = static_cast<int>(P.extadd_list.size()); op.level = lv;
-                int maxmb = 0;
-                for (int s : large) {
-                    if (P.child_ptr[s] + r >= P.child_ptr[s + 1]) continue;
-                    const int c = P.child_idx[P.child_ptr[s] + r];
-                    if (P.m[c] == P.w[c]) continue;
-                    P.extadd_list.push_back(c);
-                    maxmb = std::max(maxmb, P.m[c] - P.w[c]);
+            op.count = static_cast<int>(P.extadd_list.size()) - op.begin;
+            op.gx = maxmb;
+            if (op.count) P.ops.push_back(op);
+        }
+        // per-front step sequences, merged slot by slot
+        struct Step { bool has_trsm = false, has_gemm = false; PotrfTask po; TrsmTask tr; GemmTask ge; };
+        std::vector<std::vector<Step>> seq(large.size());
+        size_t max_steps = 0;
+        for (size_t li = 0; li < large.size(); ++li) {
+            const int s = large[li];
+            const int w = P.w[s], m = P.m[s], ld = P.ld[s];
+            const int64_t po = P.panel_off[s];
+            for (int KB = 0; KB < w; KB += NB) {
+                const int KE = std::min(KB + NB, w);
+                for (int kb = KB; kb < KE; kb += nb) {
+                    const int ke = std::min(kb + nb, KE);
+                    Step st;
+                    st.po = {po + kb + static_cast<int64_t>(kb) * ld, ld, ke - kb, P.first[s] + kb, static_cast<int>(li)};
+                    if (ke < m) {
+                        st.has_trsm = true;
+                        st.tr = {po + ke + static_cast<int64_t>(kb) * ld, ld, ke - kb, m - ke,
+                                 po + kb + static_cast<int64_t>(kb) * ld, static_cast<int>(li)};
+                    }
+                    if (ke < KE) {            // update the rest of the outer block, K = nb
+                        st.has_gemm = true;
+                        const int64_t a = po + ke + static_cast<int64_t>(kb) * ld;
+                        st.ge = {po + ke + static_cast<int64_t>(ke) * ld, a, a, ld, ld, ld,
+                                 m - ke, KE - ke, ke - kb, 0, 0};
+                    } else if (KE < w) {      // deferred update of the remaining panel, K = NB
+                        st.has_gemm = true;
+                        const int64_t a = po + KE + static_cast<int64_t>(KB) * ld;
+                        st.ge = {po + KE + static_cast<int64_t>(KE) * ld, a, a, ld, ld, ld,
+                                 m - KE, w - KE, KE - KB, 0, 0};
+                    } else if (m > w) {       // panel done: Schur complement into the cb, K = w
+                        st.has_gemm = true;
+                        const int64_t a = po + w;
+                        st.ge = {P.cb_off[s], a, a, even_up(m - w), ld, ld, m - w, m - w, w, 0, 1};
+                    }
+                    seq[li].push_back(st);
                 }
-                op.count = static_cast<int>(P.extadd_list.size()) - op.begin;
-                op.gx = maxmb;
-                if (op.count) P.ops.push_back(op);
             }
-            // per-front step sequences, merged slot by slot
-            struct Step { bool has_trsm = false, has_gemm = false; PotrfTask po; TrsmTask tr; GemmTask ge; };
-            std::vector<std::vector<Step>> seq(large.size());
-            size_t max_steps = 0;
+            max_steps = std::max(max_steps, seq[li].size());
+        }
+        for (size_t i = 0; i < max_steps; ++i) {
+            Op a{}, b{}, c{};
+            a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.level = lv;
+            b.kind = OP_TRSM;  b.begin = static_cast<int>(P.trsm_tasks.size());  b.level = lv;
+            c.kind = OP_GEMM;  c.begin = static_cast<int>(P.gemm_tasks.size());  c.level = lv;
             for (size_t li = 0; li < large.size(); ++li) {
-                const int s = large[li];
-                const int w = P.w[s], m = P.m[s], ld = P.ld[s];
-                const int64_t po = P.panel_off[s];
-                for (int KB = 0; KB < w; KB += NB) {
-                    const int KE = std::min(KB + NB, w);
-                    for (int kb = KB; kb < KE; kb += nb) {
-                        const int ke = std::min(kb + nb, KE);
-                        Step st;
-                        st.po = {po + kb + static_cast<int64_t>(kb) * ld, ld, ke - kb, P.first[s] + kb, static_cast<int>(li)};
-                        if (ke < m) {
-                            st.has_trsm = true;
-                            st.tr = {po + ke + static_cast<int64_t>(kb) * ld, ld, ke - kb, m - ke,
-                                     po + kb + static_cast<int64_t>(kb) * ld, static_cast<int>(li)};
-                        }
-                        if (ke < KE) {            // update the rest of the outer block, K = nb
-                            st.has_gemm = true;
-                            const int64_t a = po + ke + static_cast<int64_t>(kb) * ld;
-                            st.ge = {po + ke + static_cast<int64_t>(ke) * ld, a, a, ld, ld, ld,
-                                     m - ke, KE - ke, ke - kb, 0, 0};
-                        } else if (KE < w) {      // deferred update of the remaining panel, K = NB
-                            st.has_gemm = true;
-                            const int64_t a = po + KE + static_cast<int64_t>(KB) * ld;
-                            st.ge = {po + KE + static_cast<int64_t>(KE) * ld, a, a, ld, ld, ld,
-                                     m - KE, w - KE, KE - KB, 0, 0};
-                        } else if (m > w) {       // panel done: Schur complement into the cb, K = w
-                            st.has_gemm = true;
-                            const int64_t a = po + w;
-                            st.ge = {P.cb_off[s], a, a, even_up(m - w), ld, ld, m - w, m - w, w, 0, 1};
-                        }
-                        seq[li].push_back(st);
-                    }
-                }
-                max_steps = std::max(max_steps, seq[li].size());
+                if (i >= seq[li].size()) continue;
+                const Step& st = seq[li][i];
+                P.potrf_tasks.push_back(st.po);
+                if (st.has_trsm) { P.trsm_tasks.push_back(st.tr); b.gx = std::max(b.gx, st.tr.rows); }
+                if (st.has_gemm) add_gemm(c, st.ge);
             }
-            for (size_t i = 0; i < max_steps; ++i) {
-                Op a{}, b{}, c{};
-                a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.level = lv;
-                b.kind = OP_TRSM;  b.begin = static_cast<int>(P.trsm_tasks.size());  b.level = lv;
-                c.kind = OP_GEMM;  c.begin = static_cast<int>(P.gemm_tasks.size());  c.level = lv;
-                for (size_t li = 0; li < large.size(); ++li) {
-                    if (i >= seq[li].size()) continue;
-                    const Step& st = seq[li][i];
-                    P.potrf_tasks.push_back(st.po);
-                    if (st.has_trsm) { P.trsm_tasks.push_back(st.tr); b.gx = std::max(b.gx, st.tr.rows); }
-                    if (st.has_gemm) {
-                        P.gemm_tasks.push_back(st.ge);
-                        c.gx = std::max(c.gx, st.ge.M); c.gy = std::max(c.gy, st.ge.N);
-                        P.gemm_flops += 2.0 * st.ge.M * st.ge.N * st.ge.K;
-                        {   // wanted entries: column j holds rows i >= j - diag
-                            double cnt = 0;
-                            const int Mq = st.ge.M, Nq = st.ge.N, dg = st.ge.diag;
-                            const int jfull = std::min(Nq, std::max(0, dg + 1));      // columns with all M rows
-                            cnt += static_cast<double>(jfull) * Mq;
-                            const int jlast = std::min(Nq, Mq + dg);                    // beyond this: empty
-                            if (jlast > jfull) {
-                                const double a = Mq - (jfull - dg), b = Mq - (jlast - 1 - dg);
-                                cnt += (a + b) * (jlast - jfull) / 2.0;
-                            }
-                            P.gemm_flops_alg += 2.0 * cnt * st.ge.K;
-                        }
-                    }
-                }
-                a.count = static_cast<int>(P.potrf_tasks.size()) - a.begin;
-                b.count = static_cast<int>(P.trsm_tasks.size()) - b.begin;
-                c.count = static_cast<int>(P.gemm_tasks.size()) - c.begin;
-                if (a.count) P.ops.push_back(a);
-                if (b.count) P.ops.push_back(b);
-                if (c.count) P.ops.push_back(c);
+            a.count = static_cast<int>(P.potrf_tasks.size()) - a.begin;
+            b.count = static_cast<int>(P.trsm_tasks.size()) - b.begin;
+            c.count = static_cast<int>(P.gemm_tasks.size()) - c.begin;
+            if (a.count) P.ops.push_back(a);
+            if (b.count) P.ops.push_back(b);
+            if (c.count) P.ops.push_back(c);
+        }
+    };
+
+    // move child c's contribution block to every holder of its parent p (called by every rank in
+    // the same order; ranks that are neither source nor destination emit nothing)
+    auto emit_transfer = [&](int c, int p, int lv) {
+        const int mbc = P.m[c] - P.w[c];
+        if (mbc == 0) return;
+        const int ldc = even_up(mbc);
+        const int64_t size = static_cast<int64_t>(ldc) * mbc;
+        const int cl = P.own_lo[c], cn = P.own_n[c], pl = P.own_lo[p], pn = P.own_n[p];
+        const bool in_p = P.holds(p), in_c = P.holds(c);
+        if (in_p && !in_c) ws_alloc(c);                        // staged copy
+        if (cn == 1) {
+            if (pn == 1) {
+                if (pl == cl) return;
+                if (rank == cl) add_comm(COMM_SEND, 0, 0, pl, 1, P.cb_off[c], size, lv);
+                if (rank == pl) add_comm(COMM_RECV, 0, 0, cl, 1, P.cb_off[c], size, lv);
+            } else {
+                if (cl < pl || cl >= pl + pn) throw std::runtime_error("spchol: child mapped outside its parent's rank group");
+                if (in_p) add_comm(COMM_BCAST, pl, pn, cl, 1, P.cb_off[c], size, lv);
+            }
+            return;
+        }
+        const int nbp_c = (P.w[c] + DNB - 1) / DNB, nbc_c = (mbc + DNB - 1) / DNB;
+        for (int jb = 0; jb < nbc_c; ++jb) {
+            const int o = cl + (nbp_c + jb) % cn;
+            const int j0 = jb * DNB, j1 = std::min(j0 + DNB, mbc);
+            const int64_t boff = j0 + static_cast<int64_t>(j0) * ldc;
+            const int64_t count = static_cast<int64_t>(j1 - j0 - 1) * ldc + (mbc - j0);
+            if (pn == 1) {
+                if (o == pl) continue;
+                if (rank == o) add_comm(COMM_SEND, 0, 0, pl, 1, P.cb_off[c] + boff, count, lv);
+                if (rank == pl) add_comm(COMM_RECV, 0, 0, o, 1, P.cb_off[c] + boff, count, lv);
+            } else {
+                if (o < pl || o >= pl + pn) throw std::runtime_error("spchol: child group outside its parent's rank group");
+                if (in_p) add_comm(COMM_BCAST, pl, pn, o, 1, P.cb_off[c] + boff, count, lv);
             }
         }
+    };
+
+    // a front factored by its rank group: block columns of width DNB dealt round-robin; the owner
+    // factors a block column, broadcasts it in place, every rank updates the block columns it owns
+    auto emit_dist = [&](int s, int lv) {
+        const int w = P.w[s], m = P.m[s], ld = P.ld[s], mb = m - w;
+        const int64_t po = P.panel_off[s];
+        const int G = P.own_n[s], idx = P.own_idx[s], lo = P.own_lo[s];
+        const int nbp = (w + DNB - 1) / DNB, nbc = (mb + DNB - 1) / DNB;
+        const int ldcb = even_up(mb);
+        if (mb > 0) {
+            Op op{}; op.kind = OP_ZERO; op.begin = static_cast<int>(P.zero_tasks.size()); op.count = 1; op.level = lv;
+            P.zero_tasks.push_back({P.cb_off[s], cb_entries(s)});
+            P.ops.push_back(op);
+        }
+        for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) {
+            const int c = P.child_idx[q];
+            if (P.m[c] == P.w[c]) continue;
+            Op op{}; op.kind = OP_EXTADD; op.begin = static_cast<int>(P.extadd_list.size()); op.count = 1; op.level = lv;
+            op.gx = P.m[c] - P.w[c];
+            P.extadd_list.push_back(c);
+            P.ops.push_back(op);
+        }
+        for (int kb = 0; kb < nbp; ++kb) {
+            const int c0 = kb * DNB, c1 = std::min(c0 + DNB, w);
+            const int owner = kb % G;
+            if (owner == idx) {
+                for (int k0 = c0; k0 < c1; k0 += nb) {
+                    const int k1 = std::min(k0 + nb, c1);
+                    const int64_t d = po + k0 + static_cast<int64_t>(k0) * ld;
+                    Op a{}; a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.count = 1; a.level = lv;
+                    P.potrf_tasks.push_back({d, ld, k1 - k0, P.first[s] + k0, 0});
+                    P.ops.push_back(a);
+                    if (k1 < m) {
+                        Op b{}; b.kind = OP_TRSM; b.begin = static_cast<int>(P.trsm_tasks.size()); b.count = 1; b.level = lv;
+                        b.gx = m - k1;
+                        P.trsm_tasks.push_back({po + k1 + static_cast<int64_t>(k0) * ld, ld, k1 - k0, m - k1, d, 0});
+                        P.ops.push_back(b);
+                    }
+                    if (k1 < c1) {
+                        Op g{}; g.kind = OP_GEMM; g.begin = static_cast<int>(P.gemm_tasks.size()); g.count = 1; g.level = lv;
+                        const int64_t a2 = po + k1 + static_cast<int64_t>(k0) * ld;
+                        add_gemm(g, {po + k1 + static_cast<int64_t>(k1) * ld, a2, a2, ld, ld, ld, m - k1, c1 - k1, k1 - k0, 0, 0});
+                        P.ops.push_back(g);
+                    }
+                }
+            }
+            add_comm(COMM_BCAST, lo, G, lo + owner, 0, po + c0 + static_cast<int64_t>(c0) * ld,
+                     static_cast<int64_t>(c1 - c0 - 1) * ld + (m - c0), lv);
+            Op g{}; g.kind = OP_GEMM; g.begin = static_cast<int>(P.gemm_tasks.size()); g.level = lv;
+            for (int jb = kb + 1; jb < nbp; ++jb) {
+                if (jb % G != idx) continue;
+                const int j0 = jb * DNB, j1 = std::min(j0 + DNB, w);
+                const int64_t a2 = po + j0 + static_cast<int64_t>(c0) * ld;
+                add_gemm(g, {po + j0 + static_cast<int64_t>(j0) * ld, a2, a2, ld, ld, ld, m - j0, j1 - j0, c1 - c0, 0, 0});
+            }
+            g.count = static_cast<int>(P.gemm_tasks.size()) - g.begin;
+            if (g.count) P.ops.push_back(g);
+        }
+        if (mb > 0) {
+            Op g{}; g.kind = OP_GEMM; g.begin = static_cast<int>(P.gemm_tasks.size()); g.level = lv;
+            for (int jb = 0; jb < nbc; ++jb) {
+                if ((nbp + jb) % G != idx) continue;
+                const int j0 = jb * DNB, j1 = std::min(j0 + DNB, mb);
+                const int64_t a2 = po + w + j0;
+                add_gemm(g, {P.cb_off[s] + j0 + static_cast<int64_t>(j0) * ldcb, a2, a2, ldcb, ld, ld, mb - j0, j1 - j0, w, 0, 1});
+            }
+            g.count = static_cast<int>(P.gemm_tasks.size()) - g.begin;
+            if (g.count) P.ops.push_back(g);
+        }
+    };
+
+    for (int lv = 0; lv < nlev; ++lv) {
+        std::vector<int> local_a, local_b, dists;
+        for (int s : by_level[lv]) {
+            if (!P.holds(s)) continue;
+            if (P.m[s] > P.w[s]) ws_alloc(s);
+            if (P.own_n[s] > 1) { dists.push_back(s); continue; }
+            bool remote = false;
+            for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1] && !remote; ++q) {
+                const int c = P.child_idx[q];
+                remote = !(P.own_n[c] == 1 && P.own_lo[c] == rank);
+            }
+            (remote ? local_b : local_a).push_back(s);
+        }
+        emit_local(local_a, lv);
+        if (world > 1)
+            for (int p : by_level[lv])
+                for (int q = P.child_ptr[p]; q < P.child_ptr[p + 1]; ++q) emit_transfer(P.child_idx[q], p, lv);
+        emit_local(local_b, lv);
+        for (int s : dists) emit_dist(s, lv);
         // children of this level's fronts are consumed now
         for (int s : by_level[lv]) {
-            if (opt.owner && opt.owner[s] != opt.rank) continue;
             for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) {
                 const int c = P.child_idx[q];
-                if (P.cb_off[c] >= 0 && cb_size[c] > 0) { arena.release(P.cb_off[c], even_up64(cb_size[c])); cb_size[c] = 0; }
+                if (ws_size[c] > 0) { arena.release(P.cb_off[c], ws_size[c]); ws_size[c] = 0; }
             }
         }
     }

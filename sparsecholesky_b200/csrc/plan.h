@@ -21,8 +21,19 @@ struct GemmTask {
 struct PotrfTask { int64_t d_off; int ld; int nb; int col0; int slot; };         // diag block in L buffer
 struct TrsmTask  { int64_t b_off; int ld; int nb; int rows; int64_t d_off; int slot; };  // rows below the block
 struct ZeroTask  { int64_t off; int64_t count; };
+// One stream-ordered transfer between ranks (multi-GPU plans only).  Broadcasts run inside the
+// contiguous rank group [lo, lo + n); send/recv are point to point.  Ranks that do not take part
+// do not get the task at all, so the sequence of tasks is consistent on every participant.
+enum CommKind : int { COMM_BCAST = 0, COMM_SEND = 1, COMM_RECV = 2 };
+struct CommTask {
+    int kind;
+    int lo, n;          // COMM_BCAST: rank group
+    int root;           // COMM_BCAST: absolute root rank; COMM_SEND / COMM_RECV: absolute peer rank
+    int space;          // 0: L buffer, 1: contribution workspace
+    int64_t off, count; // doubles
+};
 
-enum OpKind : int { OP_SMALL = 0, OP_ZERO = 1, OP_EXTADD = 2, OP_POTRF = 3, OP_TRSM = 4, OP_GEMM = 5 };
+enum OpKind : int { OP_SMALL = 0, OP_ZERO = 1, OP_EXTADD = 2, OP_POTRF = 3, OP_TRSM = 4, OP_GEMM = 5, OP_COMM = 6 };
 struct Op {
     int kind;
     int begin, count;   // slice of the task array of that kind
@@ -37,9 +48,10 @@ struct PlanOptions {
     int nb = 64;               // diagonal block of the blocked panel factorization
     int NB = 256;              // outer block (K of the deferred panel update)
     int want_csc = 1;          // build the CSC export map (needs nnz(L) <= INT_MAX)
-    // owner filter for multi-GPU: only fronts with owner[s] == rank are scheduled (nullptr: all)
-    const int* owner = nullptr;
-    int rank = 0;
+    // multi-GPU (one plan per rank, every rank builds the same global mapping):
+    int rank = 0, world = 1;
+    int dist_NB = 256;         // block-column width of a front that is factored by a rank group
+    int dist_min_w = 1024;     // fronts narrower than this stay on one rank even if their subtree was split
 };
 
 struct HostPlan {
@@ -52,6 +64,14 @@ struct HostPlan {
     std::vector<int> ld;                               // leading dimension of the panel (>= m, even)
     std::vector<int> rel;                              // per below-row position in the parent front
     std::vector<int> child_ptr, child_idx;
+    // multi-GPU mapping (global, identical on every rank): front s is held by ranks
+    // [own_lo[s], own_lo[s] + own_n[s]); own_n > 1 means block columns of width dist_NB are dealt
+    // round-robin to the group (block b of the front -> rank own_lo + b % own_n; the blocks of
+    // the contribution block continue the count after the panel's blocks).
+    int rank = 0, world = 1, dist_NB = 256;
+    std::vector<int> own_lo, own_n;
+    std::vector<int> own_idx;                          // this rank's index in the group, -1 if not a holder
+    std::vector<double> rank_load;                     // estimated flops per rank (mapping statistic)
     int64_t lbuf_entries = 0, ws_entries = 0;
     // maps
     std::vector<int64_t> a_dest;     // nnzA  : L-buffer offset of each stored A entry
@@ -63,6 +83,7 @@ struct HostPlan {
     std::vector<PotrfTask> potrf_tasks;
     std::vector<TrsmTask> trsm_tasks;
     std::vector<GemmTask> gemm_tasks;
+    std::vector<CommTask> comm_tasks;
     std::vector<Op> ops;
     int max_potrf_slots = 0;
     // statistics
@@ -70,7 +91,14 @@ struct HostPlan {
     int max_m = 0, max_w = 0;
     double gemm_flops = 0;           // flops of the full M x N x K rectangles of OP_GEMM tasks
     double gemm_flops_alg = 0;       // flops of the wanted (lower-trapezoid) part only
+    int64_t n_dist = 0;              // fronts factored by a rank group
+    int64_t comm_doubles = 0;        // doubles this rank sends or receives per factorization
+    bool holds(int s) const { return own_idx[s] >= 0; }
 };
+
+// proportional mapping of the assembly tree onto `world` ranks (deterministic; used by build_plan)
+void map_fronts(int ns, const int* parent, const int* w, const int* m, int world, int dist_min_w,
+                std::vector<int>& own_lo, std::vector<int>& own_n, std::vector<double>& rank_load);
 
 void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P);
 

@@ -1,0 +1,264 @@
+// TEST INFRASTRUCTURE ONLY -- never linked into libspchol.so.
+//
+// Host interpreter of the numeric launch program (csrc/plan.h): builds the plan of every rank of a
+// `world`-rank factorization with the product's own planner and executes the ops with plain loops,
+// one simulated rank per program counter, transfers resolved when all their participants have
+// reached them (a mismatch or a cycle is reported as an error).  It lets the CPU-only test run
+// check the planner -- front mapping, relative indices, block-column ownership, transfer order,
+// workspace lifetimes -- against the oracle without a GPU.  The op semantics restate this repo's
+// own kernels (csrc/kernels.cuh), not reference code.
+#include <algorithm>
+#include <cmath>
+#include <cstdint>
+#include <cstdio>
+#include <cstring>
+#include <limits>
+#include <string>
+#include <vector>
+
+#include "../../sparsecholesky_b200/csrc/plan.h"
+#include "../../sparsecholesky_b200/csrc/symbolic.h"
+
+using namespace spchol;
+
+namespace {
+
+inline int even_up(int v) { return (v + 1) & ~1; }
+
+struct Rank {
+    HostPlan H;
+    std::vector<double> L, W;
+    size_t pc = 0;        // index into H.ops
+    int sub = 0;          // index inside a multi-task OP_COMM
+    int info = std::numeric_limits<int>::max();
+};
+
+void run_small(Rank& R, int s) {
+    const HostPlan& H = R.H;
+    const int w = H.w[s], m = H.m[s], ld = H.ld[s];
+    std::vector<double> F(static_cast<size_t>(m) * m, 0.0);
+    double* P = R.L.data() + H.panel_off[s];
+    for (int j = 0; j < w; ++j) for (int i = j; i < m; ++i) F[i + static_cast<size_t>(j) * m] = P[i + static_cast<size_t>(j) * ld];
+    for (int q = H.child_ptr[s]; q < H.child_ptr[s + 1]; ++q) {
+        const int c = H.child_idx[q];
+        const int mc = H.m[c] - H.w[c];
+        if (!mc) continue;
+        const int ldc = even_up(mc);
+        const double* C = R.W.data() + H.cb_off[c];
+        const int* r = H.rel.data() + H.rel_off[c];
+        for (int jj = 0; jj < mc; ++jj) for (int ii = jj; ii < mc; ++ii) F[r[ii] + static_cast<size_t>(r[jj]) * m] += C[ii + static_cast<size_t>(jj) * ldc];
+    }
+    for (int k = 0; k < w; ++k) {
+        const double d = F[k + static_cast<size_t>(k) * m];
+        if (d <= 0.0) R.info = std::min(R.info, H.first[s] + k + 1);
+        const double piv = std::sqrt(d);
+        for (int i = k + 1; i < m; ++i) F[i + static_cast<size_t>(k) * m] /= piv;
+        F[k + static_cast<size_t>(k) * m] = piv;
+        for (int j = k + 1; j < m; ++j) {
+            const double uj = F[j + static_cast<size_t>(k) * m];
+            for (int i = j; i < m; ++i) F[i + static_cast<size_t>(j) * m] -= F[i + static_cast<size_t>(k) * m] * uj;
+        }
+    }
+    for (int j = 0; j < w; ++j) for (int i = j; i < m; ++i) P[i + static_cast<size_t>(j) * ld] = F[i + static_cast<size_t>(j) * m];
+    const int mb = m - w;
+    if (mb > 0) {
+        double* C = R.W.data() + H.cb_off[s];
+        const int ldc = even_up(mb);
+        for (int j = 0; j < mb; ++j) for (int i = j; i < mb; ++i) C[i + static_cast<size_t>(j) * ldc] = F[(w + i) + static_cast<size_t>(w + j) * m];
+    }
+}
+
+void run_extadd(Rank& R, int c) {
+    const HostPlan& H = R.H;
+    const int p = H.parent[c];
+    const int mc = H.m[c] - H.w[c], ldc = even_up(mc);
+    const int wp = H.w[p], ldp = H.ld[p], ldcb = even_up(H.m[p] - wp);
+    const double* C = R.W.data() + H.cb_off[c];
+    const int* r = H.rel.data() + H.rel_off[c];
+    double* Pp = R.L.data() + H.panel_off[p];
+    double* Cp = H.cb_off[p] >= 0 ? R.W.data() + H.cb_off[p] : nullptr;
+    const int G = H.own_n[p], me = H.own_idx[p], DNB = H.dist_NB, nbp = (wp + DNB - 1) / DNB;
+    for (int jj = 0; jj < mc; ++jj) {
+        const int cj = r[jj];
+        if (G > 1) {
+            const int blk = cj < wp ? cj / DNB : nbp + (cj - wp) / DNB;
+            if (blk % G != me) continue;
+        }
+        for (int ii = jj; ii < mc; ++ii) {
+            const double v = C[ii + static_cast<size_t>(jj) * ldc];
+            if (cj < wp) Pp[r[ii] + static_cast<size_t>(cj) * ldp] += v;
+            else Cp[(r[ii] - wp) + static_cast<size_t>(cj - wp) * ldcb] += v;
+        }
+    }
+}
+
+void run_potrf(Rank& R, const PotrfTask& t) {
+    double* D = R.L.data() + t.d_off;
+    const int nb = t.nb; const size_t ld = t.ld;
+    for (int k = 0; k < nb; ++k) {
+        const double d = D[k + k * ld];
+        if (d <= 0.0) R.info = std::min(R.info, t.col0 + k + 1);
+        const double piv = std::sqrt(d);
+        for (int i = k + 1; i < nb; ++i) D[i + k * ld] /= piv;
+        D[k + k * ld] = piv;
+        for (int j = k + 1; j < nb; ++j) for (int i = j; i < nb; ++i) D[i + j * ld] -= D[i + k * ld] * D[j + k * ld];
+    }
+}
+
+void run_trsm(Rank& R, const TrsmTask& t) {
+    const double* D = R.L.data() + t.d_off;
+    double* B = R.L.data() + t.b_off;
+    const size_t ld = t.ld;
+    for (int row = 0; row < t.rows; ++row)
+        for (int k = 0; k < t.nb; ++k) {
+            const double v = B[row + k * ld] / D[k + k * ld];
+            B[row + k * ld] = v;
+            for (int j = k + 1; j < t.nb; ++j) B[row + j * ld] -= v * D[j + k * ld];
+        }
+}
+
+void run_gemm(Rank& R, const GemmTask& t) {
+    const double* A = R.L.data() + t.a_off;
+    const double* B = R.L.data() + t.b_off;
+    double* C = (t.c_space ? R.W.data() : R.L.data()) + t.c_off;
+    // read all operands first: A/B may alias rows of C's panel only outside the written region
+    for (int j = 0; j < t.N; ++j)
+        for (int i = 0; i < t.M; ++i) {
+            if (i + t.diag < j) continue;
+            double acc = 0;
+            for (int k = 0; k < t.K; ++k) acc += A[i + static_cast<size_t>(k) * t.lda] * B[j + static_cast<size_t>(k) * t.ldb];
+            C[i + static_cast<size_t>(j) * t.ldc] -= acc;
+        }
+}
+
+std::string describe(const CommTask& t, int rank) {
+    char buf[160];
+    std::snprintf(buf, sizeof buf, "rank %d: kind=%d group=(%d,%d) root/peer=%d space=%d count=%lld", rank, t.kind, t.lo, t.n,
+                  t.root, t.space, static_cast<long long>(t.count));
+    return buf;
+}
+
+}  // namespace
+
+extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double* Ax, int relax, int world,
+                              int dist_NB, int dist_min_w, int small_max_m, int nb, int NB,
+                              double* Lx, int* info_out, int64_t* stats /* 4: #dist fronts, #transfers, doubles moved, max ws */,
+                              char* err, int errlen) {
+    auto fail = [&](const std::string& msg) { std::snprintf(err, errlen, "%s", msg.c_str()); return -1; };
+    try {
+        Symbolic S;
+        RelaxParams rp; rp.enable = relax != 0;
+        analyze(n, Ap, Ai, rp, S);
+        std::vector<Rank> R(world);
+        for (int r = 0; r < world; ++r) {
+            PlanOptions opt;
+            opt.rank = r; opt.world = world;
+            if (dist_NB > 0) opt.dist_NB = dist_NB;
+            if (dist_min_w > 0) opt.dist_min_w = dist_min_w;
+            if (small_max_m > 0) opt.small_max_m = small_max_m;
+            if (nb > 0) opt.nb = nb;
+            if (NB > 0) opt.NB = NB;
+            build_plan(S, opt, R[r].H);
+            const HostPlan& H = R[r].H;
+            // poison instead of zero where the engine does not clear: the workspace is never memset
+            R[r].L.assign(static_cast<size_t>(H.lbuf_entries), 0.0);
+            R[r].W.assign(static_cast<size_t>(H.ws_entries), std::numeric_limits<double>::quiet_NaN());
+            for (int64_t i = 0; i < H.nnzA; ++i) if (H.a_dest[i] >= 0) R[r].L[H.a_dest[i]] = Ax[i];
+        }
+        if (stats) { stats[0] = stats[1] = stats[2] = stats[3] = 0; }
+        for (int r = 0; r < world; ++r) if (stats) {
+            stats[0] = std::max<int64_t>(stats[0], R[r].H.n_dist);
+            stats[1] += static_cast<int64_t>(R[r].H.comm_tasks.size());
+            stats[2] += R[r].H.comm_doubles;
+            stats[3] = std::max<int64_t>(stats[3], R[r].H.ws_entries);
+        }
+        auto at_comm = [&](int r) -> const CommTask* {
+            Rank& k = R[r];
+            if (k.pc >= k.H.ops.size()) return nullptr;
+            const Op& op = k.H.ops[k.pc];
+            if (op.kind != OP_COMM) return nullptr;
+            return &k.H.comm_tasks[op.begin + k.sub];
+        };
+        auto advance_comm = [&](int r) {
+            Rank& k = R[r];
+            if (++k.sub >= k.H.ops[k.pc].count) { k.sub = 0; ++k.pc; }
+        };
+        auto buf = [&](int r, const CommTask& t) { return (t.space ? R[r].W.data() : R[r].L.data()) + t.off; };
+        for (;;) {
+            bool progress = false, all_done = true;
+            for (int r = 0; r < world; ++r) {
+                Rank& k = R[r];
+                while (k.pc < k.H.ops.size() && k.H.ops[k.pc].kind != OP_COMM) {
+                    const Op& op = k.H.ops[k.pc];
+                    const HostPlan& H = k.H;
+                    switch (op.kind) {
+                    case OP_SMALL: for (int i = 0; i < op.count; ++i) run_small(k, H.small_list[op.begin + i]); break;
+                    case OP_ZERO: for (int i = 0; i < op.count; ++i) { const ZeroTask& z = H.zero_tasks[op.begin + i]; std::fill_n(k.W.data() + z.off, z.count, 0.0); } break;
+                    case OP_EXTADD: for (int i = 0; i < op.count; ++i) run_extadd(k, H.extadd_list[op.begin + i]); break;
+                    case OP_POTRF: for (int i = 0; i < op.count; ++i) run_potrf(k, H.potrf_tasks[op.begin + i]); break;
+                    case OP_TRSM: for (int i = 0; i < op.count; ++i) run_trsm(k, H.trsm_tasks[op.begin + i]); break;
+                    case OP_GEMM: for (int i = 0; i < op.count; ++i) run_gemm(k, H.gemm_tasks[op.begin + i]); break;
+                    default: return fail("unknown op kind");
+                    }
+                    ++k.pc; progress = true;
+                }
+                if (k.pc < k.H.ops.size()) all_done = false;
+            }
+            if (all_done) break;
+            for (int r = 0; r < world; ++r) {
+                const CommTask* t = at_comm(r);
+                if (!t) continue;
+                if (t->kind == COMM_BCAST) {
+                    if (r < t->lo || r >= t->lo + t->n) return fail("broadcast issued outside its group: " + describe(*t, r));
+                    if (r != t->lo) continue;             // resolved when visiting the group's first rank
+                    bool ready = true;
+                    for (int q = t->lo; q < t->lo + t->n && ready; ++q) {
+                        const CommTask* u = at_comm(q);
+                        if (!u) { ready = false; break; }
+                        if (u->kind != COMM_BCAST || u->lo != t->lo || u->n != t->n) { ready = false; break; }   // busy with another exchange
+                        if (u->root != t->root || u->count != t->count)
+                            return fail("broadcast mismatch: " + describe(*t, r) + " vs " + describe(*u, q));
+                    }
+                    if (!ready) continue;
+                    const CommTask root_t = *at_comm(t->root);
+                    const double* src = buf(t->root, root_t);
+                    const int lo = t->lo, cnt = t->n, root = t->root;
+                    const int64_t count = t->count;
+                    for (int q = lo; q < lo + cnt; ++q) {
+                        if (q != root) std::memcpy(buf(q, *at_comm(q)), src, static_cast<size_t>(count) * sizeof(double));
+                    }
+                    for (int q = lo; q < lo + cnt; ++q) advance_comm(q);
+                    progress = true;
+                } else if (t->kind == COMM_SEND) {
+                    const int q = t->root;
+                    const CommTask* u = at_comm(q);
+                    if (!u || u->kind != COMM_RECV || u->root != r) continue;
+                    if (u->count != t->count) return fail("send/recv length mismatch: " + describe(*t, r) + " vs " + describe(*u, q));
+                    std::memcpy(buf(q, *u), buf(r, *t), static_cast<size_t>(t->count) * sizeof(double));
+                    advance_comm(r); advance_comm(q);
+                    progress = true;
+                }
+            }
+            if (!progress) {
+                std::string msg = "deadlock:";
+                for (int r = 0; r < world; ++r) { const CommTask* t = at_comm(r); msg += t ? " [" + describe(*t, r) + "]" : " [rank " + std::to_string(r) + " done]"; }
+                return fail(msg);
+            }
+        }
+        int info = std::numeric_limits<int>::max();
+        for (int r = 0; r < world; ++r) info = std::min(info, R[r].info);
+        *info_out = info == std::numeric_limits<int>::max() ? 0 : info;
+        if (Lx) {
+            for (int64_t i = 0; i < S.nnzL; ++i) {
+                int holders = 0; double v = 0;
+                for (int r = 0; r < world; ++r) {
+                    const int64_t q = R[r].H.l_src[i];
+                    if (q >= 0) { ++holders; v += R[r].L[q]; }
+                }
+                if (holders != 1) return fail("L entry " + std::to_string(i) + " exported by " + std::to_string(holders) + " ranks");
+                Lx[i] = v;
+            }
+        }
+    } catch (const std::exception& e) { return fail(e.what()); }
+    return 0;
+}
