@@ -166,6 +166,8 @@ def main():
     ap.add_argument("--workload", default="lap3d_128", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--dist-nb", type=int, default=0, help="block-column width of distributed fronts (0: library default)")
+    ap.add_argument("--dist-min-w", type=int, default=0, help="narrowest front factored by a rank group (0: default)")
     args = ap.parse_args()
     args.warmup = max(args.warmup, 3) if args.impl == "ours" else args.warmup
     rank = int(os.environ.get("RANK", "0"))
@@ -184,13 +186,31 @@ def main():
         raise SystemExit("bench.py: no CUDA device (the numeric path has no CPU fallback)")
     torch.cuda.set_device(local_rank)
     dist = None
+    comm = None
     if world > 1:
         import torch.distributed as dist
         dist.init_process_group("nccl", device_id=torch.device("cuda", local_rank))
         from sparsecholesky_b200 import multigpu
-        multigpu.run_bench(args, rank, world, local_rank, dist, WORKLOADS, METRIC, UNIT, ClockSampler, cpu_reference_time)
-        dist.destroy_process_group()
-        return
+        comm = multigpu.Comm(dist, device=local_rank)
+
+    def barrier():
+        torch.cuda.synchronize()
+        if dist is not None:
+            dist.barrier()
+
+    def max_over_ranks(v):
+        if dist is None:
+            return float(v)
+        t = torch.tensor([float(v)], dtype=torch.float64, device=f"cuda:{local_rank}")
+        dist.all_reduce(t, op=dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def gather_list(v):
+        if dist is None:
+            return [v]
+        out = [None] * world
+        dist.all_gather_object(out, v)
+        return out
 
     dims, desc, sample = WORKLOADS[args.workload]
     t0 = time.time()
@@ -200,46 +220,54 @@ def main():
     S = sc.schol(A)
     t_sym = time.time() - t0
     t0 = time.time()
-    plan = S.plan(local_rank)
+    if comm is not None:
+        dplan = multigpu.DistPlan(S, comm, dist_NB=args.dist_nb, dist_min_w=args.dist_min_w)
+        plan_h = dplan.h
+        ps = dplan.stats()
+    else:
+        plan = S.plan(local_rank)
+        plan_h = plan.h
+        ps = S.plan_stats(local_rank)
     t_plan = time.time() - t0
-    ps = S.plan_stats(local_rank)
-    stream = torch.cuda.ExternalStream(L.spchol_stream(plan.h), device=local_rank)
+    stream = torch.cuda.ExternalStream(L.spchol_stream(plan_h), device=local_rank)
     dAx = torch.from_numpy(A.x).to(f"cuda:{local_rank}")
     info = C.c_int(0)
 
     def step():
-        check(L.spchol_factor_device(plan.h, dAx.data_ptr()), "spchol_factor_device")
+        check(L.spchol_factor_device(plan_h, dAx.data_ptr()), "spchol_factor_device")
 
     for _ in range(args.warmup):
         step()
-    check(L.spchol_sync(plan.h, C.byref(info)))
+    check(L.spchol_sync(plan_h, C.byref(info)))
     assert info.value == 0, f"factorization failed: info={info.value}"
-    torch.cuda.synchronize()
+    barrier()
     sampler = ClockSampler(local_rank)
     sampler.start()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
-    torch.cuda.synchronize()
+    barrier()
     e0.record(stream)
     for _ in range(args.steps):
         step()
     e1.record(stream)
-    check(L.spchol_sync(plan.h, C.byref(info)))
-    torch.cuda.synchronize()
+    check(L.spchol_sync(plan_h, C.byref(info)))
+    barrier()
     clocks = sampler.stop()
-    ms = e0.elapsed_time(e1) / args.steps
-    launches = int(L.spchol_last_launches(plan.h)) * args.steps
+    ms_rank = e0.elapsed_time(e1) / args.steps
+    ms = max_over_ranks(ms_rank)                       # device time, max over ranks
+    launches = int(L.spchol_last_launches(plan_h)) * args.steps
     gflops = S.flops / ms * 1e-6
 
     # roofline of the dominant kernel (DMMA SYRK/GEMM): one extra profiled step, CUDA events per launch group
-    check(L.spchol_set_profile(plan.h, 1))
+    check(L.spchol_set_profile(plan_h, 1))
     step()
-    check(L.spchol_sync(plan.h, C.byref(info)))
+    check(L.spchol_sync(plan_h, C.byref(info)))
     kms = np.zeros(8); kl = np.zeros(8, np.int64); fl2 = np.zeros(2)
-    check(L.spchol_get_profile(plan.h, ptr(kms), ptr(kl), ptr(fl2)))
-    check(L.spchol_set_profile(plan.h, 0))
+    check(L.spchol_get_profile(plan_h, ptr(kms), ptr(kl), ptr(fl2)))
+    check(L.spchol_set_profile(plan_h, 0))
+    barrier()
     peak = C.c_double(0)
     check(L.spchol_fp64_peak(local_rank, C.byref(peak)))
-    names = ["small_fronts", "zero", "extend_add", "potrf", "trsm", "gemm_dmma", "memset_assemble"]
+    names = ["small_fronts", "zero", "extend_add", "potrf", "trsm", "gemm_dmma", "transfers_nccl", "memset_assemble"]
     kind_ms = {nm: round(float(kms[i]), 3) for i, nm in enumerate(names)}
     gemm_ms = float(kms[5]); gemm_launches = int(kl[5])
     achieved = fl2[0] / gemm_ms * 1e-9 if gemm_ms > 0 else 0.0
@@ -249,14 +277,17 @@ def main():
         "peak_source": "measured live: register-resident mma.sync.m8n8k4.f64 chains on this GPU (MEASURED_PEAKS.json has no FP64 entry)",
         "launches": gemm_launches, "avg_launch_ms": round(gemm_ms / max(gemm_launches, 1), 4),
         "algorithmic_flops_per_step": fl2[0], "share_of_step": round(gemm_ms / max(float(kms.sum()), 1e-9), 3),
-        "whole_factor_frac_of_peak": round(gflops * 1e-3 / peak.value, 4) if peak.value else None,
+        "whole_factor_frac_of_peak": round(gflops * 1e-3 / (peak.value * world), 4) if peak.value else None,
+        "note": "per-rank figures of rank 0; whole_factor_frac_of_peak = value / (n_gpus * peak)" if world > 1 else None,
     }
+    per_rank = gather_list({"ms": round(ms_rank, 3), "kernel_ms": kind_ms, "gemm_tflops": round(achieved, 2),
+                            "lbuf_gb": round(ps["lbuf_entries"] * 8e-9, 2), "ws_gb": round(ps["ws_entries"] * 8e-9, 2)})
 
     # e2e: host-buffer C-ABI call, pinned host memory, H2D + D2H inside the timed region
     e2e = None
     if not args.no_e2e:
         nA = A.capacity()
-        use_csc = S.nnz <= 2**31 - 1
+        use_csc = S.nnz <= 2**31 - 1 and world == 1
         out_entries = S.nnz if use_csc else ps["lbuf_entries"]
         hA = C.c_void_p(); hL = C.c_void_p()
         check(L.spchol_host_alloc(nA * 8, C.byref(hA)), "host_alloc")
@@ -264,23 +295,26 @@ def main():
         C.memmove(hA.value, A.x.ctypes.data, nA * 8)
         fn = L.spchol_factor if use_csc else L.spchol_factor_lbuf
         e2e_steps = max(1, min(args.steps, 3))
-        check(fn(plan.h, hA.value, hL.value, C.byref(info)), "e2e warmup")
-        torch.cuda.synchronize()
+        check(fn(plan_h, hA.value, hL.value, C.byref(info)), "e2e warmup")
+        barrier()
         t0 = time.perf_counter()
         for _ in range(e2e_steps):
-            check(fn(plan.h, hA.value, hL.value, C.byref(info)), "e2e")
+            check(fn(plan_h, hA.value, hL.value, C.byref(info)), "e2e")
         torch.cuda.synchronize()
-        e2e_ms = (time.perf_counter() - t0) * 1e3 / e2e_steps
+        e2e_ms = max_over_ranks((time.perf_counter() - t0) * 1e3 / e2e_steps)
+        barrier()
         tm = np.zeros(4)
-        L.spchol_last_timing(plan.h, ptr(tm))
+        L.spchol_last_timing(plan_h, ptr(tm))
         e2e = {"value": S.flops / e2e_ms * 1e-6, "unit": UNIT, "ms_per_step": e2e_ms, "steps": e2e_steps,
-               "h2d_bytes_per_step": nA * 8, "d2h_bytes_per_step": out_entries * 8 + 4,
-               "result": "CSC L values (reference layout)" if use_csc else "supernodal L panels (nnz(L) > INT_MAX: no 32-bit CSC)",
+               "h2d_bytes_per_step": nA * 8 * world, "d2h_bytes_per_step": sum(gather_list(out_entries * 8 + 4)),
+               "result": "CSC L values (reference layout)" if use_csc else
+                         ("supernodal L panels, each rank reads back the fronts it holds" if world > 1 else
+                          "supernodal L panels (nnz(L) > INT_MAX: no 32-bit CSC)"),
                "last_step_ms": {"h2d": tm[0], "numeric": tm[1], "export": tm[2], "d2h": tm[3]}}
         L.spchol_host_free(hA); L.spchol_host_free(hL)
 
     cpu = None
-    if not args.no_cpu_baseline:
+    if not args.no_cpu_baseline and world == 1:
         kind, sec, fl, n_s, nnz_s = cpu_reference_time(sample)
         cpu = {"value": fl / sec * 1e-9, "unit": UNIT, "cores": 1, "kind": kind, "seconds": sec,
                "sample": f"{'x'.join(map(str, sample))} Laplacian, same generator + ND ordering (n={n_s}, nnz(L)={nnz_s}); "
@@ -288,18 +322,29 @@ def main():
                          f"({'32-bit nnz overflow' if S.nnz > 2**31 - 1 else 'O(n^2) workspace: minutes to hours'})",
                "host_cores_available": os.cpu_count()}
 
-    line = {
-        "metric": METRIC, "value": gflops, "unit": UNIT, "n_gpus": 1, "steps": args.steps, "warmup": args.warmup,
-        "ms_per_step": ms, "chol_ms": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
-        "dtype": "f64", "data": "synthetic",
-        "config": {"workload": args.workload, "description": desc, "n": A.n, "nnz_A": A.capacity(), "nnz_L": S.nnz,
-                   "flops": S.flops, "fronts": ps["ns"], "levels": ps["nlevels"], "l2": "inputs larger than L2 "
-                   f"(L buffer {ps['lbuf_entries'] * 8 / 1e9:.2f} GB + workspace {ps['ws_entries'] * 8 / 1e9:.2f} GB rewritten every step)",
-                   "host_seconds": {"generate": round(t_gen, 2), "schol": round(t_sym, 2), "plan_upload": round(t_plan, 2)}},
-        "roofline": roofline, "kernel_ms": kind_ms, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
-        "clocks": clocks,
-    }
-    print(json.dumps(line), flush=True)
+    if rank == 0:
+        cfg = {"workload": args.workload, "description": desc, "n": A.n, "nnz_A": A.capacity(), "nnz_L": S.nnz,
+               "flops": S.flops, "fronts": ps["ns"], "levels": ps["nlevels"], "l2": "inputs larger than L2 "
+               f"(L buffer {ps['lbuf_entries'] * 8 / 1e9:.2f} GB + workspace {ps['ws_entries'] * 8 / 1e9:.2f} GB rewritten every step)",
+               "host_seconds": {"generate": round(t_gen, 2), "schol": round(t_sym, 2), "plan_upload": round(t_plan, 2)}}
+        if world > 1:
+            cfg["parallelism"] = (f"etree subtrees -> {world} ranks (proportional mapping); {ps['fronts_dist']} top fronts factored by rank "
+                                  f"groups, block-column cyclic (NB={ps['dist_NB']}), NCCL broadcast/send/recv in stream order")
+            cfg["rank_load_flops"] = ps["rank_load"]
+        line = {
+            "metric": METRIC, "value": gflops, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
+            "ms_per_step": ms, "chol_ms": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
+            "dtype": "f64", "data": "synthetic", "config": cfg,
+            "roofline": roofline, "kernel_ms": kind_ms, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches,
+            "clocks": clocks,
+        }
+        if world > 1:
+            line["per_rank"] = per_rank
+        print(json.dumps(line), flush=True)
+    if dist is not None:
+        barrier()
+        dplan.close(); comm.close()
+        dist.destroy_process_group()
 
 
 if __name__ == "__main__":
