@@ -100,6 +100,7 @@ struct spchol_plan {
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // device buffers
     double* dL = nullptr; double* dW = nullptr; double* dAx = nullptr; double* dLx = nullptr;
+    double* dWinv = nullptr;      // inverses of the diagonal blocks of one launch (k_potrf_inv -> k_trsm_inv)
     int* dinfo = nullptr;
     int *d_first = nullptr, *d_w = nullptr, *d_m = nullptr, *d_ld = nullptr, *d_parent = nullptr;
     int64_t *d_panel_off = nullptr, *d_cb_off = nullptr, *d_rel_off = nullptr;
@@ -204,13 +205,18 @@ int run_numeric(spchol_plan* p, const double* dAx) {
             ++launches;
             break;
         case OP_POTRF:
-            k_potrf_diag<<<op.count, 256, 0, st>>>(p->d_potrf + op.begin, p->dL, p->dinfo);
+            if (op.threads <= 32)      k_potrf_inv<32><<<op.count, PI_THREADS, potrf_inv_smem(32), st>>>(p->d_potrf + op.begin, p->dL, p->dWinv, p->dinfo);
+            else if (op.threads <= 64) k_potrf_inv<64><<<op.count, PI_THREADS, potrf_inv_smem(64), st>>>(p->d_potrf + op.begin, p->dL, p->dWinv, p->dinfo);
+            else                       k_potrf_inv<128><<<op.count, PI_THREADS, potrf_inv_smem(128), st>>>(p->d_potrf + op.begin, p->dL, p->dWinv, p->dinfo);
             ++launches;
             break;
-        case OP_TRSM:
-            k_trsm<<<dim3(op.count, (op.gx + 127) / 128), 128, 0, st>>>(p->d_trsm + op.begin, p->dL);
+        case OP_TRSM: {
+            const dim3 grid(op.count, (op.gx + TI_ROWS - 1) / TI_ROWS);
+            if (op.threads <= 32)      k_trsm_inv<32><<<grid, 256, trsm_inv_smem(32), st>>>(p->d_trsm + op.begin, p->dL, p->dWinv);
+            else if (op.threads <= 64) k_trsm_inv<64><<<grid, 256, trsm_inv_smem(64), st>>>(p->d_trsm + op.begin, p->dL, p->dWinv);
+            else                       k_trsm_inv<128><<<grid, 256, trsm_inv_smem(128), st>>>(p->d_trsm + op.begin, p->dL, p->dWinv);
             ++launches;
-            break;
+        } break;
         case OP_GEMM:
             for (int b = 0; b < op.count; b += 65535) {
                 const int c = std::min(op.count - b, 65535);
@@ -340,12 +346,19 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
     if ((rc = dalloc(p, H.lbuf_entries, &p->dL))) return fail(rc);
     if ((rc = dalloc(p, H.ws_entries, &p->dW))) return fail(rc);
     if ((rc = dalloc(p, 1, &p->dinfo))) return fail(rc);
+    if ((rc = dalloc(p, static_cast<int64_t>(std::max(H.max_potrf_slots, 1)) * PB_MAX * PB_MAX, &p->dWinv))) return fail(rc);
     p->fa = FrontArrays{p->d_first, p->d_w, p->d_m, p->d_ld, p->d_parent, p->d_panel_off, p->d_cb_off,
                         p->d_rel_off, p->d_rel, p->d_child_ptr, p->d_child_idx, p->d_own_n, p->d_own_idx, H.dist_NB};
     if ((rc = set_small_attr<32>()) || (rc = set_small_attr<64>()) || (rc = set_small_attr<128>()) ||
         (rc = set_small_attr<256>())) return fail(rc);
-    if (cudaFuncSetAttribute(k_gemm_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM) != cudaSuccess) {
-        set_error("cudaFuncSetAttribute(k_gemm_dmma) failed"); return fail(SPCHOL_ECUDA);
+    if (cudaFuncSetAttribute(k_gemm_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(k_potrf_inv<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, potrf_inv_smem(32)) != cudaSuccess ||
+        cudaFuncSetAttribute(k_potrf_inv<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, potrf_inv_smem(64)) != cudaSuccess ||
+        cudaFuncSetAttribute(k_potrf_inv<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, potrf_inv_smem(128)) != cudaSuccess ||
+        cudaFuncSetAttribute(k_trsm_inv<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, trsm_inv_smem(32)) != cudaSuccess ||
+        cudaFuncSetAttribute(k_trsm_inv<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, trsm_inv_smem(64)) != cudaSuccess ||
+        cudaFuncSetAttribute(k_trsm_inv<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, trsm_inv_smem(128)) != cudaSuccess) {
+        set_error("cudaFuncSetAttribute (dynamic shared memory) failed"); return fail(SPCHOL_ECUDA);
     }
     *out = p;
     return SPCHOL_OK;

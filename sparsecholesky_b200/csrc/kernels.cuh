@@ -168,75 +168,260 @@ __global__ void __launch_bounds__(128) k_extend_add(const int* __restrict__ list
     }
 }
 
-// ---------------------------------------------------------------------------------------------
-// Large fronts, step 2a: Cholesky of one nb x nb (nb <= 64) diagonal block, in shared memory.
-// (dpotrf_ of the reference, include/chol.hpp:1263, one block of the blocked algorithm.)
-// ---------------------------------------------------------------------------------------------
-constexpr int POTRF_NB = 64;
-__global__ void __launch_bounds__(256) k_potrf_diag(const PotrfTask* __restrict__ tasks,
-                                                    double* __restrict__ L, int* __restrict__ info) {
-    __shared__ double S[POTRF_NB * (POTRF_NB + 1)];
-    const PotrfTask t = tasks[blockIdx.x];
-    const int nb = t.nb, ld = t.ld;
-    constexpr int lds = POTRF_NB + 1;
-    double* __restrict__ D = L + t.d_off;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    for (int j = warp; j < nb; j += 8)
-        for (int i = j + lane; i < nb; i += 32) S[i + j * lds] = D[i + static_cast<int64_t>(j) * ld];
-    __syncthreads();
-    for (int k = 0; k < nb; ++k) {
-        const double d = S[k + k * lds];
-        if (d <= 0.0 && tid == 0) atomicMin(info, t.col0 + k + 1);
-        const double piv = sqrt(d);
-        double* colk = S + k * lds;
-        for (int i = k + 1 + tid; i < nb; i += 256) colk[i] = colk[i] / piv;
-        __syncthreads();
-        if (tid == 0) colk[k] = piv;
-        for (int j = k + 1 + warp; j < nb; j += 8) {
-            const double uj = colk[j];
-            for (int i = j + lane; i < nb; i += 32) S[i + j * lds] -= colk[i] * uj;
-        }
-        __syncthreads();
-    }
-    for (int j = warp; j < nb; j += 8)
-        for (int i = j + lane; i < nb; i += 32) D[i + static_cast<int64_t>(j) * ld] = S[i + j * lds];
+__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
+    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
+                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
 }
 
 // ---------------------------------------------------------------------------------------------
-// Large fronts, step 2b: B <- B * D^{-T} for the rows below a diagonal block (cblas_dtrsm Right/
-// Lower/Trans, reference include/chol.hpp:1292).  One thread owns one row (64 values in
-// registers, coalesced column accesses across the CTA); D is broadcast from shared memory.
+// Large fronts, step 2a: Cholesky of one nb x nb (nb <= 128) diagonal block in shared memory AND
+// the explicit inverse of its triangular factor (written to a scratch slot), so that the panel
+// solve below the block becomes a DMMA matrix product (k_trsm_inv) instead of a substitution.
+// (dpotrf_ of the reference, include/chol.hpp:1263, one block of the blocked algorithm.)
+// Right-looking over 8-wide micro panels: warp 0 factors the 8x8 micro block in registers (row
+// per lane, shuffles) and inverts it; all threads apply the micro inverse to the rows below (no
+// divisions) and do the rank-8 update of the trailing block.  W = L^-1 is then assembled from
+// the micro inverses, one warp per block column.
 // ---------------------------------------------------------------------------------------------
-__global__ void __launch_bounds__(128) k_trsm(const TrsmTask* __restrict__ tasks, double* __restrict__ L) {
-    __shared__ double S[POTRF_NB * (POTRF_NB + 1)];
-    const TrsmTask t = tasks[blockIdx.x];
+constexpr int PB_MAX = 128;           // largest diagonal block; one scratch slot holds PB_MAX^2 doubles
+constexpr int PI_THREADS = 256;
+constexpr int PI_XLD = 9;             // row stride of the micro-panel copy (odd: conflict-free row walks)
+constexpr int potrf_inv_smem(int pb) { return (pb * (pb + 1) + 16 * 64 + pb * PI_XLD) * 8; }
+
+// PB = size class (32 / 64 / 128): bounds the shared memory so that the many narrow fronts of the
+// lower levels still get several CTAs per SM.  The scratch slot stores W with leading dimension PB.
+template <int PB>
+__global__ void __launch_bounds__(PI_THREADS) k_potrf_inv(const PotrfTask* __restrict__ tasks,
+                                                          double* __restrict__ L, double* __restrict__ Winv,
+                                                          int* __restrict__ info) {
+    extern __shared__ double sm[];
+    constexpr int PB_LD = PB + 1;            // odd leading dimension: conflict-free row and column walks
+    double* S = sm;                          // S[i + j*PB_LD]: lower = L; strict upper receives W^T at the end
+    double* T = sm + PB * PB_LD;             // 16 micro inverses (8x8 lower), T[mp*64 + i + 8*j]
+    double* X = T + 16 * 64;                 // current micro panel by rows: X[rr*PI_XLD + k], rr = row - (p+8)
+    const PotrfTask t = tasks[blockIdx.x];
     const int nb = t.nb, ld = t.ld;
-    constexpr int lds = POTRF_NB + 1;
-    const int row0 = blockIdx.y * 128;
-    if (row0 >= t.rows) return;
-    const double* __restrict__ D = L + t.d_off;
-    for (int idx = threadIdx.x; idx < POTRF_NB * POTRF_NB; idx += 128) {
-        const int i = idx % POTRF_NB, j = idx / POTRF_NB;
-        double v = (i == j) ? 1.0 : 0.0;             // identity padding when nb < 64
-        if (i < nb && j < nb && i >= j) v = D[i + static_cast<int64_t>(j) * ld];
-        S[i + j * lds] = v;
+    double* __restrict__ D = L + t.d_off;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    constexpr int NW = PI_THREADS / 32;
+    const int nmp = (nb + 7) >> 3;           // micro panels; the padded tail of the last one is an identity
+    const int np8 = nmp * 8;
+
+    for (int j = warp; j < np8; j += NW)
+        for (int i = lane; i < np8; i += 32)
+            S[i + j * PB_LD] = (i >= j && i < nb && j < nb) ? D[i + static_cast<int64_t>(j) * ld] : ((i == j) ? 1.0 : 0.0);
+    __syncthreads();
+
+    for (int mp = 0; mp < nmp; ++mp) {
+        const int p = mp * 8;
+        if (warp == 0) {
+            // ---- 8x8 micro Cholesky: lane r < 8 owns row r (lanes 8..31 mirror them) ---------
+            double a[8], rinv[8];
+            const int r = lane & 7;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) a[k] = S[(p + r) + (p + k) * PB_LD];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {
+                const double d = __shfl_sync(0xffffffffu, a[k], k);
+                if (d <= 0.0 && lane == 0 && p + k < nb) atomicMin(info, t.col0 + p + k + 1);   // reference test (chol.hpp:849)
+                const double piv = sqrt(d);
+                rinv[k] = 1.0 / piv;
+                a[k] = (r == k) ? piv : a[k] * rinv[k];
+#pragma unroll
+                for (int j = k + 1; j < 8; ++j) {
+                    const double ljk = __shfl_sync(0xffffffffu, a[k], j);
+                    a[j] -= a[k] * ljk;
+                }
+            }
+            if (lane < 8) {
+#pragma unroll
+                for (int k = 0; k < 8; ++k) if (k <= r) S[(p + r) + (p + k) * PB_LD] = a[k];
+            }
+            __syncwarp();
+            // ---- micro inverse: lane j < 8 solves L t = e_j (column j of T), no divisions -----
+            if (lane < 8) {
+                double tt[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i) {
+                    double acc = (i == lane) ? 1.0 : 0.0;
+#pragma unroll
+                    for (int k = 0; k < i; ++k) acc -= S[(p + i) + (p + k) * PB_LD] * tt[k];
+                    tt[i] = (i >= lane) ? acc * rinv[i] : 0.0;
+                }
+#pragma unroll
+                for (int i = 0; i < 8; ++i) T[mp * 64 + i + 8 * lane] = tt[i];
+            }
+        }
+        __syncthreads();
+        // ---- rows below the micro block: X = S[rows, p:p+8] * T^T ---------------------------
+        const int below = np8 - (p + 8);
+        for (int rr = tid; rr < below; rr += PI_THREADS) {
+            const int row = p + 8 + rr;
+            double b[8], x[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) b[k] = S[row + (p + k) * PB_LD];
+#pragma unroll
+            for (int j = 0; j < 8; ++j) {
+                double acc = 0.0;
+#pragma unroll
+                for (int k = 0; k <= j; ++k) acc += b[k] * T[mp * 64 + j + 8 * k];
+                x[j] = acc;
+            }
+#pragma unroll
+            for (int j = 0; j < 8; ++j) { S[row + (p + j) * PB_LD] = x[j]; X[rr * PI_XLD + j] = x[j]; }
+        }
+        __syncthreads();
+        // ---- rank-8 update of the trailing lower block: a warp owns a strip of 4 columns, its
+        // lanes walk down consecutive rows (conflict-free), the strip's X rows are broadcast -----
+        const int ncs = below >> 2;                       // column strips of 4
+        for (int cs = warp; cs < ncs; cs += NW) {
+            const int c0 = cs * 4;                        // first column of the strip (relative to p+8)
+            double xj[4][8];
+#pragma unroll
+            for (int b2 = 0; b2 < 4; ++b2)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) xj[b2][k] = X[(c0 + b2) * PI_XLD + k];
+            for (int rr = c0 + lane; rr < below; rr += 32) {
+                double xi[8];
+#pragma unroll
+                for (int k = 0; k < 8; ++k) xi[k] = X[rr * PI_XLD + k];
+#pragma unroll
+                for (int b2 = 0; b2 < 4; ++b2) {
+                    double acc = 0.0;
+#pragma unroll
+                    for (int k = 0; k < 8; ++k) acc += xi[k] * xj[b2][k];
+                    S[(p + 8 + rr) + (p + 8 + c0 + b2) * PB_LD] -= acc;   // above-diagonal entries of the strip are scratch
+                }
+            }
+        }
+        __syncthreads();
+    }
+
+    // write the factor back (lower triangle only)
+    for (int j = warp; j < nb; j += NW)
+        for (int i = j + lane; i < nb; i += 32) D[i + static_cast<int64_t>(j) * ld] = S[i + j * PB_LD];
+    __syncthreads();      // the strict upper triangle of S is reused for W^T below
+
+    // ---- W = L^-1, one warp per block column q: W_qq = T_q, W_pq = -T_p * sum_{k=q}^{p-1} L_pk W_kq.
+    // W[i][j] (i > j, different micro blocks) lives at S[j + i*PB_LD]; lanes hold entries (i0, j), (i0+4, j).
+    double* __restrict__ Wg = Winv + static_cast<int64_t>(t.slot) * PB_MAX * PB_MAX;
+    for (int q = warp; q < nmp; q += NW) {
+        const int j = lane & 7, i0 = lane >> 3;
+        for (int pb = q + 1; pb < nmp; ++pb) {
+            double acc0 = 0.0, acc1 = 0.0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {                 // k in block q: W_kq = T_q
+                const double wkj = (k >= j) ? T[q * 64 + k + 8 * j] : 0.0;
+                acc0 += S[(pb * 8 + i0) + (q * 8 + k) * PB_LD] * wkj;
+                acc1 += S[(pb * 8 + i0 + 4) + (q * 8 + k) * PB_LD] * wkj;
+            }
+            for (int kb = q + 1; kb < pb; ++kb)
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const double wkj = S[(q * 8 + j) + (kb * 8 + k) * PB_LD];
+                    acc0 += S[(pb * 8 + i0) + (kb * 8 + k) * PB_LD] * wkj;
+                    acc1 += S[(pb * 8 + i0 + 4) + (kb * 8 + k) * PB_LD] * wkj;
+                }
+            double w0 = 0.0, w1 = 0.0;
+#pragma unroll
+            for (int k = 0; k < 8; ++k) {                 // Acc[k][j] sits in lane ((k&3)<<3)|j as acc0 (k<4) / acc1
+                const double ak = __shfl_sync(0xffffffffu, (k < 4) ? acc0 : acc1, ((k & 3) << 3) | j);
+                if (k <= i0) w0 -= T[pb * 64 + i0 + 8 * k] * ak;
+                if (k <= i0 + 4) w1 -= T[pb * 64 + (i0 + 4) + 8 * k] * ak;
+            }
+            S[(q * 8 + j) + (pb * 8 + i0) * PB_LD] = w0;
+            S[(q * 8 + j) + (pb * 8 + i0 + 4) * PB_LD] = w1;
+            __syncwarp();
+        }
     }
     __syncthreads();
-    const int row = row0 + threadIdx.x;
-    if (row >= t.rows) return;
-    double* __restrict__ B = L + t.b_off + row;
-    double r[POTRF_NB];
-#pragma unroll
-    for (int j = 0; j < POTRF_NB; ++j) r[j] = (j < nb) ? B[static_cast<int64_t>(j) * ld] : 0.0;
-#pragma unroll
-    for (int k = 0; k < POTRF_NB; ++k) {
-        const double v = r[k] / S[k + k * lds];
-        r[k] = v;
-#pragma unroll
-        for (int j = k + 1; j < POTRF_NB; ++j) r[j] -= v * S[j + k * lds];
+    // scratch slot: full PB x PB column-major W (zeros above the diagonal, identity in the padded tail)
+    for (int c = warp; c < PB; c += NW)
+        for (int r = lane; r < PB; r += 32) {
+            double v;
+            if (r >= np8 || c >= np8) v = (r == c) ? 1.0 : 0.0;
+            else if (r < c) v = 0.0;
+            else if ((r >> 3) == (c >> 3)) v = T[(c >> 3) * 64 + (r & 7) + 8 * (c & 7)];
+            else v = S[c + r * PB_LD];
+            Wg[r + c * PB] = v;
+        }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Large fronts, step 2b: B <- B * L11^-T for the rows below a diagonal block (cblas_dtrsm Right/
+// Lower/Trans, reference include/chol.hpp:1292) as a DMMA product with the explicit inverse
+// W = L11^-1 from k_potrf_inv: X[i][j] = sum_{k<=j} B[i][k] W[j][k].  One CTA owns a slab of 64
+// rows: the slab and W are staged in shared memory, the product runs on the FP64 tensor cores,
+// the result replaces the slab in place (each row depends on that row only).
+// ---------------------------------------------------------------------------------------------
+constexpr int TI_ROWS = 64;
+constexpr int TI_LDB = TI_ROWS + 8;   // == 8 (mod 16): conflict-free fragment loads
+constexpr int trsm_inv_smem(int pb) { return (pb * TI_LDB + pb * (pb + 8)) * 8; }
+
+template <int PB>
+__global__ void __launch_bounds__(256) k_trsm_inv(const TrsmTask* __restrict__ tasks, double* __restrict__ L,
+                                                  const double* __restrict__ Winv) {
+    extern __shared__ double sm[];
+    const TrsmTask t = tasks[blockIdx.x];
+    const int row0 = blockIdx.y * TI_ROWS;
+    if (row0 >= t.rows) return;
+    constexpr int TI_LDW = PB + 8;
+    double* Bs = sm;                        // Bs[k*TI_LDB + r]  : B[row0 + r][k]
+    double* Ws = sm + PB * TI_LDB;          // Ws[k*TI_LDW + n]  : W[n][k]
+    const int nb = t.nb, ld = t.ld;
+    const int nk = (nb + 7) & ~7;           // padded inner/outer extent (W is identity there, B is loaded as 0)
+    double* __restrict__ B = L + t.b_off + row0;
+    const double* __restrict__ Wg = Winv + static_cast<int64_t>(t.slot) * PB_MAX * PB_MAX;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int nrows = min(TI_ROWS, t.rows - row0);
+    for (int idx = tid; idx < nk * TI_ROWS; idx += 256) {
+        const int r = idx & (TI_ROWS - 1), k = idx >> 6;
+        Bs[k * TI_LDB + r] = (r < nrows && k < nb) ? B[r + static_cast<int64_t>(k) * ld] : 0.0;
     }
+    for (int idx = tid; idx < nk * PB; idx += 256) {
+        const int n = idx % PB, k = idx / PB;
+        if (n < nk) Ws[k * TI_LDW + n] = Wg[n + k * PB];
+    }
+    __syncthreads();
+    // 8 warps = 2 (rows) x 4 (cols): warp tile 32 x 32
+    const int g = lane >> 2, tq = lane & 3;
+    const int wm = warp & 1, wn = warp >> 1;
+    double acc[4][4][2];
 #pragma unroll
-    for (int j = 0; j < POTRF_NB; ++j) if (j < nb) B[static_cast<int64_t>(j) * ld] = r[j];
+    for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < 4; ++ni) { acc[mi][ni][0] = 0.0; acc[mi][ni][1] = 0.0; }
+    if (wn * 32 < nk && wn * 32 < PB) {
+        const int kend = min(nk, wn * 32 + 32);          // W[n][k] = 0 for k > n
+        const double* a = Bs + wm * 32 + g;
+        const double* b = Ws + wn * 32 + g;
+        for (int kk = 0; kk < kend; kk += 4) {
+            double af[4], bf[4];
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi) af[mi] = a[(kk + tq) * TI_LDB + mi * 8];
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni) bf[ni] = b[(kk + tq) * TI_LDW + ni * 8];
+#pragma unroll
+            for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+                for (int ni = 0; ni < 4; ++ni) dmma884(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
+        }
+    }
+    __syncthreads();                                      // everyone is done reading the slab
+    if (wn * 32 < nk && wn * 32 < PB) {
+#pragma unroll
+        for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+            for (int ni = 0; ni < 4; ++ni)
+#pragma unroll
+                for (int e = 0; e < 2; ++e)
+                    Bs[(wn * 32 + ni * 8 + 2 * tq + e) * TI_LDB + wm * 32 + mi * 8 + g] = acc[mi][ni][e];
+    }
+    __syncthreads();
+    for (int idx = tid; idx < nb * TI_ROWS; idx += 256) {
+        const int r = idx & (TI_ROWS - 1), k = idx >> 6;
+        if (r < nrows) B[r + static_cast<int64_t>(k) * ld] = Bs[k * TI_LDB + r];
+    }
 }
 
 // ---------------------------------------------------------------------------------------------
@@ -251,11 +436,6 @@ __global__ void __launch_bounds__(128) k_trsm(const TrsmTask* __restrict__ tasks
 constexpr int G_BM = 128, G_BN = 64, G_BK = 16;
 constexpr int G_LDA = G_BM + 8, G_LDB = G_BN + 8;   // == 8 (mod 16) doubles: conflict-free fragment loads
 constexpr int G_SMEM = 2 * G_BK * (G_LDA + G_LDB) * 8;
-
-__device__ __forceinline__ void dmma884(double& c0, double& c1, double a, double b) {
-    asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
-                 : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
-}
 
 __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ tasks,
                                                    double* __restrict__ L, double* __restrict__ W) {

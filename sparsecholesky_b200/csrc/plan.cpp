@@ -411,22 +411,32 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             max_steps = std::max(max_steps, seq[li].size());
         }
         for (size_t i = 0; i < max_steps; ++i) {
-            Op a{}, b{}, c{};
-            a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.level = lv;
-            b.kind = OP_TRSM;  b.begin = static_cast<int>(P.trsm_tasks.size());  b.level = lv;
+            // diagonal blocks and panel solves, one launch per size class of the block width
+            for (int cls = 0; cls < 3; ++cls) {
+                const int lo_nb = cls == 0 ? 0 : (cls == 1 ? 32 : 64), hi_nb = cls == 0 ? 32 : (cls == 1 ? 64 : 1 << 30);
+                Op a{}, b{};
+                a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.level = lv; a.threads = 32 << cls;
+                b.kind = OP_TRSM;  b.begin = static_cast<int>(P.trsm_tasks.size());  b.level = lv; b.threads = 32 << cls;
+                for (size_t li = 0; li < large.size(); ++li) {
+                    if (i >= seq[li].size()) continue;
+                    const Step& st = seq[li][i];
+                    if (st.po.nb <= lo_nb || st.po.nb > hi_nb) continue;
+                    P.potrf_tasks.push_back(st.po);
+                    if (st.has_trsm) { P.trsm_tasks.push_back(st.tr); b.gx = std::max(b.gx, st.tr.rows); }
+                }
+                a.count = static_cast<int>(P.potrf_tasks.size()) - a.begin;
+                b.count = static_cast<int>(P.trsm_tasks.size()) - b.begin;
+                if (a.count) P.ops.push_back(a);
+                if (b.count) P.ops.push_back(b);
+            }
+            Op c{};
             c.kind = OP_GEMM;  c.begin = static_cast<int>(P.gemm_tasks.size());  c.level = lv;
             for (size_t li = 0; li < large.size(); ++li) {
                 if (i >= seq[li].size()) continue;
                 const Step& st = seq[li][i];
-                P.potrf_tasks.push_back(st.po);
-                if (st.has_trsm) { P.trsm_tasks.push_back(st.tr); b.gx = std::max(b.gx, st.tr.rows); }
                 if (st.has_gemm) add_gemm(c, st.ge);
             }
-            a.count = static_cast<int>(P.potrf_tasks.size()) - a.begin;
-            b.count = static_cast<int>(P.trsm_tasks.size()) - b.begin;
             c.count = static_cast<int>(P.gemm_tasks.size()) - c.begin;
-            if (a.count) P.ops.push_back(a);
-            if (b.count) P.ops.push_back(b);
             if (c.count) P.ops.push_back(c);
         }
     };
@@ -497,12 +507,13 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                 for (int k0 = c0; k0 < c1; k0 += nb) {
                     const int k1 = std::min(k0 + nb, c1);
                     const int64_t d = po + k0 + static_cast<int64_t>(k0) * ld;
-                    Op a{}; a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.count = 1; a.level = lv;
+                    const int cls_pb = (k1 - k0) <= 32 ? 32 : ((k1 - k0) <= 64 ? 64 : 128);
+                    Op a{}; a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.count = 1; a.level = lv; a.threads = cls_pb;
                     P.potrf_tasks.push_back({d, ld, k1 - k0, P.first[s] + k0, 0});
                     P.ops.push_back(a);
                     if (k1 < m) {
                         Op b{}; b.kind = OP_TRSM; b.begin = static_cast<int>(P.trsm_tasks.size()); b.count = 1; b.level = lv;
-                        b.gx = m - k1;
+                        b.gx = m - k1; b.threads = cls_pb;
                         P.trsm_tasks.push_back({po + k1 + static_cast<int64_t>(k0) * ld, ld, k1 - k0, m - k1, d, 0});
                         P.ops.push_back(b);
                     }

@@ -18,7 +18,7 @@ struct GemmTask {
     int diag;        // element (i,j) of C is wanted iff i + diag >= j   (lower-trapezoid mask)
     int c_space;     // 0: C lives in the L buffer, 1: in the contribution workspace
 };
-struct PotrfTask { int64_t d_off; int ld; int nb; int col0; int slot; };         // diag block in L buffer
+struct PotrfTask { int64_t d_off; int ld; int nb; int col0; int slot; };         // diag block in L buffer; slot: scratch for its inverse
 struct TrsmTask  { int64_t b_off; int ld; int nb; int rows; int64_t d_off; int slot; };  // rows below the block
 struct ZeroTask  { int64_t off; int64_t count; };
 // One stream-ordered transfer between ranks (multi-GPU plans only).  Broadcasts run inside the
@@ -38,14 +38,14 @@ struct Op {
     int kind;
     int begin, count;   // slice of the task array of that kind
     int gx, gy;         // grid extents besides the task dimension
-    int threads;        // OP_SMALL: CTA size class
+    int threads;        // OP_SMALL: CTA size class; OP_POTRF / OP_TRSM: block-width class (32 / 64 / 128)
     int smem;           // OP_SMALL: dynamic shared memory bytes
     int level;
 };
 
 struct PlanOptions {
     int small_max_m = 160;     // fronts with m <= this are factored whole in shared memory
-    int nb = 64;               // diagonal block of the blocked panel factorization
+    int nb = 128;              // diagonal block of the blocked panel factorization (<= 128, the potrf kernel's limit)
     int NB = 256;              // outer block (K of the deferred panel update)
     int want_csc = 1;          // build the CSC export map (needs nnz(L) <= INT_MAX)
     // multi-GPU (one plan per rank, every rank builds the same global mapping):
