@@ -261,13 +261,13 @@ def main():
     check(L.spchol_set_profile(plan_h, 1))
     step()
     check(L.spchol_sync(plan_h, C.byref(info)))
-    kms = np.zeros(8); kl = np.zeros(8, np.int64); fl2 = np.zeros(2)
+    kms = np.zeros(12); kl = np.zeros(12, np.int64); fl2 = np.zeros(2)
     check(L.spchol_get_profile(plan_h, ptr(kms), ptr(kl), ptr(fl2)))
     check(L.spchol_set_profile(plan_h, 0))
     barrier()
     peak = C.c_double(0)
     check(L.spchol_fp64_peak(local_rank, C.byref(peak)))
-    names = ["small_fronts", "zero", "extend_add", "potrf", "trsm", "gemm_dmma", "transfers_nccl", "memset_assemble"]
+    names = ["small_fronts", "zero", "extend_add", "potrf", "trsm", "gemm_dmma", "transfers_nccl", "pack_unpack", "memset_assemble"]
     kind_ms = {nm: round(float(kms[i]), 3) for i, nm in enumerate(names)}
     gemm_ms = float(kms[5]); gemm_launches = int(kl[5])
     achieved = fl2[0] / gemm_ms * 1e-9 if gemm_ms > 0 else 0.0

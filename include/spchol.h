@@ -145,10 +145,11 @@ int  spchol_lbuf_to_host(spchol_plan*, double* L_host);
 int  spchol_last_timing(const spchol_plan*, double* ms4);
 /* per-op-kind device timing (CUDA events around every launch group; adds a sync, so use it on an
  * extra untimed step): kinds 0 small fronts, 1 zero, 2 extend-add, 3 potrf, 4 trsm, 5 gemm/syrk (DMMA),
- * 6 inter-GPU transfers (NCCL), 7 memset+assemble (+ the info all-reduce of a multi-GPU plan).  flops2[0] = algorithmic flops of the kind-5 launches (lower trapezoids only),
+ * 6 inter-GPU transfers (NCCL), 7 pack/unpack copies of transferred block columns, 8 memset+assemble
+ * (+ the info all-reduce of a multi-GPU plan); arrays have 12 slots.  flops2[0] = algorithmic flops of the kind-5 launches (lower trapezoids only),
  * flops2[1] = flops of their full rectangles. */
 int  spchol_set_profile(spchol_plan*, int on);
-int  spchol_get_profile(const spchol_plan*, double* kind_ms8, int64_t* kind_launches8, double* flops2);
+int  spchol_get_profile(const spchol_plan*, double* kind_ms12, int64_t* kind_launches12, double* flops2);
 /* stream handle (cudaStream_t) the plan launches on, for CUDA-event timing by the caller */
 void* spchol_stream(spchol_plan*);
 /* number of kernel launches the last factorization issued */

@@ -108,6 +108,7 @@ struct spchol_plan {
     int64_t *d_a_dest = nullptr, *d_l_src = nullptr;
     int *d_small_list = nullptr, *d_extadd_list = nullptr;
     ZeroTask* d_zero = nullptr; PotrfTask* d_potrf = nullptr; TrsmTask* d_trsm = nullptr; GemmTask* d_gemm = nullptr;
+    CopyTask* d_copy = nullptr;
     int64_t device_bytes = 0;
     int64_t last_launches = 0;
     double last_ms[4] = {0, 0, 0, 0};
@@ -116,8 +117,8 @@ struct spchol_plan {
     // optional per-op-kind timing (spchol_set_profile): events around every launch group
     int profile = 0;
     std::vector<cudaEvent_t> prof_ev;
-    double kind_ms[8] = {0, 0, 0, 0, 0, 0, 0, 0};
-    int64_t kind_launches[8] = {0, 0, 0, 0, 0, 0, 0, 0};
+    double kind_ms[12] = {0};
+    int64_t kind_launches[12] = {0};
 };
 
 namespace {
@@ -170,7 +171,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         pkind.push_back(kind);
         return 0;
     };
-    mark(7);
+    mark(8);
     CK(cudaMemsetAsync(p->dL, 0, static_cast<size_t>(H.lbuf_entries) * sizeof(double), st));
     CK(cudaMemsetAsync(p->dinfo, 0x7f, sizeof(int), st));
     {
@@ -228,6 +229,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         case OP_COMM: {
             NcclApi* nc = nccl_api();
             if (!p->comm || !nc) { set_error("spchol: plan has transfers but no communicator"); return SPCHOL_EINVAL; }
+            if (op.count > 1) NCK(nc->GroupStart());      // grouped sends/recvs progress concurrently
             for (int b = 0; b < op.count; ++b) {
                 const CommTask& t = H.comm_tasks[op.begin + b];
                 double* buf = (t.space ? p->dW : p->dL) + t.off;
@@ -242,13 +244,21 @@ int run_numeric(spchol_plan* p, const double* dAx) {
                 }
                 ++launches;
             }
+            if (op.count > 1) NCK(nc->GroupEnd());
         } break;
+        case OP_COPY:
+            for (int b = 0; b < op.count; b += 65535) {
+                const int c = std::min(op.count - b, 65535);
+                k_copy2d<<<dim3(c, std::max(1, std::min(op.gx, 1024))), 256, 0, st>>>(p->d_copy + op.begin + b, p->dL, p->dW);
+                ++launches;
+            }
+            break;
         default: break;
         }
         if (prof) p->kind_launches[op.kind] += launches - before;
     }
     if (p->comm && p->comm->world > 1) {      // first failing column over all ranks
-        mark(7);
+        mark(8);
         NCK(nccl_api()->AllReduce(p->dinfo, p->dinfo, 1, kNcclInt32, kNcclMin, p->comm->world_comm, st));
     }
     mark(-1);
@@ -259,7 +269,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         for (size_t i = 0; i + 1 < pe; ++i) {
             float ms = 0;
             CK(cudaEventElapsedTime(&ms, p->prof_ev[i], p->prof_ev[i + 1]));
-            if (pkind[i] >= 0 && pkind[i] < 8) p->kind_ms[pkind[i]] += ms;
+            if (pkind[i] >= 0 && pkind[i] < 12) p->kind_ms[pkind[i]] += ms;
         }
     }
     return 0;
@@ -337,7 +347,7 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
     UP(H.own_n, p->d_own_n); UP(H.own_idx, p->d_own_idx);
     UP(H.a_dest, p->d_a_dest); UP(H.l_src, p->d_l_src);
     UP(H.small_list, p->d_small_list); UP(H.extadd_list, p->d_extadd_list);
-    UP(H.zero_tasks, p->d_zero); UP(H.potrf_tasks, p->d_potrf); UP(H.trsm_tasks, p->d_trsm); UP(H.gemm_tasks, p->d_gemm);
+    UP(H.zero_tasks, p->d_zero); UP(H.potrf_tasks, p->d_potrf); UP(H.trsm_tasks, p->d_trsm); UP(H.gemm_tasks, p->d_gemm); UP(H.copy_tasks, p->d_copy);
 #undef UP
     // the big host-side maps are only needed on the device from here on
     std::vector<int64_t>().swap(H.a_dest);
@@ -596,12 +606,12 @@ int spchol_last_timing(const spchol_plan* p, double* ms4) {
 int spchol_set_profile(spchol_plan* p, int on) {
     if (!p) return SPCHOL_EINVAL;
     p->profile = on;
-    for (int k = 0; k < 8; ++k) { p->kind_ms[k] = 0; p->kind_launches[k] = 0; }
+    for (int k = 0; k < 12; ++k) { p->kind_ms[k] = 0; p->kind_launches[k] = 0; }
     return 0;
 }
-int spchol_get_profile(const spchol_plan* p, double* kind_ms8, int64_t* kind_launches8, double* flops2) {
+int spchol_get_profile(const spchol_plan* p, double* kind_ms12, int64_t* kind_launches12, double* flops2) {
     if (!p) return SPCHOL_EINVAL;
-    for (int k = 0; k < 8; ++k) { if (kind_ms8) kind_ms8[k] = p->kind_ms[k]; if (kind_launches8) kind_launches8[k] = p->kind_launches[k]; }
+    for (int k = 0; k < 12; ++k) { if (kind_ms12) kind_ms12[k] = p->kind_ms[k]; if (kind_launches12) kind_launches12[k] = p->kind_launches[k]; }
     if (flops2) { flops2[0] = p->H.gemm_flops_alg; flops2[1] = p->H.gemm_flops; }
     return 0;
 }

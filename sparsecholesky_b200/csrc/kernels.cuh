@@ -50,6 +50,20 @@ __global__ void k_zero(const ZeroTask* __restrict__ tasks, double* __restrict__ 
         p[i] = 0.0;
 }
 
+// pack / unpack of block columns for the inter-GPU transfers: rows x cols rectangle, column-major,
+// between the L buffer and the workspace.  grid = (tasks, column slices).  HBM bound (16 B/entry).
+__global__ void __launch_bounds__(256) k_copy2d(const CopyTask* __restrict__ tasks, double* __restrict__ L,
+                                                double* __restrict__ W) {
+    const CopyTask t = tasks[blockIdx.x];
+    const double* __restrict__ src = (t.src_space ? W : L) + t.src_off;
+    double* __restrict__ dst = (t.dst_space ? W : L) + t.dst_off;
+    for (int j = blockIdx.y; j < t.cols; j += gridDim.y) {
+        const double* s = src + static_cast<int64_t>(j) * t.lds;
+        double* d = dst + static_cast<int64_t>(j) * t.ldd;
+        for (int i = threadIdx.x; i < t.rows; i += 256) d[i] = s[i];
+    }
+}
+
 // ---------------------------------------------------------------------------------------------
 // Small fronts: one CTA factors one whole front in shared memory.
 //   F (m x m, lower) = [A-panel | 0]  (+)= extend-add of every child's contribution block

@@ -441,41 +441,87 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         }
     };
 
-    // move child c's contribution block to every holder of its parent p (called by every rank in
-    // the same order; ranks that are neither source nor destination emit nothing)
+    auto add_copy = [&](Op& op, int sspace, int64_t soff, int lds, int dspace, int64_t doff, int ldd, int rows, int cols) {
+        P.copy_tasks.push_back({soff, doff, sspace, dspace, lds, ldd, rows, cols});
+        op.gx = std::max(op.gx, cols);
+    };
+    std::vector<int64_t> tmp_allocs;          // (offset, size) pairs of transfer buffers, released at the end of the level
+    auto tmp_alloc = [&](int64_t entries) {
+        const int64_t sz = even_up64(std::max<int64_t>(entries, 2));
+        const int64_t o = arena.alloc(sz);
+        tmp_allocs.push_back(o); tmp_allocs.push_back(sz);
+        return o;
+    };
+
+    // Move child c's contribution block to the holders of its parent p (called by every rank in the
+    // same order; ranks that are neither source nor destination emit nothing).  The block travels
+    // in column blocks of width DNB, each packed to its rows on and below the diagonal, and goes
+    // only to the ranks that assemble one of its columns: with a parent factored by a group that is
+    // the owner of the parent block column the child column maps to.  One grouped exchange per child.
     auto emit_transfer = [&](int c, int p, int lv) {
         const int mbc = P.m[c] - P.w[c];
         if (mbc == 0) return;
         const int ldc = even_up(mbc);
-        const int64_t size = static_cast<int64_t>(ldc) * mbc;
         const int cl = P.own_lo[c], cn = P.own_n[c], pl = P.own_lo[p], pn = P.own_n[p];
+        if (cn == 1 && pn == 1 && cl == pl) return;               // same single rank: nothing moves
         const bool in_p = P.holds(p), in_c = P.holds(c);
-        if (in_p && !in_c) ws_alloc(c);                        // staged copy
-        if (cn == 1) {
-            if (pn == 1) {
-                if (pl == cl) return;
-                if (rank == cl) add_comm(COMM_SEND, 0, 0, pl, 1, P.cb_off[c], size, lv);
-                if (rank == pl) add_comm(COMM_RECV, 0, 0, cl, 1, P.cb_off[c], size, lv);
-            } else {
-                if (cl < pl || cl >= pl + pn) throw std::runtime_error("spchol: child mapped outside its parent's rank group");
-                if (in_p) add_comm(COMM_BCAST, pl, pn, cl, 1, P.cb_off[c], size, lv);
-            }
-            return;
-        }
+        if (!in_p && !in_c) return;
+        if (cn > 1 && pn > 1 && (cl < pl || cl + cn > pl + pn)) throw std::runtime_error("spchol: child group outside its parent's rank group");
+        if (cn == 1 && pn > 1 && (cl < pl || cl >= pl + pn)) throw std::runtime_error("spchol: child mapped outside its parent's rank group");
+        if (in_p && !in_c) ws_alloc(c);                            // staged copy of the child's block (natural layout)
         const int nbp_c = (P.w[c] + DNB - 1) / DNB, nbc_c = (mbc + DNB - 1) / DNB;
+        const int wp = P.w[p], nbp_p = (wp + DNB - 1) / DNB;
+        const int* r = in_p ? P.rel.data() + P.rel_off[c] : nullptr;
+        Op pack{}, comm{}, unpack{};
+        pack.kind = OP_COPY; pack.begin = static_cast<int>(P.copy_tasks.size()); pack.level = lv;
+        std::vector<CommTask> ctasks;
+        std::vector<CopyTask> unpacks;
+        std::vector<char> need(pn);
         for (int jb = 0; jb < nbc_c; ++jb) {
-            const int o = cl + (nbp_c + jb) % cn;
+            const int o = cn == 1 ? cl : cl + (nbp_c + jb) % cn;   // holder of this column block
             const int j0 = jb * DNB, j1 = std::min(j0 + DNB, mbc);
-            const int64_t boff = j0 + static_cast<int64_t>(j0) * ldc;
-            const int64_t count = static_cast<int64_t>(j1 - j0 - 1) * ldc + (mbc - j0);
-            if (pn == 1) {
-                if (o == pl) continue;
-                if (rank == o) add_comm(COMM_SEND, 0, 0, pl, 1, P.cb_off[c] + boff, count, lv);
-                if (rank == pl) add_comm(COMM_RECV, 0, 0, o, 1, P.cb_off[c] + boff, count, lv);
-            } else {
-                if (o < pl || o >= pl + pn) throw std::runtime_error("spchol: child group outside its parent's rank group");
-                if (in_p) add_comm(COMM_BCAST, pl, pn, o, 1, P.cb_off[c] + boff, count, lv);
+            const int rows = mbc - j0, cols = j1 - j0;
+            const int64_t count = static_cast<int64_t>(rows) * cols;
+            const int64_t nat = j0 + static_cast<int64_t>(j0) * ldc;   // natural offset of the block inside the cb
+            if (rank != o && !in_p) continue;
+            // destinations
+            std::fill(need.begin(), need.end(), 0);
+            if (pn == 1) need[0] = 1;
+            else if (in_p) {
+                for (int jj = j0; jj < j1; ++jj) {
+                    const int cj = r[jj];
+                    const int blk = cj < wp ? cj / DNB : nbp_p + (cj - wp) / DNB;
+                    need[blk % pn] = 1;
+                }
             }
+            if (rank == o) {
+                // (o holds p whenever pn > 1, so `need` is known here; for pn == 1 it is {pl})
+                int64_t stage = -1;
+                for (int q = 0; q < pn; ++q) {
+                    if (!need[q] || pl + q == o) continue;
+                    if (stage < 0) {
+                        stage = tmp_alloc(count);
+                        add_copy(pack, 1, P.cb_off[c] + nat, ldc, 1, stage, rows, rows, cols);
+                    }
+                    ctasks.push_back({COMM_SEND, 0, 0, pl + q, 1, stage, count});
+                }
+            } else if (in_p && need[rank - pl]) {
+                const int64_t stage = tmp_alloc(count);
+                ctasks.push_back({COMM_RECV, 0, 0, o, 1, stage, count});
+                unpacks.push_back({stage, P.cb_off[c] + nat, 1, 1, rows, ldc, rows, cols});
+            }
+        }
+        pack.count = static_cast<int>(P.copy_tasks.size()) - pack.begin;
+        if (pack.count) P.ops.push_back(pack);
+        if (!ctasks.empty()) {
+            comm.kind = OP_COMM; comm.begin = static_cast<int>(P.comm_tasks.size()); comm.count = static_cast<int>(ctasks.size()); comm.level = lv;
+            for (const CommTask& t : ctasks) { P.comm_tasks.push_back(t); P.comm_doubles += t.count; }
+            P.ops.push_back(comm);
+        }
+        if (!unpacks.empty()) {
+            unpack.kind = OP_COPY; unpack.begin = static_cast<int>(P.copy_tasks.size()); unpack.count = static_cast<int>(unpacks.size()); unpack.level = lv;
+            for (const CopyTask& t : unpacks) { P.copy_tasks.push_back(t); unpack.gx = std::max(unpack.gx, t.cols); }
+            P.ops.push_back(unpack);
         }
     };
 
@@ -487,6 +533,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         const int G = P.own_n[s], idx = P.own_idx[s], lo = P.own_lo[s];
         const int nbp = (w + DNB - 1) / DNB, nbc = (mb + DNB - 1) / DNB;
         const int ldcb = even_up(mb);
+        const int64_t stage = tmp_alloc(static_cast<int64_t>(m) * std::min(DNB, w));    // packed block column in flight
         if (mb > 0) {
             Op op{}; op.kind = OP_ZERO; op.begin = static_cast<int>(P.zero_tasks.size()); op.count = 1; op.level = lv;
             P.zero_tasks.push_back({P.cb_off[s], cb_entries(s)});
@@ -525,8 +572,21 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                     }
                 }
             }
-            add_comm(COMM_BCAST, lo, G, lo + owner, 0, po + c0 + static_cast<int64_t>(c0) * ld,
-                     static_cast<int64_t>(c1 - c0 - 1) * ld + (m - c0), lv);
+            {   // the factored block column travels packed to its rows c0..m-1
+                const int rows = m - c0, cols = c1 - c0;
+                const int64_t src = po + c0 + static_cast<int64_t>(c0) * ld;
+                if (owner == idx) {
+                    Op cp{}; cp.kind = OP_COPY; cp.begin = static_cast<int>(P.copy_tasks.size()); cp.count = 1; cp.level = lv;
+                    add_copy(cp, 0, src, ld, 1, stage, rows, rows, cols);
+                    P.ops.push_back(cp);
+                }
+                add_comm(COMM_BCAST, lo, G, lo + owner, 1, stage, static_cast<int64_t>(rows) * cols, lv);
+                if (owner != idx) {
+                    Op cp{}; cp.kind = OP_COPY; cp.begin = static_cast<int>(P.copy_tasks.size()); cp.count = 1; cp.level = lv;
+                    add_copy(cp, 1, stage, rows, 0, src, ld, rows, cols);
+                    P.ops.push_back(cp);
+                }
+            }
             Op g{}; g.kind = OP_GEMM; g.begin = static_cast<int>(P.gemm_tasks.size()); g.level = lv;
             for (int jb = kb + 1; jb < nbp; ++jb) {
                 if (jb % G != idx) continue;
@@ -569,6 +629,8 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                 for (int q = P.child_ptr[p]; q < P.child_ptr[p + 1]; ++q) emit_transfer(P.child_idx[q], p, lv);
         emit_local(local_b, lv);
         for (int s : dists) emit_dist(s, lv);
+        for (size_t q = 0; q + 1 < tmp_allocs.size(); q += 2) arena.release(tmp_allocs[q], tmp_allocs[q + 1]);
+        tmp_allocs.clear();
         // children of this level's fronts are consumed now
         for (int s : by_level[lv]) {
             for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) {

@@ -33,7 +33,17 @@ struct CommTask {
     int64_t off, count; // doubles
 };
 
-enum OpKind : int { OP_SMALL = 0, OP_ZERO = 1, OP_EXTADD = 2, OP_POTRF = 3, OP_TRSM = 4, OP_GEMM = 5, OP_COMM = 6 };
+// Strided rectangle copy (rows x cols, column-major) between / inside the two device spaces:
+// packs a block column into a contiguous transfer buffer and unpacks it on the receiver, so that
+// only the rows below the diagonal travel.
+struct CopyTask {
+    int64_t src_off, dst_off;
+    int src_space, dst_space;   // 0: L buffer, 1: contribution workspace
+    int lds, ldd;
+    int rows, cols;
+};
+
+enum OpKind : int { OP_SMALL = 0, OP_ZERO = 1, OP_EXTADD = 2, OP_POTRF = 3, OP_TRSM = 4, OP_GEMM = 5, OP_COMM = 6, OP_COPY = 7 };
 struct Op {
     int kind;
     int begin, count;   // slice of the task array of that kind
@@ -84,6 +94,7 @@ struct HostPlan {
     std::vector<TrsmTask> trsm_tasks;
     std::vector<GemmTask> gemm_tasks;
     std::vector<CommTask> comm_tasks;
+    std::vector<CopyTask> copy_tasks;
     std::vector<Op> ops;
     int max_potrf_slots = 0;
     // statistics

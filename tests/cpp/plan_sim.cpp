@@ -29,7 +29,7 @@ struct Rank {
     HostPlan H;
     std::vector<double> L, W;
     size_t pc = 0;        // index into H.ops
-    int sub = 0;          // index inside a multi-task OP_COMM
+    std::vector<char> done;   // per task of the current OP_COMM (grouped sends/recvs complete in any order)
     int info = std::numeric_limits<int>::max();
 };
 
@@ -172,18 +172,27 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
             stats[2] += R[r].H.comm_doubles;
             stats[3] = std::max<int64_t>(stats[3], R[r].H.ws_entries);
         }
-        auto at_comm = [&](int r) -> const CommTask* {
+        auto comm_op = [&](int r) -> const Op* {
             Rank& k = R[r];
             if (k.pc >= k.H.ops.size()) return nullptr;
             const Op& op = k.H.ops[k.pc];
             if (op.kind != OP_COMM) return nullptr;
-            return &k.H.comm_tasks[op.begin + k.sub];
+            if (k.done.size() != static_cast<size_t>(op.count)) k.done.assign(op.count, 0);
+            return &op;
         };
-        auto advance_comm = [&](int r) {
+        auto finish_if_done = [&](int r) {
             Rank& k = R[r];
-            if (++k.sub >= k.H.ops[k.pc].count) { k.sub = 0; ++k.pc; }
+            for (char d : k.done) if (!d) return;
+            k.done.clear(); ++k.pc;
         };
         auto buf = [&](int r, const CommTask& t) { return (t.space ? R[r].W.data() : R[r].L.data()) + t.off; };
+        auto describe_rank = [&](int r) -> std::string {
+            const Op* op = comm_op(r);
+            if (!op) return "[rank " + std::to_string(r) + (R[r].pc >= R[r].H.ops.size() ? " done]" : " busy]");
+            std::string m2 = "[";
+            for (int i = 0; i < op->count && i < 4; ++i) if (!R[r].done[i]) m2 += describe(R[r].H.comm_tasks[op->begin + i], r) + "; ";
+            return m2 + "]";
+        };
         for (;;) {
             bool progress = false, all_done = true;
             for (int r = 0; r < world; ++r) {
@@ -198,6 +207,14 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
                     case OP_POTRF: for (int i = 0; i < op.count; ++i) run_potrf(k, H.potrf_tasks[op.begin + i]); break;
                     case OP_TRSM: for (int i = 0; i < op.count; ++i) run_trsm(k, H.trsm_tasks[op.begin + i]); break;
                     case OP_GEMM: for (int i = 0; i < op.count; ++i) run_gemm(k, H.gemm_tasks[op.begin + i]); break;
+                    case OP_COPY:
+                        for (int i = 0; i < op.count; ++i) {
+                            const CopyTask& c = H.copy_tasks[op.begin + i];
+                            const double* src = (c.src_space ? k.W.data() : k.L.data()) + c.src_off;
+                            double* dst = (c.dst_space ? k.W.data() : k.L.data()) + c.dst_off;
+                            for (int j = 0; j < c.cols; ++j) for (int ii = 0; ii < c.rows; ++ii) dst[ii + static_cast<size_t>(j) * c.ldd] = src[ii + static_cast<size_t>(j) * c.lds];
+                        }
+                        break;
                     default: return fail("unknown op kind");
                     }
                     ++k.pc; progress = true;
@@ -206,42 +223,59 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
             }
             if (all_done) break;
             for (int r = 0; r < world; ++r) {
-                const CommTask* t = at_comm(r);
-                if (!t) continue;
-                if (t->kind == COMM_BCAST) {
+                const Op* op = comm_op(r);
+                if (!op) continue;
+                const CommTask* tasks = R[r].H.comm_tasks.data() + op->begin;
+                if (tasks[0].kind == COMM_BCAST) {
+                    const CommTask* t = &tasks[0];
+                    if (op->count != 1) return fail("broadcasts are not grouped");
                     if (r < t->lo || r >= t->lo + t->n) return fail("broadcast issued outside its group: " + describe(*t, r));
                     if (r != t->lo) continue;             // resolved when visiting the group's first rank
                     bool ready = true;
                     for (int q = t->lo; q < t->lo + t->n && ready; ++q) {
-                        const CommTask* u = at_comm(q);
-                        if (!u) { ready = false; break; }
+                        const Op* uo = comm_op(q);
+                        if (!uo) { ready = false; break; }
+                        const CommTask* u = &R[q].H.comm_tasks[uo->begin];
                         if (u->kind != COMM_BCAST || u->lo != t->lo || u->n != t->n) { ready = false; break; }   // busy with another exchange
                         if (u->root != t->root || u->count != t->count)
                             return fail("broadcast mismatch: " + describe(*t, r) + " vs " + describe(*u, q));
                     }
                     if (!ready) continue;
-                    const CommTask root_t = *at_comm(t->root);
-                    const double* src = buf(t->root, root_t);
                     const int lo = t->lo, cnt = t->n, root = t->root;
                     const int64_t count = t->count;
-                    for (int q = lo; q < lo + cnt; ++q) {
-                        if (q != root) std::memcpy(buf(q, *at_comm(q)), src, static_cast<size_t>(count) * sizeof(double));
+                    const double* src = buf(root, R[root].H.comm_tasks[comm_op(root)->begin]);
+                    for (int q = lo; q < lo + cnt; ++q)
+                        if (q != root) std::memcpy(buf(q, R[q].H.comm_tasks[comm_op(q)->begin]), src, static_cast<size_t>(count) * sizeof(double));
+                    for (int q = lo; q < lo + cnt; ++q) { R[q].done[0] = 1; finish_if_done(q); }
+                    progress = true;
+                    continue;
+                }
+                // grouped point-to-point: the i-th pending send r -> q pairs with the i-th pending recv q <- r
+                for (int i = 0; i < op->count; ++i) {
+                    if (R[r].done[i] || tasks[i].kind != COMM_SEND) continue;
+                    const int q = tasks[i].root;
+                    bool earlier = false;                  // FIFO per pair
+                    for (int i2 = 0; i2 < i; ++i2) if (!R[r].done[i2] && tasks[i2].kind == COMM_SEND && tasks[i2].root == q) earlier = true;
+                    if (earlier) continue;
+                    const Op* uo = comm_op(q);
+                    if (!uo) continue;
+                    const CommTask* ut = R[q].H.comm_tasks.data() + uo->begin;
+                    if (ut[0].kind == COMM_BCAST) continue;
+                    for (int i2 = 0; i2 < uo->count; ++i2) {
+                        if (R[q].done[i2] || ut[i2].kind != COMM_RECV || ut[i2].root != r) continue;
+                        if (ut[i2].count != tasks[i].count)
+                            return fail("send/recv length mismatch: " + describe(tasks[i], r) + " vs " + describe(ut[i2], q));
+                        std::memcpy(buf(q, ut[i2]), buf(r, tasks[i]), static_cast<size_t>(tasks[i].count) * sizeof(double));
+                        R[q].done[i2] = 1; R[r].done[i] = 1;
+                        progress = true;
+                        break;
                     }
-                    for (int q = lo; q < lo + cnt; ++q) advance_comm(q);
-                    progress = true;
-                } else if (t->kind == COMM_SEND) {
-                    const int q = t->root;
-                    const CommTask* u = at_comm(q);
-                    if (!u || u->kind != COMM_RECV || u->root != r) continue;
-                    if (u->count != t->count) return fail("send/recv length mismatch: " + describe(*t, r) + " vs " + describe(*u, q));
-                    std::memcpy(buf(q, *u), buf(r, *t), static_cast<size_t>(t->count) * sizeof(double));
-                    advance_comm(r); advance_comm(q);
-                    progress = true;
                 }
             }
+            for (int r = 0; r < world; ++r) if (comm_op(r)) { const size_t before = R[r].pc; finish_if_done(r); if (R[r].pc != before) progress = true; }
             if (!progress) {
                 std::string msg = "deadlock:";
-                for (int r = 0; r < world; ++r) { const CommTask* t = at_comm(r); msg += t ? " [" + describe(*t, r) + "]" : " [rank " + std::to_string(r) + " done]"; }
+                for (int r = 0; r < world; ++r) msg += " " + describe_rank(r);
                 return fail(msg);
             }
         }
