@@ -124,6 +124,14 @@ int  spchol_map_fronts(const spchol_symbolic*, int world, int dist_min_w, int* o
 /* Host-buffer call (what chol(A,S) binds): H2D of Ax, factor, CSC gather, D2H of Lx.
  * info = 0, or (1-based) a column whose pivot was <= 0 -> "A is not positive definite." (chol.hpp:849-850). */
 int  spchol_factor(spchol_plan*, const double* Ax_host, double* Lx_host, int* info);
+/* Batched numeric factorization: nbatch value sets over ONE pattern (BASELINE config 5; the reference
+ * would loop chol(A_b), include/chol.hpp:750).  Ax[nbatch][nnzA] -> Lx[nbatch][nnzL] in the CSC order of S,
+ * info[nbatch] = 0 or the 1-based failing column of that matrix.  Every launch of the level program covers
+ * all matrices of a chunk (chunks sized to the free HBM).  Single-GPU plans whose fronts all fit the
+ * shared-memory front kernel (m <= 160, e.g. 1138_bus); across GPUs the batch index is sharded by the caller. */
+int  spchol_factor_batched(spchol_plan*, int nbatch, const double* Ax_host, double* Lx_host, int* info_host);
+int  spchol_factor_batched_device(spchol_plan*, int nbatch, const double* dAx, double* dLx, int* dinfo);
+
 /* Device-resident call: dAx is a device pointer (nnzA doubles); L stays on the device in
  * supernodal panels.  Asynchronous on the plan's stream; *info is valid after spchol_sync. */
 int  spchol_factor_device(spchol_plan*, const double* dAx);

@@ -54,6 +54,8 @@ SIGNATURES = {
     "spchol_map_fronts": (C.c_int, [_VP, C.c_int, C.c_int, _VP, _VP, _VP]),
     "spchol_factor": (C.c_int, [_VP, _VP, _VP, C.POINTER(C.c_int)]),
     "spchol_factor_device": (C.c_int, [_VP, _VP]),
+    "spchol_factor_batched": (C.c_int, [_VP, C.c_int, _VP, _VP, _VP]),
+    "spchol_factor_batched_device": (C.c_int, [_VP, C.c_int, _VP, _VP, _VP]),
     "spchol_export_csc_device": (C.c_int, [_VP, _VP]),
     "spchol_sync": (C.c_int, [_VP, C.POINTER(C.c_int)]),
     "spchol_factor_lbuf": (C.c_int, [_VP, _VP, _VP, C.POINTER(C.c_int)]),

@@ -275,6 +275,21 @@ def chol(A, S=None, device=0):
     return Expected(value=CscMatrix(A.n, S.p, S.i, Lx, Sym.none))
 
 
+def chol_batched(S, Ax, device=0):
+    """Config 5: numeric factorization of many matrices sharing the pattern behind S.
+    Ax: (nbatch, nnz(A)) values in the CSC order of the pattern A.  Returns (Lx (nbatch, nnz(L)) in
+    the CSC order of S.p / S.i, info (nbatch,) with 0 or the 1-based failing column per matrix) --
+    what a loop of chol(A_b, S) over the batch would give (reference include/chol.hpp:750)."""
+    Ax = np.ascontiguousarray(Ax, np.float64)
+    assert Ax.ndim == 2
+    nb = Ax.shape[0]
+    plan = S.plan(device)
+    Lx = np.empty((nb, S.nnz), np.float64)
+    info = np.zeros(nb, np.int32)
+    check(lib().spchol_factor_batched(plan.h, nb, ptr(Ax), ptr(Lx), ptr(info)), "chol_batched")
+    return Lx, info
+
+
 def csc_to_dense(M):                                       # chol.hpp:1449-1479 (column-major in the reference)
     D = np.zeros((M.m, M.n))
     for j in range(M.n):

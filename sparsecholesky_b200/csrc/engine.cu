@@ -100,6 +100,7 @@ struct spchol_plan {
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // device buffers
     double* dL = nullptr; double* dW = nullptr; double* dAx = nullptr; double* dLx = nullptr;
+    double *bL = nullptr, *bW = nullptr; int* binfo = nullptr; int b_chunk = 0;   // batched factorization buffers
     double* dWinv = nullptr;      // inverses of the diagonal blocks of one launch (k_potrf_inv -> k_trsm_inv)
     int* dinfo = nullptr;
     int *d_first = nullptr, *d_w = nullptr, *d_m = nullptr, *d_ld = nullptr, *d_parent = nullptr;
@@ -176,7 +177,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
     CK(cudaMemsetAsync(p->dinfo, 0x7f, sizeof(int), st));
     {
         const int64_t nb = (H.nnzA + 255) / 256;
-        k_assemble<<<static_cast<unsigned>(nb), 256, 0, st>>>(H.nnzA, p->d_a_dest, dAx, p->dL);
+        k_assemble<<<static_cast<unsigned>(nb), 256, 0, st>>>(H.nnzA, p->d_a_dest, dAx, p->dL, 0);
         ++launches;
     }
     for (const Op& op : H.ops) {
@@ -187,10 +188,10 @@ int run_numeric(spchol_plan* p, const double* dAx) {
             const int* list = p->d_small_list + op.begin;
             const unsigned g = static_cast<unsigned>(op.count);
             switch (op.threads) {
-            case 32:  k_front_small<32><<<g, 32, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo); break;
-            case 64:  k_front_small<64><<<g, 64, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo); break;
-            case 128: k_front_small<128><<<g, 128, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo); break;
-            default:  k_front_small<256><<<g, 256, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo); break;
+            case 32:  k_front_small<32><<<g, 32, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo, 0, 0); break;
+            case 64:  k_front_small<64><<<g, 64, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo, 0, 0); break;
+            case 128: k_front_small<128><<<g, 128, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo, 0, 0); break;
+            default:  k_front_small<256><<<g, 256, op.smem, st>>>(list, p->fa, p->dL, p->dW, p->dinfo, 0, 0); break;
             }
             ++launches;
         } break;
@@ -426,6 +427,9 @@ void spchol_plan_destroy(spchol_plan* p) {
     if (!p) return;
     cudaSetDevice(p->device);
     for (void* d : p->allocs) cudaFree(d);
+    if (p->bL) cudaFree(p->bL);
+    if (p->bW) cudaFree(p->bW);
+    if (p->binfo) cudaFree(p->binfo);
     for (auto& e : p->ev) if (e) cudaEventDestroy(e);
     for (auto& e : p->prof_ev) cudaEventDestroy(e);
     if (p->stream) cudaStreamDestroy(p->stream);
@@ -463,7 +467,7 @@ int spchol_export_csc_device(spchol_plan* p, double* dLx) {
     if (p->H.nnzL > INT_MAX) { set_error("nnz(L) exceeds the 32-bit CSC of the reference API"); return SPCHOL_ERANGE; }
     CK(cudaSetDevice(p->device));
     const int64_t nb = (p->H.nnzL + 255) / 256;
-    k_export<<<static_cast<unsigned>(nb), 256, 0, p->stream>>>(p->H.nnzL, p->d_l_src, p->dL, dLx);
+    k_export<<<static_cast<unsigned>(nb), 256, 0, p->stream>>>(p->H.nnzL, p->d_l_src, p->dL, dLx, 0);
     CK(cudaGetLastError());
     return 0;
 }
@@ -523,6 +527,100 @@ int spchol_factor_lbuf(spchol_plan* p, const double* Ax, double* Lbuf_host, int*
         p->last_ms[i] = ms;
     }
     return SPCHOL_OK;
+}
+
+// ---- batched numeric factorization: many value sets over one pattern (config 5) ---------------
+// Every matrix gets its own L buffer and contribution workspace (matrix-major); each launch of the
+// level program covers all matrices of the chunk (grid.y = matrix).  Patterns whose fronts all fit
+// the shared-memory front kernel only (true for 1138_bus-sized problems).
+static int batched_chunk(const spchol_plan* p) {
+    size_t fr = 0, tot = 0;
+    if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) return 1;
+    const double per = 8.0 * (static_cast<double>(p->H.lbuf_entries) + p->H.ws_entries + p->H.nnzA + p->H.nnzL) + 64;
+    const double c = 0.8 * static_cast<double>(fr) / per;
+    return static_cast<int>(std::max(1.0, std::min(c, 65535.0)));
+}
+
+static int batched_reserve(spchol_plan* p, int chunk) {
+    if (p->b_chunk >= chunk) return 0;
+    for (void* d : {static_cast<void*>(p->bL), static_cast<void*>(p->bW), static_cast<void*>(p->binfo)}) if (d) cudaFree(d);
+    p->bL = p->bW = nullptr; p->binfo = nullptr; p->b_chunk = 0;
+    CK(cudaMalloc(&p->bL, sizeof(double) * std::max<int64_t>(p->H.lbuf_entries, 1) * chunk));
+    CK(cudaMalloc(&p->bW, sizeof(double) * std::max<int64_t>(p->H.ws_entries, 1) * chunk));
+    CK(cudaMalloc(&p->binfo, sizeof(int) * chunk));
+    p->b_chunk = chunk;
+    return 0;
+}
+
+// device-resident: dAx[nbatch][nnzA] -> dLx[nbatch][nnzL] (CSC order of S), dinfo[nbatch] (0 or failing column)
+int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, double* dLx, int* dinfo) {
+    if (!p || !dAx || !dLx || !dinfo || nbatch < 0) { set_error("spchol_factor_batched_device: bad argument"); return SPCHOL_EINVAL; }
+    const HostPlan& H = p->H;
+    if (H.n_large > 0 || H.world > 1 || H.nnzL > INT_MAX) {
+        set_error("spchol_factor_batched: only single-GPU plans whose fronts all fit the shared-memory front kernel (m <= 160)");
+        return SPCHOL_EINVAL;
+    }
+    CK(cudaSetDevice(p->device));
+    cudaStream_t st = p->stream;
+    int chunk = p->b_chunk > 0 ? p->b_chunk : std::min(batched_chunk(p), std::max(nbatch, 1));
+    int rc;
+    if ((rc = batched_reserve(p, std::min(chunk, std::max(nbatch, 1))))) return rc;
+    chunk = p->b_chunk;
+    int64_t launches = 0;
+    for (int b0 = 0; b0 < nbatch; b0 += chunk) {
+        const int nb = std::min(chunk, nbatch - b0);
+        CK(cudaMemsetAsync(p->bL, 0, sizeof(double) * H.lbuf_entries * nb, st));
+        CK(cudaMemsetAsync(p->binfo, 0x7f, sizeof(int) * nb, st));
+        k_assemble<<<dim3(static_cast<unsigned>((H.nnzA + 255) / 256), nb), 256, 0, st>>>(
+            H.nnzA, p->d_a_dest, dAx + static_cast<int64_t>(b0) * H.nnzA, p->bL, H.lbuf_entries);
+        ++launches;
+        for (const Op& op : H.ops) {
+            if (op.kind != OP_SMALL) continue;
+            const int* list = p->d_small_list + op.begin;
+            const dim3 g(static_cast<unsigned>(op.count), nb);
+            switch (op.threads) {
+            case 32:  k_front_small<32><<<g, 32, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
+            case 64:  k_front_small<64><<<g, 64, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
+            case 128: k_front_small<128><<<g, 128, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
+            default:  k_front_small<256><<<g, 256, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
+            }
+            ++launches;
+        }
+        k_export<<<dim3(static_cast<unsigned>((H.nnzL + 255) / 256), nb), 256, 0, st>>>(
+            H.nnzL, p->d_l_src, p->bL, dLx + static_cast<int64_t>(b0) * H.nnzL, H.lbuf_entries);
+        k_fix_info<<<(nb + 255) / 256, 256, 0, st>>>(p->binfo, dinfo + b0, nb);
+        launches += 2;
+    }
+    CK(cudaGetLastError());
+    p->last_launches = launches;
+    return 0;
+}
+
+// host buffers: Ax[nbatch][nnzA] in, Lx[nbatch][nnzL] and info[nbatch] out; chunks sized to the free HBM
+int spchol_factor_batched(spchol_plan* p, int nbatch, const double* Ax, double* Lx, int* info) {
+    if (!p || !Ax || !Lx || !info || nbatch < 0) { set_error("spchol_factor_batched: bad argument"); return SPCHOL_EINVAL; }
+    CK(cudaSetDevice(p->device));
+    const HostPlan& H = p->H;
+    const int chunk = std::min(batched_chunk(p), std::max(nbatch, 1));
+    int rc;
+    if ((rc = batched_reserve(p, chunk))) return rc;
+    double *dA = nullptr, *dLx = nullptr; int* dI = nullptr;
+    CK(cudaMalloc(&dA, sizeof(double) * H.nnzA * p->b_chunk));
+    CK(cudaMalloc(&dLx, sizeof(double) * H.nnzL * p->b_chunk));
+    CK(cudaMalloc(&dI, sizeof(int) * p->b_chunk));
+    cudaStream_t st = p->stream;
+    for (int b0 = 0; b0 < nbatch && !rc; b0 += p->b_chunk) {
+        const int nb = std::min(p->b_chunk, nbatch - b0);
+        cudaMemcpyAsync(dA, Ax + static_cast<int64_t>(b0) * H.nnzA, sizeof(double) * H.nnzA * nb, cudaMemcpyHostToDevice, st);
+        rc = spchol_factor_batched_device(p, nb, dA, dLx, dI);
+        cudaMemcpyAsync(Lx + static_cast<int64_t>(b0) * H.nnzL, dLx, sizeof(double) * H.nnzL * nb, cudaMemcpyDeviceToHost, st);
+        cudaMemcpyAsync(info + b0, dI, sizeof(int) * nb, cudaMemcpyDeviceToHost, st);
+    }
+    cudaError_t e = cudaStreamSynchronize(st);
+    cudaFree(dA); cudaFree(dLx); cudaFree(dI);
+    if (rc) return rc;
+    if (e != cudaSuccess) { set_error(std::string("spchol_factor_batched: ") + cudaGetErrorString(e)); return SPCHOL_ECUDA; }
+    return 0;
 }
 
 int spchol_host_alloc(int64_t bytes, void** out) {

@@ -28,8 +28,10 @@ __device__ __forceinline__ int even_up_d(int v) { return (v + 1) & ~1; }
 // Replaces the csc_matrix(A, S) constructor (reference include/chol.hpp:190-217) + extract_panel
 // (:1118-1159).  HBM bound: 8 B value + 8 B map read, 8 B scattered write per entry.
 // ---------------------------------------------------------------------------------------------
+// Batched use (many value sets over one pattern): blockIdx.y = matrix, Ax / L advance by one matrix.
 __global__ void k_assemble(int64_t nnzA, const int64_t* __restrict__ a_dest,
-                           const double* __restrict__ Ax, double* __restrict__ L) {
+                           const double* __restrict__ Ax, double* __restrict__ L, int64_t lstride) {
+    Ax += blockIdx.y * nnzA; L += blockIdx.y * lstride;
     const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
     if (i < nnzA) { const int64_t d = a_dest[i]; if (d >= 0) L[d] = Ax[i]; }   // d < 0: front held by another rank
 }
@@ -37,9 +39,16 @@ __global__ void k_assemble(int64_t nnzA, const int64_t* __restrict__ a_dest,
 // gather the CSC values of L out of the supernodal panels (replaces
 // scatter_panel_column_into_L, reference include/chol.hpp:1178-1189)
 __global__ void k_export(int64_t nnzL, const int64_t* __restrict__ l_src,
-                         const double* __restrict__ L, double* __restrict__ Lx) {
+                         const double* __restrict__ L, double* __restrict__ Lx, int64_t lstride) {
+    L += blockIdx.y * lstride; Lx += blockIdx.y * nnzL;
     const int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
     if (i < nnzL) { const int64_t q = l_src[i]; Lx[i] = q >= 0 ? L[q] : 0.0; }   // q < 0: exported by another rank
+}
+
+// batched factorization: per-matrix info words (atomicMin targets preset to 0x7f7f7f7f) -> 0 or failing column
+__global__ void k_fix_info(const int* __restrict__ raw, int* __restrict__ out, int n) {
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i < n) out[i] = raw[i] == 0x7f7f7f7f ? 0 : raw[i];
 }
 
 __global__ void k_zero(const ZeroTask* __restrict__ tasks, double* __restrict__ W) {
@@ -76,8 +85,10 @@ __global__ void __launch_bounds__(256) k_copy2d(const CopyTask* __restrict__ tas
 template <int T>
 __global__ void __launch_bounds__(T) k_front_small(const int* __restrict__ list, FrontArrays fa,
                                                    double* __restrict__ L, double* __restrict__ W,
-                                                   int* __restrict__ info) {
+                                                   int* __restrict__ info, int64_t lstride, int64_t wstride) {
     extern __shared__ double F[];
+    // batched use: blockIdx.y = matrix; every matrix has its own L buffer, workspace and info word
+    L += blockIdx.y * lstride; W += blockIdx.y * wstride; info += blockIdx.y;
     const int s = list[blockIdx.x];
     const int w = fa.w[s], m = fa.m[s], ld = fa.ld[s];
     const int ldf = m | 1;

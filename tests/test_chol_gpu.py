@@ -154,3 +154,36 @@ def test_midsize_3d_large_front_path():
     assert rc == 0 and (L.p == Lp).all() and (L.i == Li).all()
     assert rel_err(L.x, Lx) <= REL_TOL
     assert residual(A, L) <= RES_TOL
+
+
+def test_batched_shared_pattern_vs_oracle():
+    # config 5 in small: 48 matrices D_b A D_b over the 1138_bus pattern, one of them made indefinite
+    g = np.load(os.path.join(GOLD, "1138_bus.npz"))
+    n = int(g["n"])
+    A = sc.CscMatrix(n, g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A)
+    nbatch = 48
+    Ax = np.stack([synth.batch_values(A.p, A.i, A.x, b) for b in range(nbatch)])
+    bad = 17
+    diag_pos = A.p[1:] - 1                       # diagonal = last entry of every column of triu(A)
+    Ax[bad, diag_pos[500]] = -1.0
+    Lx, info = sc.chol_batched(S, Ax)
+    assert info[bad] == 501 and (np.delete(info, bad) == 0).all()
+    for b in (0, 1, 16, 18, 47):
+        rc, Lp, Li, ref = po.chol(n, A.p, A.i, Ax[b])
+        assert rc == 0
+        assert rel_err(Lx[b], ref) <= REL_TOL
+    # same numbers as the one-matrix path (identical kernels and summation order)
+    L1 = sc.chol(sc.CscMatrix(n, A.p, A.i, Ax[5]), S).value()
+    assert (L1.x == Lx[5]).all()
+
+
+def test_batched_refuses_large_front_patterns():
+    perm = synth.nd_perm(40, 40, 1)
+    ti, tj, tx, n = synth.laplacian_triplets(40, 40, 1, perm)
+    A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
+    S = sc.schol(A)
+    if S.plan_dryrun()["n_large"] == 0:
+        pytest.skip("pattern has no large front")
+    with pytest.raises(Exception):
+        sc.chol_batched(S, A.x[None, :])
