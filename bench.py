@@ -32,6 +32,8 @@ WORKLOADS = {
     "lap3d_32": ((32, 32, 32), "3D 7-point Laplacian 32^3, geometric ND", (32, 32, 32)),
     "lap2d_1024": ((1024, 1024, 1), "2D 5-point Laplacian 1024^2 (1.05M rows), geometric ND", (256, 256, 1)),
     "lap2d_256": ((256, 256, 1), "2D 5-point Laplacian 256^2, geometric ND", (256, 256, 1)),
+    # config 5: handled by sparsecholesky_b200/bench_batched.py
+    "batched_1138": (None, "16k SPD matrices over the 1138_bus pattern (batched numeric chol)", None),
 }
 METRIC = "fp64_factor_gflops"
 UNIT = "GFLOP/s"
@@ -166,6 +168,7 @@ def main():
     ap.add_argument("--workload", default="lap3d_128", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--nbatch", type=int, default=16384, help="batched_1138: matrices in the batch (whole job)")
     ap.add_argument("--dist-nb", type=int, default=0, help="block-column width of distributed fronts (0: library default)")
     ap.add_argument("--dist-min-w", type=int, default=0, help="narrowest front factored by a rank group (0: default)")
     args = ap.parse_args()
@@ -175,7 +178,13 @@ def main():
     local_rank = int(os.environ.get("LOCAL_RANK", "0"))
 
     if args.impl == "reference":
+        if args.workload == "batched_1138":
+            args.workload = "lap3d_128"          # the reference arm times the headline workload's bounded sample
         run_reference(args, rank)
+        return
+    if args.workload == "batched_1138":
+        from sparsecholesky_b200 import bench_batched
+        bench_batched.run(args, rank, world, local_rank, ClockSampler, METRIC, UNIT)
         return
 
     import torch
