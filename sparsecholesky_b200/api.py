@@ -256,7 +256,7 @@ def atree(S, sn_id, supernodes):
 def schol(A, relax=True):
     assert A.sym is Sym.upper
     h = C.c_void_p()
-    check(lib().spchol_symbolic_create_ex(A.n, ptr(A.p), ptr(A.i), 1 if relax else 0, C.byref(h)), "schol")
+    check(lib().spchol_symbolic_create_ex(A.n, ptr(A.p), ptr(A.i), int(relax), C.byref(h)), "schol")
     return SChol(_Handle(h, lib().spchol_symbolic_destroy), A.n)
 
 

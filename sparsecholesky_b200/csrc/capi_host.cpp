@@ -93,6 +93,11 @@ int spchol_symbolic_create_ex(int n, const int* Ap, const int* Ai, int relax, sp
     if (!s) return SPCHOL_ENOMEM;
     try {
         RelaxParams rp; rp.enable = relax != 0;
+        if (relax == 2) {      // batched use: latency bound, so trade explicit zeros for far fewer, wider fronts
+            rp.nrelax[0] = 32; rp.nrelax[1] = 96; rp.nrelax[2] = 160;
+            rp.zrelax[0] = 0.9; rp.zrelax[1] = 0.7; rp.zrelax[2] = 0.5;
+            rp.max_m = 160;
+        }
         analyze(n, Ap, Ai, rp, s->S);
     } catch (const std::bad_alloc&) { delete s; set_error("out of host memory"); return SPCHOL_ENOMEM;
     } catch (const std::exception& e) { delete s; set_error(e.what()); return SPCHOL_EINVAL; }

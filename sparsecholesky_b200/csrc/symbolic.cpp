@@ -299,7 +299,8 @@ void analyze(int n, const int* Ap, const int* Ai, const RelaxParams& rp, Symboli
             nz_new = g_zeros + g_w * (m_new - m_group_old);
             const int64_t w_new = g_w + wf;
             const double frac = static_cast<double>(nz_new) / static_cast<double>(lower_entries(w_new, m_new));
-            if (nz_new == 0) merge = true;   // nothing introduced: always merge
+            if (rp.max_m > 0 && m_new > rp.max_m) merge = false;
+            else if (nz_new == 0) merge = true;   // nothing introduced: always merge
             else if (w_new <= rp.nrelax[0]) merge = true;
             else if (w_new <= rp.nrelax[1]) merge = frac <= rp.zrelax[0];
             else if (w_new <= rp.nrelax[2]) merge = frac <= rp.zrelax[1];

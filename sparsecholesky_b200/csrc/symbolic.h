@@ -32,6 +32,7 @@ struct RelaxParams {
     int    nrelax[3] = {4, 16, 48};
     double zrelax[3] = {0.8, 0.1, 0.05};
     bool   enable = true;
+    int    max_m = 0;          // > 0: never grow a merged front beyond this many rows (keeps fronts on the shared-memory kernel)
 };
 
 // Result of the symbolic phase (what the reference's SChol carries, plus supernodes).
