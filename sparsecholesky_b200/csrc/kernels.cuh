@@ -232,56 +232,105 @@ __global__ void __launch_bounds__(PI_THREADS) k_potrf_inv(const PotrfTask* __res
     const int nmp = (nb + 7) >> 3;           // micro panels; the padded tail of the last one is an identity
     const int np8 = nmp * 8;
 
-    for (int j = warp; j < np8; j += NW)
-        for (int i = lane; i < np8; i += 32)
-            S[i + j * PB_LD] = (i >= j && i < nb && j < nb) ? D[i + static_cast<int64_t>(j) * ld] : ((i == j) ? 1.0 : 0.0);
+    // stage the block: 8 independent global loads in flight per thread (the block was just written by
+    // the previous update kernel, so every load is an L2 / HBM round trip)
+    for (int base = 0; base < np8 * PB; base += PI_THREADS * 8) {
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int idx = base + u * PI_THREADS + tid;
+            const int i = idx % PB, j = idx / PB;
+            v[u] = (j < nb && i >= j && i < nb) ? D[i + static_cast<int64_t>(j) * ld] : ((i == j) ? 1.0 : 0.0);
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int idx = base + u * PI_THREADS + tid;
+            const int i = idx % PB, j = idx / PB;
+            if (j < np8 && i < np8) S[i + j * PB_LD] = v[u];
+        }
+    }
     __syncthreads();
 
-    for (int mp = 0; mp < nmp; ++mp) {
+    // 8x8 micro Cholesky + inverse of the diagonal micro block at p, entirely in registers of ONE
+    // warp (operands are shared-memory broadcasts, no shuffles); results go to S (factor) and T
+    // (inverse).  sqrt and reciprocal of a pivot come from one rsqrt refined by a Newton step each.
+    auto micro_factor = [&](int mp) {
         const int p = mp * 8;
-        if (warp == 0) {
-            // ---- 8x8 micro Cholesky: lane r < 8 owns row r (lanes 8..31 mirror them) ---------
-            double a[8], rinv[8];
-            const int r = lane & 7;
+        double l[8][8], tm[8][8], rinv[8];
 #pragma unroll
-            for (int k = 0; k < 8; ++k) a[k] = S[(p + r) + (p + k) * PB_LD];
+        for (int i = 0; i < 8; ++i)
 #pragma unroll
-            for (int k = 0; k < 8; ++k) {
-                const double d = __shfl_sync(0xffffffffu, a[k], k);
-                if (d <= 0.0 && lane == 0 && p + k < nb) atomicMin(info, t.col0 + p + k + 1);   // reference test (chol.hpp:849)
-                const double piv = sqrt(d);
-                rinv[k] = 1.0 / piv;
-                a[k] = (r == k) ? piv : a[k] * rinv[k];
+            for (int j = 0; j <= i; ++j) l[i][j] = S[(p + i) + (p + j) * PB_LD];
 #pragma unroll
-                for (int j = k + 1; j < 8; ++j) {
-                    const double ljk = __shfl_sync(0xffffffffu, a[k], j);
-                    a[j] -= a[k] * ljk;
-                }
-            }
-            if (lane < 8) {
+        for (int k = 0; k < 8; ++k) {
+            const double d = l[k][k];
+            if (d <= 0.0 && lane == 0 && p + k < nb) atomicMin(info, t.col0 + p + k + 1);   // reference test (chol.hpp:849)
+            double y = rsqrt(d);
+            double piv = d * y;
+            piv = fma(fma(-piv, piv, d), 0.5 * y, piv);  // sqrt(d), Newton-corrected
+            y = fma(fma(-piv, y, 1.0), y, y);            // 1/piv, Newton-corrected
+            rinv[k] = y;
+            l[k][k] = piv;
 #pragma unroll
-                for (int k = 0; k < 8; ++k) if (k <= r) S[(p + r) + (p + k) * PB_LD] = a[k];
-            }
-            __syncwarp();
-            // ---- micro inverse: lane j < 8 solves L t = e_j (column j of T), no divisions -----
-            if (lane < 8) {
-                double tt[8];
+            for (int i = k + 1; i < 8; ++i) l[i][k] *= y;
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    double acc = (i == lane) ? 1.0 : 0.0;
+            for (int j = k + 1; j < 8; ++j)
 #pragma unroll
-                    for (int k = 0; k < i; ++k) acc -= S[(p + i) + (p + k) * PB_LD] * tt[k];
-                    tt[i] = (i >= lane) ? acc * rinv[i] : 0.0;
-                }
+                for (int i = j; i < 8; ++i) l[i][j] = fma(-l[i][k], l[j][k], l[i][j]);
+        }
 #pragma unroll
-                for (int i = 0; i < 8; ++i) T[mp * 64 + i + 8 * lane] = tt[i];
+        for (int j = 0; j < 8; ++j) {                  // column j of the inverse: L t = e_j
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                if (i < j) { tm[i][j] = 0.0; continue; }
+                double acc = (i == j) ? 1.0 : 0.0;
+#pragma unroll
+                for (int k = j; k < i; ++k) acc = fma(-l[i][k], tm[k][j], acc);
+                tm[i][j] = acc * rinv[i];
             }
         }
-        __syncthreads();
-        // ---- rows below the micro block: X = S[rows, p:p+8] * T^T ---------------------------
+        if (lane < 8) {                                  // lane i stores row i
+#pragma unroll
+            for (int i = 0; i < 8; ++i)
+                if (i == lane) {
+#pragma unroll
+                    for (int j = 0; j < 8; ++j) {
+                        if (j <= i) S[(p + i) + (p + j) * PB_LD] = l[i][j];
+                        T[mp * 64 + i + 8 * j] = tm[i][j];
+                    }
+                }
+        }
+    };
+    // rank-8 update of one strip of 4 columns (c0 relative to p+8) for rows rr = r_begin + lane, +32, ...
+    auto update_strip = [&](int p, int c0, int r_begin, int r_end) {
+        double xj[4][8];
+#pragma unroll
+        for (int b2 = 0; b2 < 4; ++b2)
+#pragma unroll
+            for (int k = 0; k < 8; ++k) xj[b2][k] = X[(c0 + b2) * PI_XLD + k];
+        for (int rr = r_begin + lane; rr < r_end; rr += 32) {
+            double xi[8];
+#pragma unroll
+            for (int k = 0; k < 8; ++k) xi[k] = X[rr * PI_XLD + k];
+#pragma unroll
+            for (int b2 = 0; b2 < 4; ++b2) {
+                double acc = 0.0;
+#pragma unroll
+                for (int k = 0; k < 8; ++k) acc = fma(xi[k], xj[b2][k], acc);
+                S[(p + 8 + rr) + (p + 8 + c0 + b2) * PB_LD] -= acc;   // above-diagonal entries of the strip are scratch
+            }
+        }
+    };
+
+    if (warp == 0) micro_factor(0);
+    __syncthreads();
+    for (int mp = 0; mp < nmp; ++mp) {
+        const int p = mp * 8;
         const int below = np8 - (p + 8);
-        for (int rr = tid; rr < below; rr += PI_THREADS) {
-            const int row = p + 8 + rr;
+        if (below == 0) break;
+        // ---- rows below the micro block: X = S[rows, p:p+8] * T^T (PB <= 128 < threads: a row per thread)
+        if (tid < below) {
+            const int row = p + 8 + tid;
             double b[8], x[8];
 #pragma unroll
             for (int k = 0; k < 8; ++k) b[k] = S[row + (p + k) * PB_LD];
@@ -289,35 +338,26 @@ __global__ void __launch_bounds__(PI_THREADS) k_potrf_inv(const PotrfTask* __res
             for (int j = 0; j < 8; ++j) {
                 double acc = 0.0;
 #pragma unroll
-                for (int k = 0; k <= j; ++k) acc += b[k] * T[mp * 64 + j + 8 * k];
+                for (int k = 0; k <= j; ++k) acc = fma(b[k], T[mp * 64 + j + 8 * k], acc);
                 x[j] = acc;
             }
 #pragma unroll
-            for (int j = 0; j < 8; ++j) { S[row + (p + j) * PB_LD] = x[j]; X[rr * PI_XLD + j] = x[j]; }
+            for (int j = 0; j < 8; ++j) { S[row + (p + j) * PB_LD] = x[j]; X[tid * PI_XLD + j] = x[j]; }
         }
         __syncthreads();
-        // ---- rank-8 update of the trailing lower block: a warp owns a strip of 4 columns, its
-        // lanes walk down consecutive rows (conflict-free), the strip's X rows are broadcast -----
-        const int ncs = below >> 2;                       // column strips of 4
-        for (int cs = warp; cs < ncs; cs += NW) {
-            const int c0 = cs * 4;                        // first column of the strip (relative to p+8)
-            double xj[4][8];
-#pragma unroll
-            for (int b2 = 0; b2 < 4; ++b2)
-#pragma unroll
-                for (int k = 0; k < 8; ++k) xj[b2][k] = X[(c0 + b2) * PI_XLD + k];
-            for (int rr = c0 + lane; rr < below; rr += 32) {
-                double xi[8];
-#pragma unroll
-                for (int k = 0; k < 8; ++k) xi[k] = X[rr * PI_XLD + k];
-#pragma unroll
-                for (int b2 = 0; b2 < 4; ++b2) {
-                    double acc = 0.0;
-#pragma unroll
-                    for (int k = 0; k < 8; ++k) acc += xi[k] * xj[b2][k];
-                    S[(p + 8 + rr) + (p + 8 + c0 + b2) * PB_LD] -= acc;   // above-diagonal entries of the strip are scratch
-                }
-            }
+        // ---- the next micro panel (8 columns) first, by all warps: 2 strips x up to 4 row chunks of 32
+        {
+            const int c0 = (warp & 1) * 4, chunk = warp >> 1;
+            const int rb = c0 + chunk * 32;
+            update_strip(p, c0, rb, min(rb + 32, below));
+        }
+        __syncthreads();
+        // ---- look-ahead: warp 0 factors the next diagonal micro block while the other warps finish the
+        // rank-8 update of the columns to its right (a warp owns strips of 4 columns, lanes walk down rows)
+        if (warp == 0) micro_factor(mp + 1);
+        else {
+            const int ncs = below >> 2;
+            for (int cs = 2 + (warp - 1); cs < ncs; cs += NW - 1) update_strip(p, cs * 4, cs * 4, below);
         }
         __syncthreads();
     }
@@ -333,7 +373,7 @@ __global__ void __launch_bounds__(PI_THREADS) k_potrf_inv(const PotrfTask* __res
     for (int q = warp; q < nmp; q += NW) {
         const int j = lane & 7, i0 = lane >> 3;
         for (int pb = q + 1; pb < nmp; ++pb) {
-            double acc0 = 0.0, acc1 = 0.0;
+            double acc0 = 0.0, acc1 = 0.0, acc2 = 0.0, acc3 = 0.0;      // two partial sums per entry (ILP)
 #pragma unroll
             for (int k = 0; k < 8; ++k) {                 // k in block q: W_kq = T_q
                 const double wkj = (k >= j) ? T[q * 64 + k + 8 * j] : 0.0;
@@ -342,11 +382,15 @@ __global__ void __launch_bounds__(PI_THREADS) k_potrf_inv(const PotrfTask* __res
             }
             for (int kb = q + 1; kb < pb; ++kb)
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
+                for (int k = 0; k < 8; k += 2) {
                     const double wkj = S[(q * 8 + j) + (kb * 8 + k) * PB_LD];
+                    const double wkj2 = S[(q * 8 + j) + (kb * 8 + k + 1) * PB_LD];
                     acc0 += S[(pb * 8 + i0) + (kb * 8 + k) * PB_LD] * wkj;
                     acc1 += S[(pb * 8 + i0 + 4) + (kb * 8 + k) * PB_LD] * wkj;
+                    acc2 += S[(pb * 8 + i0) + (kb * 8 + k + 1) * PB_LD] * wkj2;
+                    acc3 += S[(pb * 8 + i0 + 4) + (kb * 8 + k + 1) * PB_LD] * wkj2;
                 }
+            acc0 += acc2; acc1 += acc3;
             double w0 = 0.0, w1 = 0.0;
 #pragma unroll
             for (int k = 0; k < 8; ++k) {                 // Acc[k][j] sits in lane ((k&3)<<3)|j as acc0 (k<4) / acc1
@@ -399,13 +443,36 @@ __global__ void __launch_bounds__(256) k_trsm_inv(const TrsmTask* __restrict__ t
     const double* __restrict__ Wg = Winv + static_cast<int64_t>(t.slot) * PB_MAX * PB_MAX;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nrows = min(TI_ROWS, t.rows - row0);
-    for (int idx = tid; idx < nk * TI_ROWS; idx += 256) {
-        const int r = idx & (TI_ROWS - 1), k = idx >> 6;
-        Bs[k * TI_LDB + r] = (r < nrows && k < nb) ? B[r + static_cast<int64_t>(k) * ld] : 0.0;
+    // stage slab and inverse with 8 independent global loads in flight per thread
+    for (int base = 0; base < nk * TI_ROWS; base += 256 * 8) {
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int idx = base + u * 256 + tid;
+            const int r = idx & (TI_ROWS - 1), k = idx >> 6;
+            v[u] = (r < nrows && k < nb) ? B[r + static_cast<int64_t>(k) * ld] : 0.0;
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int idx = base + u * 256 + tid;
+            const int r = idx & (TI_ROWS - 1), k = idx >> 6;
+            if (k < nk) Bs[k * TI_LDB + r] = v[u];
+        }
     }
-    for (int idx = tid; idx < nk * PB; idx += 256) {
-        const int n = idx % PB, k = idx / PB;
-        if (n < nk) Ws[k * TI_LDW + n] = Wg[n + k * PB];
+    for (int base = 0; base < nk * PB; base += 256 * 8) {
+        double v[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int idx = base + u * 256 + tid;
+            const int n = idx % PB, k = idx / PB;
+            v[u] = (k < nk && n < nk && n >= k) ? Wg[n + k * PB] : 0.0;      // W is lower triangular
+        }
+#pragma unroll
+        for (int u = 0; u < 8; ++u) {
+            const int idx = base + u * 256 + tid;
+            const int n = idx % PB, k = idx / PB;
+            if (k < nk && n < nk) Ws[k * TI_LDW + n] = v[u];
+        }
     }
     __syncthreads();
     // 8 warps = 2 (rows) x 4 (cols): warp tile 32 x 32
