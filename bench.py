@@ -276,8 +276,15 @@ def main():
     barrier()
     peak = C.c_double(0)
     check(L.spchol_fp64_peak(local_rank, C.byref(peak)))
+    fl3 = np.zeros(3)
+    check(L.spchol_get_gemm_classes(plan_h, ptr(fl3)))
     names = ["small_fronts", "zero", "extend_add", "potrf", "trsm", "gemm_dmma", "transfers_nccl", "pack_unpack", "memset_assemble"]
+    # the DMMA update launches are timed in three K classes (profile slots 9..11)
+    kms[5] = kms[9:12].sum(); kl[5] = kl[9:12].sum()
     kind_ms = {nm: round(float(kms[i]), 3) for i, nm in enumerate(names)}
+    gemm_classes = {nm: {"ms": round(float(kms[9 + i]), 3), "launches": int(kl[9 + i]),
+                         "tflops": round(float(fl3[i] / kms[9 + i] * 1e-9), 2) if kms[9 + i] > 0 else None}
+                    for i, nm in enumerate(["K<=128", "K<=256", "K>256"])}
     gemm_ms = float(kms[5]); gemm_launches = int(kl[5])
     achieved = fl2[0] / gemm_ms * 1e-9 if gemm_ms > 0 else 0.0
     roofline = {
@@ -285,7 +292,8 @@ def main():
         "unit": "TFLOP/s", "frac": round(achieved / peak.value, 4) if peak.value else None, "traffic": None,
         "peak_source": "measured live: register-resident mma.sync.m8n8k4.f64 chains on this GPU (MEASURED_PEAKS.json has no FP64 entry)",
         "launches": gemm_launches, "avg_launch_ms": round(gemm_ms / max(gemm_launches, 1), 4),
-        "algorithmic_flops_per_step": fl2[0], "share_of_step": round(gemm_ms / max(float(kms.sum()), 1e-9), 3),
+        "algorithmic_flops_per_step": fl2[0], "share_of_step": round(gemm_ms / max(float(kms[:9].sum()), 1e-9), 3),
+        "by_K_class": gemm_classes,
         "whole_factor_frac_of_peak": round(gflops * 1e-3 / (peak.value * world), 4) if peak.value else None,
         "note": "per-rank figures of rank 0; whole_factor_frac_of_peak = value / (n_gpus * peak)" if world > 1 else None,
     }

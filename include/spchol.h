@@ -159,6 +159,8 @@ int  spchol_last_timing(const spchol_plan*, double* ms4);
  * flops2[1] = flops of their full rectangles. */
 int  spchol_set_profile(spchol_plan*, int on);
 int  spchol_get_profile(const spchol_plan*, double* kind_ms12, int64_t* kind_launches12, double* flops2);
+/* algorithmic flops of the DMMA update tasks by K class (K <= 128, <= 256, larger); their times are profile slots 9..11 */
+int  spchol_get_gemm_classes(const spchol_plan*, double* flops3);
 /* stream handle (cudaStream_t) the plan launches on, for CUDA-event timing by the caller */
 void* spchol_stream(spchol_plan*);
 /* number of kernel launches the last factorization issued */

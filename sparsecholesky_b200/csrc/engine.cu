@@ -181,7 +181,8 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         ++launches;
     }
     for (const Op& op : H.ops) {
-        mark(op.kind);
+        const int pk = op.kind == OP_GEMM ? 9 + gemm_k_class(op.threads) : op.kind;   // profile slot
+        mark(pk);
         const int64_t before = launches;
         switch (op.kind) {
         case OP_SMALL: {
@@ -256,7 +257,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
             break;
         default: break;
         }
-        if (prof) p->kind_launches[op.kind] += launches - before;
+        if (prof) p->kind_launches[pk] += launches - before;
     }
     if (p->comm && p->comm->world > 1) {      // first failing column over all ranks
         mark(8);
@@ -711,6 +712,12 @@ int spchol_get_profile(const spchol_plan* p, double* kind_ms12, int64_t* kind_la
     if (!p) return SPCHOL_EINVAL;
     for (int k = 0; k < 12; ++k) { if (kind_ms12) kind_ms12[k] = p->kind_ms[k]; if (kind_launches12) kind_launches12[k] = p->kind_launches[k]; }
     if (flops2) { flops2[0] = p->H.gemm_flops_alg; flops2[1] = p->H.gemm_flops; }
+    return 0;
+}
+// algorithmic flops of the update tasks by K class (K <= 128, <= 256, larger): profile slots 9, 10, 11
+int spchol_get_gemm_classes(const spchol_plan* p, double* flops3) {
+    if (!p || !flops3) return SPCHOL_EINVAL;
+    for (int k = 0; k < 3; ++k) flops3[k] = p->H.gemm_flops_alg_k[k];
     return 0;
 }
 

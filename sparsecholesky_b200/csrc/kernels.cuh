@@ -526,7 +526,10 @@ __global__ void __launch_bounds__(256) k_trsm_inv(const TrsmTask* __restrict__ t
 // grid = (M tiles, N tiles, tasks).
 // ---------------------------------------------------------------------------------------------
 constexpr int G_BM = 128, G_BN = 64, G_BK = 16;
-constexpr int G_LDA = G_BM + 8, G_LDB = G_BN + 8;   // == 8 (mod 16) doubles: conflict-free fragment loads
+#ifndef SPCHOL_G_PAD
+#define SPCHOL_G_PAD 8
+#endif
+constexpr int G_LDA = G_BM + SPCHOL_G_PAD, G_LDB = G_BN + SPCHOL_G_PAD;
 constexpr int G_SMEM = 2 * G_BK * (G_LDA + G_LDB) * 8;
 
 __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ tasks,
@@ -615,6 +618,118 @@ __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ 
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const int col = j0 + wn * 32 + ni * 8 + 2 * tq + e;
+                if (col < t.N && row + t.diag >= col) {
+                    double* c = C + row + static_cast<int64_t>(col) * ldc;
+                    *c -= acc[mi][ni][e];
+                }
+            }
+        }
+    }
+}
+
+// ---------------------------------------------------------------------------------------------
+// Same operation as k_gemm_dmma, asynchronous-copy pipeline: operands go global -> shared with
+// cp.async (LDGSTS, no register staging) through ST stages of K step 16, one __syncthreads per
+// step.  Tile and warp grid are template parameters; the shared leading dimensions are == 4
+// (mod 16) doubles so that the 64-bit fragment loads of a half-warp (4 k-rows x 4 consecutive
+// elements) hit 16 distinct 8-byte bank pairs.
+// ---------------------------------------------------------------------------------------------
+__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc, bool valid) {
+    const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
+    const int sz = valid ? 8 : 0;      // src-size 0: the 8 destination bytes are zero-filled
+    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz));
+}
+__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
+template <int N>
+__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
+
+constexpr int G2_BK = 16;
+template <int BM, int BN, int ST>
+constexpr int gemm2_smem() { return ST * G2_BK * (BM + 4 + BN + 4) * 8; }
+
+template <int BM, int BN, int WGM, int WGN, int ST>
+__global__ void __launch_bounds__(WGM * WGN * 32) k_gemm2(const GemmTask* __restrict__ tasks,
+                                                          double* __restrict__ L, double* __restrict__ W) {
+    constexpr int NT = WGM * WGN * 32;
+    constexpr int LDA = BM + 4, LDB = BN + 4;
+    constexpr int STAGE = G2_BK * (LDA + LDB);
+    constexpr int TM = BM / WGM, TN = BN / WGN, MI = TM / 8, NI = TN / 8;
+    static_assert((BM * G2_BK) % NT == 0 && (BN * G2_BK) % NT == 0, "tile / thread mismatch");
+    extern __shared__ double sm[];
+    const GemmTask t = tasks[blockIdx.z];
+    const int i0 = blockIdx.x * BM, j0 = blockIdx.y * BN;
+    if (i0 >= t.M || j0 >= t.N) return;
+    if (i0 + BM - 1 + t.diag < j0) return;            // tile entirely above the wanted trapezoid
+    const double* __restrict__ A = L + t.a_off + i0;
+    const double* __restrict__ B = L + t.b_off + j0;
+    double* __restrict__ C = (t.c_space ? W : L) + t.c_off;
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, tq = lane & 3;
+    const int wm = warp % WGM, wn = warp / WGM;
+    const int K = t.K, lda = t.lda, ldb = t.ldb;
+    const int mrows = t.M - i0, nrows = t.N - j0;
+
+    auto issue = [&](int stage, int kt) {
+        double* as = sm + stage * STAGE;
+        double* bs = as + G2_BK * LDA;
+#pragma unroll
+        for (int r = 0; r < (BM * G2_BK) / NT; ++r) {
+            const int e = tid + r * NT, row = e % BM, k = e / BM;
+            const bool ok = row < mrows && kt + k < K;
+            cp_async8(as + k * LDA + row, ok ? A + row + static_cast<int64_t>(kt + k) * lda : A, ok);
+        }
+#pragma unroll
+        for (int r = 0; r < (BN * G2_BK) / NT; ++r) {
+            const int e = tid + r * NT, row = e % BN, k = e / BN;
+            const bool ok = row < nrows && kt + k < K;
+            cp_async8(bs + k * LDB + row, ok ? B + row + static_cast<int64_t>(kt + k) * ldb : B, ok);
+        }
+    };
+
+    double acc[MI][NI][2];
+#pragma unroll
+    for (int mi = 0; mi < MI; ++mi)
+#pragma unroll
+        for (int ni = 0; ni < NI; ++ni) { acc[mi][ni][0] = 0.0; acc[mi][ni][1] = 0.0; }
+
+    const int nk = (K + G2_BK - 1) / G2_BK;
+#pragma unroll
+    for (int s = 0; s < ST - 1; ++s) {
+        if (s < nk) issue(s, s * G2_BK);
+        cp_async_commit();
+    }
+    for (int it = 0; it < nk; ++it) {
+        cp_async_wait<ST - 2>();
+        __syncthreads();                                   // stage `it` has landed; stage it-1 is free
+        if (it + ST - 1 < nk) issue((it + ST - 1) % ST, (it + ST - 1) * G2_BK);
+        cp_async_commit();
+        const double* a = sm + (it % ST) * STAGE + wm * TM + g;
+        const double* b = sm + (it % ST) * STAGE + G2_BK * LDA + wn * TN + g;
+#pragma unroll
+        for (int kk = 0; kk < G2_BK; kk += 4) {
+            double af[MI], bf[NI];
+#pragma unroll
+            for (int mi = 0; mi < MI; ++mi) af[mi] = a[(kk + tq) * LDA + mi * 8];
+#pragma unroll
+            for (int ni = 0; ni < NI; ++ni) bf[ni] = b[(kk + tq) * LDB + ni * 8];
+#pragma unroll
+            for (int mi = 0; mi < MI; ++mi)
+#pragma unroll
+                for (int ni = 0; ni < NI; ++ni) dmma884(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
+        }
+    }
+    cp_async_wait<0>();
+
+    const int ldc = t.ldc;
+#pragma unroll
+    for (int mi = 0; mi < MI; ++mi) {
+        const int row = i0 + wm * TM + mi * 8 + g;
+        if (row >= t.M) continue;
+#pragma unroll
+        for (int ni = 0; ni < NI; ++ni) {
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+                const int col = j0 + wn * TN + ni * 8 + 2 * tq + e;
                 if (col < t.N && row + t.diag >= col) {
                     double* c = C + row + static_cast<int64_t>(col) * ldc;
                     *c -= acc[mi][ni][e];

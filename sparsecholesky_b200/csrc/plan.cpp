@@ -297,6 +297,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     auto add_gemm = [&](Op& op, const GemmTask& ge) {
         P.gemm_tasks.push_back(ge);
         op.gx = std::max(op.gx, ge.M); op.gy = std::max(op.gy, ge.N);
+        op.threads = std::max(op.threads, ge.K);                    // OP_GEMM: largest K of the launch (profiling classes)
         P.gemm_flops += 2.0 * ge.M * ge.N * ge.K;
         // wanted entries: column j holds rows i >= j - diag
         double cnt = 0;
@@ -309,6 +310,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             cnt += (a + b) * (jlast - jfull) / 2.0;
         }
         P.gemm_flops_alg += 2.0 * cnt * ge.K;
+        P.gemm_flops_alg_k[gemm_k_class(ge.K)] += 2.0 * cnt * ge.K;
     };
     auto add_comm = [&](int kind, int lo, int cn, int root, int space, int64_t coff, int64_t count, int lv) {
         Op op{}; op.kind = OP_COMM; op.begin = static_cast<int>(P.comm_tasks.size()); op.count = 1; op.level = lv;

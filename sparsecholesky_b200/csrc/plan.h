@@ -102,10 +102,14 @@ struct HostPlan {
     int max_m = 0, max_w = 0;
     double gemm_flops = 0;           // flops of the full M x N x K rectangles of OP_GEMM tasks
     double gemm_flops_alg = 0;       // flops of the wanted (lower-trapezoid) part only
+    double gemm_flops_alg_k[3] = {0, 0, 0};   // the same split by K class of the task (gemm_k_class)
     int64_t n_dist = 0;              // fronts factored by a rank group
     int64_t comm_doubles = 0;        // doubles this rank sends or receives per factorization
     bool holds(int s) const { return own_idx[s] >= 0; }
 };
+
+// K classes of the update tasks (profiling only): inner block updates, deferred panel updates, Schur complements
+inline int gemm_k_class(int K) { return K <= 128 ? 0 : (K <= 256 ? 1 : 2); }
 
 // proportional mapping of the assembly tree onto `world` ranks (deterministic; used by build_plan)
 void map_fronts(int ns, const int* parent, const int* w, const int* m, int world, int dist_min_w,

@@ -34,8 +34,9 @@ for dims in cases:
             best = ms.copy()
     lib().spchol_set_profile(plan.h, 1)
     sc.chol(A, S) if S.nnz < 2**31 else None
-    kms = np.zeros(8); kl = np.zeros(8, np.int64); fl2 = np.zeros(2)
+    kms = np.zeros(12); kl = np.zeros(12, np.int64); fl2 = np.zeros(2)
     lib().spchol_get_profile(plan.h, ptr(kms), ptr(kl), ptr(fl2))
+    kms[5] = kms[9:12].sum(); kl[5] = kl[9:12].sum()      # DMMA updates are timed in three K classes
     lib().spchol_set_profile(plan.h, 0)
     names = ["small", "zero", "extadd", "potrf", "trsm", "gemm", "memset+asm"]
     print("   per-kind ms: " + " ".join(f"{nm}={kms[i]:.2f}({kl[i]})" for i, nm in enumerate(names)) +
