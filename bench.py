@@ -226,7 +226,7 @@ def main():
     A = make_matrix(dims)
     t_gen = time.time() - t0
     t0 = time.time()
-    S = sc.schol(A)
+    S = sc.schol(A, relax=3 if world > 1 else 1)      # relax 3: tree-parallel amalgamation (see spchol.h)
     t_sym = time.time() - t0
     t0 = time.time()
     if comm is not None:

@@ -65,7 +65,9 @@ int spchol_atree(int n, const int* parent, const int* sn_id, int ns, const int* 
 /* ---- symbolic phase: replaces schol<T>(A) (include/chol.hpp:874-946) ---------------------- */
 int     spchol_symbolic_create(int n, const int* Ap, const int* Ai, spchol_symbolic** out);
 /* same, with explicit amalgamation control: relax = 0 keeps the reference's fundamental supernodes, 1 = default,
- * 2 = aggressive chain merging capped at 160 rows per front (for spchol_factor_batched: fewer, wider fronts) */
+ * 2 = aggressive chain merging capped at 160 rows per front (for spchol_factor_batched: fewer, wider fronts),
+ * 3 = default, except that a chain of >= 1024 columns is not merged into a parent that has other children (multi-GPU
+ *     plans: keeps sibling separators as separate fronts so that proportional mapping can split the ranks evenly) */
 int     spchol_symbolic_create_ex(int n, const int* Ap, const int* Ai, int relax, spchol_symbolic** out);
 void    spchol_symbolic_destroy(spchol_symbolic*);
 int     spchol_symbolic_n(const spchol_symbolic*);

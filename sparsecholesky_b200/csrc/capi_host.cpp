@@ -98,6 +98,7 @@ int spchol_symbolic_create_ex(int n, const int* Ap, const int* Ai, int relax, sp
             rp.zrelax[0] = 0.9; rp.zrelax[1] = 0.7; rp.zrelax[2] = 0.5;
             rp.max_m = 160;
         }
+        if (relax == 3) rp.par_min_w = 1024;   // multi-GPU plans: keep wide sibling separators as fronts of their own
         analyze(n, Ap, Ai, rp, s->S);
     } catch (const std::bad_alloc&) { delete s; set_error("out of host memory"); return SPCHOL_ENOMEM;
     } catch (const std::exception& e) { delete s; set_error(e.what()); return SPCHOL_EINVAL; }

@@ -97,6 +97,8 @@ struct spchol_plan {
     int device = 0;
     HostPlan H;
     cudaStream_t stream = nullptr;
+    cudaStream_t stream2 = nullptr;                 // look-ahead stream (panel work of large fronts), high priority
+    cudaEvent_t ring[kEventRing] = {nullptr};       // OP_EV_RECORD / OP_EV_WAIT
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // device buffers
     double* dL = nullptr; double* dW = nullptr; double* dAx = nullptr; double* dLx = nullptr;
@@ -180,7 +182,17 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         k_assemble<<<static_cast<unsigned>(nb), 256, 0, st>>>(H.nnzA, p->d_a_dest, dAx, p->dL, 0);
         ++launches;
     }
+    // profiling replays the program on one stream (program order is a valid serial order)
+    cudaStream_t sts[2] = {p->stream, prof ? p->stream : p->stream2};
     for (const Op& op : H.ops) {
+        if (op.kind == OP_EV_RECORD || op.kind == OP_EV_WAIT) {
+            if (sts[0] == sts[1]) continue;
+            cudaEvent_t e = p->ring[op.begin % kEventRing];
+            if (op.kind == OP_EV_RECORD) CK(cudaEventRecord(e, sts[op.stream]));
+            else CK(cudaStreamWaitEvent(sts[op.stream], e, 0));
+            continue;
+        }
+        st = sts[op.stream];
         const int pk = op.kind == OP_GEMM ? 9 + gemm_k_class(op.threads) : op.kind;   // profile slot
         mark(pk);
         const int64_t before = launches;
@@ -199,7 +211,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         case OP_ZERO:
             for (int b = 0; b < op.count; b += 65535) {
                 const int c = std::min(op.count - b, 65535);
-                k_zero<<<dim3(256, c), 256, 0, st>>>(p->d_zero + op.begin + b, p->dW);
+                k_zero<<<dim3(std::max(1, std::min(op.gx, 1184)), c), 256, 0, st>>>(p->d_zero + op.begin + b, p->dW);
                 ++launches;
             }
             break;
@@ -259,6 +271,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         }
         if (prof) p->kind_launches[pk] += launches - before;
     }
+    st = p->stream;
     if (p->comm && p->comm->world > 1) {      // first failing column over all ranks
         mark(8);
         NCK(nccl_api()->AllReduce(p->dinfo, p->dinfo, 1, kNcclInt32, kNcclMin, p->comm->world_comm, st));
@@ -312,6 +325,8 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
         const Symbolic& S = symbolic_of(sym);
         opt.want_csc = S.nnzL <= INT_MAX ? 1 : 0;
         if (comm) { opt.rank = comm->rank; opt.world = comm->world; }
+        if (const char* la = getenv("SPCHOL_LOOKAHEAD")) opt.lookahead = atoi(la) != 0;   // development switch (A/B timing)
+        if (const char* v = getenv("SPCHOL_NB")) { const int x = atoi(v); if (x >= 128) opt.NB = x; }
         if (dist_opts) {
             if (dist_opts[0] > 0) opt.dist_NB = dist_opts[0];
             if (dist_opts[1] > 0) opt.dist_min_w = dist_opts[1];
@@ -340,6 +355,12 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
     }
     if (cudaSetDevice(device) != cudaSuccess) { set_error("cudaSetDevice failed"); return fail(SPCHOL_ECUDA); }
     if (cudaStreamCreateWithFlags(&p->stream, cudaStreamNonBlocking) != cudaSuccess) { set_error("cudaStreamCreate failed"); return fail(SPCHOL_ECUDA); }
+    {
+        int prio_lo = 0, prio_hi = 0;
+        cudaDeviceGetStreamPriorityRange(&prio_lo, &prio_hi);
+        if (cudaStreamCreateWithPriority(&p->stream2, cudaStreamNonBlocking, prio_hi) != cudaSuccess) { set_error("cudaStreamCreate failed"); return fail(SPCHOL_ECUDA); }
+        for (auto& e : p->ring) if (cudaEventCreateWithFlags(&e, cudaEventDisableTiming) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(SPCHOL_ECUDA); }
+    }
     for (auto& e : p->ev) if (cudaEventCreate(&e) != cudaSuccess) { set_error("cudaEventCreate failed"); return fail(SPCHOL_ECUDA); }
     HostPlan& H = p->H;
 #define UP(vec, ptr) if ((rc = upload(p, vec, &ptr))) return fail(rc)
@@ -433,6 +454,8 @@ void spchol_plan_destroy(spchol_plan* p) {
     if (p->binfo) cudaFree(p->binfo);
     for (auto& e : p->ev) if (e) cudaEventDestroy(e);
     for (auto& e : p->prof_ev) cudaEventDestroy(e);
+    for (auto& e : p->ring) if (e) cudaEventDestroy(e);
+    if (p->stream2) cudaStreamDestroy(p->stream2);
     if (p->stream) cudaStreamDestroy(p->stream);
     delete p;
 }

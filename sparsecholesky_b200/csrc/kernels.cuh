@@ -51,12 +51,18 @@ __global__ void k_fix_info(const int* __restrict__ raw, int* __restrict__ out, i
     if (i < n) out[i] = raw[i] == 0x7f7f7f7f ? 0 : raw[i];
 }
 
-__global__ void k_zero(const ZeroTask* __restrict__ tasks, double* __restrict__ W) {
+// grid = (slices, tasks): 16-byte stores, four in flight per thread (offsets and counts are even: the arena
+// hands out even-sized blocks and a contribution block has an even leading dimension)
+__global__ void __launch_bounds__(256) k_zero(const ZeroTask* __restrict__ tasks, double* __restrict__ W) {
     const ZeroTask t = tasks[blockIdx.y];
-    double* p = W + t.off;
-    for (int64_t i = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x; i < t.count;
-         i += static_cast<int64_t>(gridDim.x) * blockDim.x)
-        p[i] = 0.0;
+    double2* p = reinterpret_cast<double2*>(W + t.off);
+    const int64_t n2 = t.count >> 1;
+    const int64_t stride = static_cast<int64_t>(gridDim.x) * 256;
+    const double2 z = make_double2(0.0, 0.0);
+    int64_t i = blockIdx.x * static_cast<int64_t>(256) + threadIdx.x;
+    for (; i + 3 * stride < n2; i += 4 * stride) { p[i] = z; p[i + stride] = z; p[i + 2 * stride] = z; p[i + 3 * stride] = z; }
+    for (; i < n2; i += stride) p[i] = z;
+    if ((t.count & 1) && blockIdx.x == 0 && threadIdx.x == 0) W[t.off + t.count - 1] = 0.0;
 }
 
 // pack / unpack of block columns for the inter-GPU transfers: rows x cols rectangle, column-major,
@@ -183,13 +189,17 @@ __global__ void __launch_bounds__(128) k_extend_add(const int* __restrict__ list
             if (blk % G != me) continue;
         }
         const double* src = C + static_cast<int64_t>(jj) * ldc;
-        if (cj < wp) {
-            double* dst = Pp + static_cast<int64_t>(cj) * ldp;
-            for (int ii = jj + threadIdx.x; ii < mc; ii += blockDim.x) dst[r[ii]] += src[ii];
-        } else {
-            double* dst = Cp + static_cast<int64_t>(cj - wp) * ldcb - wp;
-            for (int ii = jj + threadIdx.x; ii < mc; ii += blockDim.x) dst[r[ii]] += src[ii];
+        double* dst = cj < wp ? Pp + static_cast<int64_t>(cj) * ldp : Cp + static_cast<int64_t>(cj - wp) * ldcb - wp;
+        // four independent gather / scatter-add chains per thread (the loop is latency bound otherwise)
+        const int T = blockDim.x;
+        int ii = jj + threadIdx.x;
+        for (; ii + 3 * T < mc; ii += 4 * T) {
+            const int r0 = r[ii], r1 = r[ii + T], r2 = r[ii + 2 * T], r3 = r[ii + 3 * T];
+            const double s0 = src[ii], s1 = src[ii + T], s2 = src[ii + 2 * T], s3 = src[ii + 3 * T];
+            const double d0 = dst[r0], d1 = dst[r1], d2 = dst[r2], d3 = dst[r3];
+            dst[r0] = d0 + s0; dst[r1] = d1 + s1; dst[r2] = d2 + s2; dst[r3] = d3 + s3;
         }
+        for (; ii < mc; ii += T) dst[r[ii]] += src[ii];
     }
 }
 
@@ -424,8 +434,8 @@ __global__ void __launch_bounds__(PI_THREADS) k_potrf_inv(const PotrfTask* __res
 // the result replaces the slab in place (each row depends on that row only).
 // ---------------------------------------------------------------------------------------------
 constexpr int TI_ROWS = 64;
-constexpr int TI_LDB = TI_ROWS + 8;   // == 8 (mod 16): conflict-free fragment loads
-constexpr int trsm_inv_smem(int pb) { return (pb * TI_LDB + pb * (pb + 8)) * 8; }
+constexpr int TI_LDB = TI_ROWS + 4;   // == 4 (mod 16): conflict-free fragment loads (see G_LDA)
+constexpr int trsm_inv_smem(int pb) { return (pb * TI_LDB + pb * (pb + 4)) * 8; }
 
 template <int PB>
 __global__ void __launch_bounds__(256) k_trsm_inv(const TrsmTask* __restrict__ tasks, double* __restrict__ L,
@@ -434,7 +444,7 @@ __global__ void __launch_bounds__(256) k_trsm_inv(const TrsmTask* __restrict__ t
     const TrsmTask t = tasks[blockIdx.x];
     const int row0 = blockIdx.y * TI_ROWS;
     if (row0 >= t.rows) return;
-    constexpr int TI_LDW = PB + 8;
+    constexpr int TI_LDW = PB + 4;
     double* Bs = sm;                        // Bs[k*TI_LDB + r]  : B[row0 + r][k]
     double* Ws = sm + PB * TI_LDB;          // Ws[k*TI_LDW + n]  : W[n][k]
     const int nb = t.nb, ld = t.ld;
@@ -526,8 +536,11 @@ __global__ void __launch_bounds__(256) k_trsm_inv(const TrsmTask* __restrict__ t
 // grid = (M tiles, N tiles, tasks).
 // ---------------------------------------------------------------------------------------------
 constexpr int G_BM = 128, G_BN = 64, G_BK = 16;
+// leading dimensions == 4 (mod 16) doubles: the 64-bit fragment loads of a half-warp (4 k-rows x 4 consecutive
+// elements) then cover 16 distinct 8-byte bank pairs (with == 8 the k-rows tq and tq+2 collide: measured 2x the
+// shared-memory wavefronts, -4.5 % on the largest Schur complements)
 #ifndef SPCHOL_G_PAD
-#define SPCHOL_G_PAD 8
+#define SPCHOL_G_PAD 4
 #endif
 constexpr int G_LDA = G_BM + SPCHOL_G_PAD, G_LDB = G_BN + SPCHOL_G_PAD;
 constexpr int G_SMEM = 2 * G_BK * (G_LDA + G_LDB) * 8;

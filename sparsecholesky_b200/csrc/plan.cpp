@@ -319,6 +319,18 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         P.comm_doubles += count;
     };
 
+    // stream ordering (see Op in plan.h): a record hands out a fresh event id, the wait names it
+    auto ev_record = [&](int stream, int lv) {
+        Op op{}; op.kind = OP_EV_RECORD; op.begin = P.n_events++; op.stream = stream; op.level = lv;
+        P.ops.push_back(op);
+        return op.begin;
+    };
+    auto ev_wait = [&](int stream, int ev, int lv) {
+        if (P.n_events - ev > kEventRing) throw std::runtime_error("spchol: event waited on after its ring slot was reused");
+        Op op{}; op.kind = OP_EV_WAIT; op.begin = ev; op.stream = stream; op.level = lv;
+        P.ops.push_back(op);
+    };
+
     static const int cls_m[] = {16, 24, 32, 48, 64, 96, 128, 1 << 30};
     static const int cls_thr[] = {32, 32, 64, 64, 128, 128, 256, 256};
     const int ncls = 8;
@@ -353,8 +365,10 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         P.max_potrf_slots = std::max(P.max_potrf_slots, static_cast<int>(large.size()));
         {
             Op op{}; op.kind = OP_ZERO; op.begin = static_cast<int>(P.zero_tasks.size()); op.level = lv;
-            for (int s : large) if (P.cb_off[s] >= 0) P.zero_tasks.push_back({P.cb_off[s], cb_entries(s)});
+            int64_t zmax = 0;
+            for (int s : large) if (P.cb_off[s] >= 0) { P.zero_tasks.push_back({P.cb_off[s], cb_entries(s)}); zmax = std::max(zmax, cb_entries(s)); }
             op.count = static_cast<int>(P.zero_tasks.size()) - op.begin;
+            op.gx = static_cast<int>(std::min<int64_t>((zmax + 2047) / 2048, 1184));      // slices of 2048 doubles per CTA pass
             if (op.count) P.ops.push_back(op);
         }
         int max_children = 0;
@@ -373,73 +387,99 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             op.gx = maxmb;
             if (op.count) P.ops.push_back(op);
         }
-        // per-front step sequences, merged slot by slot
-        struct Step { bool has_trsm = false, has_gemm = false; PotrfTask po; TrsmTask tr; GemmTask ge; };
-        std::vector<std::vector<Step>> seq(large.size());
-        size_t max_steps = 0;
-        for (size_t li = 0; li < large.size(); ++li) {
-            const int s = large[li];
-            const int w = P.w[s], m = P.m[s], ld = P.ld[s];
-            const int64_t po = P.panel_off[s];
-            for (int KB = 0; KB < w; KB += NB) {
-                const int KE = std::min(KB + NB, w);
-                for (int kb = KB; kb < KE; kb += nb) {
+        // Blocked right-looking factorization of the panels, all fronts of the level in lockstep.
+        // Outer step J covers the block column [KB, KE) of width NB:
+        //   panel phase  : inner blocks of width nb -- diagonal block + inverse, panel solve, update
+        //                  of the rest of the outer block (K = nb)
+        //   update phase : (a) the NEXT outer block column [KE, KE2) gets the deferred update (K = NB),
+        //                  (b) then the remaining columns [KE2, w); a front whose panel is complete
+        //                  computes its Schur complement (K = w) instead.
+        // With look-ahead the panel phase of step J+1 (stream 1) only waits for (a) of step J, so it
+        // overlaps (b) on stream 0: the latency-bound panel kernels hide behind the big updates.
+        int maxJ = 0;
+        for (int s : large) maxJ = std::max(maxJ, (P.w[s] + NB - 1) / NB);
+        const bool pipe = opt.lookahead && maxJ > 1;
+        const int sp = pipe ? 1 : 0;
+        if (pipe) { const int e = ev_record(0, lv); ev_wait(1, e, lv); }     // assembly done before the first panel
+        int ev_next = -1;
+        const int max_inner = (NB + nb - 1) / nb;
+        for (int J = 0; J < maxJ; ++J) {
+            if (pipe && ev_next >= 0) ev_wait(1, ev_next, lv);
+            for (int i = 0; i < max_inner; ++i) {
+                // diagonal blocks and panel solves, one launch per size class of the block width
+                for (int cls = 0; cls < 3; ++cls) {
+                    const int lo_nb = cls == 0 ? 0 : (cls == 1 ? 32 : 64), hi_nb = cls == 0 ? 32 : (cls == 1 ? 64 : 1 << 30);
+                    Op a{}, b{};
+                    a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.level = lv; a.threads = 32 << cls; a.stream = sp;
+                    b.kind = OP_TRSM;  b.begin = static_cast<int>(P.trsm_tasks.size());  b.level = lv; b.threads = 32 << cls; b.stream = sp;
+                    for (size_t li = 0; li < large.size(); ++li) {
+                        const int s = large[li];
+                        const int w = P.w[s], m = P.m[s], ld = P.ld[s];
+                        const int kb = J * NB + i * nb;
+                        if (kb >= w || kb >= std::min((J + 1) * NB, w)) continue;
+                        const int ke = std::min(std::min(kb + nb, (J + 1) * NB), w);
+                        if (ke - kb <= lo_nb || ke - kb > hi_nb) continue;
+                        const int64_t po = P.panel_off[s];
+                        const int64_t d = po + kb + static_cast<int64_t>(kb) * ld;
+                        P.potrf_tasks.push_back({d, ld, ke - kb, P.first[s] + kb, static_cast<int>(li)});
+                        if (ke < m) {
+                            P.trsm_tasks.push_back({po + ke + static_cast<int64_t>(kb) * ld, ld, ke - kb, m - ke, d, static_cast<int>(li)});
+                            b.gx = std::max(b.gx, m - ke);
+                        }
+                    }
+                    a.count = static_cast<int>(P.potrf_tasks.size()) - a.begin;
+                    b.count = static_cast<int>(P.trsm_tasks.size()) - b.begin;
+                    if (a.count) P.ops.push_back(a);
+                    if (b.count) P.ops.push_back(b);
+                }
+                Op c{};
+                c.kind = OP_GEMM; c.begin = static_cast<int>(P.gemm_tasks.size()); c.level = lv; c.stream = sp;
+                for (int s : large) {
+                    const int w = P.w[s], m = P.m[s], ld = P.ld[s];
+                    const int KE = std::min((J + 1) * NB, w);
+                    const int kb = J * NB + i * nb;
+                    if (kb >= KE) continue;
                     const int ke = std::min(kb + nb, KE);
-                    Step st;
-                    st.po = {po + kb + static_cast<int64_t>(kb) * ld, ld, ke - kb, P.first[s] + kb, static_cast<int>(li)};
-                    if (ke < m) {
-                        st.has_trsm = true;
-                        st.tr = {po + ke + static_cast<int64_t>(kb) * ld, ld, ke - kb, m - ke,
-                                 po + kb + static_cast<int64_t>(kb) * ld, static_cast<int>(li)};
-                    }
-                    if (ke < KE) {            // update the rest of the outer block, K = nb
-                        st.has_gemm = true;
-                        const int64_t a = po + ke + static_cast<int64_t>(kb) * ld;
-                        st.ge = {po + ke + static_cast<int64_t>(ke) * ld, a, a, ld, ld, ld,
-                                 m - ke, KE - ke, ke - kb, 0, 0};
-                    } else if (KE < w) {      // deferred update of the remaining panel, K = NB
-                        st.has_gemm = true;
-                        const int64_t a = po + KE + static_cast<int64_t>(KB) * ld;
-                        st.ge = {po + KE + static_cast<int64_t>(KE) * ld, a, a, ld, ld, ld,
-                                 m - KE, w - KE, KE - KB, 0, 0};
-                    } else if (m > w) {       // panel done: Schur complement into the cb, K = w
-                        st.has_gemm = true;
-                        const int64_t a = po + w;
-                        st.ge = {P.cb_off[s], a, a, even_up(m - w), ld, ld, m - w, m - w, w, 0, 1};
-                    }
-                    seq[li].push_back(st);
+                    if (ke >= KE) continue;               // last inner block: nothing left inside the outer block
+                    const int64_t po = P.panel_off[s];
+                    const int64_t a2 = po + ke + static_cast<int64_t>(kb) * ld;
+                    add_gemm(c, {po + ke + static_cast<int64_t>(ke) * ld, a2, a2, ld, ld, ld, m - ke, KE - ke, ke - kb, 0, 0});
                 }
+                c.count = static_cast<int>(P.gemm_tasks.size()) - c.begin;
+                if (c.count) P.ops.push_back(c);
             }
-            max_steps = std::max(max_steps, seq[li].size());
-        }
-        for (size_t i = 0; i < max_steps; ++i) {
-            // diagonal blocks and panel solves, one launch per size class of the block width
-            for (int cls = 0; cls < 3; ++cls) {
-                const int lo_nb = cls == 0 ? 0 : (cls == 1 ? 32 : 64), hi_nb = cls == 0 ? 32 : (cls == 1 ? 64 : 1 << 30);
-                Op a{}, b{};
-                a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.level = lv; a.threads = 32 << cls;
-                b.kind = OP_TRSM;  b.begin = static_cast<int>(P.trsm_tasks.size());  b.level = lv; b.threads = 32 << cls;
-                for (size_t li = 0; li < large.size(); ++li) {
-                    if (i >= seq[li].size()) continue;
-                    const Step& st = seq[li][i];
-                    if (st.po.nb <= lo_nb || st.po.nb > hi_nb) continue;
-                    P.potrf_tasks.push_back(st.po);
-                    if (st.has_trsm) { P.trsm_tasks.push_back(st.tr); b.gx = std::max(b.gx, st.tr.rows); }
+            if (pipe) { const int e = ev_record(1, lv); ev_wait(0, e, lv); }  // panels of step J are final
+            Op un{}, ur{};
+            un.kind = OP_GEMM; un.begin = static_cast<int>(P.gemm_tasks.size()); un.level = lv;
+            for (int s : large) {
+                const int w = P.w[s], m = P.m[s], ld = P.ld[s];
+                const int KB = J * NB, KE = std::min(KB + NB, w);
+                if (KB >= w || KE >= w) continue;
+                const int KE2 = std::min(KE + NB, w);
+                const int64_t po = P.panel_off[s];
+                const int64_t a2 = po + KE + static_cast<int64_t>(KB) * ld;
+                add_gemm(un, {po + KE + static_cast<int64_t>(KE) * ld, a2, a2, ld, ld, ld, m - KE, KE2 - KE, KE - KB, 0, 0});
+            }
+            un.count = static_cast<int>(P.gemm_tasks.size()) - un.begin;
+            if (un.count) P.ops.push_back(un);
+            ev_next = (pipe && un.count) ? ev_record(0, lv) : -1;
+            ur.kind = OP_GEMM; ur.begin = static_cast<int>(P.gemm_tasks.size()); ur.level = lv;
+            for (int s : large) {
+                const int w = P.w[s], m = P.m[s], ld = P.ld[s];
+                const int KB = J * NB, KE = std::min(KB + NB, w);
+                if (KB >= w) continue;
+                const int64_t po = P.panel_off[s];
+                if (KE >= w) {                           // panel complete: Schur complement into the cb, K = w
+                    if (m > w) { const int64_t a2 = po + w; add_gemm(ur, {P.cb_off[s], a2, a2, even_up(m - w), ld, ld, m - w, m - w, w, 0, 1}); }
+                    continue;
                 }
-                a.count = static_cast<int>(P.potrf_tasks.size()) - a.begin;
-                b.count = static_cast<int>(P.trsm_tasks.size()) - b.begin;
-                if (a.count) P.ops.push_back(a);
-                if (b.count) P.ops.push_back(b);
+                const int KE2 = std::min(KE + NB, w);
+                if (KE2 >= w) continue;
+                const int64_t a2 = po + KE2 + static_cast<int64_t>(KB) * ld;
+                add_gemm(ur, {po + KE2 + static_cast<int64_t>(KE2) * ld, a2, a2, ld, ld, ld, m - KE2, w - KE2, KE - KB, 0, 0});
             }
-            Op c{};
-            c.kind = OP_GEMM;  c.begin = static_cast<int>(P.gemm_tasks.size());  c.level = lv;
-            for (size_t li = 0; li < large.size(); ++li) {
-                if (i >= seq[li].size()) continue;
-                const Step& st = seq[li][i];
-                if (st.has_gemm) add_gemm(c, st.ge);
-            }
-            c.count = static_cast<int>(P.gemm_tasks.size()) - c.begin;
-            if (c.count) P.ops.push_back(c);
+            ur.count = static_cast<int>(P.gemm_tasks.size()) - ur.begin;
+            if (ur.count) P.ops.push_back(ur);
         }
     };
 
@@ -538,6 +578,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         const int64_t stage = tmp_alloc(static_cast<int64_t>(m) * std::min(DNB, w));    // packed block column in flight
         if (mb > 0) {
             Op op{}; op.kind = OP_ZERO; op.begin = static_cast<int>(P.zero_tasks.size()); op.count = 1; op.level = lv;
+            op.gx = static_cast<int>(std::min<int64_t>((cb_entries(s) + 2047) / 2048, 1184));
             P.zero_tasks.push_back({P.cb_off[s], cb_entries(s)});
             P.ops.push_back(op);
         }
@@ -549,25 +590,33 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             P.extadd_list.push_back(c);
             P.ops.push_back(op);
         }
+        // Look-ahead (see Op in plan.h): the owner of block column kb+1 applies panel kb to that
+        // block column first, then factors and broadcasts it on stream 1 while every rank is still
+        // applying panel kb to the rest of its block columns on stream 0.
+        const bool pipe = opt.lookahead && nbp > 1;
+        const int sp = pipe ? 1 : 0;
+        if (pipe) { const int e = ev_record(0, lv); ev_wait(1, e, lv); }      // assembly done before the first panel
+        int ev_next = -1;
         for (int kb = 0; kb < nbp; ++kb) {
             const int c0 = kb * DNB, c1 = std::min(c0 + DNB, w);
             const int owner = kb % G;
             if (owner == idx) {
+                if (pipe && ev_next >= 0) ev_wait(1, ev_next, lv);
                 for (int k0 = c0; k0 < c1; k0 += nb) {
                     const int k1 = std::min(k0 + nb, c1);
                     const int64_t d = po + k0 + static_cast<int64_t>(k0) * ld;
                     const int cls_pb = (k1 - k0) <= 32 ? 32 : ((k1 - k0) <= 64 ? 64 : 128);
-                    Op a{}; a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.count = 1; a.level = lv; a.threads = cls_pb;
+                    Op a{}; a.kind = OP_POTRF; a.begin = static_cast<int>(P.potrf_tasks.size()); a.count = 1; a.level = lv; a.threads = cls_pb; a.stream = sp;
                     P.potrf_tasks.push_back({d, ld, k1 - k0, P.first[s] + k0, 0});
                     P.ops.push_back(a);
                     if (k1 < m) {
                         Op b{}; b.kind = OP_TRSM; b.begin = static_cast<int>(P.trsm_tasks.size()); b.count = 1; b.level = lv;
-                        b.gx = m - k1; b.threads = cls_pb;
+                        b.gx = m - k1; b.threads = cls_pb; b.stream = sp;
                         P.trsm_tasks.push_back({po + k1 + static_cast<int64_t>(k0) * ld, ld, k1 - k0, m - k1, d, 0});
                         P.ops.push_back(b);
                     }
                     if (k1 < c1) {
-                        Op g{}; g.kind = OP_GEMM; g.begin = static_cast<int>(P.gemm_tasks.size()); g.count = 1; g.level = lv;
+                        Op g{}; g.kind = OP_GEMM; g.begin = static_cast<int>(P.gemm_tasks.size()); g.count = 1; g.level = lv; g.stream = sp;
                         const int64_t a2 = po + k1 + static_cast<int64_t>(k0) * ld;
                         add_gemm(g, {po + k1 + static_cast<int64_t>(k1) * ld, a2, a2, ld, ld, ld, m - k1, c1 - k1, k1 - k0, 0, 0});
                         P.ops.push_back(g);
@@ -578,19 +627,31 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                 const int rows = m - c0, cols = c1 - c0;
                 const int64_t src = po + c0 + static_cast<int64_t>(c0) * ld;
                 if (owner == idx) {
-                    Op cp{}; cp.kind = OP_COPY; cp.begin = static_cast<int>(P.copy_tasks.size()); cp.count = 1; cp.level = lv;
+                    Op cp{}; cp.kind = OP_COPY; cp.begin = static_cast<int>(P.copy_tasks.size()); cp.count = 1; cp.level = lv; cp.stream = sp;
                     add_copy(cp, 0, src, ld, 1, stage, rows, rows, cols);
                     P.ops.push_back(cp);
                 }
                 add_comm(COMM_BCAST, lo, G, lo + owner, 1, stage, static_cast<int64_t>(rows) * cols, lv);
+                P.ops.back().stream = sp;
                 if (owner != idx) {
-                    Op cp{}; cp.kind = OP_COPY; cp.begin = static_cast<int>(P.copy_tasks.size()); cp.count = 1; cp.level = lv;
+                    Op cp{}; cp.kind = OP_COPY; cp.begin = static_cast<int>(P.copy_tasks.size()); cp.count = 1; cp.level = lv; cp.stream = sp;
                     add_copy(cp, 1, stage, rows, 0, src, ld, rows, cols);
                     P.ops.push_back(cp);
                 }
             }
+            if (pipe) { const int e = ev_record(1, lv); ev_wait(0, e, lv); }  // panel kb is final on this rank
+            ev_next = -1;
+            if (kb + 1 < nbp && (kb + 1) % G == idx) {    // the next block column first
+                const int jb = kb + 1;
+                Op g{}; g.kind = OP_GEMM; g.begin = static_cast<int>(P.gemm_tasks.size()); g.count = 1; g.level = lv;
+                const int j0 = jb * DNB, j1 = std::min(j0 + DNB, w);
+                const int64_t a2 = po + j0 + static_cast<int64_t>(c0) * ld;
+                add_gemm(g, {po + j0 + static_cast<int64_t>(j0) * ld, a2, a2, ld, ld, ld, m - j0, j1 - j0, c1 - c0, 0, 0});
+                P.ops.push_back(g);
+                if (pipe) ev_next = ev_record(0, lv);
+            }
             Op g{}; g.kind = OP_GEMM; g.begin = static_cast<int>(P.gemm_tasks.size()); g.level = lv;
-            for (int jb = kb + 1; jb < nbp; ++jb) {
+            for (int jb = kb + 2; jb < nbp; ++jb) {
                 if (jb % G != idx) continue;
                 const int j0 = jb * DNB, j1 = std::min(j0 + DNB, w);
                 const int64_t a2 = po + j0 + static_cast<int64_t>(c0) * ld;

@@ -43,14 +43,24 @@ struct CopyTask {
     int rows, cols;
 };
 
-enum OpKind : int { OP_SMALL = 0, OP_ZERO = 1, OP_EXTADD = 2, OP_POTRF = 3, OP_TRSM = 4, OP_GEMM = 5, OP_COMM = 6, OP_COPY = 7 };
+// The program runs on two streams: stream 0 carries everything by default; with look-ahead the
+// panel work of a large front (diagonal blocks, panel solves, inner updates, and for a front
+// factored by a rank group the packing / broadcast / unpacking of the factored block column) runs
+// on stream 1 while stream 0 is still applying the previous panel to the rest of the front.
+// OP_EV_RECORD / OP_EV_WAIT order the two (begin = event id, unique per record; a wait refers to
+// the record with the same id, which precedes it in program order).  Program order is itself a
+// valid serial order, so a single-stream replay (profiling, the host simulator) is correct.
+enum OpKind : int { OP_SMALL = 0, OP_ZERO = 1, OP_EXTADD = 2, OP_POTRF = 3, OP_TRSM = 4, OP_GEMM = 5, OP_COMM = 6, OP_COPY = 7,
+                    OP_EV_RECORD = 8, OP_EV_WAIT = 9 };
+constexpr int kEventRing = 64;      // the engine keeps this many CUDA events; event id -> slot id % kEventRing
 struct Op {
     int kind;
-    int begin, count;   // slice of the task array of that kind
+    int begin, count;   // slice of the task array of that kind (OP_EV_*: begin = event id)
     int gx, gy;         // grid extents besides the task dimension
-    int threads;        // OP_SMALL: CTA size class; OP_POTRF / OP_TRSM: block-width class (32 / 64 / 128)
+    int threads;        // OP_SMALL: CTA size class; OP_POTRF / OP_TRSM: block-width class (32 / 64 / 128); OP_GEMM: largest K
     int smem;           // OP_SMALL: dynamic shared memory bytes
     int level;
+    int stream;         // 0 or 1
 };
 
 struct PlanOptions {
@@ -58,6 +68,7 @@ struct PlanOptions {
     int nb = 128;              // diagonal block of the blocked panel factorization (<= 128, the potrf kernel's limit)
     int NB = 256;              // outer block (K of the deferred panel update)
     int want_csc = 1;          // build the CSC export map (needs nnz(L) <= INT_MAX)
+    int lookahead = 1;         // 1: panel work of large fronts on stream 1, overlapped with the trailing update (see Op)
     // multi-GPU (one plan per rank, every rank builds the same global mapping):
     int rank = 0, world = 1;
     int dist_NB = 256;         // block-column width of a front that is factored by a rank group
@@ -96,6 +107,7 @@ struct HostPlan {
     std::vector<CommTask> comm_tasks;
     std::vector<CopyTask> copy_tasks;
     std::vector<Op> ops;
+    int n_events = 0;                // event ids handed out (OP_EV_RECORD count)
     int max_potrf_slots = 0;
     // statistics
     int64_t n_small = 0, n_large = 0;

@@ -281,6 +281,9 @@ void analyze(int n, const int* Ap, const int* Ai, const RelaxParams& rp, Symboli
     int64_t g_w = S.fsn_start[1] - S.fsn_start[0];
     int64_t g_zeros = 0;
     auto lower_entries = [](int64_t w, int64_t m) { return w * m - w * (w - 1) / 2; };
+    std::vector<int> nchild(rp.par_min_w > 0 ? nsf : 0, 0);
+    if (rp.par_min_w > 0)
+        for (int f = 0; f < nsf; ++f) if (S.fsn_parent[f] >= 0) ++nchild[S.fsn_parent[f]];
     auto close_group = [&](int f_end) {  // group = [g_first, f_end)
         S.sn_start.push_back(S.fsn_start[g_first]);
         S.sn_top.push_back(f_end - 1);
@@ -300,6 +303,7 @@ void analyze(int n, const int* Ap, const int* Ai, const RelaxParams& rp, Symboli
             const int64_t w_new = g_w + wf;
             const double frac = static_cast<double>(nz_new) / static_cast<double>(lower_entries(w_new, m_new));
             if (rp.max_m > 0 && m_new > rp.max_m) merge = false;
+            else if (rp.par_min_w > 0 && g_w >= rp.par_min_w && nchild[f] > 1) merge = false;
             else if (nz_new == 0) merge = true;   // nothing introduced: always merge
             else if (w_new <= rp.nrelax[0]) merge = true;
             else if (w_new <= rp.nrelax[1]) merge = frac <= rp.zrelax[0];

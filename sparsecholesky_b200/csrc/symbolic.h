@@ -33,6 +33,9 @@ struct RelaxParams {
     double zrelax[3] = {0.8, 0.1, 0.05};
     bool   enable = true;
     int    max_m = 0;          // > 0: never grow a merged front beyond this many rows (keeps fronts on the shared-memory kernel)
+    int    par_min_w = 0;      // > 0 (multi-GPU plans): a chain of >= this many columns is not merged into a parent that
+                               // has other children -- the merge is free in storage but turns two balanced subtrees
+                               // into one wide front plus unequal children, which proportional mapping cannot split evenly
 };
 
 // Result of the symbolic phase (what the reference's SChol carries, plus supernodes).

@@ -28,8 +28,13 @@ inline int even_up(int v) { return (v + 1) & ~1; }
 struct Rank {
     HostPlan H;
     std::vector<double> L, W;
-    size_t pc = 0;        // index into H.ops
+    // one program counter per stream (lane): q[s] lists the indices of the ops of stream s in program order
+    std::vector<size_t> q[2];
+    size_t pc[2] = {0, 0};
+    int cl = -1;              // lane whose head is the OP_COMM being resolved
+    std::vector<char> ev_done;   // per event id: its OP_EV_RECORD has executed
     std::vector<char> done;   // per task of the current OP_COMM (grouped sends/recvs complete in any order)
+    bool finished() const { return pc[0] >= q[0].size() && pc[1] >= q[1].size(); }
     int info = std::numeric_limits<int>::max();
 };
 
@@ -140,14 +145,18 @@ std::string describe(const CommTask& t, int rank) {
 
 }  // namespace
 
+// order: 0 = replay in program order (what a single stream does); 1 = let stream 1 run ahead as far
+// as its event waits allow; 2 = let stream 0 run ahead.  All three must give the same factor: a
+// missing event dependency in the look-ahead program shows up as a wrong result in one of them.
 extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double* Ax, int relax, int world,
-                              int dist_NB, int dist_min_w, int small_max_m, int nb, int NB,
-                              double* Lx, int* info_out, int64_t* stats /* 4: #dist fronts, #transfers, doubles moved, max ws */,
+                              int dist_NB, int dist_min_w, int small_max_m, int nb, int NB, int order,
+                              double* Lx, int* info_out, int64_t* stats /* 5: #dist fronts, #transfers, doubles moved, max ws, #stream events */,
                               char* err, int errlen) {
     auto fail = [&](const std::string& msg) { std::snprintf(err, errlen, "%s", msg.c_str()); return -1; };
     try {
         Symbolic S;
         RelaxParams rp; rp.enable = relax != 0;
+        if (relax == 3) rp.par_min_w = 8;         // tree-parallel amalgamation at test scale
         analyze(n, Ap, Ai, rp, S);
         std::vector<Rank> R(world);
         for (int r = 0; r < world; ++r) {
@@ -160,35 +169,56 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
             if (NB > 0) opt.NB = NB;
             build_plan(S, opt, R[r].H);
             const HostPlan& H = R[r].H;
+            for (size_t i = 0; i < H.ops.size(); ++i) R[r].q[H.ops[i].stream & 1].push_back(i);
+            R[r].ev_done.assign(static_cast<size_t>(H.n_events) + 1, 0);
             // poison instead of zero where the engine does not clear: the workspace is never memset
             R[r].L.assign(static_cast<size_t>(H.lbuf_entries), 0.0);
             R[r].W.assign(static_cast<size_t>(H.ws_entries), std::numeric_limits<double>::quiet_NaN());
             for (int64_t i = 0; i < H.nnzA; ++i) if (H.a_dest[i] >= 0) R[r].L[H.a_dest[i]] = Ax[i];
         }
-        if (stats) { stats[0] = stats[1] = stats[2] = stats[3] = 0; }
+        if (stats) { stats[0] = stats[1] = stats[2] = stats[3] = stats[4] = 0; }
         for (int r = 0; r < world; ++r) if (stats) {
             stats[0] = std::max<int64_t>(stats[0], R[r].H.n_dist);
             stats[1] += static_cast<int64_t>(R[r].H.comm_tasks.size());
             stats[2] += R[r].H.comm_doubles;
             stats[3] = std::max<int64_t>(stats[3], R[r].H.ws_entries);
+            stats[4] = std::max<int64_t>(stats[4], R[r].H.n_events);
         }
+        auto head = [&](const Rank& k, int lane) -> const Op* {
+            return k.pc[lane] < k.q[lane].size() ? &k.H.ops[k.q[lane][k.pc[lane]]] : nullptr;
+        };
+        // lanes of rank r in the order the policy wants them tried
+        auto lane_order = [&](const Rank& k, int* lanes) {
+            if (order == 0) {      // program order: only the lane holding the earliest pending op may move
+                const size_t i0 = k.pc[0] < k.q[0].size() ? k.q[0][k.pc[0]] : SIZE_MAX;
+                const size_t i1 = k.pc[1] < k.q[1].size() ? k.q[1][k.pc[1]] : SIZE_MAX;
+                lanes[0] = i0 <= i1 ? 0 : 1; lanes[1] = -1;
+            } else if (order == 1) { lanes[0] = 1; lanes[1] = 0; }
+            else { lanes[0] = 0; lanes[1] = 1; }
+        };
         auto comm_op = [&](int r) -> const Op* {
             Rank& k = R[r];
-            if (k.pc >= k.H.ops.size()) return nullptr;
-            const Op& op = k.H.ops[k.pc];
-            if (op.kind != OP_COMM) return nullptr;
-            if (k.done.size() != static_cast<size_t>(op.count)) k.done.assign(op.count, 0);
-            return &op;
+            int lanes[2]; lane_order(k, lanes);
+            for (int li = 0; li < 2; ++li) {
+                const int lane = lanes[li];
+                if (lane < 0) continue;
+                const Op* op = head(k, lane);
+                if (!op || op->kind != OP_COMM) continue;
+                if (k.cl != lane) { k.cl = lane; k.done.clear(); }
+                if (k.done.size() != static_cast<size_t>(op->count)) k.done.assign(op->count, 0);
+                return op;
+            }
+            return nullptr;
         };
         auto finish_if_done = [&](int r) {
             Rank& k = R[r];
             for (char d : k.done) if (!d) return;
-            k.done.clear(); ++k.pc;
+            k.done.clear(); ++k.pc[k.cl]; k.cl = -1;
         };
         auto buf = [&](int r, const CommTask& t) { return (t.space ? R[r].W.data() : R[r].L.data()) + t.off; };
         auto describe_rank = [&](int r) -> std::string {
             const Op* op = comm_op(r);
-            if (!op) return "[rank " + std::to_string(r) + (R[r].pc >= R[r].H.ops.size() ? " done]" : " busy]");
+            if (!op) return "[rank " + std::to_string(r) + (R[r].finished() ? " done]" : " busy]");
             std::string m2 = "[";
             for (int i = 0; i < op->count && i < 4; ++i) if (!R[r].done[i]) m2 += describe(R[r].H.comm_tasks[op->begin + i], r) + "; ";
             return m2 + "]";
@@ -197,8 +227,18 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
             bool progress = false, all_done = true;
             for (int r = 0; r < world; ++r) {
                 Rank& k = R[r];
-                while (k.pc < k.H.ops.size() && k.H.ops[k.pc].kind != OP_COMM) {
-                    const Op& op = k.H.ops[k.pc];
+                for (;;) {
+                    int lanes[2]; lane_order(k, lanes);
+                    int lane = -1;
+                    for (int li = 0; li < 2 && lane < 0; ++li) {
+                        if (lanes[li] < 0) continue;
+                        const Op* h = head(k, lanes[li]);
+                        if (!h || h->kind == OP_COMM) continue;
+                        if (h->kind == OP_EV_WAIT && !k.ev_done[h->begin]) continue;      // blocked on the other stream
+                        lane = lanes[li];
+                    }
+                    if (lane < 0) break;
+                    const Op& op = *head(k, lane);
                     const HostPlan& H = k.H;
                     switch (op.kind) {
                     case OP_SMALL: for (int i = 0; i < op.count; ++i) run_small(k, H.small_list[op.begin + i]); break;
@@ -215,11 +255,13 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
                             for (int j = 0; j < c.cols; ++j) for (int ii = 0; ii < c.rows; ++ii) dst[ii + static_cast<size_t>(j) * c.ldd] = src[ii + static_cast<size_t>(j) * c.lds];
                         }
                         break;
+                    case OP_EV_RECORD: k.ev_done[op.begin] = 1; break;
+                    case OP_EV_WAIT: break;
                     default: return fail("unknown op kind");
                     }
-                    ++k.pc; progress = true;
+                    ++k.pc[lane]; progress = true;
                 }
-                if (k.pc < k.H.ops.size()) all_done = false;
+                if (!k.finished()) all_done = false;
             }
             if (all_done) break;
             for (int r = 0; r < world; ++r) {
@@ -272,7 +314,7 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
                     }
                 }
             }
-            for (int r = 0; r < world; ++r) if (comm_op(r)) { const size_t before = R[r].pc; finish_if_done(r); if (R[r].pc != before) progress = true; }
+            for (int r = 0; r < world; ++r) if (comm_op(r)) { const size_t before = R[r].pc[0] + R[r].pc[1]; finish_if_done(r); if (R[r].pc[0] + R[r].pc[1] != before) progress = true; }
             if (!progress) {
                 std::string msg = "deadlock:";
                 for (int r = 0; r < world; ++r) msg += " " + describe_rank(r);

@@ -28,20 +28,30 @@ def sim():
         subprocess.run(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-o", SO] + srcs, check=True)
     L = C.CDLL(SO)
     L.plansim_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
-                                 C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_char_p, C.c_int]
+                                 C.c_int, C.c_int, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_char_p, C.c_int]
     return L
 
 
 def run_sim(L, A, world, relax=1, dist_NB=0, dist_min_w=0, small_max_m=0, nb=0, NB=0):
+    """Interprets the launch program three times: in program order (one stream), with the look-ahead
+    stream running as far ahead as its event waits allow, and with the main stream running ahead.  The
+    three factors must be identical bit for bit -- a missing event dependency between the streams
+    would reorder a read and a write and change the result."""
     S = sc.schol(A, relax=bool(relax))
-    Lx = np.empty(S.nnz)
-    info = C.c_int(0)
-    st = np.zeros(4, np.int64)
-    err = C.create_string_buffer(2048)
-    rc = L.plansim_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, relax, world, dist_NB, dist_min_w,
-                          small_max_m, nb, NB, Lx.ctypes.data, C.byref(info), st.ctypes.data, err, 2048)
-    assert rc == 0, err.value.decode()
-    return S, Lx, info.value, dict(zip(["n_dist", "transfers", "doubles", "ws"], (int(v) for v in st)))
+    out = []
+    for order in (0, 1, 2):
+        Lx = np.empty(S.nnz)
+        info = C.c_int(0)
+        st = np.zeros(5, np.int64)
+        err = C.create_string_buffer(2048)
+        rc = L.plansim_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, relax, world, dist_NB, dist_min_w,
+                              small_max_m, nb, NB, order, Lx.ctypes.data, C.byref(info), st.ctypes.data, err, 2048)
+        assert rc == 0, f"order {order}: " + err.value.decode()
+        out.append((Lx, info.value))
+    for Lx, info_v in out[1:]:
+        assert info_v == out[0][1] and np.array_equal(Lx, out[0][0], equal_nan=True), "stream interleavings disagree"
+    Lx, info = out[0]
+    return S, Lx, info, dict(zip(["n_dist", "transfers", "doubles", "ws", "events"], (int(v) for v in st)))
 
 
 def check(A, Lx, tol=1e-10):
@@ -77,6 +87,16 @@ def test_multi_rank_program_matches_oracle(sim, world, dims):
     S, Lx, info, st = run_sim(sim, A, world, dist_NB=8, dist_min_w=16, small_max_m=24, nb=8, NB=16)
     assert info == 0
     assert st["n_dist"] > 0 and st["transfers"] > 0
+    check(A, Lx)
+
+
+@pytest.mark.parametrize("world", [1, 2, 8])
+def test_lookahead_program_and_tree_parallel_amalgamation(sim, world):
+    # relax=3 keeps wide sibling separators as fronts of their own (multi-GPU mapping); the blocked
+    # fronts are wide enough (w > NB) that the two-stream look-ahead program is really emitted
+    A = lap((14, 14, 14))
+    S, Lx, info, st = run_sim(sim, A, world, relax=3, dist_NB=8, dist_min_w=16, small_max_m=24, nb=8, NB=16)
+    assert info == 0 and st["events"] > 4
     check(A, Lx)
 
 
