@@ -184,12 +184,21 @@ int run_numeric(spchol_plan* p, const double* dAx) {
     }
     // profiling replays the program on one stream (program order is a valid serial order)
     cudaStream_t sts[2] = {p->stream, prof ? p->stream : p->stream2};
+    // development aid: SPCHOL_TRACE=<file> dumps the device time of every stream event of one factorization
+    static const char* trace_path = getenv("SPCHOL_TRACE");
+    std::vector<cudaEvent_t> tev;
+    std::vector<int> tinfo;
+    cudaEvent_t t0 = nullptr;
+    if (trace_path && !prof) { cudaEventCreate(&t0); cudaEventRecord(t0, p->stream); }
     for (const Op& op : H.ops) {
         if (op.kind == OP_EV_RECORD || op.kind == OP_EV_WAIT) {
             if (sts[0] == sts[1]) continue;
             cudaEvent_t e = p->ring[op.begin % kEventRing];
-            if (op.kind == OP_EV_RECORD) CK(cudaEventRecord(e, sts[op.stream]));
-            else CK(cudaStreamWaitEvent(sts[op.stream], e, 0));
+            if (op.kind == OP_EV_RECORD) {
+                CK(cudaEventRecord(e, sts[op.stream]));
+                if (t0) { cudaEvent_t te; cudaEventCreate(&te); cudaEventRecord(te, sts[op.stream]); tev.push_back(te);
+                          tinfo.push_back(op.begin); tinfo.push_back(op.stream); tinfo.push_back(op.level); }
+            } else CK(cudaStreamWaitEvent(sts[op.stream], e, 0));
             continue;
         }
         st = sts[op.stream];
@@ -279,6 +288,20 @@ int run_numeric(spchol_plan* p, const double* dAx) {
     mark(-1);
     CK(cudaGetLastError());
     p->last_launches = launches;
+    if (t0) {
+        cudaEvent_t te; cudaEventCreate(&te); cudaEventRecord(te, p->stream); tev.push_back(te);
+        tinfo.push_back(-1); tinfo.push_back(0); tinfo.push_back(-1);
+        CK(cudaStreamSynchronize(p->stream));
+        if (FILE* f = fopen(trace_path, "w")) {
+            for (size_t i = 0; i < tev.size(); ++i) {
+                float ms = 0; cudaEventElapsedTime(&ms, t0, tev[i]);
+                fprintf(f, "%d %d %d %.4f\n", tinfo[3 * i], tinfo[3 * i + 1], tinfo[3 * i + 2], ms);
+            }
+            fclose(f);
+        }
+        for (cudaEvent_t e : tev) cudaEventDestroy(e);
+        cudaEventDestroy(t0);
+    }
     if (prof) {
         CK(cudaStreamSynchronize(st));
         for (size_t i = 0; i + 1 < pe; ++i) {
@@ -327,6 +350,8 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
         if (comm) { opt.rank = comm->rank; opt.world = comm->world; }
         if (const char* la = getenv("SPCHOL_LOOKAHEAD")) opt.lookahead = atoi(la) != 0;   // development switch (A/B timing)
         if (const char* v = getenv("SPCHOL_NB")) { const int x = atoi(v); if (x >= 128) opt.NB = x; }
+        if (const char* v = getenv("SPCHOL_NB_WIDE")) { const int x = atoi(v); if (x >= 128) opt.NB_wide = x; }
+        if (const char* v = getenv("SPCHOL_WIDE_W")) { const int x = atoi(v); if (x >= 1) opt.wide_w = x; }
         if (dist_opts) {
             if (dist_opts[0] > 0) opt.dist_NB = dist_opts[0];
             if (dist_opts[1] > 0) opt.dist_min_w = dist_opts[1];
@@ -384,6 +409,20 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
                         p->d_rel_off, p->d_rel, p->d_child_ptr, p->d_child_idx, p->d_own_n, p->d_own_idx, H.dist_NB};
     if ((rc = set_small_attr<32>()) || (rc = set_small_attr<64>()) || (rc = set_small_attr<128>()) ||
         (rc = set_small_attr<256>())) return fail(rc);
+    // The kernels that run concurrently under look-ahead all ask for the largest shared-memory carve-out: an SM
+    // cannot change its L1 / shared split while CTAs are resident, so a panel CTA (103-150 KB) could otherwise
+    // not be placed next to an update CTA on an SM configured for the update kernel's 2 x 51 KB.
+    {
+        const int mx = cudaSharedmemCarveoutMaxShared;
+        const auto A = cudaFuncAttributePreferredSharedMemoryCarveout;
+        if (cudaFuncSetAttribute(k_gemm_dmma, A, mx) != cudaSuccess ||
+            cudaFuncSetAttribute(k_potrf_inv<32>, A, mx) != cudaSuccess || cudaFuncSetAttribute(k_potrf_inv<64>, A, mx) != cudaSuccess ||
+            cudaFuncSetAttribute(k_potrf_inv<128>, A, mx) != cudaSuccess ||
+            cudaFuncSetAttribute(k_trsm_inv<32>, A, mx) != cudaSuccess || cudaFuncSetAttribute(k_trsm_inv<64>, A, mx) != cudaSuccess ||
+            cudaFuncSetAttribute(k_trsm_inv<128>, A, mx) != cudaSuccess || cudaFuncSetAttribute(k_copy2d, A, mx) != cudaSuccess) {
+            set_error("cudaFuncSetAttribute (shared memory carve-out) failed"); return fail(SPCHOL_ECUDA);
+        }
+    }
     if (cudaFuncSetAttribute(k_gemm_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(k_potrf_inv<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, potrf_inv_smem(32)) != cudaSuccess ||
         cudaFuncSetAttribute(k_potrf_inv<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, potrf_inv_smem(64)) != cudaSuccess ||

@@ -226,7 +226,7 @@ constexpr int potrf_inv_smem(int pb) { return (pb * (pb + 1) + 16 * 64 + pb * PI
 // PB = size class (32 / 64 / 128): bounds the shared memory so that the many narrow fronts of the
 // lower levels still get several CTAs per SM.  The scratch slot stores W with leading dimension PB.
 template <int PB>
-__global__ void __launch_bounds__(PI_THREADS) k_potrf_inv(const PotrfTask* __restrict__ tasks,
+__global__ void __launch_bounds__(PI_THREADS, 2) k_potrf_inv(const PotrfTask* __restrict__ tasks,
                                                           double* __restrict__ L, double* __restrict__ Winv,
                                                           int* __restrict__ info) {
     extern __shared__ double sm[];
@@ -435,7 +435,10 @@ __global__ void __launch_bounds__(PI_THREADS) k_potrf_inv(const PotrfTask* __res
 // ---------------------------------------------------------------------------------------------
 constexpr int TI_ROWS = 64;
 constexpr int TI_LDB = TI_ROWS + 4;   // == 4 (mod 16): conflict-free fragment loads (see G_LDA)
-constexpr int trsm_inv_smem(int pb) { return (pb * TI_LDB + pb * (pb + 4)) * 8; }
+constexpr int TI_KC = 32;             // W is streamed through shared memory in chunks of 32 columns (k)
+// the slab stays resident, W does not: 103 KB at PB = 128, so that a CTA of this kernel fits next to a CTA of
+// the DMMA update kernel -- with look-ahead the two run concurrently (stream 1 / stream 0)
+constexpr int trsm_inv_smem(int pb) { return (pb * TI_LDB + (pb < TI_KC ? pb : TI_KC) * (pb + 4)) * 8; }
 
 template <int PB>
 __global__ void __launch_bounds__(256) k_trsm_inv(const TrsmTask* __restrict__ tasks, double* __restrict__ L,
@@ -445,15 +448,16 @@ __global__ void __launch_bounds__(256) k_trsm_inv(const TrsmTask* __restrict__ t
     const int row0 = blockIdx.y * TI_ROWS;
     if (row0 >= t.rows) return;
     constexpr int TI_LDW = PB + 4;
+    constexpr int KC = PB < TI_KC ? PB : TI_KC;
     double* Bs = sm;                        // Bs[k*TI_LDB + r]  : B[row0 + r][k]
-    double* Ws = sm + PB * TI_LDB;          // Ws[k*TI_LDW + n]  : W[n][k]
+    double* Ws = sm + PB * TI_LDB;          // Ws[(k - k0)*TI_LDW + n]  : W[n][k], k in the current chunk
     const int nb = t.nb, ld = t.ld;
     const int nk = (nb + 7) & ~7;           // padded inner/outer extent (W is identity there, B is loaded as 0)
     double* __restrict__ B = L + t.b_off + row0;
     const double* __restrict__ Wg = Winv + static_cast<int64_t>(t.slot) * PB_MAX * PB_MAX;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int nrows = min(TI_ROWS, t.rows - row0);
-    // stage slab and inverse with 8 independent global loads in flight per thread
+    // stage the slab with 8 independent global loads in flight per thread
     for (int base = 0; base < nk * TI_ROWS; base += 256 * 8) {
         double v[8];
 #pragma unroll
@@ -469,48 +473,52 @@ __global__ void __launch_bounds__(256) k_trsm_inv(const TrsmTask* __restrict__ t
             if (k < nk) Bs[k * TI_LDB + r] = v[u];
         }
     }
-    for (int base = 0; base < nk * PB; base += 256 * 8) {
-        double v[8];
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const int idx = base + u * 256 + tid;
-            const int n = idx % PB, k = idx / PB;
-            v[u] = (k < nk && n < nk && n >= k) ? Wg[n + k * PB] : 0.0;      // W is lower triangular
-        }
-#pragma unroll
-        for (int u = 0; u < 8; ++u) {
-            const int idx = base + u * 256 + tid;
-            const int n = idx % PB, k = idx / PB;
-            if (k < nk && n < nk) Ws[k * TI_LDW + n] = v[u];
-        }
-    }
-    __syncthreads();
     // 8 warps = 2 (rows) x 4 (cols): warp tile 32 x 32
     const int g = lane >> 2, tq = lane & 3;
     const int wm = warp & 1, wn = warp >> 1;
+    const bool active = wn * 32 < nk && wn * 32 < PB;
     double acc[4][4][2];
 #pragma unroll
     for (int mi = 0; mi < 4; ++mi)
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) { acc[mi][ni][0] = 0.0; acc[mi][ni][1] = 0.0; }
-    if (wn * 32 < nk && wn * 32 < PB) {
-        const int kend = min(nk, wn * 32 + 32);          // W[n][k] = 0 for k > n
-        const double* a = Bs + wm * 32 + g;
-        const double* b = Ws + wn * 32 + g;
-        for (int kk = 0; kk < kend; kk += 4) {
-            double af[4], bf[4];
+    for (int k0 = 0; k0 < nk; k0 += KC) {
+        __syncthreads();                                  // slab staged (first pass) / previous chunk consumed
+        for (int base = 0; base < KC * PB; base += 256 * 8) {
+            double v[8];
 #pragma unroll
-            for (int mi = 0; mi < 4; ++mi) af[mi] = a[(kk + tq) * TI_LDB + mi * 8];
+            for (int u = 0; u < 8; ++u) {
+                const int idx = base + u * 256 + tid;
+                const int n = idx % PB, k = k0 + idx / PB;
+                v[u] = (idx < KC * PB && k < nk && n < nk && n >= k) ? Wg[n + k * PB] : 0.0;   // W is lower triangular
+            }
 #pragma unroll
-            for (int ni = 0; ni < 4; ++ni) bf[ni] = b[(kk + tq) * TI_LDW + ni * 8];
+            for (int u = 0; u < 8; ++u) {
+                const int idx = base + u * 256 + tid;
+                const int n = idx % PB, kc = idx / PB;
+                if (idx < KC * PB) Ws[kc * TI_LDW + n] = v[u];
+            }
+        }
+        __syncthreads();
+        if (active && k0 < wn * 32 + 32) {                // W[n][k] = 0 for k > n
+            const int kend = min(min(nk, wn * 32 + 32), k0 + KC);
+            const double* a = Bs + wm * 32 + g;
+            const double* b = Ws + wn * 32 + g;
+            for (int kk = k0; kk < kend; kk += 4) {
+                double af[4], bf[4];
 #pragma unroll
-            for (int mi = 0; mi < 4; ++mi)
+                for (int mi = 0; mi < 4; ++mi) af[mi] = a[(kk + tq) * TI_LDB + mi * 8];
 #pragma unroll
-                for (int ni = 0; ni < 4; ++ni) dmma884(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
+                for (int ni = 0; ni < 4; ++ni) bf[ni] = b[(kk - k0 + tq) * TI_LDW + ni * 8];
+#pragma unroll
+                for (int mi = 0; mi < 4; ++mi)
+#pragma unroll
+                    for (int ni = 0; ni < 4; ++ni) dmma884(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
+            }
         }
     }
     __syncthreads();                                      // everyone is done reading the slab
-    if (wn * 32 < nk && wn * 32 < PB) {
+    if (active) {
 #pragma unroll
         for (int mi = 0; mi < 4; ++mi)
 #pragma unroll

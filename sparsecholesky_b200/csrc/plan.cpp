@@ -150,7 +150,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     const int ns = S.ns, n = S.n;
     const int rank = opt.rank, world = std::max(opt.world, 1);
     if (rank < 0 || rank >= world) throw std::runtime_error("spchol: rank outside [0, world)");
-    const int nb = opt.nb, NB = std::max(opt.NB, opt.nb);
+    const int nb = opt.nb, NB_base = std::max(opt.NB, opt.nb), NB_wide = std::max(opt.NB_wide, NB_base);
     const int DNB = std::max(opt.dist_NB, 1);
     P.n = n; P.ns = ns; P.nnzA = S.nnzA; P.nnzL = S.nnzL; P.flops = S.flops;
     P.rank = rank; P.world = world; P.dist_NB = DNB;
@@ -396,7 +396,9 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         //                  computes its Schur complement (K = w) instead.
         // With look-ahead the panel phase of step J+1 (stream 1) only waits for (a) of step J, so it
         // overlaps (b) on stream 0: the latency-bound panel kernels hide behind the big updates.
-        int maxJ = 0;
+        int maxJ = 0, maxw = 0;
+        for (int s : large) maxw = std::max(maxw, P.w[s]);
+        const int NB = maxw >= opt.wide_w ? NB_wide : NB_base;
         for (int s : large) maxJ = std::max(maxJ, (P.w[s] + NB - 1) / NB);
         const bool pipe = opt.lookahead && maxJ > 1;
         const int sp = pipe ? 1 : 0;

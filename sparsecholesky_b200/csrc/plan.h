@@ -67,6 +67,9 @@ struct PlanOptions {
     int small_max_m = 160;     // fronts with m <= this are factored whole in shared memory
     int nb = 128;              // diagonal block of the blocked panel factorization (<= 128, the potrf kernel's limit)
     int NB = 256;              // outer block (K of the deferred panel update)
+    int NB_wide = 512;         // outer block of the levels whose widest front has >= wide_w columns: the deferred
+    int wide_w = 6144;         //   updates run at a longer K (measured 29 vs 23.6 TFLOP/s); narrower fronts keep NB
+                               //   because their panel phase would no longer hide behind the trailing update
     int want_csc = 1;          // build the CSC export map (needs nnz(L) <= INT_MAX)
     int lookahead = 1;         // 1: panel work of large fronts on stream 1, overlapped with the trailing update (see Op)
     // multi-GPU (one plan per rank, every rank builds the same global mapping):

@@ -166,7 +166,7 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
             if (dist_min_w > 0) opt.dist_min_w = dist_min_w;
             if (small_max_m > 0) opt.small_max_m = small_max_m;
             if (nb > 0) opt.nb = nb;
-            if (NB > 0) opt.NB = NB;
+            if (NB > 0) { opt.NB = NB; opt.NB_wide = 2 * NB; opt.wide_w = 3 * NB; }    // both outer-block widths get exercised
             build_plan(S, opt, R[r].H);
             const HostPlan& H = R[r].H;
             for (size_t i = 0; i < H.ops.size(); ++i) R[r].q[H.ops[i].stream & 1].push_back(i);

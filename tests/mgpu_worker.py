@@ -32,7 +32,7 @@ def main():
         cases.append((name, sc.CscMatrix(int(g["n"]), g["Ap"], g["Ai"], g["Ax"]), 4, 4))
     worst = 0.0
     for name, A, nb, mw in cases:
-        S = sc.schol(A)
+        S = sc.schol(A, relax=3)                  # tree-parallel amalgamation, as bench.py uses for world > 1
         plan = multigpu.DistPlan(S, comm, dist_NB=nb, dist_min_w=mw)
         st = plan.stats()
         for rep in range(2):                      # the plan is reusable
