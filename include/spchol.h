@@ -168,8 +168,11 @@ void* spchol_stream(spchol_plan*);
 /* number of kernel launches the last factorization issued */
 int64_t spchol_last_launches(const spchol_plan*);
 
-/* ||A - L L^T||_F / ||A||_F evaluated on the device over the pattern of L (exact, not sampled):
- * uses the CSC L of the last spchol_factor / export. Only for nnz(L) <= INT_MAX. */
+/* ||A - L L^T||_F / ||A||_F of the factor the plan holds (the last spchol_factor* call), for the values Ax_host
+ * that were factored.  Estimated on the device with 8 Rademacher probes z: sqrt(mean ||(A - L L^T) z||^2) / ||A||_F
+ * (E||Rz||^2 = ||R||_F^2), using two panel-times-vectors passes over the supernodal L buffer -- no CSC, so it also
+ * works when nnz(L) > INT_MAX (128^3 Laplacian), where the reference's dense comparison (tests/test_chol.cpp:87)
+ * cannot run.  Single-GPU plans. */
 int  spchol_residual(spchol_plan*, const double* Ax_host, double* rel_fro);
 
 #ifdef __cplusplus

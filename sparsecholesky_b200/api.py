@@ -275,6 +275,15 @@ def chol(A, S=None, device=0):
     return Expected(value=CscMatrix(A.n, S.p, S.i, Lx, Sym.none))
 
 
+def residual(A, S, device=0):
+    """||A - L L^T||_F / ||A||_F of the factor currently held by S's device plan (the last chol(A, S)),
+    estimated on the GPU with 8 random +-1 probes (spchol_residual; works without a CSC L)."""
+    out = C.c_double(0)
+    Ax = np.ascontiguousarray(A.x, np.float64)
+    check(lib().spchol_residual(S.plan(device).h, ptr(Ax), C.byref(out)), "residual")
+    return float(out.value)
+
+
 def chol_batched(S, Ax, device=0):
     """Config 5: numeric factorization of many matrices sharing the pattern behind S.
     Ax: (nbatch, nnz(A)) values in the CSC order of the pattern A.  Returns (Lx (nbatch, nnz(L)) in

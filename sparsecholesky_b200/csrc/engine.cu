@@ -1,6 +1,7 @@
 // Device engine + numeric C-ABI (see include/spchol.h).  No CPU fallback: every numeric entry
 // point returns SPCHOL_ENOGPU when no CUDA device is usable.
 #include <climits>
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -15,6 +16,7 @@
 #include "../../include/spchol.h"
 #include "capi_internal.h"
 #include "kernels.cuh"
+#include "residual.cuh"
 
 using namespace spchol;
 
@@ -112,6 +114,10 @@ struct spchol_plan {
     int *d_small_list = nullptr, *d_extadd_list = nullptr;
     ZeroTask* d_zero = nullptr; PotrfTask* d_potrf = nullptr; TrsmTask* d_trsm = nullptr; GemmTask* d_gemm = nullptr;
     CopyTask* d_copy = nullptr;
+    // residual check (built on first use): global row index of every below-row, task lists, A coordinates
+    int* d_rowidx = nullptr; RTask* d_rt_cols = nullptr; RTask* d_rt_rows = nullptr; int n_rt_cols = 0, n_rt_rows = 0;
+    int *d_a_row = nullptr, *d_a_col = nullptr; int* d_level_list = nullptr;
+    std::vector<int> level_ptr;
     int64_t device_bytes = 0;
     int64_t last_launches = 0;
     double last_ms[4] = {0, 0, 0, 0};
@@ -272,13 +278,15 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         case OP_COPY:
             for (int b = 0; b < op.count; b += 65535) {
                 const int c = std::min(op.count - b, 65535);
-                k_copy2d<<<dim3(c, std::max(1, std::min(op.gx, 1024))), 256, 0, st>>>(p->d_copy + op.begin + b, p->dL, p->dW);
+                k_copy2d<<<dim3(c, std::max(1, std::min(op.gx, 1024)), std::max(1, std::min(op.gy, 16))), 256, 0, st>>>(p->d_copy + op.begin + b, p->dL, p->dW);
                 ++launches;
             }
             break;
         default: break;
         }
         if (prof) p->kind_launches[pk] += launches - before;
+        if (t0) { cudaEvent_t te; cudaEventCreate(&te); cudaEventRecord(te, st); tev.push_back(te);
+                  tinfo.push_back(100 + pk); tinfo.push_back(op.stream); tinfo.push_back(op.level); }
     }
     st = p->stream;
     if (p->comm && p->comm->world > 1) {      // first failing column over all ranks
@@ -292,7 +300,9 @@ int run_numeric(spchol_plan* p, const double* dAx) {
         cudaEvent_t te; cudaEventCreate(&te); cudaEventRecord(te, p->stream); tev.push_back(te);
         tinfo.push_back(-1); tinfo.push_back(0); tinfo.push_back(-1);
         CK(cudaStreamSynchronize(p->stream));
-        if (FILE* f = fopen(trace_path, "w")) {
+        std::string tp = trace_path;
+        if (p->comm) tp += ".r" + std::to_string(p->comm->rank);
+        if (FILE* f = fopen(tp.c_str(), "w")) {
             for (size_t i = 0; i < tev.size(); ++i) {
                 float ms = 0; cudaEventElapsedTime(&ms, t0, tev[i]);
                 fprintf(f, "%d %d %d %.4f\n", tinfo[3 * i], tinfo[3 * i + 1], tinfo[3 * i + 2], ms);
@@ -786,9 +796,63 @@ int spchol_get_gemm_classes(const spchol_plan* p, double* flops3) {
 void* spchol_stream(spchol_plan* p) { return p ? static_cast<void*>(p->stream) : nullptr; }
 int64_t spchol_last_launches(const spchol_plan* p) { return p ? p->last_launches : 0; }
 
-int spchol_residual(spchol_plan*, const double*, double*) {
-    set_error("spchol_residual: not implemented yet");
-    return SPCHOL_EINVAL;
+// ||A - L L^T||_F / ||A||_F of the factor the plan holds (last spchol_factor* call), estimated with
+// NPROBE Rademacher probes on the device (residual.cuh); Ax_host = the values that were factored.
+static int residual_prepare(spchol_plan* p) {
+    if (p->d_rowidx) return 0;
+    const HostPlan& H = p->H;
+    int rc;
+    std::vector<int> order(H.ns);
+    p->level_ptr.assign(H.nlevels + 1, 0);
+    for (int s = 0; s < H.ns; ++s) ++p->level_ptr[H.level[s] + 1];
+    for (int l = 0; l < H.nlevels; ++l) p->level_ptr[l + 1] += p->level_ptr[l];
+    { std::vector<int> cur(p->level_ptr.begin(), p->level_ptr.end() - 1);
+      for (int s = 0; s < H.ns; ++s) order[cur[H.level[s]]++] = s; }
+    std::vector<RTask> tc, tr;
+    for (int s = 0; s < H.ns; ++s) {
+        for (int c0 = 0; c0 < H.w[s]; c0 += 32) tc.push_back({s, c0});
+        for (int r0 = 0; r0 < H.m[s]; r0 += 256) tr.push_back({s, r0});
+    }
+    p->n_rt_cols = static_cast<int>(tc.size()); p->n_rt_rows = static_cast<int>(tr.size());
+    if ((rc = upload(p, order, &p->d_level_list)) || (rc = upload(p, tc, &p->d_rt_cols)) || (rc = upload(p, tr, &p->d_rt_rows)) ||
+        (rc = upload(p, p->H.a_row, &p->d_a_row)) || (rc = upload(p, p->H.a_col, &p->d_a_col)) ||
+        (rc = dalloc(p, H.rel_off[H.ns], &p->d_rowidx))) return rc;
+    std::vector<int>().swap(p->H.a_row); std::vector<int>().swap(p->H.a_col);
+    for (int l = H.nlevels - 1; l >= 0; --l) {           // parents before children
+        const int cnt = p->level_ptr[l + 1] - p->level_ptr[l];
+        if (cnt) k_rowidx_level<<<std::min(cnt, 4096), 128, 0, p->stream>>>(p->d_level_list + p->level_ptr[l], cnt, p->fa, p->d_rowidx);
+    }
+    CK(cudaGetLastError());
+    return 0;
+}
+
+int spchol_residual(spchol_plan* p, const double* Ax, double* rel_fro) {
+    if (!p || !Ax || !rel_fro) { set_error("spchol_residual: null argument"); return SPCHOL_EINVAL; }
+    const HostPlan& H = p->H;
+    if (H.world > 1) { set_error("spchol_residual: single-GPU plans only"); return SPCHOL_EINVAL; }
+    CK(cudaSetDevice(p->device));
+    int rc;
+    if ((rc = residual_prepare(p))) return rc;
+    cudaStream_t st = p->stream;
+    const int64_t nv = static_cast<int64_t>(H.n) * NPROBE;
+    double *z = nullptr, *dA = nullptr;                  // z, y, u, r, 2 scalars
+    CK(cudaMalloc(&z, sizeof(double) * (4 * nv + 2)));
+    if (cudaMalloc(&dA, sizeof(double) * std::max<int64_t>(H.nnzA, 1)) != cudaSuccess) { cudaFree(z); set_error("spchol_residual: out of device memory"); return SPCHOL_ECUDA; }
+    double *y = z + nv, *u = y + nv, *r = u + nv, *scal = r + nv;
+    cudaMemcpyAsync(dA, Ax, sizeof(double) * H.nnzA, cudaMemcpyHostToDevice, st);
+    cudaMemsetAsync(scal, 0, 2 * sizeof(double), st);
+    k_probe_init<<<static_cast<unsigned>((nv + 255) / 256), 256, 0, st>>>(H.n, z, y, u, r);
+    if (p->n_rt_cols) k_lt_mult<<<p->n_rt_cols, 256, 0, st>>>(p->d_rt_cols, p->fa, p->d_rowidx, p->dL, z, y);
+    if (p->n_rt_rows) k_l_mult<<<p->n_rt_rows, 256, 0, st>>>(p->d_rt_rows, p->fa, p->d_rowidx, p->dL, y, u);
+    k_sym_mult<<<static_cast<unsigned>((H.nnzA + 255) / 256), 256, 0, st>>>(H.nnzA, p->d_a_row, p->d_a_col, dA, z, r, scal);
+    k_diff_norm<<<1184, 256, 0, st>>>(nv, r, u, scal);
+    double h[2] = {0, 0};
+    cudaMemcpyAsync(h, scal, sizeof(h), cudaMemcpyDeviceToHost, st);
+    const cudaError_t e = cudaStreamSynchronize(st);
+    cudaFree(z); cudaFree(dA);
+    if (e != cudaSuccess) { set_error(std::string("spchol_residual: ") + cudaGetErrorString(e)); return SPCHOL_ECUDA; }
+    *rel_fro = h[1] > 0 ? std::sqrt(h[0] / NPROBE / h[1]) : 0.0;
+    return SPCHOL_OK;
 }
 
 }  // extern "C"

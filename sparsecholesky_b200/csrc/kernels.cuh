@@ -72,10 +72,19 @@ __global__ void __launch_bounds__(256) k_copy2d(const CopyTask* __restrict__ tas
     const CopyTask t = tasks[blockIdx.x];
     const double* __restrict__ src = (t.src_space ? W : L) + t.src_off;
     double* __restrict__ dst = (t.dst_space ? W : L) + t.dst_off;
+    // grid.y = column slices, grid.z = row slices of 2048 (the packed block columns on the critical path of a
+    // distributed front are tall: rows x 256); four independent 8-byte copies in flight per thread
     for (int j = blockIdx.y; j < t.cols; j += gridDim.y) {
         const double* s = src + static_cast<int64_t>(j) * t.lds;
         double* d = dst + static_cast<int64_t>(j) * t.ldd;
-        for (int i = threadIdx.x; i < t.rows; i += 256) d[i] = s[i];
+        for (int i0 = blockIdx.z * 2048; i0 < t.rows; i0 += gridDim.z * 2048) {
+            const int i = i0 + threadIdx.x;
+            double v[8];
+#pragma unroll
+            for (int u = 0; u < 8; ++u) v[u] = (i + u * 256 < t.rows) ? s[i + u * 256] : 0.0;
+#pragma unroll
+            for (int u = 0; u < 8; ++u) if (i + u * 256 < t.rows) d[i + u * 256] = v[u];
+        }
     }
 }
 

@@ -252,6 +252,12 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         }
     }
 
+    if (world == 1) {
+        P.a_row.assign(S.Ai.begin(), S.Ai.end());
+        P.a_col.resize(S.nnzA);
+        for (int j = 0; j < n; ++j) for (int p = S.Ap[j]; p < S.Ap[j + 1]; ++p) P.a_col[p] = j;
+    }
+
     // CSC export map; a panel replicated over a rank group is exported by the group's first rank
     if (opt.want_csc) {
         P.l_src.resize(S.nnzL);
@@ -488,6 +494,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     auto add_copy = [&](Op& op, int sspace, int64_t soff, int lds, int dspace, int64_t doff, int ldd, int rows, int cols) {
         P.copy_tasks.push_back({soff, doff, sspace, dspace, lds, ldd, rows, cols});
         op.gx = std::max(op.gx, cols);
+        op.gy = std::max(op.gy, (rows + 2047) / 2048);          // row slices
     };
     std::vector<int64_t> tmp_allocs;          // (offset, size) pairs of transfer buffers, released at the end of the level
     auto tmp_alloc = [&](int64_t entries) {
@@ -564,7 +571,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         }
         if (!unpacks.empty()) {
             unpack.kind = OP_COPY; unpack.begin = static_cast<int>(P.copy_tasks.size()); unpack.count = static_cast<int>(unpacks.size()); unpack.level = lv;
-            for (const CopyTask& t : unpacks) { P.copy_tasks.push_back(t); unpack.gx = std::max(unpack.gx, t.cols); }
+            for (const CopyTask& t : unpacks) { P.copy_tasks.push_back(t); unpack.gx = std::max(unpack.gx, t.cols); unpack.gy = std::max(unpack.gy, (t.rows + 2047) / 2048); }
             P.ops.push_back(unpack);
         }
     };

@@ -100,6 +100,7 @@ struct HostPlan {
     // maps
     std::vector<int64_t> a_dest;     // nnzA  : L-buffer offset of each stored A entry
     std::vector<int64_t> l_src;      // nnzL  : L-buffer offset of each CSC entry of L (want_csc)
+    std::vector<int> a_row, a_col;   // nnzA  : coordinates of the stored entries of triu(A) (residual check; single-rank plans)
     // schedule
     std::vector<int> small_list;
     std::vector<int> extadd_list;    // child front ids

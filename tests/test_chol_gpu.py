@@ -156,6 +156,40 @@ def test_midsize_3d_large_front_path():
     assert residual(A, L) <= RES_TOL
 
 
+@pytest.mark.parametrize("name", ["bcsstk01", "1138_bus", "lap2d_24", "lap3d_10"])
+def test_device_residual_estimate(name):
+    """spchol_residual (8 Rademacher probes on the supernodal factor, no CSC) against the exact
+    ||A - L L^T||_F / ||A||_F computed on the host from the exported L; and its response to a wrong A."""
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    A = sc.CscMatrix(int(g["n"]), g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A)
+    L = sc.chol(A, S).value()
+    exact = residual(A, L)
+    est = sc.residual(A, S)
+    assert exact <= RES_TOL and est <= RES_TOL
+    assert est <= 50 * max(exact, 1e-17)        # rounding-level residuals: same order of magnitude
+    # a factor of A checked against 2A leaves the residual A: ||A|| / ||2A|| = 0.5
+    A2 = sc.CscMatrix(A.n, A.p, A.i, 2.0 * A.x)
+    est2 = sc.residual(A2, S)
+    assert 0.3 <= est2 <= 0.7, est2
+
+
+def test_device_residual_large_fronts():
+    # blocked large-front path (w > 256 at the root): the estimate sees every panel and the relative index chains
+    dims = (40, 40, 40)
+    perm = synth.nd_perm(*dims)
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
+    A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
+    S = sc.schol(A)
+    L = sc.chol(A, S).value()
+    assert sc.residual(A, S) <= RES_TOL
+    # perturb one diagonal value of A after the factorization: the residual must show it
+    Ax = A.x.copy(); Ax[A.p[n // 2 + 1] - 1] += 1e-3
+    est = sc.residual(sc.CscMatrix(n, A.p, A.i, Ax), S)
+    nrm = np.sqrt((A.x ** 2).sum() * 2 - 36.0 * n)            # ||A||_F of the 7-point Laplacian (diag 6, off-diag -1)
+    assert 0.3e-3 / nrm <= est <= 3e-3 / nrm, (est, 1e-3 / nrm)
+
+
 def test_batched_shared_pattern_vs_oracle():
     # config 5 in small: 48 matrices D_b A D_b over the 1138_bus pattern, one of them made indefinite
     g = np.load(os.path.join(GOLD, "1138_bus.npz"))
