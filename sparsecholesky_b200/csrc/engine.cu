@@ -105,6 +105,8 @@ struct spchol_plan {
     // device buffers
     double* dL = nullptr; double* dW = nullptr; double* dAx = nullptr; double* dLx = nullptr;
     double *bL = nullptr, *bW = nullptr; int* binfo = nullptr; int b_chunk = 0;   // batched factorization buffers
+    // batched factorization: fronts of the levels >= chain_level0 are walked by one CTA per matrix (k_front_chain)
+    int* d_chain_list = nullptr; int* d_tri_tab = nullptr; int chain_count = 0, chain_level0 = -1, chain_smem = 0; bool chain_ready = false;
     double* dWinv = nullptr;      // inverses of the diagonal blocks of one launch (k_potrf_inv -> k_trsm_inv)
     int* dinfo = nullptr;
     int *d_first = nullptr, *d_w = nullptr, *d_m = nullptr, *d_ld = nullptr, *d_parent = nullptr;
@@ -640,6 +642,28 @@ int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, 
     if ((rc = batched_reserve(p, std::min(chunk, std::max(nbatch, 1))))) return rc;
     chunk = p->b_chunk;
     int64_t launches = 0;
+    if (!p->chain_ready) {
+        // upper part of the tree = the levels from which on no level has more than 16 fronts: too few fronts per
+        // launch to fill the GPU, and mostly chains whose contribution blocks can stay on the SM
+        p->chain_ready = true;
+        std::vector<int> cnt(H.nlevels + 1, 0);
+        for (int s = 0; s < H.ns; ++s) ++cnt[H.level[s]];
+        int l0 = H.nlevels;
+        while (l0 > 0 && cnt[l0 - 1] <= 16) --l0;
+        std::vector<int> lst;
+        int mm = 0;
+        for (int s = 0; s < H.ns; ++s) if (H.level[s] >= l0) { lst.push_back(s); mm = std::max(mm, H.m[s]); }
+        const int smem = mm * (mm + 1) / 2 * 8;            // packed lower triangle
+        const char* off = getenv("SPCHOL_BATCH_CHAIN");
+        if (lst.size() >= 8 && smem <= 72 * 1024 && !(off && atoi(off) == 0)) {
+            std::vector<int> tab;
+            for (int ii = 0; static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++ii)
+                for (int jj = 0; jj <= ii && static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++jj) tab.push_back((ii << 16) | jj);
+            if ((rc = upload(p, lst, &p->d_chain_list)) || (rc = upload(p, tab, &p->d_tri_tab))) return rc;
+            p->chain_count = static_cast<int>(lst.size()); p->chain_level0 = l0; p->chain_smem = smem;
+            CK(cudaFuncSetAttribute(k_front_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
+        }
+    }
     for (int b0 = 0; b0 < nbatch; b0 += chunk) {
         const int nb = std::min(chunk, nbatch - b0);
         CK(cudaMemsetAsync(p->bL, 0, sizeof(double) * H.lbuf_entries * nb, st));
@@ -649,6 +673,7 @@ int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, 
         ++launches;
         for (const Op& op : H.ops) {
             if (op.kind != OP_SMALL) continue;
+            if (p->chain_count && op.level >= p->chain_level0) continue;      // walked by k_front_chain below
             const int* list = p->d_small_list + op.begin;
             const dim3 g(static_cast<unsigned>(op.count), nb);
             switch (op.threads) {
@@ -657,6 +682,11 @@ int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, 
             case 128: k_front_small<128><<<g, 128, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
             default:  k_front_small<256><<<g, 256, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
             }
+            ++launches;
+        }
+        if (p->chain_count) {
+            k_front_chain<<<nb, CH_T, p->chain_smem, st>>>(p->d_chain_list, p->chain_count, p->fa, p->d_tri_tab, p->bL, p->bW, p->binfo,
+                                                           H.lbuf_entries, H.ws_entries);
             ++launches;
         }
         k_export<<<dim3(static_cast<unsigned>((H.nnzL + 255) / 256), nb), 256, 0, st>>>(
