@@ -650,9 +650,13 @@ int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, 
         for (int s = 0; s < H.ns; ++s) ++cnt[H.level[s]];
         int l0 = H.nlevels;
         while (l0 > 0 && cnt[l0 - 1] <= 16) --l0;
+        // the fronts of those levels in (level, id) order: the order the level-by-level program runs them in, which is
+        // what the lifetimes of the contribution blocks in the workspace arena were planned for.  In the chain part
+        // (one front per level) a front is followed by its parent and its contribution block stays in registers.
         std::vector<int> lst;
         int mm = 0;
-        for (int s = 0; s < H.ns; ++s) if (H.level[s] >= l0) { lst.push_back(s); mm = std::max(mm, H.m[s]); }
+        for (int l = l0; l < H.nlevels; ++l)
+            for (int s = 0; s < H.ns; ++s) if (H.level[s] == l) { lst.push_back(s); mm = std::max(mm, H.m[s]); }
         const int smem = mm * (mm + 1) / 2 * 8;            // packed lower triangle
         const char* off = getenv("SPCHOL_BATCH_CHAIN");
         if (lst.size() >= 8 && smem <= 72 * 1024 && !(off && atoi(off) == 0)) {

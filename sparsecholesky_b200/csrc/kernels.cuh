@@ -227,6 +227,7 @@ __global__ void __launch_bounds__(CH_T, CH_CTAS) k_front_chain(const int* __rest
                 __syncthreads();
 #pragma unroll
                 for (int u = 0; u < CH_MAXE; ++u) {
+                    if (u * CH_T >= ne) break;          // uniform: small blocks leave the unrolled loop early
                     const int e = tid + u * CH_T;
                     if (e < ne) { const int t = __ldg(tri_tab + e); colp(srel[t & 0xffff])[srel[t >> 16]] += carry[u]; }
                 }
@@ -283,6 +284,7 @@ __global__ void __launch_bounds__(CH_T, CH_CTAS) k_front_chain(const int* __rest
             if (q + 1 < count && list[q + 1] == fa.parent[s] && ne <= CH_MAXE * CH_T) {
 #pragma unroll
                 for (int u = 0; u < CH_MAXE; ++u) {
+                    if (u * CH_T >= ne) break;
                     const int e = tid + u * CH_T;
                     if (e < ne) { const int t = __ldg(tri_tab + e); carry[u] = colp(w + (t & 0xffff))[w + (t >> 16)]; }
                 }
