@@ -287,9 +287,19 @@ def main():
                     for i, nm in enumerate(["K<=128", "K<=256", "K>256"])}
     gemm_ms = float(kms[5]); gemm_launches = int(kl[5])
     achieved = fl2[0] / gemm_ms * 1e-9 if gemm_ms > 0 else 0.0
+    # DRAM traffic of the dominant kernel per launch: from the committed `ncu --set full` capture of this command
+    # (profiles/ncu_gemm_traffic.json, written by tools/ncu_traffic.py), not measured live
+    traffic, traffic_src = None, None
+    try:
+        tj = json.load(open(os.path.join(ROOT, "profiles", "ncu_gemm_traffic.json")))
+        if tj.get("workload") == args.workload:
+            traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
+    except Exception:
+        pass
     roofline = {
         "kernel": "k_gemm_dmma", "bound": "tensor", "achieved": round(achieved, 3), "peak": round(peak.value, 3),
-        "unit": "TFLOP/s", "frac": round(achieved / peak.value, 4) if peak.value else None, "traffic": None,
+        "unit": "TFLOP/s", "frac": round(achieved / peak.value, 4) if peak.value else None, "traffic": traffic,
+        "traffic_source": traffic_src,
         "peak_source": "measured live: register-resident mma.sync.m8n8k4.f64 chains on this GPU (MEASURED_PEAKS.json has no FP64 entry)",
         "launches": gemm_launches, "avg_launch_ms": round(gemm_ms / max(gemm_launches, 1), 4),
         "algorithmic_flops_per_step": fl2[0], "share_of_step": round(gemm_ms / max(float(kms[:9].sum()), 1e-9), 3),
@@ -342,6 +352,23 @@ def main():
                  "how": "sqrt(mean_k ||(A - L L^T) z_k||^2) / ||A||_F on the device-resident supernodal factor (spchol_residual)"}
         assert out.value <= 1e-12, f"residual {out.value} exceeds the 1e-12 bound"
 
+    # consumer of the factor: x = A^-1 b on the device-resident panels (spchol_solve), checked end to end
+    solve = None
+    if world == 1:
+        import scipy.sparse as sp
+        Au = sp.csc_matrix((A.x, A.i, A.p), shape=(A.n, A.n))
+        Af = Au + sp.triu(Au, 1).T
+        xt = np.random.default_rng(1).standard_normal(A.n)
+        bv = np.asfortranarray((Af @ xt).reshape(A.n, 1))
+        xv = np.empty_like(bv, order="F")
+        check(L.spchol_solve(plan_h, bv.ctypes.data, xv.ctypes.data, 1), "spchol_solve")     # builds the task lists
+        t0 = time.perf_counter()
+        check(L.spchol_solve(plan_h, bv.ctypes.data, xv.ctypes.data, 1), "spchol_solve")
+        sec = time.perf_counter() - t0
+        solve = {"seconds_host_to_host": round(sec, 4), "nrhs": 1, "launches": int(L.spchol_last_launches(plan_h)),
+                 "rel_residual": float(np.linalg.norm(Af @ xv[:, 0] - bv[:, 0]) / np.linalg.norm(bv)),
+                 "max_abs_error_vs_known_x": float(np.abs(xv[:, 0] - xt).max())}
+
     cpu = None
     if not args.no_cpu_baseline and world == 1:
         kind, sec, fl, n_s, nnz_s = cpu_reference_time(sample)
@@ -364,7 +391,8 @@ def main():
             "metric": METRIC, "value": gflops, "unit": UNIT, "n_gpus": world, "steps": args.steps, "warmup": args.warmup,
             "ms_per_step": ms, "chol_ms": ms, "higher_is_better": True, "scaling": "strong", "vs_baseline": None,
             "dtype": "f64", "data": "synthetic", "config": cfg,
-            "roofline": roofline, "kernel_ms": kind_ms, "cpu_baseline": cpu, "e2e": e2e, "residual": resid, "gpu_launches": launches,
+            "roofline": roofline, "kernel_ms": kind_ms, "cpu_baseline": cpu, "e2e": e2e, "residual": resid, "solve": solve,
+            "gpu_launches": launches,
             "clocks": clocks,
         }
         if world > 1:

@@ -175,6 +175,11 @@ int64_t spchol_last_launches(const spchol_plan*);
  * cannot run.  Single-GPU plans. */
 int  spchol_residual(spchol_plan*, const double* Ax_host, double* rel_fro);
 
+/* x = A^-1 b with the factor the plan holds: L y = b, then L^T x = y, on the device-resident supernodal panels
+ * (level by level; L is streamed once per direction).  b, x: n x nrhs column-major host arrays (may alias).
+ * The reference stops at the factor (it has no solve); single-GPU plans. */
+int  spchol_solve(spchol_plan*, const double* b_host, double* x_host, int nrhs);
+
 #ifdef __cplusplus
 }
 #endif

@@ -71,6 +71,7 @@ SIGNATURES = {
     "spchol_stream": (_VP, [_VP]),
     "spchol_last_launches": (C.c_int64, [_VP]),
     "spchol_residual": (C.c_int, [_VP, _VP, C.POINTER(C.c_double)]),
+    "spchol_solve": (C.c_int, [_VP, _VP, _VP, C.c_int]),
 }
 
 _lib = None

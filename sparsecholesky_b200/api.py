@@ -284,6 +284,17 @@ def residual(A, S, device=0):
     return float(out.value)
 
 
+def solve(S, b, device=0):
+    """x = A^-1 b with the factor held by S's device plan (the last chol(A, S)): forward and backward
+    substitution on the supernodal factor on the GPU (spchol_solve).  b: (n,) or (n, nrhs)."""
+    b = np.asarray(b, np.float64)
+    one = b.ndim == 1
+    B = np.asfortranarray(b.reshape(S.n, -1))
+    X = np.empty_like(B, order="F")
+    check(lib().spchol_solve(S.plan(device).h, B.ctypes.data, X.ctypes.data, B.shape[1]), "solve")
+    return X[:, 0].copy() if one else X
+
+
 def chol_batched(S, Ax, device=0):
     """Config 5: numeric factorization of many matrices sharing the pattern behind S.
     Ax: (nbatch, nnz(A)) values in the CSC order of the pattern A.  Returns (Lx (nbatch, nnz(L)) in

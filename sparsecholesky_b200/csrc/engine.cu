@@ -17,6 +17,7 @@
 #include "capi_internal.h"
 #include "kernels.cuh"
 #include "residual.cuh"
+#include "solve.cuh"
 
 using namespace spchol;
 
@@ -120,6 +121,11 @@ struct spchol_plan {
     int* d_rowidx = nullptr; RTask* d_rt_cols = nullptr; RTask* d_rt_rows = nullptr; int n_rt_cols = 0, n_rt_rows = 0;
     int *d_a_row = nullptr, *d_a_col = nullptr; int* d_level_list = nullptr;
     std::vector<int> level_ptr;
+    // triangular solves (built on first use): per (level, block step) slices of the task arrays
+    struct SolveStep { int b0, bn, u0, un, g0, gn, smem; };
+    std::vector<SolveStep> solve_steps;        // forward order; the backward solve walks it in reverse
+    SBlock* d_sblocks = nullptr; SChunk* d_supd = nullptr; SChunk* d_sgat = nullptr;
+    bool solve_ready = false;
     int64_t device_bytes = 0;
     int64_t last_launches = 0;
     double last_ms[4] = {0, 0, 0, 0};
@@ -192,6 +198,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
     }
     // profiling replays the program on one stream (program order is a valid serial order)
     cudaStream_t sts[2] = {p->stream, prof ? p->stream : p->stream2};
+    static const int gemm_swizzle = getenv("SPCHOL_GEMM_SWIZZLE") ? atoi(getenv("SPCHOL_GEMM_SWIZZLE")) : 1;
     // development aid: SPCHOL_TRACE=<file> dumps the device time of every stream event of one factorization
     static const char* trace_path = getenv("SPCHOL_TRACE");
     std::vector<cudaEvent_t> tev;
@@ -253,7 +260,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
             for (int b = 0; b < op.count; b += 65535) {
                 const int c = std::min(op.count - b, 65535);
                 k_gemm_dmma<<<dim3((op.gx + G_BM - 1) / G_BM, (op.gy + G_BN - 1) / G_BN, c), 256, G_SMEM, st>>>(
-                    p->d_gemm + op.begin + b, p->dL, p->dW);
+                    p->d_gemm + op.begin + b, p->dL, p->dW, gemm_swizzle);
                 ++launches;
             }
             break;
@@ -829,6 +836,86 @@ int spchol_get_gemm_classes(const spchol_plan* p, double* flops3) {
 
 void* spchol_stream(spchol_plan* p) { return p ? static_cast<void*>(p->stream) : nullptr; }
 int64_t spchol_last_launches(const spchol_plan* p) { return p ? p->last_launches : 0; }
+
+static int residual_prepare(spchol_plan* p);
+static int solve_prepare(spchol_plan* p) {
+    if (p->solve_ready) return 0;
+    int rc;
+    if ((rc = residual_prepare(p))) return rc;       // global row indices of the fronts
+    const HostPlan& H = p->H;
+    std::vector<std::vector<int>> by_level(H.nlevels);
+    for (int s = 0; s < H.ns; ++s) by_level[H.level[s]].push_back(s);
+    std::vector<SBlock> blocks; std::vector<SChunk> upd, gat;
+    for (int l = 0; l < H.nlevels; ++l) {
+        int maxJ = 0;
+        for (int s : by_level[l]) maxJ = std::max(maxJ, (H.w[s] + SOLVE_NB - 1) / SOLVE_NB);
+        for (int j = 0; j < maxJ; ++j) {
+            spchol_plan::SolveStep st{static_cast<int>(blocks.size()), 0, static_cast<int>(upd.size()), 0, static_cast<int>(gat.size()), 0, 0};
+            int mnb = 0;
+            for (int s : by_level[l]) {
+                const int c0 = j * SOLVE_NB;
+                if (c0 >= H.w[s]) continue;
+                const int nb = std::min(SOLVE_NB, H.w[s] - c0), end = c0 + nb;
+                mnb = std::max(mnb, nb);
+                blocks.push_back({s, c0});
+                for (int r0 = end; r0 < H.m[s]; r0 += 256) upd.push_back({s, c0, r0});
+                if (end < H.m[s]) for (int cs = c0; cs < end; cs += 32) gat.push_back({s, cs, end});
+            }
+            st.bn = static_cast<int>(blocks.size()) - st.b0; st.un = static_cast<int>(upd.size()) - st.u0;
+            st.gn = static_cast<int>(gat.size()) - st.g0; st.smem = solve_diag_smem(mnb);
+            p->solve_steps.push_back(st);
+        }
+    }
+    if ((rc = upload(p, blocks, &p->d_sblocks)) || (rc = upload(p, upd, &p->d_supd)) || (rc = upload(p, gat, &p->d_sgat))) return rc;
+    CK(cudaFuncSetAttribute(k_solve_diag<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, solve_diag_smem(SOLVE_NB)));
+    CK(cudaFuncSetAttribute(k_solve_diag<true>, cudaFuncAttributeMaxDynamicSharedMemorySize, solve_diag_smem(SOLVE_NB)));
+    p->solve_ready = true;
+    return 0;
+}
+
+// x = A^-1 b with the factor the plan holds (last spchol_factor* call): L y = b, L^T x = y on the supernodal panels.
+// b, x: n x nrhs column-major host arrays (may alias).  Single-GPU plans.
+int spchol_solve(spchol_plan* p, const double* b, double* x, int nrhs) {
+    if (!p || !b || !x || nrhs < 1) { set_error("spchol_solve: bad argument"); return SPCHOL_EINVAL; }
+    const HostPlan& H = p->H;
+    if (H.world > 1) { set_error("spchol_solve: single-GPU plans only"); return SPCHOL_EINVAL; }
+    CK(cudaSetDevice(p->device));
+    int rc;
+    if ((rc = solve_prepare(p))) return rc;
+    cudaStream_t st = p->stream;
+    const int64_t nv = static_cast<int64_t>(H.n) * SOLVE_NR;
+    double* dv = nullptr;                               // [0, nv): right-hand sides / solution, [nv, 2 nv): gather sums
+    CK(cudaMalloc(&dv, sizeof(double) * 2 * nv));
+    std::vector<double> hv(static_cast<size_t>(nv));
+    int64_t launches = 0;
+    cudaError_t e = cudaSuccess;
+    for (int k0 = 0; k0 < nrhs && e == cudaSuccess; k0 += SOLVE_NR) {
+        const int nr = std::min(SOLVE_NR, nrhs - k0);
+        for (int64_t i = 0; i < H.n; ++i)
+            for (int k = 0; k < SOLVE_NR; ++k) hv[i * SOLVE_NR + k] = k < nr ? b[static_cast<int64_t>(k0 + k) * H.n + i] : 0.0;
+        cudaMemcpyAsync(dv, hv.data(), sizeof(double) * nv, cudaMemcpyHostToDevice, st);
+        cudaMemsetAsync(dv + nv, 0, sizeof(double) * nv, st);
+        for (const auto& sp : p->solve_steps) {         // L y = b
+            k_solve_diag<false><<<sp.bn, 256, sp.smem, st>>>(p->d_sblocks + sp.b0, p->fa, p->dL, dv, nullptr);
+            if (sp.un) k_solve_update<<<sp.un, 256, 0, st>>>(p->d_supd + sp.u0, p->fa, p->d_rowidx, p->dL, dv);
+            launches += 1 + (sp.un ? 1 : 0);
+        }
+        for (auto it = p->solve_steps.rbegin(); it != p->solve_steps.rend(); ++it) {     // L^T x = y
+            if (it->gn) k_solve_gather<<<it->gn, 256, 0, st>>>(p->d_sgat + it->g0, p->fa, p->d_rowidx, p->dL, dv, dv + nv);
+            k_solve_diag<true><<<it->bn, 256, it->smem, st>>>(p->d_sblocks + it->b0, p->fa, p->dL, dv, dv + nv);
+            launches += 1 + (it->gn ? 1 : 0);
+        }
+        cudaMemcpyAsync(hv.data(), dv, sizeof(double) * nv, cudaMemcpyDeviceToHost, st);
+        e = cudaStreamSynchronize(st);
+        if (e == cudaSuccess) e = cudaGetLastError();
+        for (int64_t i = 0; i < H.n && e == cudaSuccess; ++i)
+            for (int k = 0; k < nr; ++k) x[static_cast<int64_t>(k0 + k) * H.n + i] = hv[i * SOLVE_NR + k];
+    }
+    cudaFree(dv);
+    p->last_launches = launches;
+    if (e != cudaSuccess) { set_error(std::string("spchol_solve: ") + cudaGetErrorString(e)); return SPCHOL_ECUDA; }
+    return SPCHOL_OK;
+}
 
 // ||A - L L^T||_F / ||A||_F of the factor the plan holds (last spchol_factor* call), estimated with
 // NPROBE Rademacher probes on the device (residual.cuh); Ax_host = the values that were factored.

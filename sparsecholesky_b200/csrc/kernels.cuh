@@ -695,11 +695,25 @@ constexpr int G_BM = 128, G_BN = 64, G_BK = 16;
 constexpr int G_LDA = G_BM + SPCHOL_G_PAD, G_LDB = G_BN + SPCHOL_G_PAD;
 constexpr int G_SMEM = 2 * G_BK * (G_LDA + G_LDB) * 8;
 
+constexpr int G_SWZ = 8;      // CTAs are dealt to tiles in bands of 8 tile rows (see below)
 __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ tasks,
-                                                   double* __restrict__ L, double* __restrict__ W) {
+                                                   double* __restrict__ L, double* __restrict__ W, int swizzle) {
     extern __shared__ double sm[];
     const GemmTask t = tasks[blockIdx.z];
-    const int i0 = blockIdx.x * G_BM, j0 = blockIdx.y * G_BN;
+    // Tile order.  CTAs start in linear blockIdx order (x fastest); taken literally one wave of 296 CTAs covers
+    // ~2 tile columns over ALL tile rows, so every wave streams the whole A panel again (ncu, 128^3 Schur
+    // complement with K = 8192: 81 GB of DRAM reads for 2.1 GB of operands).  Dealing the linear index out in
+    // bands of G_SWZ tile rows makes a wave cover 8 x ~37 tiles: A and B rows touched per wave drop ~5x.
+    int bx = blockIdx.x, by = blockIdx.y;
+    if (swizzle) {
+        const int lin = blockIdx.x + blockIdx.y * gridDim.x;
+        const int band = lin / (G_SWZ * gridDim.y);
+        const int rows = min(G_SWZ, static_cast<int>(gridDim.x) - band * G_SWZ);
+        const int within = lin - band * G_SWZ * gridDim.y;
+        bx = band * G_SWZ + within % rows;
+        by = within / rows;
+    }
+    const int i0 = bx * G_BM, j0 = by * G_BN;
     if (i0 >= t.M || j0 >= t.N) return;
     if (i0 + G_BM - 1 + t.diag < j0) return;          // tile entirely above the wanted trapezoid
     double* As = sm;                                   // [2][G_BK][G_LDA]

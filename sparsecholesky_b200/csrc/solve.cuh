@@ -1,0 +1,167 @@
+// Triangular solves on the device-resident supernodal factor (included only by engine.cu):
+//   L y = b (fronts bottom-up, level by level), L^T x = y (top-down).
+// The reference has no solve at all; a factor that cannot be applied is of little
+// use, and the solve gives an end-to-end check ||A x - b|| / ||b|| where nnz(L) > INT_MAX rules out
+// the reference's CSC container.  Right-hand sides are processed SOLVE_NR at a time, stored
+// [n][SOLVE_NR] row-major on the device.
+//
+// Every front is cut into column blocks of SOLVE_NB: per block one CTA solves with the dense
+// diagonal block (staged in shared memory), then many CTAs stream the rows below the block
+// (HBM bound: L is read exactly once per solve direction).
+#pragma once
+#include <cstdint>
+#include <cuda_runtime.h>
+
+#include "kernels.cuh"
+#include "residual.cuh"
+
+namespace spchol {
+
+constexpr int SOLVE_NR = NPROBE;      // 8 right-hand sides per pass
+constexpr int SOLVE_NB = 128;         // column block
+struct SBlock { int s, c0; };         // front, first column of the block
+struct SChunk { int s, c0, r0; };     // + first row of a chunk of 256 rows (forward update) / unused (backward)
+constexpr int solve_diag_smem(int nb) { return (nb * (nb | 1) + nb * SOLVE_NR) * 8; }
+
+// diagonal block solve, forward (TRANS = false): y = L_jj^-1 x   or backward (TRANS = true): x = L_jj^-T (y - t)
+template <bool TRANS>
+__global__ void __launch_bounds__(256) k_solve_diag(const SBlock* __restrict__ tasks, FrontArrays fa, const double* __restrict__ L,
+                                                    double* __restrict__ b, const double* __restrict__ tsum) {
+    extern __shared__ double sm[];
+    const SBlock t = tasks[blockIdx.x];
+    const int s = t.s, w = fa.w[s], ld = fa.ld[s];
+    const int nb = min(SOLVE_NB, w - t.c0), lds = nb | 1;
+    double* S = sm;                       // S[i + j*lds] = L[c0 + i][c0 + j], i >= j
+    double* X = sm + nb * lds;            // X[i*SOLVE_NR + k]
+    const double* __restrict__ D = L + fa.panel_off[s] + t.c0 + static_cast<int64_t>(t.c0) * ld;
+    const int tid = threadIdx.x;
+    for (int idx = tid; idx < nb * nb; idx += 256) {
+        const int i = idx % nb, j = idx / nb;
+        if (i >= j) S[i + j * lds] = D[i + static_cast<int64_t>(j) * ld];
+    }
+    const int64_t g0 = static_cast<int64_t>(fa.first[s] + t.c0) * SOLVE_NR;
+    for (int idx = tid; idx < nb * SOLVE_NR; idx += 256) X[idx] = b[g0 + idx] - (TRANS ? tsum[g0 + idx] : 0.0);
+    __syncthreads();
+    // thread (i, h): row i of the block, right-hand sides 4h .. 4h+3
+    const int i = tid >> 1, h = (tid & 1) * 4;
+    double x[4];
+#pragma unroll
+    for (int k = 0; k < 4; ++k) x[k] = i < nb ? X[i * SOLVE_NR + h + k] : 0.0;
+    if (!TRANS) {
+        for (int c = 0; c < nb; ++c) {
+            if (i == c) {
+                const double d = S[c + c * lds];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { x[k] = x[k] / d; X[c * SOLVE_NR + h + k] = x[k]; }
+            }
+            __syncthreads();
+            if (i > c && i < nb) {
+                const double l = S[i + c * lds];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) x[k] = fma(-l, X[c * SOLVE_NR + h + k], x[k]);
+            }
+        }
+    } else {
+        for (int c = nb - 1; c >= 0; --c) {
+            if (i == c) {
+                const double d = S[c + c * lds];
+#pragma unroll
+                for (int k = 0; k < 4; ++k) { x[k] = x[k] / d; X[c * SOLVE_NR + h + k] = x[k]; }
+            }
+            __syncthreads();
+            if (i < c) {
+                const double l = S[c + i * lds];          // L[c][i]
+#pragma unroll
+                for (int k = 0; k < 4; ++k) x[k] = fma(-l, X[c * SOLVE_NR + h + k], x[k]);
+            }
+        }
+    }
+    __syncthreads();
+    for (int idx = tid; idx < nb * SOLVE_NR; idx += 256) b[g0 + idx] = X[idx];
+}
+
+// forward update: b[row(i)] -= sum_{c in block} L[i][c] y[c]   for the rows i >= block end of the front
+__global__ void __launch_bounds__(256) k_solve_update(const SChunk* __restrict__ tasks, FrontArrays fa, const int* __restrict__ rowidx,
+                                                      const double* __restrict__ L, double* __restrict__ b) {
+    __shared__ double Y[SOLVE_NB * SOLVE_NR];
+    const SChunk t = tasks[blockIdx.x];
+    const int s = t.s, w = fa.w[s], m = fa.m[s], ld = fa.ld[s];
+    const int nb = min(SOLVE_NB, w - t.c0);
+    const int64_t g0 = static_cast<int64_t>(fa.first[s] + t.c0) * SOLVE_NR;
+    for (int idx = threadIdx.x; idx < nb * SOLVE_NR; idx += 256) Y[idx] = b[g0 + idx];
+    __syncthreads();
+    const int i = t.r0 + threadIdx.x;
+    if (i >= m) return;
+    const double* __restrict__ P = L + fa.panel_off[s] + i + static_cast<int64_t>(t.c0) * ld;
+    double acc[SOLVE_NR];
+#pragma unroll
+    for (int k = 0; k < SOLVE_NR; ++k) acc[k] = 0.0;
+    for (int c = 0; c < nb; c += 4) {
+        double v[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u) v[u] = c + u < nb ? P[static_cast<int64_t>(c + u) * ld] : 0.0;
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+            if (c + u < nb) {
+#pragma unroll
+                for (int k = 0; k < SOLVE_NR; ++k) acc[k] = fma(v[u], Y[(c + u) * SOLVE_NR + k], acc[k]);
+            }
+    }
+    if (i < w) {          // a later column of this front: only this thread touches it
+        double* dst = b + static_cast<int64_t>(fa.first[s] + i) * SOLVE_NR;
+#pragma unroll
+        for (int k = 0; k < SOLVE_NR; ++k) dst[k] -= acc[k];
+    } else {              // a row of an ancestor: other fronts of this level may update it too
+        double* dst = b + static_cast<int64_t>(rowidx[fa.rel_off[s] + i - w]) * SOLVE_NR;
+#pragma unroll
+        for (int k = 0; k < SOLVE_NR; ++k) atomicAdd(dst + k, -acc[k]);
+    }
+}
+
+// backward gather: tsum[first + c] = sum_{i >= block end} L[i][c] x[row(i)]   for 32 columns c0 .. c0+31 of a block
+// (task.r0 = end of the SOLVE_NB block the columns belong to)
+__global__ void __launch_bounds__(256) k_solve_gather(const SChunk* __restrict__ tasks, FrontArrays fa, const int* __restrict__ rowidx,
+                                                      const double* __restrict__ L, const double* __restrict__ x, double* __restrict__ tsum) {
+    __shared__ double Z[128][SOLVE_NR + 1];
+    const SChunk t = tasks[blockIdx.x];
+    const int s = t.s, w = fa.w[s], m = fa.m[s], ld = fa.ld[s];
+    const double* __restrict__ P = L + fa.panel_off[s];
+    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+    const int cb = t.c0 + warp * 4;
+    double acc[4][SOLVE_NR];
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int k = 0; k < SOLVE_NR; ++k) acc[a][k] = 0.0;
+    for (int i0 = t.r0; i0 < m; i0 += 128) {
+        __syncthreads();
+        for (int e = tid; e < 128 * SOLVE_NR; e += 256) {
+            const int i = i0 + e / SOLVE_NR;
+            Z[e / SOLVE_NR][e % SOLVE_NR] = i < m ? x[static_cast<int64_t>(front_row(fa, rowidx, s, w, i)) * SOLVE_NR + e % SOLVE_NR] : 0.0;
+        }
+        __syncthreads();
+        for (int ii = lane; ii < 128; ii += 32) {
+            const int i = i0 + ii;
+            if (i >= m) break;
+#pragma unroll
+            for (int a = 0; a < 4; ++a) {
+                const int c = cb + a;
+                if (c < w && c < t.r0) {
+                    const double v = P[i + static_cast<int64_t>(c) * ld];
+#pragma unroll
+                    for (int k = 0; k < SOLVE_NR; ++k) acc[a][k] = fma(v, Z[ii][k], acc[a][k]);
+                }
+            }
+        }
+    }
+#pragma unroll
+    for (int a = 0; a < 4; ++a)
+#pragma unroll
+        for (int k = 0; k < SOLVE_NR; ++k) {
+            double v = acc[a][k];
+            for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+            if (lane == 0 && cb + a < w && cb + a < t.r0) tsum[static_cast<int64_t>(fa.first[s] + cb + a) * SOLVE_NR + k] = v;
+        }
+}
+
+}  // namespace spchol

@@ -190,6 +190,50 @@ def test_device_residual_large_fronts():
     assert 0.3e-3 / nrm <= est <= 3e-3 / nrm, (est, 1e-3 / nrm)
 
 
+def _sym_matvec(A, X):
+    import scipy.sparse as sp
+    Au = sp.csc_matrix((A.x, A.i, A.p), shape=(A.n, A.n))
+    return (Au + sp.triu(Au, 1).T) @ X
+
+
+@pytest.mark.parametrize("name", ["test3", "bcsstk01", "1138_bus", "lap2d_24", "lap3d_10"])
+def test_solve_on_device_factor(name):
+    """spchol_solve (L y = b, L^T x = y on the supernodal panels) against the oracle's L applied on the host."""
+    import scipy.sparse as sp
+    import scipy.sparse.linalg as spl
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    A = sc.CscMatrix(int(g["n"]), g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A)
+    assert sc.chol(A, S).has_value()
+    rng = np.random.default_rng(7)
+    for nrhs in (1, 3, 11):                      # 11 > 8: two passes of right-hand sides
+        B = rng.standard_normal((A.n, nrhs))
+        X = sc.solve(S, B if nrhs > 1 else B[:, 0])
+        X = X.reshape(A.n, -1)
+        Lref = sp.csc_matrix((g["Lx"], g["Li"], g["Lp"]), shape=(A.n, A.n))
+        Y = spl.spsolve_triangular(Lref.tocsr(), B, lower=True)
+        Xref = spl.spsolve_triangular(Lref.T.tocsr(), Y, lower=False)
+        assert np.abs(X - Xref).max() <= 1e-9 * max(np.abs(Xref).max(), 1e-300)
+        # backward stable solve: ||A x - b|| <~ eps * cond(A) * ||b|| (cond ~ 1e6..1e7 for the two Harwell-Boeing matrices)
+        assert np.linalg.norm(_sym_matvec(A, X) - B) <= 1e-8 * np.linalg.norm(B)
+
+
+def test_solve_large_fronts_end_to_end():
+    # 40^3: root front w > 1000 -> many 128-column blocks per front, atomics across fronts of a level
+    dims = (40, 40, 40)
+    perm = synth.nd_perm(*dims)
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
+    A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
+    S = sc.schol(A)
+    assert sc.chol(A, S).has_value()
+    rng = np.random.default_rng(3)
+    Xtrue = rng.standard_normal((n, 4))
+    B = _sym_matvec(A, Xtrue)
+    X = sc.solve(S, B)
+    assert np.linalg.norm(_sym_matvec(A, X) - B) <= 1e-12 * np.linalg.norm(B)
+    assert np.abs(X - Xtrue).max() <= 1e-9
+
+
 def test_batched_shared_pattern_vs_oracle():
     # config 5 in small: 48 matrices D_b A D_b over the 1138_bus pattern, one of them made indefinite
     g = np.load(os.path.join(GOLD, "1138_bus.npz"))

@@ -54,10 +54,10 @@ static void launch2(const GemmTask* dt, int nt, int gx, int gy, double* L, doubl
     if (!init) { CK(cudaFuncSetAttribute(k_gemm2<BM, BN, WGM, WGN, ST>, cudaFuncAttributeMaxDynamicSharedMemorySize, gemm2_smem<BM, BN, ST>())); init = true; }
     k_gemm2<BM, BN, WGM, WGN, ST><<<dim3((gx + BM - 1) / BM, (gy + BN - 1) / BN, nt), WGM * WGN * 32, gemm2_smem<BM, BN, ST>()>>>(dt, L, W);
 }
-static void launch1(const GemmTask* dt, int nt, int gx, int gy, double* L, double* W) {
+static void launch1(const GemmTask* dt, int nt, int gx, int gy, double* L, double* W, int swz = 0) {
     static bool init = false;
     if (!init) { CK(cudaFuncSetAttribute(k_gemm_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM)); init = true; }
-    k_gemm_dmma<<<dim3((gx + G_BM - 1) / G_BM, (gy + G_BN - 1) / G_BN, nt), 256, G_SMEM>>>(dt, L, W);
+    k_gemm_dmma<<<dim3((gx + G_BM - 1) / G_BM, (gy + G_BN - 1) / G_BN, nt), 256, G_SMEM>>>(dt, L, W, swz);
 }
 
 int main(int argc, char** argv) {
@@ -66,6 +66,7 @@ int main(int argc, char** argv) {
         {"schur_8k_k2k", 8192, 8192, 2048, 0, 1, 0},
         {"schur_8k_k2k_odd", 8192, 8192, 2048, 0, 1, 1},
         {"schur_12k_k4k", 12288, 12288, 4096, 0, 1, 1},
+        {"schur_16k_k8k_x2", 16256, 16256, 8192, 0, 2, 0},
         {"panel_16k_n256_k256", 16384, 256, 256, 0, 1, 0},
         {"panel_16k_n1792_k256", 16384, 1792, 256, 0, 1, 0},
         {"inner_16k_n128_k128", 16384, 128, 128, 0, 1, 0},
@@ -114,6 +115,7 @@ int main(int argc, char** argv) {
             fflush(stdout);
         };
         run("v1_128x64_regstage", [&] { launch1(dt, s.ntask, s.M, s.N, L, W); });
+        run("v1s_128x64_regstage_swizzle8", [&] { launch1(dt, s.ntask, s.M, s.N, L, W, 1); });
         run("v2_128x64_w4x2_s3", [&] { launch2<128, 64, 4, 2, 3>(dt, s.ntask, s.M, s.N, L, W); });
         run("v2_128x64_w4x2_s4", [&] { launch2<128, 64, 4, 2, 4>(dt, s.ntask, s.M, s.N, L, W); });
         run("v2_128x128_w2x4_s3", [&] { launch2<128, 128, 2, 4, 3>(dt, s.ntask, s.M, s.N, L, W); });
