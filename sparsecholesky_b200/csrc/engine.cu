@@ -198,7 +198,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
     }
     // profiling replays the program on one stream (program order is a valid serial order)
     cudaStream_t sts[2] = {p->stream, prof ? p->stream : p->stream2};
-    static const int gemm_swizzle = getenv("SPCHOL_GEMM_SWIZZLE") ? atoi(getenv("SPCHOL_GEMM_SWIZZLE")) : 1;
+    static const int gemm_swizzle = getenv("SPCHOL_GEMM_SWIZZLE") ? atoi(getenv("SPCHOL_GEMM_SWIZZLE")) : 3;
     // development aid: SPCHOL_TRACE=<file> dumps the device time of every stream event of one factorization
     static const char* trace_path = getenv("SPCHOL_TRACE");
     std::vector<cudaEvent_t> tev;

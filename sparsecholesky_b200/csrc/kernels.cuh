@@ -697,7 +697,7 @@ constexpr int G_SMEM = 2 * G_BK * (G_LDA + G_LDB) * 8;
 
 constexpr int G_SWZ = 8;      // CTAs are dealt to tiles in bands of 8 tile rows (see below)
 __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ tasks,
-                                                   double* __restrict__ L, double* __restrict__ W, int swizzle) {
+                                                   double* __restrict__ L, double* __restrict__ W, int swizzle /* bit 0: banded tile order, bit 1: C prefetch */) {
     extern __shared__ double sm[];
     const GemmTask t = tasks[blockIdx.z];
     // Tile order.  CTAs start in linear blockIdx order (x fastest); taken literally one wave of 296 CTAs covers
@@ -705,7 +705,7 @@ __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ 
     // complement with K = 8192: 81 GB of DRAM reads for 2.1 GB of operands).  Dealing the linear index out in
     // bands of G_SWZ tile rows makes a wave cover 8 x ~37 tiles: A and B rows touched per wave drop ~5x.
     int bx = blockIdx.x, by = blockIdx.y;
-    if (swizzle) {
+    if (swizzle & 1) {
         const int lin = blockIdx.x + blockIdx.y * gridDim.x;
         const int band = lin / (G_SWZ * gridDim.y);
         const int rows = min(G_SWZ, static_cast<int>(gridDim.x) - band * G_SWZ);
@@ -726,6 +726,16 @@ __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ 
     const int wm = warp & 3, wn = warp >> 2;
     const int K = t.K, lda = t.lda, ldb = t.ldb;
 
+    if ((swizzle & 2) && K <= 1024) {
+        // short K: the read-modify-write of the C tile at the end is a visible part of the CTA's life and its loads
+        // miss L2 (C is the trailing matrix, streamed from HBM) -- pull the tile towards L2 now, 2 lines per thread
+        const int pc = tid >> 2, pr = (tid & 3) * 32;                  // column of the tile, 32-row segment (2 x 128 B)
+        if (j0 + pc < t.N && i0 + pr < t.M) {
+            const double* cp = C + (i0 + pr) + static_cast<int64_t>(j0 + pc) * t.ldc;
+            asm volatile("prefetch.global.L2 [%0];" ::"l"(cp));
+            if (i0 + pr + 16 < t.M) asm volatile("prefetch.global.L2 [%0];" ::"l"(cp + 16));
+        }
+    }
     const int arow = tid & 127, ak = tid >> 7;         // A: 8 loads per thread, k = ak + 2 r
     const int brow = tid & 63, bk = tid >> 6;          // B: 4 loads per thread, k = bk + 4 r
     const bool a_ok = (i0 + arow) < t.M, b_ok = (j0 + brow) < t.N;
