@@ -240,7 +240,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
             }
             break;
         case OP_EXTADD:
-            k_extend_add<<<dim3(op.count, std::min(op.gx, 2048)), 128, 0, st>>>(p->d_extadd_list + op.begin, p->fa, p->dL, p->dW);
+            k_extend_add<<<dim3(op.count, std::min(op.gx, 2048)), 128, 0, st>>>(p->d_extadd_list + op.begin, p->fa, p->dL, p->dW, op.threads);
             ++launches;
             break;
         case OP_POTRF:
@@ -367,7 +367,8 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
         const Symbolic& S = symbolic_of(sym);
         opt.want_csc = S.nnzL <= INT_MAX ? 1 : 0;
         if (comm) { opt.rank = comm->rank; opt.world = comm->world; }
-        if (const char* la = getenv("SPCHOL_LOOKAHEAD")) opt.lookahead = atoi(la) != 0;   // development switch (A/B timing)
+        if (const char* la = getenv("SPCHOL_LOOKAHEAD")) opt.lookahead = atoi(la) != 0;
+        if (const char* v = getenv("SPCHOL_DEFER_CB")) opt.defer_cb_add = atoi(v) != 0;   // development switch (A/B timing)
         if (const char* v = getenv("SPCHOL_NB")) { const int x = atoi(v); if (x >= 128) opt.NB = x; }
         if (const char* v = getenv("SPCHOL_NB_WIDE")) { const int x = atoi(v); if (x >= 128) opt.NB_wide = x; }
         if (const char* v = getenv("SPCHOL_WIDE_W")) { const int x = atoi(v); if (x >= 1) opt.wide_w = x; }

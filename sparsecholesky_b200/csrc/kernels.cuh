@@ -309,8 +309,11 @@ __global__ void __launch_bounds__(CH_T, CH_CTAS) k_front_chain(const int* __rest
 // Replaces apply_update (reference include/chol.hpp:1196-1216): relative-index scatter instead
 // of a binary search per entry.
 // ---------------------------------------------------------------------------------------------
+// mode 0: every column of the child's block; 1: only the columns that land in the parent's panel; 2: only those
+// that land in the parent's contribution block (relative indices are increasing, so the two sets are a prefix and
+// the remaining suffix of the child's columns)
 __global__ void __launch_bounds__(128) k_extend_add(const int* __restrict__ list, FrontArrays fa,
-                                                    double* __restrict__ L, double* __restrict__ W) {
+                                                    double* __restrict__ L, double* __restrict__ W, int mode) {
     const int c = list[blockIdx.x];
     const int p = fa.parent[c];
     const int mc = fa.m[c] - fa.w[c];
@@ -326,6 +329,8 @@ __global__ void __launch_bounds__(128) k_extend_add(const int* __restrict__ list
     const int nbp = (wp + DNB - 1) / DNB;
     for (int jj = blockIdx.y; jj < mc; jj += gridDim.y) {
         const int cj = r[jj];
+        if (mode == 1 && cj >= wp) break;
+        if (mode == 2 && cj < wp) continue;
         if (G > 1) {
             const int blk = cj < wp ? cj / DNB : nbp + (cj - wp) / DNB;
             if (blk % G != me) continue;
@@ -720,13 +725,13 @@ __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ 
     double* Bs = sm + 2 * G_BK * G_LDA;                // [2][G_BK][G_LDB]
     const double* __restrict__ A = L + t.a_off;
     const double* __restrict__ B = L + t.b_off;
-    double* __restrict__ C = (t.c_space ? W : L) + t.c_off;
+    double* __restrict__ C = ((t.c_space & 1) ? W : L) + t.c_off;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, tq = lane & 3;
     const int wm = warp & 3, wn = warp >> 2;
     const int K = t.K, lda = t.lda, ldb = t.ldb;
 
-    if ((swizzle & 2) && K <= 1024) {
+    if ((swizzle & 2) && K <= 1024 && !(t.c_space & 2)) {
         // short K: the read-modify-write of the C tile at the end is a visible part of the CTA's life and its loads
         // miss L2 (C is the trailing matrix, streamed from HBM) -- pull the tile towards L2 now, 2 lines per thread
         const int pc = tid >> 2, pr = (tid & 3) * 32;                  // column of the tile, 32-row segment (2 x 128 B)
@@ -796,6 +801,7 @@ __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ 
     }
 
     const int ldc = t.ldc;
+    const bool beta0 = (t.c_space & 2) != 0;
 #pragma unroll
     for (int mi = 0; mi < 4; ++mi) {
         const int row = i0 + wm * 32 + mi * 8 + g;
@@ -807,7 +813,7 @@ __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ 
                 const int col = j0 + wn * 32 + ni * 8 + 2 * tq + e;
                 if (col < t.N && row + t.diag >= col) {
                     double* c = C + row + static_cast<int64_t>(col) * ldc;
-                    *c -= acc[mi][ni][e];
+                    if (beta0) *c = -acc[mi][ni][e]; else *c -= acc[mi][ni][e];
                 }
             }
         }
@@ -849,7 +855,7 @@ __global__ void __launch_bounds__(WGM * WGN * 32) k_gemm2(const GemmTask* __rest
     if (i0 + BM - 1 + t.diag < j0) return;            // tile entirely above the wanted trapezoid
     const double* __restrict__ A = L + t.a_off + i0;
     const double* __restrict__ B = L + t.b_off + j0;
-    double* __restrict__ C = (t.c_space ? W : L) + t.c_off;
+    double* __restrict__ C = ((t.c_space & 1) ? W : L) + t.c_off;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, tq = lane & 3;
     const int wm = warp % WGM, wn = warp / WGM;

@@ -369,7 +369,8 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         if (large.empty()) return;
         P.n_large += static_cast<int64_t>(large.size());
         P.max_potrf_slots = std::max(P.max_potrf_slots, static_cast<int>(large.size()));
-        {
+        const bool defer = opt.defer_cb_add != 0;
+        if (!defer) {
             Op op{}; op.kind = OP_ZERO; op.begin = static_cast<int>(P.zero_tasks.size()); op.level = lv;
             int64_t zmax = 0;
             for (int s : large) if (P.cb_off[s] >= 0) { P.zero_tasks.push_back({P.cb_off[s], cb_entries(s)}); zmax = std::max(zmax, cb_entries(s)); }
@@ -379,20 +380,27 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         }
         int max_children = 0;
         for (int s : large) max_children = std::max(max_children, P.child_ptr[s + 1] - P.child_ptr[s]);
-        for (int r = 0; r < max_children; ++r) {
-            Op op{}; op.kind = OP_EXTADD; op.begin = static_cast<int>(P.extadd_list.size()); op.level = lv;
-            int maxmb = 0;
-            for (int s : large) {
-                if (P.child_ptr[s] + r >= P.child_ptr[s + 1]) continue;
-                const int c = P.child_idx[P.child_ptr[s] + r];
-                if (P.m[c] == P.w[c]) continue;
-                P.extadd_list.push_back(c);
-                maxmb = std::max(maxmb, P.m[c] - P.w[c]);
+        // one child per parent per round (no two CTAs of a launch touch the same parent).  mode 0: the whole block;
+        // with defer_cb_add the columns landing in the parent's panel go in before the factorization (mode 1) and
+        // those landing in its contribution block after the Schur complement has been stored there (mode 2)
+        auto emit_extadd = [&](int mode) {
+            for (int r = 0; r < max_children; ++r) {
+                Op op{}; op.kind = OP_EXTADD; op.begin = static_cast<int>(P.extadd_list.size()); op.level = lv; op.threads = mode;
+                int maxmb = 0;
+                for (int s : large) {
+                    if (P.child_ptr[s] + r >= P.child_ptr[s + 1]) continue;
+                    if (mode == 2 && P.m[s] == P.w[s]) continue;
+                    const int c = P.child_idx[P.child_ptr[s] + r];
+                    if (P.m[c] == P.w[c]) continue;
+                    P.extadd_list.push_back(c);
+                    maxmb = std::max(maxmb, P.m[c] - P.w[c]);
+                }
+                op.count = static_cast<int>(P.extadd_list.size()) - op.begin;
+                op.gx = maxmb;
+                if (op.count) P.ops.push_back(op);
             }
-            op.count = static_cast<int>(P.extadd_list.size()) - op.begin;
-            op.gx = maxmb;
-            if (op.count) P.ops.push_back(op);
-        }
+        };
+        emit_extadd(defer ? 1 : 0);
         // Blocked right-looking factorization of the panels, all fronts of the level in lockstep.
         // Outer step J covers the block column [KB, KE) of width NB:
         //   panel phase  : inner blocks of width nb -- diagonal block + inverse, panel solve, update
@@ -478,7 +486,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                 if (KB >= w) continue;
                 const int64_t po = P.panel_off[s];
                 if (KE >= w) {                           // panel complete: Schur complement into the cb, K = w
-                    if (m > w) { const int64_t a2 = po + w; add_gemm(ur, {P.cb_off[s], a2, a2, even_up(m - w), ld, ld, m - w, m - w, w, 0, 1}); }
+                    if (m > w) { const int64_t a2 = po + w; add_gemm(ur, {P.cb_off[s], a2, a2, even_up(m - w), ld, ld, m - w, m - w, w, 0, defer ? 3 : 1}); }
                     continue;
                 }
                 const int KE2 = std::min(KE + NB, w);
@@ -489,6 +497,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             ur.count = static_cast<int>(P.gemm_tasks.size()) - ur.begin;
             if (ur.count) P.ops.push_back(ur);
         }
+        if (defer) emit_extadd(2);
     };
 
     auto add_copy = [&](Op& op, int sspace, int64_t soff, int lds, int dspace, int64_t doff, int ldd, int rows, int cols) {
@@ -585,20 +594,24 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         const int nbp = (w + DNB - 1) / DNB, nbc = (mb + DNB - 1) / DNB;
         const int ldcb = even_up(mb);
         const int64_t stage = tmp_alloc(static_cast<int64_t>(m) * std::min(DNB, w));    // packed block column in flight
-        if (mb > 0) {
+        const bool defer = opt.defer_cb_add != 0;
+        if (mb > 0 && !defer) {
             Op op{}; op.kind = OP_ZERO; op.begin = static_cast<int>(P.zero_tasks.size()); op.count = 1; op.level = lv;
             op.gx = static_cast<int>(std::min<int64_t>((cb_entries(s) + 2047) / 2048, 1184));
             P.zero_tasks.push_back({P.cb_off[s], cb_entries(s)});
             P.ops.push_back(op);
         }
-        for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) {
-            const int c = P.child_idx[q];
-            if (P.m[c] == P.w[c]) continue;
-            Op op{}; op.kind = OP_EXTADD; op.begin = static_cast<int>(P.extadd_list.size()); op.count = 1; op.level = lv;
-            op.gx = P.m[c] - P.w[c];
-            P.extadd_list.push_back(c);
-            P.ops.push_back(op);
-        }
+        auto emit_extadd = [&](int mode) {
+            for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) {
+                const int c = P.child_idx[q];
+                if (P.m[c] == P.w[c]) continue;
+                Op op{}; op.kind = OP_EXTADD; op.begin = static_cast<int>(P.extadd_list.size()); op.count = 1; op.level = lv; op.threads = mode;
+                op.gx = P.m[c] - P.w[c];
+                P.extadd_list.push_back(c);
+                P.ops.push_back(op);
+            }
+        };
+        emit_extadd(defer ? 1 : 0);
         // Look-ahead (see Op in plan.h): the owner of block column kb+1 applies panel kb to that
         // block column first, then factors and broadcasts it on stream 1 while every rank is still
         // applying panel kb to the rest of its block columns on stream 0.
@@ -675,10 +688,11 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                 if ((nbp + jb) % G != idx) continue;
                 const int j0 = jb * DNB, j1 = std::min(j0 + DNB, mb);
                 const int64_t a2 = po + w + j0;
-                add_gemm(g, {P.cb_off[s] + j0 + static_cast<int64_t>(j0) * ldcb, a2, a2, ldcb, ld, ld, mb - j0, j1 - j0, w, 0, 1});
+                add_gemm(g, {P.cb_off[s] + j0 + static_cast<int64_t>(j0) * ldcb, a2, a2, ldcb, ld, ld, mb - j0, j1 - j0, w, 0, defer ? 3 : 1});
             }
             g.count = static_cast<int>(P.gemm_tasks.size()) - g.begin;
             if (g.count) P.ops.push_back(g);
+            if (defer) emit_extadd(2);
         }
     };
 

@@ -16,7 +16,8 @@ struct GemmTask {
     int ldc, lda, ldb;
     int M, N, K;
     int diag;        // element (i,j) of C is wanted iff i + diag >= j   (lower-trapezoid mask)
-    int c_space;     // 0: C lives in the L buffer, 1: in the contribution workspace
+    int c_space;     // bit 0: C lives in the L buffer (0) / the contribution workspace (1); bit 1: C = -A B^T (the target
+                     // holds no data yet: Schur complement into a fresh contribution block) instead of C -= A B^T
 };
 struct PotrfTask { int64_t d_off; int ld; int nb; int col0; int slot; };         // diag block in L buffer; slot: scratch for its inverse
 struct TrsmTask  { int64_t b_off; int ld; int nb; int rows; int64_t d_off; int slot; };  // rows below the block
@@ -57,7 +58,8 @@ struct Op {
     int kind;
     int begin, count;   // slice of the task array of that kind (OP_EV_*: begin = event id)
     int gx, gy;         // grid extents besides the task dimension
-    int threads;        // OP_SMALL: CTA size class; OP_POTRF / OP_TRSM: block-width class (32 / 64 / 128); OP_GEMM: largest K
+    int threads;        // OP_EXTADD: 0 = every column of the child block, 1 = only those landing in the parent's panel,
+                        // 2 = only those landing in the parent's contribution block; OP_SMALL: CTA size class; OP_POTRF / OP_TRSM: block-width class (32 / 64 / 128); OP_GEMM: largest K
     int smem;           // OP_SMALL: dynamic shared memory bytes
     int level;
     int stream;         // 0 or 1
@@ -71,6 +73,8 @@ struct PlanOptions {
     int wide_w = 6144;         //   updates run at a longer K (measured 29 vs 23.6 TFLOP/s); narrower fronts keep NB
                                //   because their panel phase would no longer hide behind the trailing update
     int want_csc = 1;          // build the CSC export map (needs nnz(L) <= INT_MAX)
+    int defer_cb_add = 1;      // 1: large fronts never zero their contribution block: the Schur complement is stored (C = -A B^T)
+                               // and the children's contributions to it are extend-added afterwards
     int lookahead = 1;         // 1: panel work of large fronts on stream 1, overlapped with the trailing update (see Op)
     // multi-GPU (one plan per rank, every rank builds the same global mapping):
     int rank = 0, world = 1;

@@ -73,7 +73,7 @@ void run_small(Rank& R, int s) {
     }
 }
 
-void run_extadd(Rank& R, int c) {
+void run_extadd(Rank& R, int c, int mode) {
     const HostPlan& H = R.H;
     const int p = H.parent[c];
     const int mc = H.m[c] - H.w[c], ldc = even_up(mc);
@@ -85,6 +85,7 @@ void run_extadd(Rank& R, int c) {
     const int G = H.own_n[p], me = H.own_idx[p], DNB = H.dist_NB, nbp = (wp + DNB - 1) / DNB;
     for (int jj = 0; jj < mc; ++jj) {
         const int cj = r[jj];
+        if ((mode == 1 && cj >= wp) || (mode == 2 && cj < wp)) continue;
         if (G > 1) {
             const int blk = cj < wp ? cj / DNB : nbp + (cj - wp) / DNB;
             if (blk % G != me) continue;
@@ -125,14 +126,14 @@ void run_trsm(Rank& R, const TrsmTask& t) {
 void run_gemm(Rank& R, const GemmTask& t) {
     const double* A = R.L.data() + t.a_off;
     const double* B = R.L.data() + t.b_off;
-    double* C = (t.c_space ? R.W.data() : R.L.data()) + t.c_off;
+    double* C = ((t.c_space & 1) ? R.W.data() : R.L.data()) + t.c_off;
     // read all operands first: A/B may alias rows of C's panel only outside the written region
     for (int j = 0; j < t.N; ++j)
         for (int i = 0; i < t.M; ++i) {
             if (i + t.diag < j) continue;
             double acc = 0;
             for (int k = 0; k < t.K; ++k) acc += A[i + static_cast<size_t>(k) * t.lda] * B[j + static_cast<size_t>(k) * t.ldb];
-            C[i + static_cast<size_t>(j) * t.ldc] -= acc;
+            if (t.c_space & 2) C[i + static_cast<size_t>(j) * t.ldc] = -acc; else C[i + static_cast<size_t>(j) * t.ldc] -= acc;
         }
 }
 
@@ -243,7 +244,7 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
                     switch (op.kind) {
                     case OP_SMALL: for (int i = 0; i < op.count; ++i) run_small(k, H.small_list[op.begin + i]); break;
                     case OP_ZERO: for (int i = 0; i < op.count; ++i) { const ZeroTask& z = H.zero_tasks[op.begin + i]; std::fill_n(k.W.data() + z.off, z.count, 0.0); } break;
-                    case OP_EXTADD: for (int i = 0; i < op.count; ++i) run_extadd(k, H.extadd_list[op.begin + i]); break;
+                    case OP_EXTADD: for (int i = 0; i < op.count; ++i) run_extadd(k, H.extadd_list[op.begin + i], op.threads); break;
                     case OP_POTRF: for (int i = 0; i < op.count; ++i) run_potrf(k, H.potrf_tasks[op.begin + i]); break;
                     case OP_TRSM: for (int i = 0; i < op.count; ++i) run_trsm(k, H.trsm_tasks[op.begin + i]); break;
                     case OP_GEMM: for (int i = 0; i < op.count; ++i) run_gemm(k, H.gemm_tasks[op.begin + i]); break;
