@@ -65,7 +65,7 @@ int spchol_atree(int n, const int* parent, const int* sn_id, int ns, const int* 
 /* ---- symbolic phase: replaces schol<T>(A) (include/chol.hpp:874-946) ---------------------- */
 int     spchol_symbolic_create(int n, const int* Ap, const int* Ai, spchol_symbolic** out);
 /* same, with explicit amalgamation control: relax = 0 keeps the reference's fundamental supernodes, 1 = default,
- * 2 = aggressive chain merging capped at 160 rows per front (for spchol_factor_batched: fewer, wider fronts),
+ * 2 = aggressive chain merging capped at 128 rows per front (for spchol_factor_batched: fewer, wider fronts),
  * 3 = default, except that a chain of >= 1024 columns is not merged into a parent that has other children (multi-GPU
  *     plans: keeps sibling separators as separate fronts so that proportional mapping can split the ranks evenly) */
 int     spchol_symbolic_create_ex(int n, const int* Ap, const int* Ai, int relax, spchol_symbolic** out);
@@ -131,7 +131,7 @@ int  spchol_factor(spchol_plan*, const double* Ax_host, double* Lx_host, int* in
  * would loop chol(A_b), include/chol.hpp:750).  Ax[nbatch][nnzA] -> Lx[nbatch][nnzL] in the CSC order of S,
  * info[nbatch] = 0 or the 1-based failing column of that matrix.  Every launch of the level program covers
  * all matrices of a chunk (chunks sized to the free HBM).  Single-GPU plans whose fronts all fit the
- * shared-memory front kernel (m <= 160, e.g. 1138_bus); across GPUs the batch index is sharded by the caller. */
+ * shared-memory front kernel (m <= 128, e.g. 1138_bus); across GPUs the batch index is sharded by the caller. */
 int  spchol_factor_batched(spchol_plan*, int nbatch, const double* Ax_host, double* Lx_host, int* info_host);
 int  spchol_factor_batched_device(spchol_plan*, int nbatch, const double* dAx, double* dLx, int* dinfo);
 

@@ -94,9 +94,9 @@ int spchol_symbolic_create_ex(int n, const int* Ap, const int* Ai, int relax, sp
     try {
         RelaxParams rp; rp.enable = relax != 0;
         if (relax == 2) {      // batched use: latency bound, so trade explicit zeros for far fewer, wider fronts
-            rp.nrelax[0] = 32; rp.nrelax[1] = 96; rp.nrelax[2] = 160;
+            rp.nrelax[0] = 32; rp.nrelax[1] = 96; rp.nrelax[2] = 128;
             rp.zrelax[0] = 0.9; rp.zrelax[1] = 0.7; rp.zrelax[2] = 0.5;
-            rp.max_m = 160;
+            rp.max_m = 128;
         }
         if (relax == 3) rp.par_min_w = 1024;   // multi-GPU plans: keep wide sibling separators as fronts of their own
         analyze(n, Ap, Ai, rp, s->S);

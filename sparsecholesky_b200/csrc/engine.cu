@@ -368,7 +368,8 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
         opt.want_csc = S.nnzL <= INT_MAX ? 1 : 0;
         if (comm) { opt.rank = comm->rank; opt.world = comm->world; }
         if (const char* la = getenv("SPCHOL_LOOKAHEAD")) opt.lookahead = atoi(la) != 0;
-        if (const char* v = getenv("SPCHOL_DEFER_CB")) opt.defer_cb_add = atoi(v) != 0;   // development switch (A/B timing)
+        if (const char* v = getenv("SPCHOL_DEFER_CB")) opt.defer_cb_add = atoi(v) != 0;
+        if (const char* v = getenv("SPCHOL_SMALL_MAX_M")) { const int x = atoi(v); if (x >= 16 && x <= 224) opt.small_max_m = x; }   // development switch (A/B timing)
         if (const char* v = getenv("SPCHOL_NB")) { const int x = atoi(v); if (x >= 128) opt.NB = x; }
         if (const char* v = getenv("SPCHOL_NB_WIDE")) { const int x = atoi(v); if (x >= 128) opt.NB_wide = x; }
         if (const char* v = getenv("SPCHOL_WIDE_W")) { const int x = atoi(v); if (x >= 1) opt.wide_w = x; }
@@ -640,7 +641,7 @@ int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, 
     if (!p || !dAx || !dLx || !dinfo || nbatch < 0) { set_error("spchol_factor_batched_device: bad argument"); return SPCHOL_EINVAL; }
     const HostPlan& H = p->H;
     if (H.n_large > 0 || H.world > 1 || H.nnzL > INT_MAX) {
-        set_error("spchol_factor_batched: only single-GPU plans whose fronts all fit the shared-memory front kernel (m <= 160)");
+        set_error("spchol_factor_batched: only single-GPU plans whose fronts all fit the shared-memory front kernel (m <= 128)");
         return SPCHOL_EINVAL;
     }
     CK(cudaSetDevice(p->device));

@@ -97,6 +97,8 @@ __global__ void __launch_bounds__(256) k_copy2d(const CopyTask* __restrict__ tas
 // Fuses dpotrf_ + dtrsm + dsyrk + apply_update of the reference's factorize_sn for a front
 // (include/chol.hpp:1232-1335, :1196-1216).  Bound: HBM / latency (flops per byte ~ w).
 // ---------------------------------------------------------------------------------------------
+// The front is held packed (lower triangle only: column j at F + j m - j (j - 1) / 2 - j, so that col[i] is valid
+// for i >= j), m (m + 1) / 2 doubles: twice as many fronts of the larger classes fit an SM.
 template <int T>
 __global__ void __launch_bounds__(T) k_front_small(const int* __restrict__ list, FrontArrays fa,
                                                    double* __restrict__ L, double* __restrict__ W,
@@ -106,18 +108,18 @@ __global__ void __launch_bounds__(T) k_front_small(const int* __restrict__ list,
     L += blockIdx.y * lstride; W += blockIdx.y * wstride; info += blockIdx.y;
     const int s = list[blockIdx.x];
     const int w = fa.w[s], m = fa.m[s], ld = fa.ld[s];
-    const int ldf = m | 1;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = T / 32;
     double* __restrict__ P = L + fa.panel_off[s];
+    auto colp = [&](int j) { return F + (j * m - j * (j - 1) / 2 - j); };
 
     for (int j = warp; j < m; j += NW) {
-        double* col = F + j * ldf;
+        double* col = colp(j);
         if (j < w) {
             const double* src = P + static_cast<int64_t>(j) * ld;
-            for (int i = lane; i < m; i += 32) col[i] = (i >= j) ? src[i] : 0.0;
+            for (int i = j + lane; i < m; i += 32) col[i] = src[i];
         } else {
-            for (int i = lane; i < m; i += 32) col[i] = 0.0;
+            for (int i = j + lane; i < m; i += 32) col[i] = 0.0;
         }
     }
     __syncthreads();
@@ -131,7 +133,7 @@ __global__ void __launch_bounds__(T) k_front_small(const int* __restrict__ list,
         const double* __restrict__ C = W + fa.cb_off[c];
         const int* __restrict__ r = fa.rel + fa.rel_off[c];
         for (int jj = warp; jj < mc; jj += NW) {
-            double* col = F + r[jj] * ldf;
+            double* col = colp(r[jj]);
             const double* src = C + static_cast<int64_t>(jj) * ldc;
             for (int ii = jj + lane; ii < mc; ii += 32) col[r[ii]] += src[ii];
         }
@@ -140,24 +142,25 @@ __global__ void __launch_bounds__(T) k_front_small(const int* __restrict__ list,
 
     // partial factorization of columns 0..w-1
     for (int k = 0; k < w; ++k) {
-        const double d = F[k + k * ldf];
+        double* colk = colp(k);
+        const double d = colk[k];
         // reference test: d <= T(0) (chol.hpp:849); info = smallest failing 1-based column
         if (d <= 0.0 && tid == 0) atomicMin(info, fa.first[s] + k + 1);
         const double piv = sqrt(d);
-        double* colk = F + k * ldf;
+        __syncthreads();                               // everyone has read the pivot before it is overwritten
         for (int i = k + 1 + tid; i < m; i += T) colk[i] = colk[i] / piv;
-        __syncthreads();
         if (tid == 0) colk[k] = piv;
+        __syncthreads();
         for (int j = k + 1 + warp; j < m; j += NW) {
             const double uj = colk[j];
-            double* col = F + j * ldf;
+            double* col = colp(j);
             for (int i = j + lane; i < m; i += 32) col[i] -= colk[i] * uj;
         }
         __syncthreads();
     }
 
     for (int j = warp; j < m; j += NW) {
-        const double* col = F + j * ldf;
+        const double* col = colp(j);
         if (j < w) {
             double* dst = P + static_cast<int64_t>(j) * ld;
             for (int i = j + lane; i < m; i += 32) dst[i] = col[i];

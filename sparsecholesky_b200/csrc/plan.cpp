@@ -360,7 +360,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             op.kind = OP_SMALL; op.begin = static_cast<int>(P.small_list.size());
             op.count = static_cast<int>(small[c].size());
             op.threads = cls_thr[c];
-            op.smem = mm * (mm | 1) * 8;
+            op.smem = mm * (mm + 1) / 2 * 8;             // packed lower triangle
             op.level = lv;
             P.small_list.insert(P.small_list.end(), small[c].begin(), small[c].end());
             P.ops.push_back(op);
