@@ -1,5 +1,6 @@
 // Device engine + numeric C-ABI (see include/spchol.h).  No CPU fallback: every numeric entry
 // point returns SPCHOL_ENOGPU when no CUDA device is usable.
+#include <algorithm>
 #include <climits>
 #include <cmath>
 #include <cstdio>
@@ -121,6 +122,11 @@ struct spchol_plan {
     int* d_rowidx = nullptr; RTask* d_rt_cols = nullptr; RTask* d_rt_rows = nullptr; int n_rt_cols = 0, n_rt_rows = 0;
     int *d_a_row = nullptr, *d_a_col = nullptr; int* d_level_list = nullptr;
     std::vector<int> level_ptr;
+    // overlapped read-back of the supernodal panels (spchol_factor_lbuf with pinned host memory): contiguous runs of
+    // the L buffer that are final once a given level has run, copied on a third stream while the upper levels compute
+    std::vector<std::vector<std::pair<int64_t, int64_t>>> export_runs;   // [level] -> (offset, count) in doubles
+    std::vector<cudaEvent_t> export_ev;
+    cudaStream_t stream3 = nullptr;
     // triangular solves (built on first use): per (level, block step) slices of the task arrays
     struct SolveStep { int b0, bn, u0, un, g0, gn, smem; };
     std::vector<SolveStep> solve_steps;        // forward order; the backward solve walks it in reverse
@@ -170,7 +176,37 @@ int set_small_attr() {
 }
 
 // issue the whole numeric factorization on the plan's stream
-int run_numeric(spchol_plan* p, const double* dAx) {
+int export_prepare(spchol_plan* p) {
+    if (!p->export_runs.empty()) return 0;
+    const HostPlan& H = p->H;
+    std::vector<int> cnt(H.nlevels + 1, 0);
+    for (int s = 0; s < H.ns; ++s) if (H.holds(s)) ++cnt[H.level[s]];
+    // the few fronts of the top levels are read back level by level, everything below the cut in one go
+    int cut = H.nlevels, above = 0;
+    while (cut > 0 && above + cnt[cut - 1] <= 512) { --cut; above += cnt[cut]; }
+    std::vector<std::vector<std::pair<int64_t, int64_t>>> raw(H.nlevels);
+    for (int s = 0; s < H.ns; ++s) {
+        if (!H.holds(s)) continue;
+        const int bucket = H.level[s] >= cut ? H.level[s] : std::max(cut - 1, 0);
+        raw[bucket].push_back({H.panel_off[s], static_cast<int64_t>(H.ld[s]) * H.w[s]});
+    }
+    p->export_runs.assign(H.nlevels, {});
+    for (int l = 0; l < H.nlevels; ++l) {
+        std::sort(raw[l].begin(), raw[l].end());
+        for (const auto& r : raw[l]) {
+            auto& out = p->export_runs[l];
+            if (!out.empty() && out.back().first + out.back().second == r.first) out.back().second += r.second;
+            else out.push_back(r);
+        }
+    }
+    p->export_ev.resize(H.nlevels + 1, nullptr);
+    for (auto& e : p->export_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    CK(cudaStreamCreateWithFlags(&p->stream3, cudaStreamNonBlocking));
+    return 0;
+}
+
+// host_out != nullptr (pinned host memory): the panels are copied to host_out level by level while later levels run
+int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
     const HostPlan& H = p->H;
     cudaStream_t st = p->stream;
     int64_t launches = 0;
@@ -199,6 +235,20 @@ int run_numeric(spchol_plan* p, const double* dAx) {
     // profiling replays the program on one stream (program order is a valid serial order)
     cudaStream_t sts[2] = {p->stream, prof ? p->stream : p->stream2};
     static const int gemm_swizzle = getenv("SPCHOL_GEMM_SWIZZLE") ? atoi(getenv("SPCHOL_GEMM_SWIZZLE")) : 3;
+    if (prof) host_out = nullptr;
+    int level_next = 0;                  // levels below this one have been handed to the copy stream
+    auto levels_done = [&](int upto) -> int {          // every op of the levels < upto has been issued
+        for (; level_next < upto; ++level_next) {
+            const auto& runs = p->export_runs[level_next];
+            if (runs.empty()) continue;
+            CK(cudaEventRecord(p->export_ev[level_next], p->stream));      // stream 0 has joined stream 1 at the end of a level
+            CK(cudaStreamWaitEvent(p->stream3, p->export_ev[level_next], 0));
+            for (const auto& r : runs)
+                CK(cudaMemcpyAsync(host_out + r.first, p->dL + r.first, static_cast<size_t>(r.second) * sizeof(double),
+                                   cudaMemcpyDeviceToHost, p->stream3));
+        }
+        return 0;
+    };
     // development aid: SPCHOL_TRACE=<file> dumps the device time of every stream event of one factorization
     static const char* trace_path = getenv("SPCHOL_TRACE");
     std::vector<cudaEvent_t> tev;
@@ -206,6 +256,7 @@ int run_numeric(spchol_plan* p, const double* dAx) {
     cudaEvent_t t0 = nullptr;
     if (trace_path && !prof) { cudaEventCreate(&t0); cudaEventRecord(t0, p->stream); }
     for (const Op& op : H.ops) {
+        if (host_out && op.level > level_next) { const int rc2 = levels_done(op.level); if (rc2) return rc2; }
         if (op.kind == OP_EV_RECORD || op.kind == OP_EV_WAIT) {
             if (sts[0] == sts[1]) continue;
             cudaEvent_t e = p->ring[op.begin % kEventRing];
@@ -298,6 +349,12 @@ int run_numeric(spchol_plan* p, const double* dAx) {
                   tinfo.push_back(100 + pk); tinfo.push_back(op.stream); tinfo.push_back(op.level); }
     }
     st = p->stream;
+    if (host_out) {
+        const int rc2 = levels_done(H.nlevels);
+        if (rc2) return rc2;
+        CK(cudaEventRecord(p->export_ev[H.nlevels], p->stream3));          // the caller's stream waits for the read-back
+        CK(cudaStreamWaitEvent(p->stream, p->export_ev[H.nlevels], 0));
+    }
     if (p->comm && p->comm->world > 1) {      // first failing column over all ranks
         mark(8);
         NCK(nccl_api()->AllReduce(p->dinfo, p->dinfo, 1, kNcclInt32, kNcclMin, p->comm->world_comm, st));
@@ -515,6 +572,8 @@ void spchol_plan_destroy(spchol_plan* p) {
     for (auto& e : p->ev) if (e) cudaEventDestroy(e);
     for (auto& e : p->prof_ev) cudaEventDestroy(e);
     for (auto& e : p->ring) if (e) cudaEventDestroy(e);
+    for (auto& e : p->export_ev) if (e) cudaEventDestroy(e);
+    if (p->stream3) cudaStreamDestroy(p->stream3);
     if (p->stream2) cudaStreamDestroy(p->stream2);
     if (p->stream) cudaStreamDestroy(p->stream);
     delete p;
@@ -599,10 +658,18 @@ int spchol_factor_lbuf(spchol_plan* p, const double* Ax, double* Lbuf_host, int*
     CK(cudaEventRecord(p->ev[0], st));
     CK(cudaMemcpyAsync(p->dAx, Ax, static_cast<size_t>(p->H.nnzA) * sizeof(double), cudaMemcpyHostToDevice, st));
     CK(cudaEventRecord(p->ev[1], st));
-    if ((rc = run_numeric(p, p->dAx))) return rc;
+    // pinned host memory: read the panels back level by level while the upper levels are still being factored
+    // (only the panels of the last level are left when the factorization ends); pageable memory: one copy at the end
+    cudaPointerAttributes pa{};
+    const bool pinned = cudaPointerGetAttributes(&pa, Lbuf_host) == cudaSuccess && pa.type == cudaMemoryTypeHost &&
+                        !(getenv("SPCHOL_OVERLAP_D2H") && atoi(getenv("SPCHOL_OVERLAP_D2H")) == 0);
+    cudaGetLastError();
+    if (pinned && (rc = export_prepare(p))) return rc;
+    if ((rc = run_numeric(p, p->dAx, pinned ? Lbuf_host : nullptr))) return rc;
     CK(cudaEventRecord(p->ev[2], st));
     CK(cudaEventRecord(p->ev[3], st));
-    CK(cudaMemcpyAsync(Lbuf_host, p->dL, static_cast<size_t>(p->H.lbuf_entries) * sizeof(double), cudaMemcpyDeviceToHost, st));
+    if (!pinned)
+        CK(cudaMemcpyAsync(Lbuf_host, p->dL, static_cast<size_t>(p->H.lbuf_entries) * sizeof(double), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(p->ev[4], st));
     if ((rc = read_info(p, info))) return rc;
     for (int i = 0; i < 4; ++i) {

@@ -234,6 +234,36 @@ def test_solve_large_fronts_end_to_end():
     assert np.abs(X - Xtrue).max() <= 1e-9
 
 
+def test_factor_lbuf_overlapped_readback_matches_plain_copy():
+    """spchol_factor_lbuf: with pinned host memory the panels are read back level by level on a copy stream while
+    the upper levels are still being factored; with pageable memory there is one copy at the end.  Same bytes."""
+    import ctypes as C
+    from sparsecholesky_b200._lib import check, lib, ptr
+    L = lib()
+    dims = (40, 40, 40)
+    perm = synth.nd_perm(*dims)
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
+    A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
+    S = sc.schol(A)
+    plan = S.plan(0)
+    entries = S.plan_stats(0)["lbuf_entries"]
+    info = C.c_int(0)
+    plain = np.full(entries, np.nan)
+    check(L.spchol_factor_lbuf(plan.h, ptr(A.x), ptr(plain), C.byref(info)), "lbuf pageable")
+    assert info.value == 0
+    h = C.c_void_p()
+    check(L.spchol_host_alloc(entries * 8, C.byref(h)), "host_alloc")
+    try:
+        pinned = np.ctypeslib.as_array(C.cast(h, C.POINTER(C.c_double)), shape=(entries,))
+        for _ in range(2):
+            pinned[:] = np.nan
+            check(L.spchol_factor_lbuf(plan.h, ptr(A.x), h.value, C.byref(info)), "lbuf pinned")
+            assert info.value == 0
+            assert np.array_equal(pinned, plain)
+    finally:
+        L.spchol_host_free(h)
+
+
 def test_batched_shared_pattern_vs_oracle():
     # config 5 in small: 48 matrices D_b A D_b over the 1138_bus pattern, one of them made indefinite
     g = np.load(os.path.join(GOLD, "1138_bus.npz"))
