@@ -261,6 +261,27 @@ std::expected<csc_matrix<T, sym::none>, std::string> chol(const csc_matrix<T, sy
     return chol(A, schol(A));
 }
 
+// ---- beyond the reference: consumers of the device-resident factor of the last chol(A, S) ----
+// x = A^-1 b: forward and backward substitution on the supernodal panels on the GPU.  b: n x nrhs, column-major.
+template <typename T>
+std::expected<std::vector<T>, std::string> chol_solve(const SChol& S, const std::vector<T>& b, int nrhs = 1) {
+    static_assert(std::is_same_v<T, double>, "the B200 path is fp64");
+    if (!S.plan) return std::unexpected(std::string("chol_solve: call chol(A, S) first"));
+    if (b.size() != S.size() * static_cast<std::size_t>(nrhs)) return std::unexpected(std::string("chol_solve: b must hold n x nrhs values"));
+    std::vector<T> x(b.size());
+    if (spchol_solve(S.plan.get(), b.data(), x.data(), nrhs) != SPCHOL_OK) return std::unexpected(std::string(spchol_last_error()));
+    return x;
+}
+// ||A - L L^T||_F / ||A||_F of that factor, estimated on the GPU (what the reference's tests do densely, tests/test_chol.cpp:87)
+template <typename T>
+std::expected<double, std::string> chol_residual(const csc_matrix<T, sym::upper>& A, const SChol& S) {
+    static_assert(std::is_same_v<T, double>, "the B200 path is fp64");
+    if (!S.plan) return std::unexpected(std::string("chol_residual: call chol(A, S) first"));
+    double r = 0;
+    if (spchol_residual(S.plan.get(), A.x().data(), &r) != SPCHOL_OK) return std::unexpected(std::string(spchol_last_error()));
+    return r;
+}
+
 // reference chol.hpp:1449-1479
 template <typename T, sym S>
 std::vector<T> csc_to_dense(const csc_matrix<T, S>& A) {

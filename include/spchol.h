@@ -84,6 +84,15 @@ int     spchol_symbolic_supernodes(const spchol_symbolic*, int which, int* ns_ou
 /* stats[0..7] = ns_fund, ns_relaxed, sum_m, panel_entries, padded_zeros, max_w, max_m, nlevels(relaxed) */
 int     spchol_symbolic_stats(const spchol_symbolic*, int64_t* stats);
 
+/* Supernodal export format (for spchol_factor_lbuf / spchol_lbuf_to_host of a single-GPU plan; the way L comes back
+ * when nnz(L) > INT_MAX and the reference's 32-bit CSC cannot hold it): front k = relaxed supernode k owns the columns
+ * sn_start[k] .. sn_start[k+1]-1 and a dense column-major panel of m[k] rows x w[k] columns with leading dimension
+ * ld[k] at Lbuf + panel_off[k]; row i of the panel is global row rows[i] (spchol_symbolic_front_rows: the front's own
+ * columns first, then its below-rows ascending); only the lower trapezoid (i >= column) is meaningful.  Entries that
+ * relaxed amalgamation added to the pattern are exact zeros. */
+int     spchol_symbolic_panel_layout(const spchol_symbolic*, int* w, int* m, int* ld, int64_t* panel_off, int64_t* lbuf_entries);
+int     spchol_symbolic_front_rows(const spchol_symbolic*, int front, int* rows /* m[front] */);
+
 /* ---- numeric plan + factorization: replaces chol<T>(A) (include/chol.hpp:750-863) --------- */
 /* device: CUDA ordinal. The plan owns the device L buffer and contribution workspace. */
 int  spchol_plan_create(const spchol_symbolic*, int device, spchol_plan** out);

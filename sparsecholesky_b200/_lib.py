@@ -70,6 +70,8 @@ SIGNATURES = {
     "spchol_get_gemm_classes": (C.c_int, [_VP, _VP]),
     "spchol_stream": (_VP, [_VP]),
     "spchol_last_launches": (C.c_int64, [_VP]),
+    "spchol_symbolic_panel_layout": (C.c_int, [_VP, _VP, _VP, _VP, _VP, C.POINTER(C.c_int64)]),
+    "spchol_symbolic_front_rows": (C.c_int, [_VP, C.c_int, _VP]),
     "spchol_residual": (C.c_int, [_VP, _VP, C.POINTER(C.c_double)]),
     "spchol_solve": (C.c_int, [_VP, _VP, _VP, C.c_int]),
 }

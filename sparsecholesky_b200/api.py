@@ -133,6 +133,20 @@ class SChol:
         check(lib().spchol_symbolic_supernodes(self._sym.h, 1 if relaxed else 0, C.byref(ns), ptr(st), ptr(pa)))
         return st[: ns.value + 1].copy(), pa[: ns.value].copy()
 
+    def panel_layout(self):
+        """Supernodal export format of a single-GPU plan: dict(w, m, ld, panel_off, lbuf_entries) per front
+        (see include/spchol.h, spchol_symbolic_panel_layout)."""
+        ns = self.stats()["ns_relaxed"]
+        w = np.empty(ns, np.int32); m = np.empty(ns, np.int32); ld = np.empty(ns, np.int32)
+        off = np.empty(ns, np.int64); tot = C.c_int64(0)
+        check(lib().spchol_symbolic_panel_layout(self._sym.h, ptr(w), ptr(m), ptr(ld), ptr(off), C.byref(tot)))
+        return {"w": w, "m": m, "ld": ld, "panel_off": off, "lbuf_entries": int(tot.value)}
+
+    def front_rows(self, front, m):
+        rows = np.empty(int(m), np.int32)
+        check(lib().spchol_symbolic_front_rows(self._sym.h, int(front), ptr(rows)))
+        return rows
+
     def stats(self):
         st = np.zeros(8, np.int64)
         check(lib().spchol_symbolic_stats(self._sym.h, ptr(st)))
@@ -293,6 +307,24 @@ def solve(S, b, device=0):
     X = np.empty_like(B, order="F")
     check(lib().spchol_solve(S.plan(device).h, B.ctypes.data, X.ctypes.data, B.shape[1]), "solve")
     return X[:, 0].copy() if one else X
+
+
+def lbuf_to_csc(S, lbuf):
+    """Values of L in the CSC order of S.p / S.i, gathered on the host from a supernodal L buffer
+    (spchol_factor_lbuf / spchol_lbuf_to_host of a single-GPU plan) through the documented export format."""
+    lay = S.panel_layout()
+    st, _ = S.supernodes(relaxed=True)
+    Lp, Li = S.p64, S.i
+    Lx = np.empty(int(Lp[-1]), np.float64)
+    for k in range(len(lay["w"])):
+        rows = S.front_rows(k, lay["m"][k])
+        base, ld = int(lay["panel_off"][k]), int(lay["ld"][k])
+        for c in range(int(lay["w"][k])):
+            j = int(st[k]) + c
+            a, b = int(Lp[j]), int(Lp[j + 1])
+            pos = np.searchsorted(rows, Li[a:b])
+            Lx[a:b] = lbuf[base + c * ld + pos]
+    return Lx
 
 
 def chol_batched(S, Ax, device=0):

@@ -162,6 +162,32 @@ int spchol_symbolic_stats(const spchol_symbolic* s, int64_t* st) {
     return 0;
 }
 
+// Supernodal export format: where the panel of every front sits in the L buffer that
+// spchol_factor_lbuf / spchol_lbuf_to_host return for a single-GPU plan, and which rows it has.
+int spchol_symbolic_panel_layout(const spchol_symbolic* s, int* w, int* m, int* ld, int64_t* panel_off, int64_t* lbuf_entries) {
+    if (!s) return SPCHOL_EINVAL;
+    const Symbolic& S = s->S;
+    int64_t off = 0;
+    for (int k = 0; k < S.ns; ++k) {
+        const int mk = S.m(k), wk = S.w(k), ldk = (mk + 1) & ~1;
+        if (w) w[k] = wk;
+        if (m) m[k] = mk;
+        if (ld) ld[k] = ldk;
+        if (panel_off) panel_off[k] = off;
+        off += static_cast<int64_t>(ldk) * wk;
+    }
+    if (lbuf_entries) *lbuf_entries = off;
+    return 0;
+}
+int spchol_symbolic_front_rows(const spchol_symbolic* s, int front, int* rows) {
+    if (!s || !rows || front < 0 || front >= s->S.ns) { set_error("spchol_symbolic_front_rows: bad argument"); return SPCHOL_EINVAL; }
+    const Symbolic& S = s->S;
+    const int wk = S.w(front), nb = S.below_count(front);
+    for (int c = 0; c < wk; ++c) rows[c] = S.sn_start[front] + c;
+    std::memcpy(rows + wk, S.below(front), sizeof(int) * nb);
+    return 0;
+}
+
 static int dryrun_impl(const spchol_symbolic* s, int rank, int world, const int* dist_opts, int64_t* st,
                        int64_t* extra, int nextra, int64_t* comm_sig) {
     if (!s || !st) return SPCHOL_EINVAL;

@@ -74,6 +74,16 @@ int main(int argc, char** argv) {
             CHECK(std::fabs(L.x()[0] - 1682.9344962059574) < 1e-9 && std::fabs(L.x()[3] - (-1.9806673051415467)) < 1e-9);
             auto L2 = chol(A, S).value();
             CHECK(L2.x() == L.x());
+            // consumers of the resident factor: residual estimate and solve (A x = A e, e = ones)
+            auto res = chol_residual(A, S);
+            CHECK(res.has_value() && *res <= 1e-12);
+            const int n = static_cast<int>(A.size());
+            std::vector<double> b(n, 0.0);
+            for (int j = 0; j < n; ++j)
+                for (int k = A.p()[j]; k < A.p()[j + 1]; ++k) { const int i = A.i()[k]; b[i] += A.x()[k]; if (i != j) b[j] += A.x()[k]; }
+            auto x = chol_solve(S, b);
+            CHECK(x.has_value());
+            for (int i = 0; i < n; ++i) CHECK(std::fabs((*x)[i] - 1.0) < 1e-8);
         }
         {   // error path (reference chol.hpp:850)
             auto A = triplet_to_csc_matrix<double>({0, 0, 1}, {0, 1, 1}, {1.0, 2.0, 1.0}, 2);
@@ -84,6 +94,9 @@ int main(int argc, char** argv) {
         auto A = triplet_to_csc_matrix<double>({0, 0, 1}, {0, 1, 1}, {4.0, 1.0, 3.0}, 2);
         auto L = chol(A);
         if (spchol_device_count() == 0) CHECK(!L.has_value() && L.error().find("no CUDA device") != std::string::npos);
+        auto S0 = schol(A);
+        CHECK(!chol_solve(S0, std::vector<double>{1.0, 2.0}).has_value());       // no factor yet: refused, not guessed
+        CHECK(!chol_residual(A, S0).has_value());
     }
     std::printf("test_dropin OK (%s)\n", gpu ? "gpu" : "host only");
     return 0;

@@ -264,6 +264,23 @@ def test_factor_lbuf_overlapped_readback_matches_plain_copy():
         L.spchol_host_free(h)
 
 
+@pytest.mark.parametrize("name", ["bcsstk01", "1138_bus", "lap3d_10"])
+def test_supernodal_export_round_trip(name):
+    """L returned as supernodal panels (the only form available when nnz(L) > INT_MAX) and gathered on the host through
+    the documented export format equals the CSC L of chol(A, S) bit for bit."""
+    import ctypes as C
+    from sparsecholesky_b200._lib import check, lib, ptr
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    A = sc.CscMatrix(int(g["n"]), g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A)
+    Lcsc = sc.chol(A, S).value()
+    lbuf = np.empty(S.panel_layout()["lbuf_entries"])
+    info = C.c_int(0)
+    check(lib().spchol_factor_lbuf(S.plan(0).h, ptr(A.x), ptr(lbuf), C.byref(info)), "factor_lbuf")
+    assert info.value == 0
+    assert np.array_equal(sc.lbuf_to_csc(S, lbuf), Lcsc.x)
+
+
 def test_batched_shared_pattern_vs_oracle():
     # config 5 in small: 48 matrices D_b A D_b over the 1138_bus pattern, one of them made indefinite
     g = np.load(os.path.join(GOLD, "1138_bus.npz"))

@@ -110,6 +110,33 @@ def test_survey_check_values_large():
     assert st["ns_relaxed"] < st["ns_fund"] and st["panel_entries"] >= S.nnz
 
 
+@pytest.mark.parametrize("relax", [0, 1, 3])
+def test_supernodal_export_format(relax):
+    """The documented layout of the supernodal L buffer (spchol_symbolic_panel_layout / _front_rows): panels tile
+    the buffer exactly as the planner lays it out, and every entry of the reference's pattern has a slot."""
+    g = np.load(os.path.join(GOLD, "1138_bus.npz"))
+    A = sc.CscMatrix(int(g["n"]), g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A, relax=relax)
+    lay = S.panel_layout()
+    st, pa = S.supernodes(relaxed=True)
+    ns = len(pa)
+    assert lay["lbuf_entries"] == S.plan_dryrun()["lbuf_entries"]
+    assert (lay["w"] == np.diff(st)).all() and (lay["ld"] >= lay["m"]).all() and (lay["ld"] % 2 == 0).all()
+    off = np.concatenate([[0], np.cumsum(lay["ld"].astype(np.int64) * lay["w"])])
+    assert (lay["panel_off"] == off[:-1]).all() and off[-1] == lay["lbuf_entries"]
+    Lp, Li = S.p, S.i
+    for k in range(ns):
+        rows = S.front_rows(k, lay["m"][k])
+        assert (np.diff(rows) > 0).all() and (rows[: lay["w"][k]] == np.arange(st[k], st[k + 1])).all()
+        for j in range(st[k], st[k + 1]):
+            col = Li[Lp[j]:Lp[j + 1]]
+            pos = np.searchsorted(rows, col)
+            assert (pos < len(rows)).all() and (rows[pos] == col).all()      # every true entry has a slot
+        if pa[k] >= 0:                                                        # below-rows live in the parent front
+            prow = S.front_rows(pa[k], lay["m"][pa[k]])
+            assert np.isin(rows[lay["w"][k]:], prow).all()
+
+
 def test_numeric_path_fails_loudly_without_gpu():
     if sc.device_count() > 0:
         pytest.skip("GPU present")
