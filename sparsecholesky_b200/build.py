@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libspchol.so")
 SOURCES = ["symbolic.cpp", "plan.cpp", "capi_host.cpp", "engine.cu"]
-HEADERS = ["symbolic.h", "plan.h", "capi_internal.h", "kernels.cuh", "../../include/spchol.h"]
+HEADERS = ["symbolic.h", "plan.h", "capi_internal.h", "kernels.cuh", "residual.cuh", "solve.cuh", "../../include/spchol.h"]
 
 
 def needs_build() -> bool:

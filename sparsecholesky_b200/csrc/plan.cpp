@@ -261,6 +261,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     // CSC export map; a panel replicated over a rank group is exported by the group's first rank
     if (opt.want_csc) {
         P.l_src.resize(S.nnzL);
+        const std::vector<int>& fbelow = S.fundamental_below();
         for (int j = 0; j < n; ++j) {
             const int s = S.sn_id[j], f = S.fsn_id[j];
             int64_t q = S.Lp[j];
@@ -272,7 +273,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             const int64_t colbase = P.panel_off[s] + static_cast<int64_t>(c) * P.ld[s];
             const int fend = S.fsn_start[f + 1];
             for (int r = j; r < fend; ++r) P.l_src[q++] = colbase + (r - P.first[s]);
-            const int* fb = S.fbelow.data() + S.fbelow_ptr[f];
+            const int* fb = fbelow.data() + S.fbelow_ptr[f];
             const int nfb = static_cast<int>(S.fbelow_ptr[f + 1] - S.fbelow_ptr[f]);
             if (S.sn_top[s] == f) {
                 for (int t = 0; t < nfb; ++t) P.l_src[q++] = colbase + P.w[s] + t;

@@ -4,10 +4,26 @@
 #include "symbolic.h"
 
 #include <algorithm>
+#include <chrono>
+#include <cstdio>
+#include <cstdlib>
+#include <mutex>
 #include <numeric>
 #include <stdexcept>
 
 namespace spchol {
+
+// SPCHOL_TIME_HOST=1: print the wall time of every host phase to stderr
+struct PhaseTimer {
+    bool on = std::getenv("SPCHOL_TIME_HOST") != nullptr;
+    std::chrono::steady_clock::time_point t0 = std::chrono::steady_clock::now();
+    void lap(const char* what) {
+        if (!on) return;
+        const auto t1 = std::chrono::steady_clock::now();
+        std::fprintf(stderr, "[spchol host] %-28s %8.1f ms\n", what, std::chrono::duration<double, std::milli>(t1 - t0).count());
+        t0 = t1;
+    }
+};
 
 // ---------------------------------------------------------------------------------------------
 // Elimination tree (semantics of reference include/chol.hpp:378-410).
@@ -208,11 +224,35 @@ int64_t triplet_to_csc(int64_t nz, const int* ti, const int* tj, const double* t
 }
 
 // ---------------------------------------------------------------------------------------------
+// Row structure of a supernode partition: for each row i (ascending) and each A(k,i), k < i, walk
+// the assembly tree from the supernode of k towards the supernode of i, appending i to every
+// supernode not yet marked for row i.  This is the reference's ereach-based schol (:910-943)
+// lifted to supernodes: rows come out ascending per supernode, total work = sum_s (m_s - w_s).
+// ---------------------------------------------------------------------------------------------
+static void walk_rows(int n, const int* Ap, const int* Ai, int ns, const int* sn_id, const int* sn_parent,
+                      const int64_t* ptr, int* rows) {
+    std::vector<int64_t> cur(ptr, ptr + ns);
+    std::vector<int> mark(ns, -1);
+    for (int i = 0; i < n; ++i) {
+        const int si = sn_id[i];
+        for (int p = Ap[i]; p < Ap[i + 1]; ++p) {
+            const int k = Ai[p];
+            if (k >= i) continue;
+            for (int s = sn_id[k]; s != si && s >= 0 && mark[s] != i; s = sn_parent[s]) {
+                mark[s] = i;
+                if (cur[s] >= ptr[s + 1]) throw std::runtime_error("spchol: internal row-structure overflow");
+                rows[cur[s]++] = i;
+            }
+        }
+    }
+    for (int s = 0; s < ns; ++s)
+        if (cur[s] != ptr[s + 1]) throw std::runtime_error("spchol: internal row-structure count mismatch");
+}
+
+// ---------------------------------------------------------------------------------------------
 // analyze(): everything schol() produces, at supernode granularity.
-// Row structure: for each row i (ascending) and each A(k,i), k < i, walk the assembly tree from
-// the supernode of k towards the supernode of i, appending i to every supernode not yet marked
-// for row i.  This is the reference's ereach-based schol (:910-943) lifted to supernodes: rows
-// come out ascending per supernode and the total work is sum_s (m_s - w_s).
+// The amalgamation needs the column counts only, so it runs before the row structure, and the row
+// structure is built for the fronts alone (walk_rows on the relaxed assembly tree).
 // ---------------------------------------------------------------------------------------------
 void analyze(int n, const int* Ap, const int* Ai, const RelaxParams& rp, Symbolic& S) {
     if (n <= 0) throw std::runtime_error("spchol: n must be positive");
@@ -228,10 +268,15 @@ void analyze(int n, const int* Ap, const int* Ai, const RelaxParams& rp, Symboli
             if (p > Ap[j] && Ai[p] <= Ai[p - 1]) throw std::runtime_error("spchol: rows must be strictly ascending in a column");
         }
     }
+    PhaseTimer tm;
     S.parent.resize(n); S.post.resize(n); S.colcount.resize(n); S.Lp.resize(n + 1);
+    tm.lap("validate + copy A");
     etree(n, Ap, Ai, S.parent.data());
+    tm.lap("etree");
     post_order(n, S.parent.data(), S.post.data());
+    tm.lap("post_order");
     col_count(n, Ap, Ai, S.parent.data(), S.post.data(), S.colcount.data());
+    tm.lap("col_count");
     int64_t nnz = 0; double fl = 0;
     for (int j = 0; j < n; ++j) {
         S.Lp[j] = nnz; nnz += S.colcount[j];
@@ -246,34 +291,15 @@ void analyze(int n, const int* Ap, const int* Ai, const RelaxParams& rp, Symboli
     S.fsn_parent.resize(S.nsf);
     atree_from_etree(n, S.parent.data(), S.fsn_id.data(), S.nsf, S.fsn_start.data(), S.fsn_parent.data());
 
-    // below-row lists
+    tm.lap("fundamental supernodes");
     const int nsf = S.nsf;
     S.fbelow_ptr.assign(nsf + 1, 0);
     for (int f = 0; f < nsf; ++f) {
         const int wf = S.fsn_start[f + 1] - S.fsn_start[f];
         S.fbelow_ptr[f + 1] = S.fbelow_ptr[f] + (S.colcount[S.fsn_start[f]] - wf);
     }
-    S.fbelow.resize(S.fbelow_ptr[nsf] > 0 ? S.fbelow_ptr[nsf] : 0);
-    {
-        std::vector<int64_t> cur(S.fbelow_ptr.begin(), S.fbelow_ptr.end() - 1);
-        std::vector<int> mark(nsf, -1);
-        for (int i = 0; i < n; ++i) {
-            const int fi = S.fsn_id[i];
-            for (int p = Ap[i]; p < Ap[i + 1]; ++p) {
-                const int k = Ai[p];
-                if (k >= i) continue;
-                for (int f = S.fsn_id[k]; f != fi && f >= 0 && mark[f] != i; f = S.fsn_parent[f]) {
-                    mark[f] = i;
-                    if (cur[f] >= S.fbelow_ptr[f + 1]) throw std::runtime_error("spchol: internal row-structure overflow");
-                    S.fbelow[cur[f]++] = i;
-                }
-            }
-        }
-        for (int f = 0; f < nsf; ++f)
-            if (cur[f] != S.fbelow_ptr[f + 1]) throw std::runtime_error("spchol: internal row-structure count mismatch");
-    }
 
-    // relaxed amalgamation of contiguous parent/child chains
+    // relaxed amalgamation of contiguous parent/child chains (needs the column counts only)
     S.sn_start.clear(); S.sn_top.clear(); S.sn_padded.clear();
     S.sn_start.reserve(nsf + 1);
     auto mf = [&](int f) { return S.colcount[S.fsn_start[f]]; };
@@ -324,14 +350,41 @@ void analyze(int n, const int* Ap, const int* Ai, const RelaxParams& rp, Symboli
         const int pj = S.parent[S.sn_start[s + 1] - 1];
         S.sn_parent[s] = pj < 0 ? -1 : S.sn_id[pj];
     }
+    tm.lap("amalgamation");
+
+    // below-row lists of the fronts: a front's rows below its own columns are those of its top
+    // fundamental supernode, so the walk runs on the (much smaller) relaxed assembly tree
+    const int ns = S.ns;
+    S.below_ptr.assign(ns + 1, 0);
+    for (int s = 0; s < ns; ++s) {
+        const int f = S.sn_top[s];
+        S.below_ptr[s + 1] = S.below_ptr[s] + (S.fbelow_ptr[f + 1] - S.fbelow_ptr[f]);
+    }
+    S.below_rows.resize(S.below_ptr[ns] > 0 ? S.below_ptr[ns] : 0);
+    walk_rows(n, Ap, Ai, ns, S.sn_id.data(), S.sn_parent.data(), S.below_ptr.data(), S.below_rows.data());
     S.panel_entries = 0; S.sum_m = 0;
     for (int s = 0; s < S.ns; ++s) {
         S.panel_entries += static_cast<int64_t>(S.m(s)) * S.w(s);
         S.sum_m += S.m(s);
     }
+    S.lazy = std::make_shared<Symbolic::Lazy>();
+    tm.lap("below-row lists");
+}
+
+// the true (unpadded) pattern below every fundamental supernode: only the 32-bit CSC views of L
+// need it (S.i(), the CSC export map), so it is built on first use
+const std::vector<int>& Symbolic::fundamental_below() const {
+    std::call_once(lazy->once, [&] {
+        PhaseTimer tm;
+        lazy->rows.resize(fbelow_ptr[nsf] > 0 ? fbelow_ptr[nsf] : 0);
+        walk_rows(n, Ap.data(), Ai.data(), nsf, fsn_id.data(), fsn_parent.data(), fbelow_ptr.data(), lazy->rows.data());
+        tm.lap("fundamental below-rows");
+    });
+    return lazy->rows;
 }
 
 void Symbolic::fill_Li(int* Li) const {
+    const std::vector<int>& fbelow = fundamental_below();
     for (int f = 0; f < nsf; ++f) {
         const int last = fsn_start[f + 1];
         const int* b = fbelow.data() + fbelow_ptr[f];

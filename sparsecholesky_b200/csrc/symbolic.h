@@ -7,6 +7,8 @@
 // 128^3 Laplacian (nnz(L) = 2.83e9 > INT_MAX) can be planned although the reference cannot run it.
 #pragma once
 #include <cstdint>
+#include <memory>
+#include <mutex>
 #include <string>
 #include <vector>
 
@@ -52,23 +54,30 @@ struct Symbolic {
     std::vector<int> fsn_start;       // nsf+1
     std::vector<int> fsn_id;          // n
     std::vector<int> fsn_parent;      // nsf  (assembly tree = atree())
-    std::vector<int64_t> fbelow_ptr;  // nsf+1 : rows of supernode f strictly below its own columns
-    std::vector<int> fbelow;          // sum (m_f - w_f)
+    std::vector<int64_t> fbelow_ptr;  // nsf+1 : offsets into fundamental_below() (counts come from colcount)
     // relaxed supernodes = the fronts the numeric phase factors
     int ns = 0;
     std::vector<int> sn_start;        // ns+1
     std::vector<int> sn_id;           // n
     std::vector<int> sn_parent;       // ns
     std::vector<int> sn_top;          // ns : last fundamental supernode inside (owns the below-rows)
+    std::vector<int64_t> below_ptr;   // ns+1
+    std::vector<int> below_rows;      // sum_s (m_s - w_s) : rows of front s strictly below its own columns, ascending
     std::vector<char> sn_padded;      // ns : 1 if amalgamation introduced explicit zeros
     int64_t panel_entries = 0;        // sum m_s * w_s
     int64_t sum_m = 0;                // sum_s m_s
     int64_t padded_zeros = 0;
 
     int w(int s) const { return sn_start[s + 1] - sn_start[s]; }
-    int below_count(int s) const { int f = sn_top[s]; return (int)(fbelow_ptr[f + 1] - fbelow_ptr[f]); }
-    const int* below(int s) const { return fbelow.data() + fbelow_ptr[sn_top[s]]; }
+    int below_count(int s) const { return (int)(below_ptr[s + 1] - below_ptr[s]); }
+    const int* below(int s) const { return below_rows.data() + below_ptr[s]; }
     int m(int s) const { return w(s) + below_count(s); }
+
+    // rows strictly below every FUNDAMENTAL supernode (the unpadded pattern of L), sum_f (m_f - w_f)
+    // entries indexed by fbelow_ptr; built on first use (thread-safe), see symbolic.cpp
+    const std::vector<int>& fundamental_below() const;
+    struct Lazy { std::once_flag once; std::vector<int> rows; };
+    std::shared_ptr<Lazy> lazy;
 
     // fills Li[nnzL] with the reference's layout (diagonal first, rows ascending; :931-941)
     void fill_Li(int* Li) const;
