@@ -282,6 +282,26 @@ std::expected<double, std::string> chol_residual(const csc_matrix<T, sym::upper>
     return r;
 }
 
+// ---- beyond the reference: fill-reducing ordering (the reference has none) ----
+// perm[new] = old: approximate minimum degree on the pattern of A, composed with an etree postorder
+template <typename T>
+std::vector<int> order_amd(const csc_matrix<T, sym::upper>& A) {
+    std::vector<int> perm(A.size());
+    if (spchol_order_amd(static_cast<int>(A.size()), A.p().data(), A.i().data(), perm.data()) != SPCHOL_OK) internal::throw_last("order_amd");
+    return perm;
+}
+// triu(P A P^T), perm[new] = old
+template <typename T>
+csc_matrix<T, sym::upper> permute(const csc_matrix<T, sym::upper>& A, const std::vector<int>& perm) {
+    static_assert(std::is_same_v<T, double>, "the B200 path is fp64");
+    const int n = static_cast<int>(A.size());
+    if (perm.size() != A.size()) throw std::invalid_argument("permute: perm must hold n entries");
+    csc_matrix<T, sym::upper> B(A.size(), A.capacity());
+    if (spchol_permute_upper(n, A.p().data(), A.i().data(), A.x().data(), perm.data(), B.p().data(), B.i().data(), B.x().data(), nullptr) != SPCHOL_OK)
+        internal::throw_last("permute");
+    return B;
+}
+
 // reference chol.hpp:1449-1479
 template <typename T, sym S>
 std::vector<T> csc_to_dense(const csc_matrix<T, S>& A) {

@@ -49,6 +49,18 @@ int spchol_triplet_to_csc(int64_t nz, const int* ti, const int* tj, const double
  * Two-call protocol: with ti == NULL only *n_out / *nz_out are written. */
 int spchol_mtx_read(const char* path, int* n_out, int64_t* nz_out, int* ti, int* tj, double* tx);
 
+/* ---- orderings (host; additive: the reference has no ordering code) -------- */
+/* geometric nested dissection of an nx*ny*nz grid, the fixed permutation of the benchmark Laplacians
+ * (SURVEY.md 8d): perm[new] = old grid id, id = x + nx*(y + ny*z) */
+int spchol_nd_perm_grid(int nx, int ny, int nz, int64_t* perm);
+/* approximate-minimum-degree ordering of a symmetric pattern given as its upper triangle (CSC, diagonal
+ * optional), composed with an elimination-tree postorder: perm[new] = old */
+int spchol_order_amd(int n, const int* Ap, const int* Ai, int* perm);
+/* B = triu(P A P^T), rows ascending per column; Bp[n+1], Bi/Bx[nnz(A)].  Ax/Bx may be NULL (pattern only);
+ * map (optional, nnz(A)): position in B of every entry of A, to permute further value sets over the same pattern */
+int spchol_permute_upper(int n, const int* Ap, const int* Ai, const double* Ax, const int* perm,
+                         int* Bp, int* Bi, double* Bx, int64_t* map);
+
 /* ---- symbolic helpers (integer only, host) ------------------------------------------------ */
 int spchol_etree(int n, const int* Ap, const int* Ai, int* parent);                 /* chol.hpp:378  */
 int spchol_post_order(int n, const int* parent, int* post);                          /* chol.hpp:466  */

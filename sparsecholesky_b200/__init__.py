@@ -2,6 +2,6 @@
 from .api import (  # noqa: F401
     CscMatrix, SChol, Expected, Sym,
     triplet_to_csc_matrix, load_matrix_market_to_csc, build_csc_matrix_from_pattern,
-    etree, post_order, col_count, ereach, compute_levels, compute_supernodes, atree,
+    etree, post_order, col_count, ereach, compute_levels, compute_supernodes, atree, order_amd, permute,
     schol, chol, chol_batched, residual, solve, lbuf_to_csc, csc_to_dense, device_count,
 )

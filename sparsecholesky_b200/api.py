@@ -205,6 +205,26 @@ def load_matrix_market_to_csc(filename):
     return triplet_to_csc_matrix(ti, tj, tx, n.value)
 
 
+def order_amd(A):
+    """Approximate-minimum-degree ordering of the pattern of A (upper CSC): perm[new] = old.  Additive:
+    the reference has no ordering."""
+    perm = np.empty(A.n, np.int32)
+    check(lib().spchol_order_amd(A.n, ptr(A.p), ptr(A.i), ptr(perm)), "order_amd")
+    return perm
+
+
+def permute(A, perm, return_map=False):
+    """triu(P A P^T) with perm[new] = old; with return_map also the position in the result of every entry of A."""
+    assert A.sym is Sym.upper
+    perm = np.ascontiguousarray(perm, np.int32)
+    Bp = np.empty(A.n + 1, np.int32); Bi = np.empty(A.i.shape[0], np.int32); Bx = np.empty(A.i.shape[0], np.float64)
+    mp = np.empty(A.i.shape[0], np.int64)
+    Ax = np.ascontiguousarray(A.x, np.float64)
+    check(lib().spchol_permute_upper(A.n, ptr(A.p), ptr(A.i), ptr(Ax), ptr(perm), ptr(Bp), ptr(Bi), ptr(Bx), ptr(mp)), "permute")
+    B = CscMatrix(A.n, Bp, Bi, Bx, Sym.upper)
+    return (B, mp) if return_map else B
+
+
 def build_csc_matrix_from_pattern(pattern):               # chol.hpp:416-435
     ti, tj = [], []
     for i, cols in enumerate(pattern):

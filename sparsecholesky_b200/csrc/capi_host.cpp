@@ -10,6 +10,7 @@
 
 #include "../../include/spchol.h"
 #include "capi_internal.h"
+#include "ordering.h"
 #include "plan.h"
 
 namespace spchol {
@@ -253,6 +254,30 @@ int spchol_map_fronts(const spchol_symbolic* s, int world, int dist_min_w, int* 
                lo, cnt, load);
     for (int k = 0; k < S.ns; ++k) { if (own_lo) own_lo[k] = lo[k]; if (own_n) own_n[k] = cnt[k]; }
     if (rank_load) for (int r = 0; r < world; ++r) rank_load[r] = load[r];
+    return 0;
+}
+
+// ---- orderings (ordering.h) -------------------------------------------------------------------
+int spchol_nd_perm_grid(int nx, int ny, int nz, int64_t* perm) {
+    if (!perm || nx < 1 || ny < 1 || nz < 1) { set_error("spchol_nd_perm_grid: bad argument"); return SPCHOL_EINVAL; }
+    try { nd_perm_grid(nx, ny, nz, perm); } catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
+    return 0;
+}
+
+int spchol_order_amd(int n, const int* Ap, const int* Ai, int* perm) {
+    if (n < 0 || !Ap || (!Ai && Ap[n] > 0) || (!perm && n > 0)) { set_error("spchol_order_amd: bad argument"); return SPCHOL_EINVAL; }
+    try { order_amd(n, Ap, Ai, perm); }
+    catch (const std::bad_alloc&) { set_error("out of host memory"); return SPCHOL_ENOMEM; }
+    catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
+    return 0;
+}
+
+int spchol_permute_upper(int n, const int* Ap, const int* Ai, const double* Ax, const int* perm,
+                         int* Bp, int* Bi, double* Bx, int64_t* map) {
+    if (n < 0 || !Ap || !perm || !Bp || (Ap[n] > 0 && (!Ai || !Bi))) { set_error("spchol_permute_upper: bad argument"); return SPCHOL_EINVAL; }
+    try { permute_upper(n, Ap, Ai, Ax, perm, Bp, Bi, Bx, map); }
+    catch (const std::bad_alloc&) { set_error("out of host memory"); return SPCHOL_ENOMEM; }
+    catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
     return 0;
 }
 

@@ -5,7 +5,15 @@ import numpy as np
 
 
 def nd_perm(nx, ny=1, nz=1):
-    """perm[new] = old grid id (id = x + nx*(y + ny*z)); geometric nested dissection, leaf volume <= 8."""
+    """perm[new] = old grid id (id = x + nx*(y + ny*z)); geometric nested dissection, leaf volume <= 8
+    (spchol_nd_perm_grid; nd_perm_py below is the same in numpy and checks it in the tests)."""
+    from ._lib import check, lib, ptr
+    out = np.empty(nx * ny * nz, np.int64)
+    check(lib().spchol_nd_perm_grid(nx, ny, nz, ptr(out)), "nd_perm")
+    return out
+
+
+def nd_perm_py(nx, ny=1, nz=1):
     out = np.empty(nx * ny * nz, np.int64)
     pos = 0
 

@@ -114,6 +114,27 @@ def test_random_spd_vs_oracle(seed):
     assert residual(A, L) <= RES_TOL
 
 
+@pytest.mark.parametrize("name", ["bcsstk01", "1138_bus"])
+def test_amd_permuted_matrix_vs_oracle(name):
+    # ordering is additive (the reference has none): chol of triu(P A P^T) must match the reference's
+    # algorithm on that same permuted matrix, and x = P^T (P A P^T)^-1 P b must solve the original system
+    A = sc.load_matrix_market_to_csc(os.path.join(ROOT, "tests", "data", name + ".mtx"))
+    perm = sc.order_amd(A)
+    B = sc.permute(A, perm)
+    rc, Lp, Li, ref = po.chol(B.n, B.p, B.i, B.x)
+    assert rc == 0
+    S = sc.schol(B)
+    L = sc.chol(B, S).value()
+    assert (L.p == Lp).all() and (L.i == Li).all()
+    assert rel_err(L.x, ref) <= REL_TOL
+    assert residual(B, L) <= RES_TOL
+    b = np.linspace(1.0, 2.0, A.n)
+    y = sc.solve(S, b[perm])
+    x = np.empty(A.n); x[perm] = np.asarray(y).ravel()
+    r = _sym_matvec(A, x[:, None]).ravel() - b
+    assert np.linalg.norm(r) / np.linalg.norm(b) <= 1e-8          # eps * cond(A), as in test_solve_on_device_factor
+
+
 def test_plan_reuse_many_values():
     # chol(A, S) with one S and several value sets (config 5's usage pattern), batch family D A D
     g = np.load(os.path.join(GOLD, "1138_bus.npz"))
