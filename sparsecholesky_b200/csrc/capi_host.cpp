@@ -1,6 +1,8 @@
 // Host-only part of the C-ABI (ingest + symbolic); see include/spchol.h for the contract and
 // the reference interfaces each entry point replaces.
+#include <charconv>
 #include <climits>
+#include <cstdlib>
 #include <cstdio>
 #include <cstring>
 #include <fstream>
@@ -39,24 +41,83 @@ int spchol_triplet_to_csc(int64_t nz, const int* ti, const int* tj, const double
 // Matrix Market coordinate reader with the reference's rules (include/mtx_reader.hpp:17-62):
 // leading '%' lines skipped, then "rows cols nnz", then nnz 1-based (row col value) triples,
 // each mirrored into the upper triangle.  The banner is not interpreted.
+// The reference reads the file with `ifstream >>` (mtx_reader.hpp:17-62): leading '%' lines are skipped,
+// then whitespace-separated tokens "rows cols nnz" and nnz triples "r c v" (1-based).  Same grammar here,
+// parsed from one in-memory copy of the file (from_chars: ~15x the throughput of the stream extractors).
+namespace {
+struct Cursor {
+    const char* p; const char* end;
+    void skip_ws() { while (p < end && (*p == ' ' || *p == '\n' || *p == '\t' || *p == '\r' || *p == '\f' || *p == '\v')) ++p; }
+    bool integer(long long& v) {
+        skip_ws();
+        if (p < end && *p == '+') ++p;
+        const auto r = std::from_chars(p, end, v);
+        if (r.ec != std::errc()) return false;
+        p = r.ptr; return true;
+    }
+    bool real(double& v) {
+        skip_ws();
+        if (p < end && *p == '+') ++p;
+        const auto r = std::from_chars(p, end, v);
+        if (r.ec == std::errc::result_out_of_range) {            // strtod semantics for overflow / underflow
+            std::string tok(p, r.ptr);
+            v = std::strtod(tok.c_str(), nullptr);
+        } else if (r.ec != std::errc()) return false;
+        p = r.ptr; return true;
+    }
+};
+}  // namespace
+
 int spchol_mtx_read(const char* path, int* n_out, int64_t* nz_out, int* ti, int* tj, double* tx) {
     if (!path || !n_out || !nz_out) { set_error("spchol_mtx_read: null argument"); return SPCHOL_EINVAL; }
-    std::ifstream f(path);
+    std::FILE* f = std::fopen(path, "rb");
     if (!f) { set_error(std::string("Could not open file ") + path); return SPCHOL_EIO; }
-    while (f.peek() == '%') f.ignore(1 << 20, '\n');
+    std::vector<char> buf;
+    if (!ti) {
+        // sizes only: the header sits in the first few KB unless the comment block is long
+        buf.resize(1 << 16);
+        size_t got = std::fread(buf.data(), 1, buf.size(), f);
+        auto header_complete = [&]() {
+            size_t q = 0;
+            while (q < got && buf[q] == '%') { while (q < got && buf[q] != '\n') ++q; if (q < got) ++q; }
+            int tokens = 0; bool in_tok = false;
+            for (; q < got; ++q) {
+                const bool ws = buf[q] == ' ' || buf[q] == '\n' || buf[q] == '\t' || buf[q] == '\r';
+                if (!ws && !in_tok) { in_tok = true; }
+                else if (ws && in_tok) { in_tok = false; if (++tokens == 3) return true; }
+            }
+            return false;
+        };
+        while (!header_complete() && got == buf.size()) {
+            buf.resize(buf.size() * 2);
+            got += std::fread(buf.data() + got, 1, buf.size() - got, f);
+        }
+        buf.resize(got);
+    } else {
+        std::fseek(f, 0, SEEK_END);
+        const long sz = std::ftell(f);
+        std::fseek(f, 0, SEEK_SET);
+        if (sz < 0) { std::fclose(f); set_error("spchol_mtx_read: cannot size the file"); return SPCHOL_EIO; }
+        try { buf.resize(static_cast<size_t>(sz)); } catch (const std::bad_alloc&) { std::fclose(f); set_error("out of host memory"); return SPCHOL_ENOMEM; }
+        const size_t got = std::fread(buf.data(), 1, buf.size(), f);
+        buf.resize(got);
+    }
+    std::fclose(f);
+    Cursor c{buf.data(), buf.data() + buf.size()};
+    while (c.p < c.end && *c.p == '%') { while (c.p < c.end && *c.p != '\n') ++c.p; if (c.p < c.end) ++c.p; }
     long long nr = 0, nc = 0, nl = 0;
-    if (!(f >> nr >> nc >> nl) || nr <= 0 || nr != nc || nl < 0 || nr > INT_MAX) {
+    if (!c.integer(nr) || !c.integer(nc) || !c.integer(nl) || nr <= 0 || nr != nc || nl < 0 || nr > INT_MAX) {
         set_error("spchol_mtx_read: bad size line (matrix must be square)"); return SPCHOL_EINVAL;
     }
     *n_out = static_cast<int>(nr);
     *nz_out = nl;
     if (!ti) return SPCHOL_OK;
     for (long long l = 0; l < nl; ++l) {
-        long long r, c; double v;
-        if (!(f >> r >> c >> v)) { set_error("spchol_mtx_read: truncated file"); return SPCHOL_EIO; }
-        --r; --c;
-        if (c < r) std::swap(r, c);
-        ti[l] = static_cast<int>(r); tj[l] = static_cast<int>(c); tx[l] = v;
+        long long r, col; double v;
+        if (!c.integer(r) || !c.integer(col) || !c.real(v)) { set_error("spchol_mtx_read: truncated file"); return SPCHOL_EIO; }
+        --r; --col;
+        if (col < r) std::swap(r, col);
+        ti[l] = static_cast<int>(r); tj[l] = static_cast<int>(col); tx[l] = v;
     }
     return SPCHOL_OK;
 }

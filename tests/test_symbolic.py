@@ -90,6 +90,34 @@ def test_mtx_reader():
         sc.load_matrix_market_to_csc("/nonexistent/file.mtx")
 
 
+def test_mtx_reader_token_grammar(tmp_path):
+    # same grammar as the reference's `ifstream >>` loop (mtx_reader.hpp:17-62): leading % lines, then
+    # whitespace-separated tokens; signs, exponents, CRLF, blank lines, several entries per line
+    text = ("%%MatrixMarket matrix coordinate real symmetric\r\n% a comment\r\n%\r\n"
+            "  4 4   6\r\n1 1 +2.5\r\n\r\n2 1 -1e-1   2 2 3.\n3 3 1E+2\n4 3 .5\n4 4 1e400\n")
+    f = tmp_path / "a.mtx"
+    f.write_bytes(text.encode())
+    A = sc.load_matrix_market_to_csc(str(f))
+    assert A.n == 4 and A.p.tolist() == [0, 1, 3, 4, 6] and A.i.tolist() == [0, 0, 1, 2, 2, 3]
+    assert A.x[:5].tolist() == [2.5, -0.1, 3.0, 100.0, 0.5] and np.isinf(A.x[5])
+    # values parse to the same doubles as the C library's strtod (what operator>> uses)
+    vals = ["0.1", "1138.000123456789", "-4.9406564584124654e-324", "1.7976931348623157e308", "123456789012345678", "6.02214076e23"]
+    g = tmp_path / "b.mtx"
+    g.write_text("6 6 6\n" + "".join(f"{k + 1} {k + 1} {v}\n" for k, v in enumerate(vals)))
+    B = sc.load_matrix_market_to_csc(str(g))
+    assert B.x.tolist() == [float(v) for v in vals]
+    # a long comment block (header beyond the first read of the sizes-only call)
+    h = tmp_path / "c.mtx"
+    h.write_text("% x\n" * 40000 + "2 2 2\n1 1 1\n2 2 1\n")
+    assert sc.load_matrix_market_to_csc(str(h)).n == 2
+    for bad, msg in (("3 3 2\n1 1 1.0\n", "truncated"), ("3 4 1\n1 1 1.0\n", "square"), ("% only\n", "size line"),
+                     ("2 2 1\n1 x 1.0\n", "truncated")):
+        b = tmp_path / "bad.mtx"
+        b.write_text(bad)
+        with pytest.raises(RuntimeError, match=msg):
+            sc.load_matrix_market_to_csc(str(b))
+
+
 def test_survey_check_values_large():
     # SURVEY.md §8(d) check values for the generator + symbolic at a size the reference needs minutes for
     perm = synth.nd_perm(4, 4, 1)
