@@ -17,6 +17,7 @@
 #include "../../include/spchol.h"
 #include "capi_internal.h"
 #include "kernels.cuh"
+#include "path_kernel.cuh"
 #include "residual.cuh"
 #include "solve.cuh"
 
@@ -109,6 +110,10 @@ struct spchol_plan {
     double *bL = nullptr, *bW = nullptr; int* binfo = nullptr; int b_chunk = 0;   // batched factorization buffers
     // batched factorization: fronts of the levels >= chain_level0 are walked by one CTA per matrix (k_front_chain)
     int* d_chain_list = nullptr; int* d_tri_tab = nullptr; int chain_count = 0, chain_level0 = -1, chain_smem = 0; bool chain_ready = false;
+    // ... or, with SPCHOL_BATCH_PATH=1, by the path-group program (k_front_path, path_plan.h): staged, validated on the CPU by
+    // tests/test_path_emu.py, not yet the default
+    PathArrays path{}; int path_smem = 0; bool path_on = false;
+    int64_t b_ws_entries = 0;     // workspace doubles per matrix of the batched buffers (>= H.ws_entries)
     double* dWinv = nullptr;      // inverses of the diagonal blocks of one launch (k_potrf_inv -> k_trsm_inv)
     int* dinfo = nullptr;
     int *d_first = nullptr, *d_w = nullptr, *d_m = nullptr, *d_ld = nullptr, *d_parent = nullptr;
@@ -687,7 +692,7 @@ int spchol_factor_lbuf(spchol_plan* p, const double* Ax, double* Lbuf_host, int*
 static int batched_chunk(const spchol_plan* p) {
     size_t fr = 0, tot = 0;
     if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) return 1;
-    const double per = 8.0 * (static_cast<double>(p->H.lbuf_entries) + p->H.ws_entries + p->H.nnzA + p->H.nnzL) + 64;
+    const double per = 8.0 * (static_cast<double>(p->H.lbuf_entries) + std::max(p->b_ws_entries, p->H.ws_entries) + p->H.nnzA + p->H.nnzL) + 64;
     const double c = 0.8 * static_cast<double>(fr) / per;
     return static_cast<int>(std::max(1.0, std::min(c, 65535.0)));
 }
@@ -697,31 +702,21 @@ static int batched_reserve(spchol_plan* p, int chunk) {
     for (void* d : {static_cast<void*>(p->bL), static_cast<void*>(p->bW), static_cast<void*>(p->binfo)}) if (d) cudaFree(d);
     p->bL = p->bW = nullptr; p->binfo = nullptr; p->b_chunk = 0;
     CK(cudaMalloc(&p->bL, sizeof(double) * std::max<int64_t>(p->H.lbuf_entries, 1) * chunk));
-    CK(cudaMalloc(&p->bW, sizeof(double) * std::max<int64_t>(p->H.ws_entries, 1) * chunk));
+    CK(cudaMalloc(&p->bW, sizeof(double) * std::max<int64_t>(p->b_ws_entries, 1) * chunk));
     CK(cudaMalloc(&p->binfo, sizeof(int) * chunk));
     p->b_chunk = chunk;
     return 0;
 }
 
-// device-resident: dAx[nbatch][nnzA] -> dLx[nbatch][nnzL] (CSC order of S), dinfo[nbatch] (0 or failing column)
-int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, double* dLx, int* dinfo) {
-    if (!p || !dAx || !dLx || !dinfo || nbatch < 0) { set_error("spchol_factor_batched_device: bad argument"); return SPCHOL_EINVAL; }
+// one-time setup of the batched path: which kernel walks the upper levels, and the per-matrix workspace it needs
+static int batched_prepare(spchol_plan* p) {
     const HostPlan& H = p->H;
-    if (H.n_large > 0 || H.world > 1 || H.nnzL > INT_MAX) {
-        set_error("spchol_factor_batched: only single-GPU plans whose fronts all fit the shared-memory front kernel (m <= 128)");
-        return SPCHOL_EINVAL;
-    }
-    CK(cudaSetDevice(p->device));
-    cudaStream_t st = p->stream;
-    int chunk = p->b_chunk > 0 ? p->b_chunk : std::min(batched_chunk(p), std::max(nbatch, 1));
     int rc;
-    if ((rc = batched_reserve(p, std::min(chunk, std::max(nbatch, 1))))) return rc;
-    chunk = p->b_chunk;
-    int64_t launches = 0;
     if (!p->chain_ready) {
         // upper part of the tree = the levels from which on no level has more than 16 fronts: too few fronts per
         // launch to fill the GPU, and mostly chains whose contribution blocks can stay on the SM
         p->chain_ready = true;
+        p->b_ws_entries = H.ws_entries;
         std::vector<int> cnt(H.nlevels + 1, 0);
         for (int s = 0; s < H.ns; ++s) ++cnt[H.level[s]];
         int l0 = H.nlevels;
@@ -735,15 +730,56 @@ int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, 
             for (int s = 0; s < H.ns; ++s) if (H.level[s] == l) { lst.push_back(s); mm = std::max(mm, H.m[s]); }
         const int smem = mm * (mm + 1) / 2 * 8;            // packed lower triangle
         const char* off = getenv("SPCHOL_BATCH_CHAIN");
-        if (lst.size() >= 8 && smem <= 72 * 1024 && !(off && atoi(off) == 0)) {
-            std::vector<int> tab;
-            for (int ii = 0; static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++ii)
-                for (int jj = 0; jj <= ii && static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++jj) tab.push_back((ii << 16) | jj);
+        const char* path = getenv("SPCHOL_BATCH_PATH");
+        std::vector<int> tab;
+        for (int ii = 0; static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++ii)
+            for (int jj = 0; jj <= ii && static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++jj) tab.push_back((ii << 16) | jj);
+        static_assert(PK_MAXE * PK_T == CH_MAXE * CH_T, "k_front_path and k_front_chain share the pair table");
+        if (lst.size() >= 8 && path && atoi(path) != 0) {
+            // path groups: |U| <= 160 rows keeps two CTAs per SM (103 KB each)
+            const int max_nu = getenv("SPCHOL_BATCH_PATH_NU") ? atoi(getenv("SPCHOL_BATCH_PATH_NU")) : 160;
+            PathProgram prog;
+            bool ok = false;
+            try { ok = build_path_program(H, l0, max_nu, static_cast<int64_t>(PK_MAXE) * PK_T, prog); }
+            catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
+            const int psmem = prog.max_nu * (prog.max_nu + 1) / 2 * 8;
+            if (ok && prog.max_m <= PK_SPOS_MAX && psmem <= 227 * 1024) {
+                PathGroup* dg = nullptr; PathMember* dm = nullptr; PathChild* dc = nullptr; int* dp = nullptr;
+                if ((rc = upload(p, prog.groups, &dg)) || (rc = upload(p, prog.members, &dm)) || (rc = upload(p, prog.children, &dc)) ||
+                    (rc = upload(p, prog.pos, &dp)) || (rc = upload(p, tab, &p->d_tri_tab))) return rc;
+                p->path = PathArrays{dg, static_cast<int>(prog.groups.size()), dm, dc, dp, p->d_tri_tab,
+                                     p->d_first, p->d_w, p->d_m, p->d_ld, p->d_panel_off};
+                p->path_smem = psmem; p->path_on = true; p->chain_level0 = l0;
+                p->b_ws_entries = prog.ws_entries;
+                CK(cudaFuncSetAttribute(k_front_path, cudaFuncAttributeMaxDynamicSharedMemorySize, psmem));
+            }
+        }
+        if (!p->path_on && lst.size() >= 8 && smem <= 72 * 1024 && !(off && atoi(off) == 0)) {
             if ((rc = upload(p, lst, &p->d_chain_list)) || (rc = upload(p, tab, &p->d_tri_tab))) return rc;
             p->chain_count = static_cast<int>(lst.size()); p->chain_level0 = l0; p->chain_smem = smem;
             CK(cudaFuncSetAttribute(k_front_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
         }
     }
+    return 0;
+}
+
+// device-resident: dAx[nbatch][nnzA] -> dLx[nbatch][nnzL] (CSC order of S), dinfo[nbatch] (0 or failing column)
+int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, double* dLx, int* dinfo) {
+    if (!p || !dAx || !dLx || !dinfo || nbatch < 0) { set_error("spchol_factor_batched_device: bad argument"); return SPCHOL_EINVAL; }
+    const HostPlan& H = p->H;
+    if (H.n_large > 0 || H.world > 1 || H.nnzL > INT_MAX) {
+        set_error("spchol_factor_batched: only single-GPU plans whose fronts all fit the shared-memory front kernel (m <= 128)");
+        return SPCHOL_EINVAL;
+    }
+    CK(cudaSetDevice(p->device));
+    cudaStream_t st = p->stream;
+    int rc;
+    int64_t launches = 0;
+    if ((rc = batched_prepare(p))) return rc;
+    int chunk = p->b_chunk > 0 ? p->b_chunk : std::min(batched_chunk(p), std::max(nbatch, 1));
+    if ((rc = batched_reserve(p, std::min(chunk, std::max(nbatch, 1))))) return rc;
+    chunk = p->b_chunk;
+    const int64_t wstride = p->b_ws_entries;
     for (int b0 = 0; b0 < nbatch; b0 += chunk) {
         const int nb = std::min(chunk, nbatch - b0);
         CK(cudaMemsetAsync(p->bL, 0, sizeof(double) * H.lbuf_entries * nb, st));
@@ -753,20 +789,23 @@ int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, 
         ++launches;
         for (const Op& op : H.ops) {
             if (op.kind != OP_SMALL) continue;
-            if (p->chain_count && op.level >= p->chain_level0) continue;      // walked by k_front_chain below
+            if ((p->chain_count || p->path_on) && op.level >= p->chain_level0) continue;      // walked by k_front_chain / k_front_path below
             const int* list = p->d_small_list + op.begin;
             const dim3 g(static_cast<unsigned>(op.count), nb);
             switch (op.threads) {
-            case 32:  k_front_small<32><<<g, 32, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
-            case 64:  k_front_small<64><<<g, 64, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
-            case 128: k_front_small<128><<<g, 128, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
-            default:  k_front_small<256><<<g, 256, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, H.ws_entries); break;
+            case 32:  k_front_small<32><<<g, 32, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride); break;
+            case 64:  k_front_small<64><<<g, 64, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride); break;
+            case 128: k_front_small<128><<<g, 128, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride); break;
+            default:  k_front_small<256><<<g, 256, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride); break;
             }
             ++launches;
         }
-        if (p->chain_count) {
+        if (p->path_on) {
+            k_front_path<<<nb, PK_T, p->path_smem, st>>>(p->path, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride);
+            ++launches;
+        } else if (p->chain_count) {
             k_front_chain<<<nb, CH_T, p->chain_smem, st>>>(p->d_chain_list, p->chain_count, p->fa, p->d_tri_tab, p->bL, p->bW, p->binfo,
-                                                           H.lbuf_entries, H.ws_entries);
+                                                           H.lbuf_entries, wstride);
             ++launches;
         }
         k_export<<<dim3(static_cast<unsigned>((H.nnzL + 255) / 256), nb), 256, 0, st>>>(
@@ -784,8 +823,13 @@ int spchol_factor_batched(spchol_plan* p, int nbatch, const double* Ax, double* 
     if (!p || !Ax || !Lx || !info || nbatch < 0) { set_error("spchol_factor_batched: bad argument"); return SPCHOL_EINVAL; }
     CK(cudaSetDevice(p->device));
     const HostPlan& H = p->H;
-    const int chunk = std::min(batched_chunk(p), std::max(nbatch, 1));
+    if (H.n_large > 0 || H.world > 1 || H.nnzL > INT_MAX) {
+        set_error("spchol_factor_batched: only single-GPU plans whose fronts all fit the shared-memory front kernel (m <= 128)");
+        return SPCHOL_EINVAL;
+    }
     int rc;
+    if ((rc = batched_prepare(p))) return rc;
+    const int chunk = std::min(batched_chunk(p), std::max(nbatch, 1));
     if ((rc = batched_reserve(p, chunk))) return rc;
     double *dA = nullptr, *dLx = nullptr; int* dI = nullptr;
     CK(cudaMalloc(&dA, sizeof(double) * H.nnzA * p->b_chunk));

@@ -324,6 +324,31 @@ def test_batched_shared_pattern_vs_oracle():
     assert (L1.x == Lx[5]).all()
 
 
+@pytest.mark.skipif(os.environ.get("SPCHOL_TEST_STAGED") != "1",
+                    reason="k_front_path is staged: its source is validated on host threads (tests/test_path_emu.py); "
+                           "set SPCHOL_TEST_STAGED=1 to run it on the GPU")
+@pytest.mark.parametrize("relax,max_nu", [(2, 160), (2, 128), (1, 160)])
+def test_batched_path_groups_vs_oracle(monkeypatch, relax, max_nu):
+    monkeypatch.setenv("SPCHOL_BATCH_PATH", "1")
+    monkeypatch.setenv("SPCHOL_BATCH_PATH_NU", str(max_nu))
+    g = np.load(os.path.join(GOLD, "1138_bus.npz"))
+    n = int(g["n"])
+    A = sc.CscMatrix(n, g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A, relax=relax)                  # a fresh S: the batched setup reads the switches once per plan
+    nbatch = 300                                  # more matrices than CTAs resident at once on half the SMs
+    Ax = np.stack([synth.batch_values(A.p, A.i, A.x, b) for b in range(nbatch)])
+    bad = 17
+    Ax[bad, (A.p[1:] - 1)[500]] = -1.0
+    Lx, info = sc.chol_batched(S, Ax)
+    assert info[bad] == 501 and (np.delete(info, bad) == 0).all()
+    for b in (0, 1, 16, 18, 150, 299):
+        rc, Lp, Li, ref = po.chol(n, A.p, A.i, Ax[b])
+        assert rc == 0
+        assert rel_err(Lx[b], ref) <= REL_TOL
+    Lx2, info2 = sc.chol_batched(S, Ax)           # deterministic: fixed summation order
+    assert (Lx2[np.arange(nbatch) != bad] == Lx[np.arange(nbatch) != bad]).all()
+
+
 def test_batched_refuses_large_front_patterns():
     perm = synth.nd_perm(40, 40, 1)
     ti, tj, tx, n = synth.laplacian_triplets(40, 40, 1, perm)
