@@ -747,8 +747,7 @@ static int batched_prepare(spchol_plan* p) {
                 PathGroup* dg = nullptr; PathMember* dm = nullptr; PathChild* dc = nullptr; int* dp = nullptr;
                 if ((rc = upload(p, prog.groups, &dg)) || (rc = upload(p, prog.members, &dm)) || (rc = upload(p, prog.children, &dc)) ||
                     (rc = upload(p, prog.pos, &dp)) || (rc = upload(p, tab, &p->d_tri_tab))) return rc;
-                p->path = PathArrays{dg, static_cast<int>(prog.groups.size()), dm, dc, dp, p->d_tri_tab,
-                                     p->d_first, p->d_w, p->d_m, p->d_ld, p->d_panel_off};
+                p->path = PathArrays{dg, static_cast<int>(prog.groups.size()), dm, dc, dp, p->d_tri_tab};
                 p->path_smem = psmem; p->path_on = true; p->chain_level0 = l0;
                 p->b_ws_entries = prog.ws_entries;
                 CK(cudaFuncSetAttribute(k_front_path, cudaFuncAttributeMaxDynamicSharedMemorySize, psmem));

@@ -3,7 +3,7 @@
 // group lives in shared memory (packed lower triangle over the group's row set U) while its
 // member fronts are eliminated in place.
 //
-// The body is written against four macros (thread id, CTA barrier, read-only load, atomic min) so
+// The body is written against five macros (thread id, CTA barrier, warp barrier, read-only load, atomic min) so
 // that tests/cpp/path_emu.cpp can run the SAME source on host threads (SPCHOL_HOST_EMU) and
 // compare the factor with the oracle without a GPU.
 #pragma once
@@ -16,6 +16,7 @@
 #define PK_DEVICE inline
 #define PK_TID ::spchol::emu::tid()
 #define PK_SYNC() ::spchol::emu::sync()
+#define PK_SYNCWARP() ::spchol::emu::syncwarp()
 #define PK_LDG(p) (*(p))
 #define PK_ATOMIC_MIN(p, v) ::spchol::emu::atomic_min((p), (v))
 #define PK_RESTRICT
@@ -23,6 +24,7 @@
 #define PK_DEVICE __device__ __forceinline__
 #define PK_TID static_cast<int>(threadIdx.x)
 #define PK_SYNC() __syncthreads()
+#define PK_SYNCWARP() __syncwarp()
 #define PK_LDG(p) __ldg(p)
 #define PK_ATOMIC_MIN(p, v) atomicMin((p), (v))
 #define PK_RESTRICT __restrict__
@@ -43,14 +45,19 @@ struct PathArrays {                   // device pointers
     const PathChild* children;
     const int* pos;
     const int* tri_tab;               // tri_tab[e] = (ii << 16) | jj, pairs ii >= jj row by row (see k_front_chain)
-    const int* first; const int* w; const int* m; const int* ld;
-    const int64_t* panel_off;
 };
+
+constexpr int PK_SPOS_MAX = 256;      // rows of the largest front a program may hold
+constexpr int PK_NPF = PK_SPOS_MAX / PK_T;   // position-list entries a thread prefetches for the next front
 
 // column c of the packed lower triangle of order nu starts at pk_base(c, nu): entry (r, c), r >= c, is F[base + r]
 PK_DEVICE int pk_base(int c, int nu) { return c * nu - (c * (c - 1)) / 2 - c; }
 
-// F: nu_max (nu_max + 1) / 2 doubles of shared memory; spos: max_m ints of shared memory
+// F: nu_max (nu_max + 1) / 2 doubles of shared memory; spos: 2 * PK_SPOS_MAX ints of shared memory
+//
+// Barriers per group: 4 + 3 per member front.  Everything that is added into the frontal matrix before the
+// eliminations (panels of A, blocks from outside) is dealt to the PK_OWNERS column owners, so no two warps touch
+// the same column and the additions of one column happen in program order inside one warp.
 PK_DEVICE void front_path_body(const PathArrays pa, double* PK_RESTRICT L, double* PK_RESTRICT W, int* PK_RESTRICT info,
                                double* F, int* spos) {
     const int tid = PK_TID, lane = tid & 31, warp = tid >> 5;
@@ -62,95 +69,145 @@ PK_DEVICE void front_path_body(const PathArrays pa, double* PK_RESTRICT L, doubl
         const PathGroup g = pa.groups[gq];
         const int nu = g.nu;
         const int ne_u = nu * (nu + 1) / 2;
-        // 1. zero the frontal matrix of the group
+        const PathMember* PK_RESTRICT mem = pa.members + g.member0;
+        // 1. zero the frontal matrix of the group; stage the position list of the first member
         for (int e = tid; e < ne_u; e += PK_T) F[e] = 0.0;
-        PK_SYNC();
-        // 2. the members' columns of A (already scattered into their panels of the L buffer, zeros elsewhere)
-        for (int q = 0; q < g.nmember; ++q) {
-            const PathMember M = pa.members[g.member0 + q];
-            const int w = pa.w[M.s], m = pa.m[M.s], ld = pa.ld[M.s];
-            const double* PK_RESTRICT P = L + pa.panel_off[M.s];
-            const int* PK_RESTRICT ps = pa.pos + M.pos_off;
-            for (int j = warp; j < w; j += NW) {
-                double* col = F + pk_base(M.off + j, nu);
-                const double* src = P + static_cast<int64_t>(j) * ld;
-                for (int t = j + lane; t < m; t += 32) col[PK_LDG(ps + t)] = src[t];
-            }
+        {
+            const PathMember M0 = mem[0];
+            for (int t = tid; t < M0.m; t += PK_T) spos[t] = PK_LDG(pa.pos + M0.pos_off + t);
         }
         PK_SYNC();
-        // 3. contribution blocks from outside the group, in program order (fixed summation order)
-        for (int q = 0; q < g.nchild; ++q) {
-            const PathChild ch = pa.children[g.child0 + q];
-            const int mc = ch.mc;
+        // 2. the block that arrives in registers (all threads, any column)
+        if (g.carried_child >= 0) {
+            const PathChild ch = pa.children[g.child0 + g.carried_child];
             const int* PK_RESTRICT cp = pa.pos + ch.pos_off;
-            if (ch.carried) {
-                const int ne = mc * (mc + 1) / 2;
+            const int ne = ch.mc * (ch.mc + 1) / 2;
 #pragma unroll
-                for (int u = 0; u < PK_MAXE; ++u) {
-                    if (u * PK_T >= ne) break;
-                    const int e = tid + u * PK_T;
-                    if (e < ne) {
-                        const int t = PK_LDG(pa.tri_tab + e);
-                        F[pk_base(PK_LDG(cp + (t & 0xffff)), nu) + PK_LDG(cp + (t >> 16))] += carry[u];
-                    }
+            for (int u = 0; u < PK_MAXE; ++u) {
+                if (u * PK_T >= ne) break;
+                const int e = tid + u * PK_T;
+                if (e < ne) {
+                    const int t = PK_LDG(pa.tri_tab + e);
+                    F[pk_base(PK_LDG(cp + (t & 0xffff)), nu) + PK_LDG(cp + (t >> 16))] += carry[u];
                 }
-            } else {
+            }
+            PK_SYNC();
+        }
+        // 3. by column owner: the members' columns of A (scattered into their panels of the L buffer by k_assemble, zeros
+        //    elsewhere), then the blocks from outside the group in program order (fixed summation order per column)
+        for (int o = warp; o < PK_OWNERS; o += NW) {
+            for (int q = 0; q < g.nmember; ++q) {
+                const PathMember M = mem[q];
+                const double* PK_RESTRICT P = L + M.panel_off;
+                const int* PK_RESTRICT ps = pa.pos + M.pos_off;
+                for (int j = 0; j < M.w; ++j) {
+                    if ((M.off + j) % PK_OWNERS != o) continue;
+                    double* col = F + pk_base(M.off + j, nu);
+                    const double* src = P + static_cast<int64_t>(j) * M.ld;
+                    for (int t = j + lane; t < M.m; t += 32) col[PK_LDG(ps + t)] += src[t];
+                }
+            }
+            for (int q = 0; q < g.nchild; ++q) {
+                PK_SYNCWARP();                                   // an entry is added to by different lanes for different sources
+                if (q == g.carried_child) continue;
+                const PathChild* PK_RESTRICT chp = pa.children + g.child0 + q;
+                const int mc = chp->mc, c_lo = chp->optr[o], c_hi = chp->optr[o + 1];
+                if (c_lo == c_hi) continue;
+                const int* PK_RESTRICT cp = pa.pos + chp->pos_off;
+                const int* PK_RESTRICT cols = pa.pos + chp->cols_off;
                 const int ldc = (mc + 1) & ~1;
-                const double* PK_RESTRICT C = W + ch.src;
-                for (int jj = warp; jj < mc; jj += NW) {
+                const double* PK_RESTRICT C = W + chp->src;
+                for (int cq = c_lo; cq < c_hi; ++cq) {
+                    const int jj = PK_LDG(cols + cq);
                     double* col = F + pk_base(PK_LDG(cp + jj), nu);
                     const double* src = C + static_cast<int64_t>(jj) * ldc;
                     for (int ii = jj + lane; ii < mc; ii += 32) col[PK_LDG(cp + ii)] += src[ii];
                 }
             }
-            PK_SYNC();
         }
+        PK_SYNC();
         // 4. eliminate the members in place, bottom to top
         for (int q = 0; q < g.nmember; ++q) {
-            const PathMember M = pa.members[g.member0 + q];
-            const int w = pa.w[M.s], m = pa.m[M.s];
-            for (int t = tid; t < m; t += PK_T) spos[t] = PK_LDG(pa.pos + M.pos_off + t);
-            PK_SYNC();
-            // 4a. the front's own columns, right-looking inside the panel (rows = the front's true rows only)
-            for (int k = 0; k < w; ++k) {
-                double* colk = F + pk_base(M.off + k, nu);
-                const double d = colk[M.off + k];
-                if (d <= 0.0 && tid == 0) PK_ATOMIC_MIN(info, pa.first[M.s] + k + 1);   // reference test (chol.hpp:849)
-                const double piv = sqrt(d);
-                PK_SYNC();                                       // everyone has read the pivot
-                for (int t = k + 1 + tid; t < m; t += PK_T) { const int r = spos[t]; colk[r] = colk[r] / piv; }
-                if (tid == 0) colk[M.off + k] = piv;
-                PK_SYNC();
-                for (int j = k + 1 + warp; j < w; j += NW) {
-                    const double uj = colk[M.off + j];
-                    double* col = F + pk_base(M.off + j, nu);
-                    for (int t = j + lane; t < m; t += 32) { const int r = spos[t]; col[r] -= colk[r] * uj; }
-                }
-                PK_SYNC();
+            const PathMember M = mem[q];
+            const int w = M.w, m = M.m, off = M.off;
+            const int* sp = spos + (q & 1) * PK_SPOS_MAX;
+            // position list of the next member: loaded now, stored behind the arithmetic of this one
+            int nx[PK_NPF], nxm = 0;
+            if (q + 1 < g.nmember) {
+                const PathMember Mn = mem[q + 1];
+                nxm = Mn.m;
+#pragma unroll
+                for (int u = 0; u < PK_NPF; ++u) { const int t = tid + u * PK_T; nx[u] = t < nxm ? PK_LDG(pa.pos + Mn.pos_off + t) : 0; }
             }
-            // 4b. rank-w update of the front's contribution block, which is part of the group's matrix
+            // 4a. warp 0: Cholesky of the w x w diagonal block, in place
+            if (warp == 0) {
+                for (int k = 0; k < w; ++k) {
+                    double* colk = F + pk_base(off + k, nu);
+                    const double d = colk[off + k];
+                    if (d <= 0.0 && lane == 0) PK_ATOMIC_MIN(info, M.first + k + 1);   // reference test (chol.hpp:849)
+                    const double piv = sqrt(d);
+                    PK_SYNCWARP();                               // every lane has read the pivot
+                    for (int i = k + 1 + lane; i < w; i += 32) colk[off + i] = colk[off + i] / piv;
+                    if (lane == 0) colk[off + k] = piv;
+                    PK_SYNCWARP();
+                    // entries (i, j), k < j <= i < w: pair e of the (w - k - 1) triangle
+                    const int nt = w - k - 1;
+                    if (nt <= 32) {                              // few columns: one pair per lane and step
+                        const int np = nt * (nt + 1) / 2;
+                        for (int e = lane; e < np; e += 32) {
+                            const int t = PK_LDG(pa.tri_tab + e);
+                            const int i = off + k + 1 + (t >> 16), j = off + k + 1 + (t & 0xffff);
+                            F[pk_base(j, nu) + i] -= colk[i] * colk[j];
+                        }
+                    } else {                                     // wide front: column by column, lanes down the rows
+                        for (int j = off + k + 1; j < off + w; ++j) {
+                            const double uj = colk[j];
+                            double* colj = F + pk_base(j, nu);
+                            for (int i = j + lane; i < off + w; i += 32) colj[i] -= colk[i] * uj;
+                        }
+                    }
+                    PK_SYNCWARP();
+                }
+            }
+            PK_SYNC();
+            // 4b. rows below the diagonal block: x L11^T = a, one row per thread (a thread only touches its own row)
+            for (int t = w + tid; t < m; t += PK_T) {
+                const int r = sp[t];
+                for (int k = 0; k < w; ++k) {
+                    const double* ck = F + pk_base(off + k, nu);
+                    double v = ck[r];
+                    for (int j = 0; j < k; ++j) { const double* cj = F + pk_base(off + j, nu); v -= cj[r] * cj[off + k]; }
+                    F[pk_base(off + k, nu) + r] = v / ck[off + k];
+                }
+            }
+            PK_SYNC();
+            // 4c. rank-w update of the front's contribution block, which is part of the group's matrix
             for (int j = w + warp; j < m; j += NW) {
-                const int cj = spos[j];
+                const int cj = sp[j];
                 double* col = F + pk_base(cj, nu);
                 for (int t = j + lane; t < m; t += 32) {
-                    const int r = spos[t];
+                    const int r = sp[t];
                     double acc = col[r];
-                    for (int k = 0; k < w; ++k) { const double* ck = F + pk_base(M.off + k, nu); acc -= ck[r] * ck[cj]; }
+                    for (int k = 0; k < w; ++k) { const double* ck = F + pk_base(off + k, nu); acc -= ck[r] * ck[cj]; }
                     col[r] = acc;
                 }
+            }
+            if (q + 1 < g.nmember) {
+                int* spn = spos + ((q + 1) & 1) * PK_SPOS_MAX;
+#pragma unroll
+                for (int u = 0; u < PK_NPF; ++u) { const int t = tid + u * PK_T; if (t < nxm) spn[t] = nx[u]; }
             }
             PK_SYNC();
         }
         // 5. panels -> L buffer; block of the top front -> registers (the next group consumes it) or workspace
         for (int q = 0; q < g.nmember; ++q) {
-            const PathMember M = pa.members[g.member0 + q];
-            const int w = pa.w[M.s], m = pa.m[M.s], ld = pa.ld[M.s];
-            double* PK_RESTRICT P = L + pa.panel_off[M.s];
+            const PathMember M = mem[q];
+            double* PK_RESTRICT P = L + M.panel_off;
             const int* PK_RESTRICT ps = pa.pos + M.pos_off;
-            for (int j = warp; j < w; j += NW) {
+            for (int j = warp; j < M.w; j += NW) {
                 const double* col = F + pk_base(M.off + j, nu);
-                double* dst = P + static_cast<int64_t>(j) * ld;
-                for (int t = j + lane; t < m; t += 32) dst[t] = col[PK_LDG(ps + t)];
+                double* dst = P + static_cast<int64_t>(j) * M.ld;
+                for (int t = j + lane; t < M.m; t += 32) dst[t] = col[PK_LDG(ps + t)];
             }
         }
         const int mb = g.mb, c0 = nu - mb;
@@ -178,12 +235,11 @@ PK_DEVICE void front_path_body(const PathArrays pa, double* PK_RESTRICT L, doubl
 }
 
 #ifndef SPCHOL_HOST_EMU
-constexpr int PK_SPOS_MAX = 256;      // rows of the largest front a program may hold (build_path_program's max_nu <= this)
 // grid = matrices; dynamic shared memory = max_nu (max_nu + 1) / 2 doubles
 __global__ void __launch_bounds__(PK_T, 2) k_front_path(PathArrays pa, double* __restrict__ L, double* __restrict__ W,
                                                         int* __restrict__ info, int64_t lstride, int64_t wstride) {
     extern __shared__ double pk_F[];
-    __shared__ int pk_spos[PK_SPOS_MAX];
+    __shared__ int pk_spos[2 * PK_SPOS_MAX];
     front_path_body(pa, L + blockIdx.x * lstride, W + blockIdx.x * wstride, info + blockIdx.x, pk_F, pk_spos);
 }
 #endif

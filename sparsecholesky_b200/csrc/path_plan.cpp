@@ -82,6 +82,7 @@ bool build_path_program(const HostPlan& P, int level0, int max_nu, int64_t carry
             g.nmember = static_cast<int>(i1 - i0);
             g.mb = P.m[top] - P.w[top];
             g.carry_out = 0;
+            g.carried_child = -1;
             g.cb_dst = -1;
             const int gi = static_cast<int>(out.groups.size());
             // members and their row positions, top first (a member's below rows are located through its parent's list)
@@ -90,7 +91,8 @@ bool build_path_program(const HostPlan& P, int level0, int max_nu, int64_t carry
             for (size_t i = i1; i-- > i0;) {
                 const int s = path[i];
                 PathMember& M = mem[i - i0];
-                M.s = s; M.off = off; M.pad = 0;
+                M.s = s; M.off = off; M.pad = 0; M.pad2 = 0;
+                M.w = P.w[s]; M.m = P.m[s]; M.ld = P.ld[s]; M.first = P.first[s]; M.panel_off = P.panel_off[s];
                 M.pos_off = static_cast<int>(out.pos.size());
                 pos_of[s] = M.pos_off;
                 group_of[s] = gi;
@@ -127,6 +129,14 @@ bool build_path_program(const HostPlan& P, int level0, int max_nu, int64_t carry
                     std::vector<int> cp(mc);
                     for (int t = 0; t < mc; ++t) cp[t] = ps[r[t]];
                     out.pos.insert(out.pos.end(), cp.begin(), cp.end());
+                    // the block's columns grouped by the owner of the column of the frontal matrix they are added to:
+                    // owners never share a target column, so the blocks of a group need no barrier between them
+                    ch.cols_off = static_cast<int>(out.pos.size());
+                    ch.optr[0] = 0;
+                    for (int o = 0; o < PK_OWNERS; ++o) {
+                        for (int t = 0; t < mc; ++t) if (cp[t] % PK_OWNERS == o) out.pos.push_back(t);
+                        ch.optr[o + 1] = static_cast<int>(out.pos.size()) - ch.cols_off;
+                    }
                     ps = out.pos.data() + pos_of[s];
                     if (in_region(c)) {
                         const int gc = group_of[c];
@@ -134,6 +144,7 @@ bool build_path_program(const HostPlan& P, int level0, int max_nu, int64_t carry
                         PathGroup& G = out.groups[gc];
                         if (gc == gi - 1 && static_cast<int64_t>(mc) * (mc + 1) / 2 <= carry_cap) {
                             G.carry_out = 1; ch.carried = 1; ch.src = -1; ++out.n_carried;
+                            g.carried_child = static_cast<int>(out.children.size()) - g.child0;
                         } else {
                             G.cb_dst = out.ws_entries;
                             ch.src = G.cb_dst;

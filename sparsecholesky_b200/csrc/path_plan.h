@@ -23,27 +23,38 @@
 
 namespace spchol {
 
-struct PathMember {        // a front eliminated inside a group
+constexpr int PK_OWNERS = 8;    // columns of a group's frontal matrix are dealt round-robin to 8 owners (one warp each at 256 threads)
+
+struct alignas(16) PathMember {   // a front eliminated inside a group (self-contained: one descriptor load per front)
     int s;                 // front id
     int off;               // position in U of its first column
-    int pos_off;           // pos[pos_off .. pos_off + m_s): position in U of every row of the front
+    int pos_off;           // pos[pos_off .. pos_off + m): position in U of every row of the front
+    int w, m, ld;          // the front's columns, rows, leading dimension of its panel in the L buffer
+    int first;             // global index of its first column
     int pad;
+    int64_t panel_off;     // its panel in the L buffer
+    int64_t pad2;
 };
-struct PathChild {         // a contribution block added into the group's frontal matrix
+struct alignas(16) PathChild {    // a contribution block added into the group's frontal matrix
     int c;                 // child front
     int mc;                // order of its block
     int pos_off;           // pos[pos_off .. pos_off + mc): position in U of the block's rows
     int carried;           // 1: the block sits in the registers of the CTA (top of the previous group)
     int64_t src;           // else: workspace offset (column-major lower, ld = even(mc))
+    int cols_off;          // pos[cols_off .. cols_off + mc): the block's columns jj grouped by owner of their target column
+    int pad;
+    int optr[PK_OWNERS + 1];   // owner o handles cols[optr[o] .. optr[o + 1])
+    int pad3[3];
 };
-struct PathGroup {
+struct alignas(16) PathGroup {
     int nu;                // |U|
     int member0, nmember;
     int child0, nchild;
     int mb;                // order of the top front's contribution block = nu - sum of the members' widths
     int carry_out;         // 1: that block is handed to the next group in registers
-    int pad;
+    int carried_child;     // index (relative to child0) of the child that arrives in registers, -1: none
     int64_t cb_dst;        // else: workspace offset it is written to (-1: mb == 0)
+    int64_t pad2;
 };
 
 struct PathProgram {

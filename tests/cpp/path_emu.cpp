@@ -14,6 +14,7 @@
 #include <cstdint>
 #include <cstdio>
 #include <limits>
+#include <memory>
 #include <mutex>
 #include <string>
 #include <thread>
@@ -22,9 +23,11 @@
 namespace spchol { namespace emu {
 thread_local int t_tid = 0;
 std::barrier<>* g_barrier = nullptr;
+std::vector<std::barrier<>*> g_warp_barrier;
 std::mutex g_mu;
 inline int tid() { return t_tid; }
 inline void sync() { g_barrier->arrive_and_wait(); }
+inline void syncwarp() { g_warp_barrier[t_tid >> 5]->arrive_and_wait(); }
 inline void atomic_min(int* p, int v) { std::lock_guard<std::mutex> lk(g_mu); if (v < *p) *p = v; }
 } }
 
@@ -127,11 +130,14 @@ extern "C" int pathemu_factor(int n, const int* Ap, const int* Ai, const double*
         pa.groups = prog.groups.data(); pa.ngroups = static_cast<int>(prog.groups.size());
         pa.members = prog.members.data(); pa.children = prog.children.data(); pa.pos = prog.pos.data();
         pa.tri_tab = tab.data();
-        pa.first = H.first.data(); pa.w = H.w.data(); pa.m = H.m.data(); pa.ld = H.ld.data(); pa.panel_off = H.panel_off.data();
         std::vector<double> F(static_cast<size_t>(prog.max_nu) * (prog.max_nu + 1) / 2 + 1, std::numeric_limits<double>::quiet_NaN());
-        std::vector<int> spos(static_cast<size_t>(std::max(prog.max_m, 1)), -1);
+        if (prog.max_m > PK_SPOS_MAX) return fail("a front of the region exceeds the staged position list");
+        std::vector<int> spos(2 * PK_SPOS_MAX, -1);
         std::barrier<> bar(PK_T);
         emu::g_barrier = &bar;
+        std::vector<std::unique_ptr<std::barrier<>>> wbar;
+        emu::g_warp_barrier.clear();
+        for (int wq = 0; wq < PK_T / 32; ++wq) { wbar.push_back(std::make_unique<std::barrier<>>(32)); emu::g_warp_barrier.push_back(wbar.back().get()); }
         std::vector<std::thread> th;
         th.reserve(PK_T);
         for (int t = 0; t < PK_T; ++t)
