@@ -483,7 +483,8 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
     // the big host-side maps are only needed on the device from here on
     std::vector<int64_t>().swap(H.a_dest);
     std::vector<int64_t>().swap(H.l_src);
-    std::vector<int>().swap(H.rel);
+    // (plans the batched path accepts keep the relative indices: its group program is built from them on first use)
+    if (H.n_large > 0 || H.world > 1) std::vector<int>().swap(H.rel);
     if ((rc = dalloc(p, H.lbuf_entries, &p->dL))) return fail(rc);
     if ((rc = dalloc(p, H.ws_entries, &p->dW))) return fail(rc);
     if ((rc = dalloc(p, 1, &p->dinfo))) return fail(rc);

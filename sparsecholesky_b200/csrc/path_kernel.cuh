@@ -18,6 +18,7 @@
 #define PK_SYNC() ::spchol::emu::sync()
 #define PK_SYNCWARP() ::spchol::emu::syncwarp()
 #define PK_LDG(p) (*(p))
+#define PK_RSQRT(x) (1.0 / std::sqrt(x))
 #define PK_ATOMIC_MIN(p, v) ::spchol::emu::atomic_min((p), (v))
 #define PK_RESTRICT
 #else
@@ -26,6 +27,7 @@
 #define PK_SYNC() __syncthreads()
 #define PK_SYNCWARP() __syncwarp()
 #define PK_LDG(p) __ldg(p)
+#define PK_RSQRT(x) rsqrt(x)
 #define PK_ATOMIC_MIN(p, v) atomicMin((p), (v))
 #define PK_RESTRICT __restrict__
 #endif
@@ -53,13 +55,52 @@ constexpr int PK_NPF = PK_SPOS_MAX / PK_T;   // position-list entries a thread p
 // column c of the packed lower triangle of order nu starts at pk_base(c, nu): entry (r, c), r >= c, is F[base + r]
 PK_DEVICE int pk_base(int c, int nu) { return c * nu - (c * (c - 1)) / 2 - c; }
 
-// F: nu_max (nu_max + 1) / 2 doubles of shared memory; spos: 2 * PK_SPOS_MAX ints of shared memory
+// Cholesky of the w x w diagonal block of member M, in place, by ONE warp (only __syncwarp inside); the reciprocals of
+// the pivots go to rinv[0..w).  sqrt and reciprocal come from one rsqrt refined by a Newton step each (as k_potrf_inv):
+// no division on the serial path of a front.
+PK_DEVICE void pk_diag_factor(const PathMember& M, double* F, int nu, double* rinv, const int* PK_RESTRICT tri_tab,
+                              int* PK_RESTRICT info, int lane) {
+    const int w = M.w, off = M.off;
+    int bk = pk_base(off, nu);
+    for (int k = 0; k < w; ++k) {
+        double* colk = F + bk;
+        const double d = colk[off + k];
+        if (d <= 0.0 && lane == 0) PK_ATOMIC_MIN(info, M.first + k + 1);   // reference test (chol.hpp:849)
+        double y = PK_RSQRT(d);
+        double piv = d * y;
+        piv = fma(fma(-piv, piv, d), 0.5 * y, piv);          // sqrt(d), Newton-corrected
+        y = fma(fma(-piv, y, 1.0), y, y);                    // 1 / piv, Newton-corrected
+        PK_SYNCWARP();                                       // every lane has read the pivot
+        for (int i = k + 1 + lane; i < w; i += 32) colk[off + i] = colk[off + i] * y;
+        if (lane == 0) { colk[off + k] = piv; rinv[k] = y; }
+        PK_SYNCWARP();
+        const int nt = w - k - 1;
+        if (nt <= 32) {                                      // few columns: one pair per lane and step
+            const int np = nt * (nt + 1) / 2;
+            for (int e = lane; e < np; e += 32) {
+                const int t = PK_LDG(tri_tab + e);
+                const int i = off + k + 1 + (t >> 16), j = off + k + 1 + (t & 0xffff);
+                F[pk_base(j, nu) + i] -= colk[i] * colk[j];
+            }
+        } else {                                             // wide front: column by column, lanes down the rows
+            for (int j = off + k + 1; j < off + w; ++j) {
+                const double uj = colk[j];
+                double* colj = F + pk_base(j, nu);
+                for (int i = j + lane; i < off + w; i += 32) colj[i] -= colk[i] * uj;
+            }
+        }
+        PK_SYNCWARP();
+        bk += nu - (off + k) - 1;
+    }
+}
+
+// F: nu_max (nu_max + 1) / 2 doubles of shared memory; spos: 2 * PK_SPOS_MAX ints, srinv: PK_SPOS_MAX doubles of shared memory
 //
-// Barriers per group: 4 + 3 per member front.  Everything that is added into the frontal matrix before the
+// Barriers per group: 5 + 2 per member front.  Everything that is added into the frontal matrix before the
 // eliminations (panels of A, blocks from outside) is dealt to the PK_OWNERS column owners, so no two warps touch
 // the same column and the additions of one column happen in program order inside one warp.
 PK_DEVICE void front_path_body(const PathArrays pa, double* PK_RESTRICT L, double* PK_RESTRICT W, int* PK_RESTRICT info,
-                               double* F, int* spos) {
+                               double* F, int* spos, double* srinv) {
     const int tid = PK_TID, lane = tid & 31, warp = tid >> 5;
     constexpr int NW = PK_T / 32;
     double carry[PK_MAXE];
@@ -126,73 +167,100 @@ PK_DEVICE void front_path_body(const PathArrays pa, double* PK_RESTRICT L, doubl
             }
         }
         PK_SYNC();
-        // 4. eliminate the members in place, bottom to top
+        // 4. eliminate the members in place, bottom to top.  Per member: (b) one thread per row solves against the
+        //    diagonal block, barrier, (c) rank-w update of its contribution block by warps 1.. WHILE warp 0 updates
+        //    and factors the diagonal block of the NEXT member (the serial part of a front, off the critical path),
+        //    barrier.
+        if (warp == 0) pk_diag_factor(mem[0], F, nu, srinv, pa.tri_tab, info, lane);
+        PK_SYNC();
         for (int q = 0; q < g.nmember; ++q) {
             const PathMember M = mem[q];
             const int w = M.w, m = M.m, off = M.off;
             const int* sp = spos + (q & 1) * PK_SPOS_MAX;
-            // position list of the next member: loaded now, stored behind the arithmetic of this one
+            const bool last = q + 1 == g.nmember;
+            const int b0 = pk_base(off, nu);
+            // descriptor and position list of the next member: loaded now, used behind the arithmetic of this one
+            PathMember Mn = M;
             int nx[PK_NPF], nxm = 0;
-            if (q + 1 < g.nmember) {
-                const PathMember Mn = mem[q + 1];
+            if (!last) {
+                Mn = mem[q + 1];
                 nxm = Mn.m;
 #pragma unroll
                 for (int u = 0; u < PK_NPF; ++u) { const int t = tid + u * PK_T; nx[u] = t < nxm ? PK_LDG(pa.pos + Mn.pos_off + t) : 0; }
             }
-            // 4a. warp 0: Cholesky of the w x w diagonal block, in place
-            if (warp == 0) {
-                for (int k = 0; k < w; ++k) {
-                    double* colk = F + pk_base(off + k, nu);
-                    const double d = colk[off + k];
-                    if (d <= 0.0 && lane == 0) PK_ATOMIC_MIN(info, M.first + k + 1);   // reference test (chol.hpp:849)
-                    const double piv = sqrt(d);
-                    PK_SYNCWARP();                               // every lane has read the pivot
-                    for (int i = k + 1 + lane; i < w; i += 32) colk[off + i] = colk[off + i] / piv;
-                    if (lane == 0) colk[off + k] = piv;
-                    PK_SYNCWARP();
-                    // entries (i, j), k < j <= i < w: pair e of the (w - k - 1) triangle
-                    const int nt = w - k - 1;
-                    if (nt <= 32) {                              // few columns: one pair per lane and step
-                        const int np = nt * (nt + 1) / 2;
-                        for (int e = lane; e < np; e += 32) {
-                            const int t = PK_LDG(pa.tri_tab + e);
-                            const int i = off + k + 1 + (t >> 16), j = off + k + 1 + (t & 0xffff);
-                            F[pk_base(j, nu) + i] -= colk[i] * colk[j];
-                        }
-                    } else {                                     // wide front: column by column, lanes down the rows
-                        for (int j = off + k + 1; j < off + w; ++j) {
-                            const double uj = colk[j];
-                            double* colj = F + pk_base(j, nu);
-                            for (int i = j + lane; i < off + w; i += 32) colj[i] -= colk[i] * uj;
-                        }
-                    }
-                    PK_SYNCWARP();
-                }
-            }
-            PK_SYNC();
             // 4b. rows below the diagonal block: x L11^T = a, one row per thread (a thread only touches its own row)
             for (int t = w + tid; t < m; t += PK_T) {
                 const int r = sp[t];
+                int bk = b0;
                 for (int k = 0; k < w; ++k) {
-                    const double* ck = F + pk_base(off + k, nu);
-                    double v = ck[r];
-                    for (int j = 0; j < k; ++j) { const double* cj = F + pk_base(off + j, nu); v -= cj[r] * cj[off + k]; }
-                    F[pk_base(off + k, nu) + r] = v / ck[off + k];
+                    double v = F[bk + r];
+                    int bj = b0;
+                    for (int j = 0; j < k; ++j) { v -= F[bj + r] * F[bj + off + k]; bj += nu - (off + j) - 1; }
+                    F[bk + r] = v * srinv[k];
+                    bk += nu - (off + k) - 1;
                 }
             }
             PK_SYNC();
-            // 4c. rank-w update of the front's contribution block, which is part of the group's matrix
-            for (int j = w + warp; j < m; j += NW) {
-                const int cj = sp[j];
-                double* col = F + pk_base(cj, nu);
-                for (int t = j + lane; t < m; t += 32) {
-                    const int r = sp[t];
-                    double acc = col[r];
-                    for (int k = 0; k < w; ++k) { const double* ck = F + pk_base(off + k, nu); acc -= ck[r] * ck[cj]; }
-                    col[r] = acc;
+            // 4c. rank-w update.  nd = rows of this front that are columns of the next member: that corner is the next
+            //     member's diagonal block and belongs to warp 0
+            int nd = 0;
+            if (!last) { while (w + nd < m && sp[w + nd] < Mn.off + Mn.w) ++nd; }
+            if (warp == 0 && !last) {
+                const int np = nd * (nd + 1) / 2;
+                if (nd <= 32) {
+                    for (int e = lane; e < np; e += 32) {
+                        const int tt = PK_LDG(pa.tri_tab + e);
+                        const int r = sp[w + (tt >> 16)], cj = sp[w + (tt & 0xffff)];
+                        double acc = F[pk_base(cj, nu) + r];
+                        int bk = b0;
+                        for (int k = 0; k < w; ++k) { acc -= F[bk + r] * F[bk + cj]; bk += nu - (off + k) - 1; }
+                        F[pk_base(cj, nu) + r] = acc;
+                    }
+                } else {
+                    for (int j = w; j < w + nd; ++j) {
+                        const int cj = sp[j], bc = pk_base(cj, nu);
+                        for (int t = j + lane; t < w + nd; t += 32) {
+                            const int r = sp[t];
+                            double acc = F[bc + r];
+                            int bk = b0;
+                            for (int k = 0; k < w; ++k) { acc -= F[bk + r] * F[bk + cj]; bk += nu - (off + k) - 1; }
+                            F[bc + r] = acc;
+                        }
+                    }
+                }
+                PK_SYNCWARP();
+                pk_diag_factor(Mn, F, nu, srinv, pa.tri_tab, info, lane);
+            } else {
+                // the rest: groups of 4 columns per warp step, lanes down the rows; a loaded L(r, k) serves 4 updates
+                const int nwb = last ? NW : NW - 1, wb = last ? warp : warp - 1;
+                for (int j0 = w + 4 * wb; j0 < m; j0 += 4 * nwb) {
+                    int cj[4], bc[4];
+#pragma unroll
+                    for (int c = 0; c < 4; ++c) { cj[c] = sp[min(j0 + c, m - 1)]; bc[c] = pk_base(cj[c], nu); }
+                    const int t_begin = (j0 < w + nd) ? max(j0, w + nd - 3) : j0;      // rows above belong to warp 0's corner
+                    for (int t = t_begin + lane; t < m; t += 32) {
+                        const int r = sp[t];
+                        double acc[4];
+                        bool on[4];
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) {
+                            // entry (t, j0 + c) exists if t >= j0 + c, and is warp 0's if both indices are below w + nd
+                            on[c] = j0 + c < m && t >= j0 + c && !(t < w + nd && j0 + c < w + nd);
+                            acc[c] = on[c] ? F[bc[c] + r] : 0.0;
+                        }
+                        int bk = b0;
+                        for (int k = 0; k < w; ++k) {
+                            const double lr = F[bk + r];
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) acc[c] -= lr * F[bk + cj[c]];
+                            bk += nu - (off + k) - 1;
+                        }
+#pragma unroll
+                        for (int c = 0; c < 4; ++c) if (on[c]) F[bc[c] + r] = acc[c];
+                    }
                 }
             }
-            if (q + 1 < g.nmember) {
+            if (!last) {
                 int* spn = spos + ((q + 1) & 1) * PK_SPOS_MAX;
 #pragma unroll
                 for (int u = 0; u < PK_NPF; ++u) { const int t = tid + u * PK_T; if (t < nxm) spn[t] = nx[u]; }
@@ -240,7 +308,8 @@ __global__ void __launch_bounds__(PK_T, 2) k_front_path(PathArrays pa, double* _
                                                         int* __restrict__ info, int64_t lstride, int64_t wstride) {
     extern __shared__ double pk_F[];
     __shared__ int pk_spos[2 * PK_SPOS_MAX];
-    front_path_body(pa, L + blockIdx.x * lstride, W + blockIdx.x * wstride, info + blockIdx.x, pk_F, pk_spos);
+    __shared__ double pk_rinv[PK_SPOS_MAX];
+    front_path_body(pa, L + blockIdx.x * lstride, W + blockIdx.x * wstride, info + blockIdx.x, pk_F, pk_spos, pk_rinv);
 }
 #endif
 

@@ -15,6 +15,7 @@ bool build_path_program(const HostPlan& P, int level0, int max_nu, int64_t carry
     out.ws_entries = P.ws_entries;
     const int ns = P.ns;
     if (P.world != 1) throw std::runtime_error("build_path_program: single-rank plans only");
+    if (static_cast<int64_t>(P.rel.size()) != P.rel_off[ns]) throw std::runtime_error("build_path_program: the plan no longer holds its relative indices");
     auto in_region = [&](int s) { return P.level[s] >= level0; };
 
     // heavy child of every region front: the region child with the most rows (ties: larger id)

@@ -32,6 +32,7 @@ inline void atomic_min(int* p, int v) { std::lock_guard<std::mutex> lk(g_mu); if
 } }
 
 #define SPCHOL_HOST_EMU
+using std::max; using std::min; using std::fma;
 #include "../../sparsecholesky_b200/csrc/path_kernel.cuh"
 #include "../../sparsecholesky_b200/csrc/symbolic.h"
 
@@ -133,6 +134,7 @@ extern "C" int pathemu_factor(int n, const int* Ap, const int* Ai, const double*
         std::vector<double> F(static_cast<size_t>(prog.max_nu) * (prog.max_nu + 1) / 2 + 1, std::numeric_limits<double>::quiet_NaN());
         if (prog.max_m > PK_SPOS_MAX) return fail("a front of the region exceeds the staged position list");
         std::vector<int> spos(2 * PK_SPOS_MAX, -1);
+        std::vector<double> srinv(PK_SPOS_MAX, std::numeric_limits<double>::quiet_NaN());
         std::barrier<> bar(PK_T);
         emu::g_barrier = &bar;
         std::vector<std::unique_ptr<std::barrier<>>> wbar;
@@ -141,7 +143,7 @@ extern "C" int pathemu_factor(int n, const int* Ap, const int* Ai, const double*
         std::vector<std::thread> th;
         th.reserve(PK_T);
         for (int t = 0; t < PK_T; ++t)
-            th.emplace_back([&, t] { emu::t_tid = t; front_path_body(pa, Lb.data(), Wb.data(), &info, F.data(), spos.data()); });
+            th.emplace_back([&, t] { emu::t_tid = t; front_path_body(pa, Lb.data(), Wb.data(), &info, F.data(), spos.data(), srinv.data()); });
         for (auto& x : th) x.join();
         emu::g_barrier = nullptr;
         *info_out = info == 0x7f7f7f7f ? 0 : info;
