@@ -110,8 +110,8 @@ struct spchol_plan {
     double *bL = nullptr, *bW = nullptr; int* binfo = nullptr; int b_chunk = 0;   // batched factorization buffers
     // batched factorization: fronts of the levels >= chain_level0 are walked by one CTA per matrix (k_front_chain)
     int* d_chain_list = nullptr; int* d_tri_tab = nullptr; int chain_count = 0, chain_level0 = -1, chain_smem = 0; bool chain_ready = false;
-    // ... or, with SPCHOL_BATCH_PATH=1, by the path-group program (k_front_path, path_plan.h): staged, validated on the CPU by
-    // tests/test_path_emu.py, not yet the default
+    // ... or (default; SPCHOL_BATCH_PATH=0 falls back to the chain kernel) by the path-group program (k_front_path, path_plan.h),
+    // whose source is also run on host threads by tests/test_path_emu.py
     PathArrays path{}; int path_smem = 0; bool path_on = false;
     int64_t b_ws_entries = 0;     // workspace doubles per matrix of the batched buffers (>= H.ws_entries)
     double* dWinv = nullptr;      // inverses of the diagonal blocks of one launch (k_potrf_inv -> k_trsm_inv)
@@ -736,7 +736,7 @@ static int batched_prepare(spchol_plan* p) {
         for (int ii = 0; static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++ii)
             for (int jj = 0; jj <= ii && static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++jj) tab.push_back((ii << 16) | jj);
         static_assert(PK_MAXE * PK_T == CH_MAXE * CH_T, "k_front_path and k_front_chain share the pair table");
-        if (lst.size() >= 8 && path && atoi(path) != 0) {
+        if (lst.size() >= 8 && !(path && atoi(path) == 0)) {                 // SPCHOL_BATCH_PATH=0: the older chain kernel
             // path groups: |U| <= 160 rows keeps two CTAs per SM (103 KB each)
             const int max_nu = getenv("SPCHOL_BATCH_PATH_NU") ? atoi(getenv("SPCHOL_BATCH_PATH_NU")) : 160;
             PathProgram prog;

@@ -319,17 +319,18 @@ def test_batched_shared_pattern_vs_oracle():
         rc, Lp, Li, ref = po.chol(n, A.p, A.i, Ax[b])
         assert rc == 0
         assert rel_err(Lx[b], ref) <= REL_TOL
-    # same numbers as the one-matrix path (identical kernels and summation order)
+    # the one-matrix path factors front by front, the batched path eliminates runs of fronts in one frontal matrix
+    # (different summation order, division-free pivots): equal to rounding, and reproducible from call to call
     L1 = sc.chol(sc.CscMatrix(n, A.p, A.i, Ax[5]), S).value()
-    assert (L1.x == Lx[5]).all()
+    assert rel_err(Lx[5], L1.x) <= 1e-11
+    Lx2, info2 = sc.chol_batched(S, Ax)
+    ok = np.arange(nbatch) != bad
+    assert (Lx2[ok] == Lx[ok]).all() and (info2 == info).all()
 
 
-@pytest.mark.skipif(os.environ.get("SPCHOL_TEST_STAGED") != "1",
-                    reason="k_front_path is staged: its source is validated on host threads (tests/test_path_emu.py); "
-                           "set SPCHOL_TEST_STAGED=1 to run it on the GPU")
 @pytest.mark.parametrize("relax,max_nu", [(2, 160), (2, 128), (1, 160)])
 def test_batched_path_groups_vs_oracle(monkeypatch, relax, max_nu):
-    monkeypatch.setenv("SPCHOL_BATCH_PATH", "1")
+    # the path-group kernel at several group capacities (its source also runs on host threads: tests/test_path_emu.py)
     monkeypatch.setenv("SPCHOL_BATCH_PATH_NU", str(max_nu))
     g = np.load(os.path.join(GOLD, "1138_bus.npz"))
     n = int(g["n"])
@@ -347,6 +348,21 @@ def test_batched_path_groups_vs_oracle(monkeypatch, relax, max_nu):
         assert rel_err(Lx[b], ref) <= REL_TOL
     Lx2, info2 = sc.chol_batched(S, Ax)           # deterministic: fixed summation order
     assert (Lx2[np.arange(nbatch) != bad] == Lx[np.arange(nbatch) != bad]).all()
+
+
+def test_batched_chain_kernel_fallback(monkeypatch):
+    # SPCHOL_BATCH_PATH=0: the older one-front-at-a-time chain kernel stays available
+    monkeypatch.setenv("SPCHOL_BATCH_PATH", "0")
+    g = np.load(os.path.join(GOLD, "1138_bus.npz"))
+    n = int(g["n"])
+    A = sc.CscMatrix(n, g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A)
+    Ax = np.stack([synth.batch_values(A.p, A.i, A.x, b) for b in range(8)])
+    Lx, info = sc.chol_batched(S, Ax)
+    assert (info == 0).all()
+    for b in (0, 7):
+        rc, Lp, Li, ref = po.chol(n, A.p, A.i, Ax[b])
+        assert rc == 0 and rel_err(Lx[b], ref) <= REL_TOL
 
 
 def test_batched_refuses_large_front_patterns():
