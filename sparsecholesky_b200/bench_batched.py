@@ -57,6 +57,15 @@ def run(args, rank, world, local_rank, ClockSampler, METRIC, UNIT):
         step()
     stream.synchronize()
     assert int(dinfo.abs().max().item()) == 0
+    # parity spot check (the oracle as checker, outside the timed region): first, middle and last matrix of this shard
+    from oracle import pyoracle as po
+    parity = 0.0
+    for b in sorted({0, nb // 2, nb - 1}):
+        rc, _, _, ref = po.chol(A.n, A.p, A.i, Ax[b])
+        assert rc == 0
+        got = dLx[b].cpu().numpy()
+        parity = max(parity, float((np.abs(got - ref) / np.maximum(np.abs(ref), 1e-300)).max()))
+    assert parity <= 1e-10, f"batched factor differs from the oracle: {parity:.3e}"
     barrier()
     sampler = ClockSampler(local_rank); sampler.start()
     e0 = torch.cuda.Event(enable_timing=True); e1 = torch.cuda.Event(enable_timing=True)
@@ -132,7 +141,8 @@ def run(args, rank, world, local_rank, ClockSampler, METRIC, UNIT):
                 "config": {"workload": args.workload, "description": f"{nbatch} SPD matrices D_b A D_b sharing the 1138_bus pattern/S, "
                            f"batch sharded over {world} rank(s), no collective", "n": A.n, "nnz_A": nA, "nnz_L": nL, "nbatch": nbatch,
                            "flops": flops_total, "l2": f"inputs larger than L2 ({nb * (nA + nL) * 8 / 1e9:.2f} GB of values per rank per step)"},
-                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks}
+                "roofline": roofline, "cpu_baseline": cpu, "e2e": e2e, "gpu_launches": launches, "clocks": clocks,
+                "parity": {"max_rel_err_vs_oracle": parity, "bound": 1e-10, "matrices_checked": len({0, nb // 2, nb - 1})}}
         print(json.dumps(line), flush=True)
     if dist is not None:
         barrier()
