@@ -744,7 +744,8 @@ static int batched_prepare(spchol_plan* p) {
             try { ok = build_path_program(H, l0, max_nu, static_cast<int64_t>(PK_MAXE) * PK_T, prog); }
             catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
             const int psmem = prog.max_nu * (prog.max_nu + 1) / 2 * 8;
-            if (ok && prog.max_m <= PK_SPOS_MAX && psmem <= 227 * 1024) {
+            // dynamic + the kernel's static shared arrays (position lists, pivot reciprocals) within the 227 KB of a CTA
+            if (ok && prog.max_m <= PK_SPOS_MAX && psmem + 2 * PK_SPOS_MAX * 4 + PK_SPOS_MAX * 8 + 1024 <= 227 * 1024) {
                 PathGroup* dg = nullptr; PathMember* dm = nullptr; PathChild* dc = nullptr; int* dp = nullptr;
                 if ((rc = upload(p, prog.groups, &dg)) || (rc = upload(p, prog.members, &dm)) || (rc = upload(p, prog.children, &dc)) ||
                     (rc = upload(p, prog.pos, &dp)) || (rc = upload(p, tab, &p->d_tri_tab))) return rc;
