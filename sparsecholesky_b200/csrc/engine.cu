@@ -741,7 +741,12 @@ static int batched_prepare(spchol_plan* p) {
             const int max_nu = getenv("SPCHOL_BATCH_PATH_NU") ? atoi(getenv("SPCHOL_BATCH_PATH_NU")) : 160;
             PathProgram prog;
             bool ok = false;
-            try { ok = build_path_program(H, l0, max_nu, static_cast<int64_t>(PK_MAXE) * PK_T, prog); }
+            // development switches (unmeasured alternatives): SPCHOL_BATCH_GROUPS=1 cuts subtrees instead
+            // of paths, SPCHOL_BATCH_LEVEL0=<l> moves the boundary between the level kernels and the group program
+            const int gmode = getenv("SPCHOL_BATCH_GROUPS") ? atoi(getenv("SPCHOL_BATCH_GROUPS")) : 0;
+            int pl0 = l0;
+            if (getenv("SPCHOL_BATCH_LEVEL0")) pl0 = std::max(0, std::min(H.nlevels, atoi(getenv("SPCHOL_BATCH_LEVEL0"))));
+            try { ok = build_path_program(H, pl0, max_nu, static_cast<int64_t>(PK_MAXE) * PK_T, prog, gmode); }
             catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
             const int psmem = prog.max_nu * (prog.max_nu + 1) / 2 * 8;
             // dynamic + the kernel's static shared arrays (position lists, pivot reciprocals) within the 227 KB of a CTA
@@ -750,7 +755,7 @@ static int batched_prepare(spchol_plan* p) {
                 if ((rc = upload(p, prog.groups, &dg)) || (rc = upload(p, prog.members, &dm)) || (rc = upload(p, prog.children, &dc)) ||
                     (rc = upload(p, prog.pos, &dp)) || (rc = upload(p, tab, &p->d_tri_tab))) return rc;
                 p->path = PathArrays{dg, static_cast<int>(prog.groups.size()), dm, dc, dp, p->d_tri_tab};
-                p->path_smem = psmem; p->path_on = true; p->chain_level0 = l0;
+                p->path_smem = psmem; p->path_on = true; p->chain_level0 = pl0;
                 p->b_ws_entries = prog.ws_entries;
                 CK(cudaFuncSetAttribute(k_front_path, cudaFuncAttributeMaxDynamicSharedMemorySize, psmem));
             }

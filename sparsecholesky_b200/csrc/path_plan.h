@@ -72,6 +72,9 @@ struct PathProgram {
 // Builds the program for the fronts of the levels >= level0 of a single-rank plan.  max_nu bounds |U|
 // (shared memory: max_nu (max_nu + 1) / 2 doubles), carry_cap the entries of a block kept in registers.
 // Returns false (program left empty) when a front of the region has more than max_nu rows.
-bool build_path_program(const HostPlan& P, int level0, int max_nu, int64_t carry_cap, PathProgram& out);
+// mode 0: groups are runs of consecutive fronts of the heavy paths (what the measurements of DESIGN.md 4c use);
+// mode 1: groups are subtrees grown bottom-up (a group is any connected piece of the tree that contains its top --
+//         the kernel only needs the members in a topological order), fewer groups on bushy trees.
+bool build_path_program(const HostPlan& P, int level0, int max_nu, int64_t carry_cap, PathProgram& out, int mode = 0);
 
 }  // namespace spchol

@@ -81,9 +81,10 @@ void run_small(const HostPlan& H, std::vector<double>& Lb, std::vector<double>& 
 
 // relax: 1 = default amalgamation, 2 = the batched setting of spchol_symbolic_create_ex.
 // level0 < 0: the rule of the engine (levels from which on no level has more than 16 fronts).
+// mode: 0 = path groups, 1 = subtree groups (build_path_program).
 // stats[6]: level0, #groups, #members, #children, #carried, max |U|
 extern "C" int pathemu_factor(int n, const int* Ap, const int* Ai, const double* Ax, int relax, int level0, int max_nu,
-                              int carry_cap, double* Lx, int* info_out, int64_t* stats, char* err, int errlen) {
+                              int carry_cap, int mode, double* Lx, int* info_out, int64_t* stats, char* err, int errlen) {
     auto fail = [&](const std::string& msg) { std::snprintf(err, errlen, "%s", msg.c_str()); return -1; };
     try {
         Symbolic S;
@@ -106,7 +107,7 @@ extern "C" int pathemu_factor(int n, const int* Ap, const int* Ai, const double*
             while (level0 > 0 && cnt[level0 - 1] <= 16) --level0;
         }
         PathProgram prog;
-        if (!build_path_program(H, level0, max_nu, carry_cap, prog)) return fail("a front of the region exceeds max_nu");
+        if (!build_path_program(H, level0, max_nu, carry_cap, prog, mode)) return fail("a front of the region exceeds max_nu");
         if (stats) {
             stats[0] = level0; stats[1] = static_cast<int64_t>(prog.groups.size()); stats[2] = static_cast<int64_t>(prog.members.size());
             stats[3] = static_cast<int64_t>(prog.children.size()); stats[4] = prog.n_carried; stats[5] = prog.max_nu;

@@ -27,7 +27,7 @@ def _build(threads, carry_per_thread):
         subprocess.run(["g++", "-std=c++20", "-O2", "-fPIC", "-shared", "-pthread", f"-DPK_THREADS={threads}",
                         f"-DPK_CARRY_PER_THREAD={carry_per_thread}", "-o", so] + srcs, check=True)
     L = C.CDLL(so)
-    L.pathemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int,
+    L.pathemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                  C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_char_p, C.c_int]
     return L
 
@@ -44,13 +44,13 @@ def emu256():
     return _build(256, 28)
 
 
-def run(L, A, relax=2, level0=-1, max_nu=160, carry_cap=28 * 256):
+def run(L, A, relax=2, level0=-1, max_nu=160, carry_cap=28 * 256, mode=0):
     S = sc.schol(A, relax=relax)
     Lx = np.empty(S.nnz)
     info = C.c_int(0)
     st = np.zeros(6, np.int64)
     err = C.create_string_buffer(2048)
-    rc = L.pathemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, relax, level0, max_nu, carry_cap,
+    rc = L.pathemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, relax, level0, max_nu, carry_cap, mode,
                           Lx.ctypes.data, C.byref(info), st.ctypes.data, err, 2048)
     assert rc == 0, err.value.decode()
     return Lx, info.value, dict(zip(["level0", "groups", "members", "children", "carried", "max_nu"], (int(v) for v in st)))
@@ -93,8 +93,20 @@ def test_whole_tree_as_path_groups(emu, name, relax):
     S = sc.schol(A, relax=relax)
     mm = int(S.panel_layout()["m"].max())
     for max_nu in (mm, mm + 7, 4 * mm):
-        Lx, info, st = run(emu, A, relax=relax, level0=0, max_nu=max_nu)
-        assert info == 0 and relerr(Lx, ref) <= 1e-10, (max_nu, st)
+        groups = []
+        for mode in (0, 1):                      # path groups, subtree groups
+            Lx, info, st = run(emu, A, relax=relax, level0=0, max_nu=max_nu, mode=mode)
+            assert info == 0 and relerr(Lx, ref) <= 1e-10, (max_nu, mode, st)
+            groups.append(st["groups"])
+        assert groups[1] <= groups[0]            # subtrees never need more groups than paths
+
+
+def test_1138_bus_subtree_groups(emu):
+    A, ref = golden("1138_bus")
+    Lx0, info0, st0 = run(emu, A, mode=0)
+    Lx1, info1, st1 = run(emu, A, mode=1)
+    assert info1 == 0 and relerr(Lx1, ref) <= 1e-10
+    assert st1["members"] == 174 and st1["groups"] < st0["groups"]
 
 
 def test_upper_levels_only_on_a_grid(emu):
@@ -123,7 +135,7 @@ def test_front_larger_than_the_group_capacity_is_refused(emu):
     A, _ = golden("1138_bus")
     S = sc.schol(A, relax=2)
     err = C.create_string_buffer(512)
-    rc = emu.pathemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, 2, -1, 50, 0, np.empty(S.nnz).ctypes.data,
+    rc = emu.pathemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, 2, -1, 50, 0, 0, np.empty(S.nnz).ctypes.data,
                             C.byref(C.c_int(0)), None, err, 512)
     assert rc != 0 and b"max_nu" in err.value
 
@@ -143,12 +155,12 @@ import ctypes as C, numpy as np, sys
 sys.path.insert(0, {ROOT!r})
 g = np.load({os.path.join(GOLD, 'bcsstk01.npz')!r})
 L = C.CDLL({so!r})
-L.pathemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
+L.pathemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int, C.c_void_p,
                              C.POINTER(C.c_int), C.c_void_p, C.c_char_p, C.c_int]
 Ap, Ai, Ax = (np.ascontiguousarray(g[k]) for k in ("Ap", "Ai", "Ax"))
-for max_nu, cap in ((50, 7168), (45, 0)):      # carried blocks / blocks through the workspace
+for max_nu, cap, mode in ((50, 7168, 0), (45, 0, 0), (50, 7168, 1)):      # carried blocks / through the workspace / subtree groups
     Lx = np.empty(g["Lx"].size); info = C.c_int(0); err = C.create_string_buffer(512)
-    rc = L.pathemu_factor(int(g["n"]), Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data, 1, 0, max_nu, cap, Lx.ctypes.data,
+    rc = L.pathemu_factor(int(g["n"]), Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data, 1, 0, max_nu, cap, mode, Lx.ctypes.data,
                           C.byref(info), None, err, 512)
     assert rc == 0 and info.value == 0, err.value
     assert float((np.abs(Lx - g["Lx"]) / np.abs(g["Lx"])).max()) <= 1e-10
