@@ -1,16 +1,18 @@
 #!/bin/bash
-# first GPU call of the next session: does the staged path-group kernel (SPCHOL_BATCH_PATH=1) work on the device,
-# and what does it buy on config 5?   gpurun --timeout 900 -- bash tools/run_staged.sh
+# config 5 (batched) variant sweep for the next GPU session -- every variant below is validated on host threads
+# (tests/test_path_emu.py) but only the default has been timed:   gpurun --timeout 900 -- bash tools/run_staged.sh
 mkdir -p gpurun_out
-SPCHOL_TEST_STAGED=1 timeout 600 python -m pytest tests/test_chol_gpu.py -q -k "path_groups or batched" > gpurun_out/staged_tests.log 2>&1
-echo "staged tests rc=$?"; tail -n 5 gpurun_out/staged_tests.log
 B="python bench.py --workload batched_1138 --steps 3 --warmup 3 --no-e2e --no-cpu-baseline"
-timeout 600 $B > gpurun_out/batched_chain.json 2> gpurun_out/batched_chain.err; echo "chain rc=$?"
-for NU in 128 160 200; do
-  SPCHOL_BATCH_PATH=1 SPCHOL_BATCH_PATH_NU=$NU timeout 600 $B > gpurun_out/batched_path_$NU.json 2> gpurun_out/batched_path_$NU.err; echo "path nu=$NU rc=$?"
-done
-for f in gpurun_out/batched_chain.json gpurun_out/batched_path_*.json; do echo "$f: $(grep -o '"ms_per_step": [0-9.]*' $f | head -1)"; done
-# where the time goes inside the new kernel: one capture of k_front_path (a 2048-matrix batch keeps the replay short)
-SPCHOL_BATCH_PATH=1 timeout 600 ncu --set full --clock-control none --import-source on -k regex:k_front_path -c 1 -f -o gpurun_out/prof_front_path \
-  python bench.py --workload batched_1138 --nbatch 2048 --steps 1 --warmup 3 --no-e2e --no-cpu-baseline > gpurun_out/ncu_front_path.log 2>&1
-echo "ncu rc=$?"; ls -la gpurun_out/prof_front_path.ncu-rep 2>/dev/null
+run() { name=$1; shift; env "$@" timeout 120 $B > gpurun_out/batched_$name.json 2> gpurun_out/batched_$name.err
+        echo "$name rc=$? $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/batched_$name.json | head -1) $(grep -o '"max_rel_err_vs_oracle": [0-9.e-]*' gpurun_out/batched_$name.json)"; }
+run default            SPCHOL_BATCH_PATH=1
+run chain              SPCHOL_BATCH_PATH=0
+for NU in 128 200 235; do run nu$NU SPCHOL_BATCH_PATH_NU=$NU; done
+run subtree            SPCHOL_BATCH_GROUPS=1
+run subtree_nu200      SPCHOL_BATCH_GROUPS=1 SPCHOL_BATCH_PATH_NU=200
+for L0 in 2 1 0; do run subtree_level$L0 SPCHOL_BATCH_GROUPS=1 SPCHOL_BATCH_LEVEL0=$L0; done
+# v3 of the kernel (host-computed corner size, one warp barrier per pivot, warp-uniform unmasked fast path)
+if patch -p1 --dry-run < tools/path_kernel_v3.patch > /dev/null 2>&1; then
+  patch -p1 < tools/path_kernel_v3.patch > /dev/null && python -m sparsecholesky_b200.build --force > /dev/null && run v3 SPCHOL_BATCH_PATH=1 && run v3_subtree SPCHOL_BATCH_GROUPS=1
+  patch -p1 -R < tools/path_kernel_v3.patch > /dev/null && python -m sparsecholesky_b200.build --force > /dev/null
+fi
