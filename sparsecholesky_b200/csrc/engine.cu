@@ -131,6 +131,7 @@ struct spchol_plan {
     // the L buffer that are final once a given level has run, copied on a third stream while the upper levels compute
     std::vector<std::vector<std::pair<int64_t, int64_t>>> export_runs;   // [level] -> (offset, count) in doubles
     std::vector<cudaEvent_t> export_ev;
+    std::vector<cudaEvent_t> export_mark_ev;        // one per OP_EXPORT op
     cudaStream_t stream3 = nullptr;
     // triangular solves (built on first use): per (level, block step) slices of the task arrays
     struct SolveStep { int b0, bn, u0, un, g0, gn, smem; };
@@ -191,7 +192,7 @@ int export_prepare(spchol_plan* p) {
     while (cut > 0 && above + cnt[cut - 1] <= 512) { --cut; above += cnt[cut]; }
     std::vector<std::vector<std::pair<int64_t, int64_t>>> raw(H.nlevels);
     for (int s = 0; s < H.ns; ++s) {
-        if (!H.holds(s)) continue;
+        if (!H.holds(s) || H.front_marked[s]) continue;       // marked fronts are read back block column by block column (OP_EXPORT)
         const int bucket = H.level[s] >= cut ? H.level[s] : std::max(cut - 1, 0);
         raw[bucket].push_back({H.panel_off[s], static_cast<int64_t>(H.ld[s]) * H.w[s]});
     }
@@ -206,6 +207,10 @@ int export_prepare(spchol_plan* p) {
     }
     p->export_ev.resize(H.nlevels + 1, nullptr);
     for (auto& e : p->export_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    int n_marks = 0;
+    for (const Op& op : H.ops) if (op.kind == OP_EXPORT) ++n_marks;
+    p->export_mark_ev.resize(n_marks, nullptr);
+    for (auto& e : p->export_mark_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
     CK(cudaStreamCreateWithFlags(&p->stream3, cudaStreamNonBlocking));
     return 0;
 }
@@ -242,6 +247,7 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
     static const int gemm_swizzle = getenv("SPCHOL_GEMM_SWIZZLE") ? atoi(getenv("SPCHOL_GEMM_SWIZZLE")) : 3;
     if (prof) host_out = nullptr;
     int level_next = 0;                  // levels below this one have been handed to the copy stream
+    size_t n_mark = 0;                   // OP_EXPORT ops seen so far
     auto levels_done = [&](int upto) -> int {          // every op of the levels < upto has been issued
         for (; level_next < upto; ++level_next) {
             const auto& runs = p->export_runs[level_next];
@@ -270,6 +276,20 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
                 if (t0) { cudaEvent_t te; cudaEventCreate(&te); cudaEventRecord(te, sts[op.stream]); tev.push_back(te);
                           tinfo.push_back(op.begin); tinfo.push_back(op.stream); tinfo.push_back(op.level); }
             } else CK(cudaStreamWaitEvent(sts[op.stream], e, 0));
+            continue;
+        }
+        if (op.kind == OP_EXPORT) {
+            if (host_out) {
+                cudaEvent_t e = p->export_mark_ev[n_mark];
+                CK(cudaEventRecord(e, sts[op.stream]));
+                CK(cudaStreamWaitEvent(p->stream3, e, 0));
+                for (int i = 0; i < op.count; ++i) {
+                    const ExportTask& t = H.export_tasks[op.begin + i];
+                    CK(cudaMemcpyAsync(host_out + t.off, p->dL + t.off, static_cast<size_t>(t.count) * sizeof(double),
+                                       cudaMemcpyDeviceToHost, p->stream3));
+                }
+            }
+            ++n_mark;
             continue;
         }
         st = sts[op.stream];
@@ -579,6 +599,7 @@ void spchol_plan_destroy(spchol_plan* p) {
     for (auto& e : p->prof_ev) cudaEventDestroy(e);
     for (auto& e : p->ring) if (e) cudaEventDestroy(e);
     for (auto& e : p->export_ev) if (e) cudaEventDestroy(e);
+    for (auto& e : p->export_mark_ev) if (e) cudaEventDestroy(e);
     if (p->stream3) cudaStreamDestroy(p->stream3);
     if (p->stream2) cudaStreamDestroy(p->stream2);
     if (p->stream) cudaStreamDestroy(p->stream);

@@ -167,6 +167,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     }
     map_fronts(ns, P.parent.data(), P.w.data(), P.m.data(), world, opt.dist_min_w, P.own_lo, P.own_n, P.rank_load);
     P.own_idx.assign(ns, -1);
+    P.front_marked.assign(ns, 0);
     int64_t off = 0, roff = 0;
     for (int s = 0; s < ns; ++s) {
         if (rank >= P.own_lo[s] && rank < P.own_lo[s] + P.own_n[s]) {
@@ -464,6 +465,18 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                 }
                 c.count = static_cast<int>(P.gemm_tasks.size()) - c.begin;
                 if (c.count) P.ops.push_back(c);
+            }
+            if (opt.export_mark_w > 0) {        // block column J of the wide fronts is final: its read-back may start
+                Op ex{}; ex.kind = OP_EXPORT; ex.begin = static_cast<int>(P.export_tasks.size()); ex.level = lv; ex.stream = sp;
+                for (int s : large) {
+                    const int w = P.w[s], ld = P.ld[s];
+                    const int KB = J * NB, KE = std::min(KB + NB, w);
+                    if (w < opt.export_mark_w || KB >= w) continue;
+                    P.export_tasks.push_back({P.panel_off[s] + static_cast<int64_t>(KB) * ld, static_cast<int64_t>(KE - KB) * ld});
+                    P.front_marked[s] = 1;
+                }
+                ex.count = static_cast<int>(P.export_tasks.size()) - ex.begin;
+                if (ex.count) P.ops.push_back(ex);
             }
             if (pipe) { const int e = ev_record(1, lv); ev_wait(0, e, lv); }  // panels of step J are final
             Op un{}, ur{};

@@ -52,7 +52,8 @@ struct CopyTask {
 // the record with the same id, which precedes it in program order).  Program order is itself a
 // valid serial order, so a single-stream replay (profiling, the host simulator) is correct.
 enum OpKind : int { OP_SMALL = 0, OP_ZERO = 1, OP_EXTADD = 2, OP_POTRF = 3, OP_TRSM = 4, OP_GEMM = 5, OP_COMM = 6, OP_COPY = 7,
-                    OP_EV_RECORD = 8, OP_EV_WAIT = 9 };
+                    OP_EV_RECORD = 8, OP_EV_WAIT = 9,
+                    OP_EXPORT = 10 };   // ranges of the L buffer that are final from here on (read-back of wide fronts, see ExportTask)
 constexpr int kEventRing = 64;      // the engine keeps this many CUDA events; event id -> slot id % kEventRing
 struct Op {
     int kind;
@@ -65,6 +66,11 @@ struct Op {
     int stream;         // 0 or 1
 };
 
+// A block column of a wide front is final as soon as its panel phase has run, long before the front (let alone its
+// level) is complete: spchol_factor_lbuf starts its read-back there, so that the copy of the top fronts (2.2 GB for
+// the root of 128^3) overlaps their own trailing updates instead of trailing the factorization.
+struct ExportTask { int64_t off, count; };
+
 struct PlanOptions {
     int small_max_m = 128;     // fronts with m <= this are factored whole in shared memory (160 -> 128: 2D 1024^2 9.4 -> 9.0 ms)
     int nb = 128;              // diagonal block of the blocked panel factorization (<= 128, the potrf kernel's limit)
@@ -76,6 +82,7 @@ struct PlanOptions {
     int defer_cb_add = 1;      // 1: large fronts never zero their contribution block: the Schur complement is stored (C = -A B^T)
                                // and the children's contributions to it are extend-added afterwards
     int lookahead = 1;         // 1: panel work of large fronts on stream 1, overlapped with the trailing update (see Op)
+    int export_mark_w = 1024;  // fronts at least this wide announce every finished block column (OP_EXPORT); 0: never
     // multi-GPU (one plan per rank, every rank builds the same global mapping):
     int rank = 0, world = 1;
     int dist_NB = 256;         // block-column width of a front that is factored by a rank group
@@ -114,6 +121,8 @@ struct HostPlan {
     std::vector<GemmTask> gemm_tasks;
     std::vector<CommTask> comm_tasks;
     std::vector<CopyTask> copy_tasks;
+    std::vector<ExportTask> export_tasks;
+    std::vector<char> front_marked;  // per front: 1 if all of its panel is announced by OP_EXPORT ops (not by its level)
     std::vector<Op> ops;
     int n_events = 0;                // event ids handed out (OP_EV_RECORD count)
     int max_potrf_slots = 0;

@@ -28,6 +28,7 @@ inline int even_up(int v) { return (v + 1) & ~1; }
 struct Rank {
     HostPlan H;
     std::vector<double> L, W;
+    std::vector<double> early;    // what a read-back started at the OP_EXPORT marks would have seen (NaN elsewhere)
     // one program counter per stream (lane): q[s] lists the indices of the ops of stream s in program order
     std::vector<size_t> q[2];
     size_t pc[2] = {0, 0};
@@ -151,7 +152,7 @@ std::string describe(const CommTask& t, int rank) {
 // missing event dependency in the look-ahead program shows up as a wrong result in one of them.
 extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double* Ax, int relax, int world,
                               int dist_NB, int dist_min_w, int small_max_m, int nb, int NB, int order,
-                              double* Lx, int* info_out, int64_t* stats /* 5: #dist fronts, #transfers, doubles moved, max ws, #stream events */,
+                              double* Lx, int* info_out, int64_t* stats /* 6: #dist fronts, #transfers, doubles moved, max ws, #stream events, #read-back marks */,
                               char* err, int errlen) {
     auto fail = [&](const std::string& msg) { std::snprintf(err, errlen, "%s", msg.c_str()); return -1; };
     try {
@@ -168,16 +169,18 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
             if (small_max_m > 0) opt.small_max_m = small_max_m;
             if (nb > 0) opt.nb = nb;
             if (NB > 0) { opt.NB = NB; opt.NB_wide = 2 * NB; opt.wide_w = 3 * NB; }    // both outer-block widths get exercised
+            if (NB > 0) opt.export_mark_w = 2 * NB;                                    // read-back marks at test scale
             build_plan(S, opt, R[r].H);
             const HostPlan& H = R[r].H;
             for (size_t i = 0; i < H.ops.size(); ++i) R[r].q[H.ops[i].stream & 1].push_back(i);
             R[r].ev_done.assign(static_cast<size_t>(H.n_events) + 1, 0);
             // poison instead of zero where the engine does not clear: the workspace is never memset
             R[r].L.assign(static_cast<size_t>(H.lbuf_entries), 0.0);
+            R[r].early.assign(static_cast<size_t>(H.lbuf_entries), std::numeric_limits<double>::quiet_NaN());
             R[r].W.assign(static_cast<size_t>(H.ws_entries), std::numeric_limits<double>::quiet_NaN());
             for (int64_t i = 0; i < H.nnzA; ++i) if (H.a_dest[i] >= 0) R[r].L[H.a_dest[i]] = Ax[i];
         }
-        if (stats) { stats[0] = stats[1] = stats[2] = stats[3] = stats[4] = 0; }
+        if (stats) { stats[0] = stats[1] = stats[2] = stats[3] = stats[4] = stats[5] = 0; }
         for (int r = 0; r < world; ++r) if (stats) {
             stats[0] = std::max<int64_t>(stats[0], R[r].H.n_dist);
             stats[1] += static_cast<int64_t>(R[r].H.comm_tasks.size());
@@ -256,6 +259,12 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
                             for (int j = 0; j < c.cols; ++j) for (int ii = 0; ii < c.rows; ++ii) dst[ii + static_cast<size_t>(j) * c.ldd] = src[ii + static_cast<size_t>(j) * c.lds];
                         }
                         break;
+                    case OP_EXPORT:
+                        for (int i = 0; i < op.count; ++i) {
+                            const ExportTask& t = H.export_tasks[op.begin + i];
+                            std::memcpy(k.early.data() + t.off, k.L.data() + t.off, static_cast<size_t>(t.count) * sizeof(double));
+                        }
+                        break;
                     case OP_EV_RECORD: k.ev_done[op.begin] = 1; break;
                     case OP_EV_WAIT: break;
                     default: return fail("unknown op kind");
@@ -321,6 +330,23 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
                 for (int r = 0; r < world; ++r) msg += " " + describe_rank(r);
                 return fail(msg);
             }
+        }
+        // read-back marks: what was announced as final must be what the factorization ends with, bit for bit, and a
+        // marked front must be announced completely (its level no longer reads it back)
+        for (int r = 0; r < world; ++r) {
+            const HostPlan& H = R[r].H;
+            std::vector<int64_t> covered(H.ns, 0);
+            for (const ExportTask& t : H.export_tasks) {
+                if (std::memcmp(R[r].early.data() + t.off, R[r].L.data() + t.off, static_cast<size_t>(t.count) * sizeof(double)) != 0)
+                    return fail("a range announced by OP_EXPORT changed afterwards (rank " + std::to_string(r) + ", offset " + std::to_string(t.off) + ")");
+                for (int s = 0; s < H.ns; ++s)
+                    if (H.holds(s) && t.off >= H.panel_off[s] && t.off < H.panel_off[s] + static_cast<int64_t>(H.ld[s]) * H.w[s]) { covered[s] += t.count; break; }
+            }
+            for (int s = 0; s < H.ns; ++s) {
+                const int64_t want = H.front_marked[s] ? static_cast<int64_t>(H.ld[s]) * H.w[s] : 0;
+                if (covered[s] != want) return fail("front " + std::to_string(s) + ": OP_EXPORT covers " + std::to_string(covered[s]) + " of " + std::to_string(want) + " entries");
+            }
+            if (stats) stats[5] += static_cast<int64_t>(H.export_tasks.size());
         }
         int info = std::numeric_limits<int>::max();
         for (int r = 0; r < world; ++r) info = std::min(info, R[r].info);

@@ -42,7 +42,7 @@ def run_sim(L, A, world, relax=1, dist_NB=0, dist_min_w=0, small_max_m=0, nb=0, 
     for order in (0, 1, 2):
         Lx = np.empty(S.nnz)
         info = C.c_int(0)
-        st = np.zeros(5, np.int64)
+        st = np.zeros(6, np.int64)
         err = C.create_string_buffer(2048)
         rc = L.plansim_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, relax, world, dist_NB, dist_min_w,
                               small_max_m, nb, NB, order, Lx.ctypes.data, C.byref(info), st.ctypes.data, err, 2048)
@@ -51,7 +51,7 @@ def run_sim(L, A, world, relax=1, dist_NB=0, dist_min_w=0, small_max_m=0, nb=0, 
     for Lx, info_v in out[1:]:
         assert info_v == out[0][1] and np.array_equal(Lx, out[0][0], equal_nan=True), "stream interleavings disagree"
     Lx, info = out[0]
-    return S, Lx, info, dict(zip(["n_dist", "transfers", "doubles", "ws", "events"], (int(v) for v in st)))
+    return S, Lx, info, dict(zip(["n_dist", "transfers", "doubles", "ws", "events", "marks"], (int(v) for v in st)))
 
 
 def check(A, Lx, tol=1e-10):
@@ -98,6 +98,10 @@ def test_lookahead_program_and_tree_parallel_amalgamation(sim, world):
     S, Lx, info, st = run_sim(sim, A, world, relax=3, dist_NB=8, dist_min_w=16, small_max_m=24, nb=8, NB=16)
     assert info == 0 and st["events"] > 4
     check(A, Lx)
+    # wide local fronts announce their finished block columns (OP_EXPORT): the simulator checks that an announced range
+    # never changes afterwards, under all three stream interleavings, and that marked fronts are announced completely
+    if world == 1:
+        assert st["marks"] > 4
 
 
 @pytest.mark.parametrize("world", [2, 4])
