@@ -455,6 +455,7 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
         if (const char* v = getenv("SPCHOL_NB")) { const int x = atoi(v); if (x >= 128) opt.NB = x; }
         if (const char* v = getenv("SPCHOL_NB_WIDE")) { const int x = atoi(v); if (x >= 128) opt.NB_wide = x; }
         if (const char* v = getenv("SPCHOL_WIDE_W")) { const int x = atoi(v); if (x >= 1) opt.wide_w = x; }
+        if (const char* v = getenv("SPCHOL_EXPORT_MARK_W")) { const int x = atoi(v); if (x >= 0) opt.export_mark_w = x; }   // 0: read-back by levels only
         if (dist_opts) {
             if (dist_opts[0] > 0) opt.dist_NB = dist_opts[0];
             if (dist_opts[1] > 0) opt.dist_min_w = dist_opts[1];
