@@ -82,7 +82,8 @@ struct PlanOptions {
     int defer_cb_add = 1;      // 1: large fronts never zero their contribution block: the Schur complement is stored (C = -A B^T)
                                // and the children's contributions to it are extend-added afterwards
     int lookahead = 1;         // 1: panel work of large fronts on stream 1, overlapped with the trailing update (see Op)
-    int export_mark_w = 1024;  // fronts at least this wide announce every finished block column (OP_EXPORT); 0: never
+    int export_mark_w = 0;     // > 0: fronts at least this wide announce every finished block column (OP_EXPORT).  Staged:
+                               // checked by the plan simulator, not yet run on a GPU -- SPCHOL_EXPORT_MARK_W=1024 enables it
     // multi-GPU (one plan per rank, every rank builds the same global mapping):
     int rank = 0, world = 1;
     int dist_NB = 256;         // block-column width of a front that is factored by a rank group

@@ -255,12 +255,15 @@ def test_solve_large_fronts_end_to_end():
     assert np.abs(X - Xtrue).max() <= 1e-9
 
 
-def test_factor_lbuf_overlapped_readback_matches_plain_copy():
+@pytest.mark.parametrize("mark_w", [0, pytest.param(1024, marks=pytest.mark.skipif(
+    os.environ.get("SPCHOL_TEST_STAGED") != "1", reason="per-block-column read-back marks are staged (plan simulator only so far)"))])
+def test_factor_lbuf_overlapped_readback_matches_plain_copy(monkeypatch, mark_w):
     """spchol_factor_lbuf: with pinned host memory the panels are read back level by level on a copy stream while
     the upper levels are still being factored; with pageable memory there is one copy at the end.  Same bytes."""
     import ctypes as C
     from sparsecholesky_b200._lib import check, lib, ptr
     L = lib()
+    monkeypatch.setenv("SPCHOL_EXPORT_MARK_W", str(mark_w))     # read when the plan is created
     dims = (40, 40, 40)
     perm = synth.nd_perm(*dims)
     ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)

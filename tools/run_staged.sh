@@ -16,3 +16,8 @@ if patch -p1 --dry-run < tools/path_kernel_v3.patch > /dev/null 2>&1; then
   patch -p1 < tools/path_kernel_v3.patch > /dev/null && python -m sparsecholesky_b200.build --force > /dev/null && run v3 SPCHOL_BATCH_PATH=1 && run v3_subtree SPCHOL_BATCH_GROUPS=1
   patch -p1 -R < tools/path_kernel_v3.patch > /dev/null && python -m sparsecholesky_b200.build --force > /dev/null
 fi
+# read-back marks (OP_EXPORT, staged): bytes first, then the e2e number with and without
+SPCHOL_TEST_STAGED=1 timeout 300 python -m pytest tests/test_chol_gpu.py -q -k "overlapped_readback" > gpurun_out/staged_marks.log 2>&1; echo "marks test rc=$?"; tail -n 3 gpurun_out/staged_marks.log
+timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/bench_marks_off.json 2> gpurun_out/bench_marks_off.err; echo "marks off rc=$?"
+SPCHOL_EXPORT_MARK_W=1024 timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/bench_marks_on.json 2> gpurun_out/bench_marks_on.err; echo "marks on rc=$?"
+for f in gpurun_out/bench_marks_off.json gpurun_out/bench_marks_on.json; do echo "$f: $(grep -o '"e2e": {"value": [0-9.]*, "unit": "GFLOP/s", "ms_per_step": [0-9.]*' $f)"; done
