@@ -91,11 +91,12 @@ def run(args, rank, world, local_rank, ClockSampler, METRIC, UNIT):
         pass
     hbm = float(peaks.get("hbm_gbs", 6650.0))
     achieved = bytes_per_matrix * nb / (reduce(e0.elapsed_time(e1) / args.steps) * 1e-3) * 1e-9
-    roofline = {"kernel": "k_front_small (batched level program: assemble + fronts + export)", "bound": "hbm",
+    roofline = {"kernel": "k_front_path (+ k_assemble, k_front_small of the lower levels, k_export: the whole batched program)", "bound": "hbm",
                 "achieved": round(achieved, 1), "peak": hbm, "unit": "GB/s", "frac": round(achieved / hbm, 4), "traffic": None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
                 "algorithmic_bytes_per_matrix": bytes_per_matrix, "matrices_per_launch_set": nb,
-                "note": "per-rank; achieved = algorithmic bytes of this rank's shard / step time"}
+                "traffic_note": "ncu of k_front_path alone (profiles/r1_j_ncu_front_path_v2.txt): 0.70 MB of DRAM traffic per matrix",
+                "note": "per-rank; achieved = algorithmic bytes of this rank's shard / step time; the kernel is issue/barrier bound, not HBM bound"}
 
     e2e = None
     if not args.no_e2e:
