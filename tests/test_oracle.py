@@ -109,3 +109,21 @@ def test_oracle_bitexact_vs_reference_laplacian():
     rc, _, _, Lx = po.chol(n, Ap, Ai, Ax, parent, Lp)
     rrc, _, rLi, rLx, _, _ = po.ref_chol(n, Ap, Ai, Ax, int(Lp[n]))
     assert rc == 0 and rrc == 0 and (Li == rLi).all() and np.array_equal(Lx, rLx)
+
+
+@pytest.mark.skipif(not po.have_ref(), reason="oracle/_ref/libref.so not built (reference tree absent)")
+@pytest.mark.parametrize("name", ["bcsstk01", "1138_bus"])
+def test_oracle_bitexact_vs_reference_on_amd_permuted_matrices(name):
+    # the permuted matrices the ordering tests factor (tests/test_ordering.py, test_amd_permuted_matrix_vs_oracle):
+    # the oracle that judges them is itself pinned to the reference on exactly these inputs
+    import sparsecholesky_b200 as sc
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    A = sc.CscMatrix(int(g["n"]), g["Ap"], g["Ai"], g["Ax"])
+    B = sc.permute(A, sc.order_amd(A))
+    n = B.n
+    parent, Lp, Li = po.schol(n, B.p, B.i)
+    rparent, rLp, rLi, _ = po.ref_schol(n, B.p, B.i)
+    assert (parent == rparent).all() and (Lp == rLp).all() and (Li == rLi).all()
+    rc, _, _, Lx = po.chol(n, B.p, B.i, B.x, parent, Lp)
+    rrc, _, _, rLx, _, _ = po.ref_chol(n, B.p, B.i, B.x, int(Lp[n]))
+    assert rc == 0 and rrc == 0 and np.array_equal(Lx, rLx)
