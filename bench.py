@@ -338,13 +338,35 @@ def main():
                          ("supernodal L panels, each rank reads back the fronts it holds" if world > 1 else
                           "supernodal L panels (nnz(L) > INT_MAX: no 32-bit CSC)"),
                "last_step_ms": {"h2d": tm[0], "numeric": tm[1], "export": tm[2], "d2h": tm[3]}}
-        L.spchol_host_free(hA); L.spchol_host_free(hL)
+        L.spchol_host_free(hA)
+        e2e_host_L = (hL, out_entries, use_csc)          # checked against the device copy below, then freed
 
     # full-size parity property: ||A - L L^T||_F / ||A||_F of the factor just computed (device estimate, 8 probes)
     resid = None
     if world == 1:
         step()
         check(L.spchol_sync(plan_h, C.byref(info)))
+        # the panels the e2e call delivered to the host are the panels on the device (the factorization is deterministic,
+        # so the device copy of this step must equal them bit for bit): 64 chunks of 1 Mi doubles spread over the buffer
+        if e2e is not None and not e2e_host_L[2]:
+            try:
+                hL_, ne_, _ = e2e_host_L
+                dptr = C.c_void_p(); dn = C.c_int64(0)
+                check(L.spchol_lbuf(plan_h, C.byref(dptr), C.byref(dn)))
+
+                class _Dev:
+                    __cuda_array_interface__ = {"shape": (int(dn.value),), "typestr": "<f8", "data": (int(dptr.value), True), "version": 2}
+                dt = torch.as_tensor(_Dev(), device=f"cuda:{local_rank}")
+                host = np.ctypeslib.as_array(C.cast(hL_, C.POINTER(C.c_double)), shape=(ne_,))
+                chunk = 1 << 20
+                starts = np.linspace(0, max(ne_ - chunk, 0), 64).astype(np.int64)
+                bad = sum(int(not np.array_equal(dt[a:a + chunk].cpu().numpy(), host[a:a + chunk], equal_nan=True)) for a in starts)
+                e2e["readback_check"] = {"chunks": len(starts), "doubles_per_chunk": chunk, "mismatching_chunks": bad}
+            except Exception as exc:                      # a diagnostic, never the reason a bench line is lost
+                e2e["readback_check"] = {"error": repr(exc)[:200]}
+    if e2e is not None:
+        L.spchol_host_free(e2e_host_L[0])
+    if world == 1:
         out = C.c_double(0)
         t0 = time.perf_counter()
         check(L.spchol_residual(plan_h, ptr(np.ascontiguousarray(A.x)), C.byref(out)), "spchol_residual")
