@@ -170,3 +170,13 @@ print("emu ok")
     r = subprocess.run([os.sys.executable, "-c", code], capture_output=True, text=True, env=env, timeout=600)
     assert "emu ok" in r.stdout, r.stdout + r.stderr[-2000:]
     assert "ThreadSanitizer: data race" not in r.stderr, r.stderr[:3000]
+
+
+def test_staged_kernel_variant_still_applies():
+    """tools/path_kernel_v3.patch (a kernel variant waiting for GPU time) must keep applying to the tree it is meant for."""
+    import shutil
+    if shutil.which("patch") is None:
+        pytest.skip("patch(1) not available")
+    r = subprocess.run(["patch", "-p1", "--dry-run", "-i", os.path.join("tools", "path_kernel_v3.patch")], cwd=ROOT,
+                       capture_output=True, text=True)
+    assert r.returncode == 0, r.stdout + r.stderr
