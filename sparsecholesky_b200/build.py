@@ -24,6 +24,7 @@ def build(force: bool = False, verbose: bool = False) -> str:
     cmd = [nvcc, "-std=c++17", "-O3", "-lineinfo", "-gencode", "arch=compute_100a,code=sm_100a",
            "-Xcompiler", "-fPIC,-O2,-Wall", "-shared", "--use_fast_math=false" if False else "-prec-div=true",
            "-prec-sqrt=true", "-fmad=true", "-x", "cu"]
+    cmd += os.environ.get("SPCHOL_NVCC_DEFS", "").split()      # e.g. -DPK_OPT=5: staged kernel variants (csrc/path_kernel.cuh)
     if verbose:
         cmd += ["-Xptxas", "-v"]
     cmd += [os.path.join(CSRC, s) for s in SOURCES]

@@ -19,6 +19,7 @@
 #define PK_SYNCWARP() ::spchol::emu::syncwarp()
 #define PK_LDG(p) (*(p))
 #define PK_RSQRT(x) (1.0 / std::sqrt(x))
+#define PK_PREFETCH_L2(p) ((void)(p))
 #define PK_ATOMIC_MIN(p, v) ::spchol::emu::atomic_min((p), (v))
 #define PK_RESTRICT
 #else
@@ -28,6 +29,7 @@
 #define PK_SYNCWARP() __syncwarp()
 #define PK_LDG(p) __ldg(p)
 #define PK_RSQRT(x) rsqrt(x)
+#define PK_PREFETCH_L2(p) asm volatile("prefetch.global.L2 [%0];" ::"l"(p))
 #define PK_ATOMIC_MIN(p, v) atomicMin((p), (v))
 #define PK_RESTRICT __restrict__
 #endif
@@ -37,6 +39,15 @@ namespace spchol {
 #ifndef PK_THREADS                    // the host emulation also builds a 64-thread variant (fewer OS threads per barrier)
 #define PK_THREADS 256
 #define PK_CARRY_PER_THREAD 28
+#endif
+// Compile-time variants of the kernel that are validated on host threads (tests/test_path_emu.py builds PK_OPT = 0 and 15)
+// but not yet timed on a GPU; the shipped build is PK_OPT = 0.  `SPCHOL_NVCC_DEFS=-DPK_OPT=<mask>` rebuilds with
+//   1: size of the next member's corner from the planner (PathMember::nd) instead of a serial scan per thread
+//   2: diagonal block with ONE warp barrier per pivot (the remaining columns are updated from the unscaled column)
+//   4: unmasked update for 32-row chunks that lie entirely inside the block (warp-uniform choice)
+//   8: L2 prefetch of everything a group will add (panels of A, blocks from outside) while the group is being zeroed
+#ifndef PK_OPT
+#define PK_OPT 0
 #endif
 constexpr int PK_T = PK_THREADS;              // threads per CTA
 constexpr int PK_MAXE = PK_CARRY_PER_THREAD;  // carried contribution-block entries per thread (same budget as k_front_chain)
@@ -70,6 +81,29 @@ PK_DEVICE void pk_diag_factor(const PathMember& M, double* F, int nu, double* ri
         double piv = d * y;
         piv = fma(fma(-piv, piv, d), 0.5 * y, piv);          // sqrt(d), Newton-corrected
         y = fma(fma(-piv, y, 1.0), y, y);                    // 1 / piv, Newton-corrected
+#if PK_OPT & 2
+        // update of the remaining columns from the UNSCALED column k: (a_i y)(a_j y) are exactly the products the scaled
+        // column would give, and column k itself is not read again before the CTA barrier -- so its scaling below needs
+        // no barrier of its own
+        const int nt = w - k - 1;
+        if (nt <= 32) {                                      // few columns: one pair per lane and step
+            const int np = nt * (nt + 1) / 2;
+            for (int e = lane; e < np; e += 32) {
+                const int t = PK_LDG(tri_tab + e);
+                const int i = off + k + 1 + (t >> 16), j = off + k + 1 + (t & 0xffff);
+                F[pk_base(j, nu) + i] -= (colk[i] * y) * (colk[j] * y);
+            }
+        } else {                                             // wide front: column by column, lanes down the rows
+            for (int j = off + k + 1; j < off + w; ++j) {
+                const double uj = colk[j] * y;
+                double* colj = F + pk_base(j, nu);
+                for (int i = j + lane; i < off + w; i += 32) colj[i] -= (colk[i] * y) * uj;
+            }
+        }
+        PK_SYNCWARP();                                       // column k + 1 is complete; every lane is done reading column k
+        for (int i = k + 1 + lane; i < w; i += 32) colk[off + i] = colk[off + i] * y;
+        if (lane == 0) { colk[off + k] = piv; rinv[k] = y; }
+#else
         PK_SYNCWARP();                                       // every lane has read the pivot
         for (int i = k + 1 + lane; i < w; i += 32) colk[off + i] = colk[off + i] * y;
         if (lane == 0) { colk[off + k] = piv; rinv[k] = y; }
@@ -90,6 +124,7 @@ PK_DEVICE void pk_diag_factor(const PathMember& M, double* F, int nu, double* ri
             }
         }
         PK_SYNCWARP();
+#endif
         bk += nu - (off + k) - 1;
     }
 }
@@ -112,6 +147,22 @@ PK_DEVICE void front_path_body(const PathArrays pa, double* PK_RESTRICT L, doubl
         const int ne_u = nu * (nu + 1) / 2;
         const PathMember* PK_RESTRICT mem = pa.members + g.member0;
         // 1. zero the frontal matrix of the group; stage the position list of the first member
+#if PK_OPT & 8
+        // everything step 3 will read from HBM is known now: one 128-byte line per thread and pass
+        for (int q = 0; q < g.nmember; ++q) {
+            const PathMember M = mem[q];
+            const char* base = reinterpret_cast<const char*>(L + M.panel_off);
+            const int64_t bytes = static_cast<int64_t>(M.ld) * M.w * 8;
+            for (int64_t b = static_cast<int64_t>(tid) * 128; b < bytes; b += static_cast<int64_t>(PK_T) * 128) PK_PREFETCH_L2(base + b);
+        }
+        for (int q = 0; q < g.nchild; ++q) {
+            if (q == g.carried_child) continue;
+            const PathChild* PK_RESTRICT chp = pa.children + g.child0 + q;
+            const char* base = reinterpret_cast<const char*>(W + chp->src);
+            const int64_t bytes = static_cast<int64_t>((chp->mc + 1) & ~1) * chp->mc * 8;
+            for (int64_t b = static_cast<int64_t>(tid) * 128; b < bytes; b += static_cast<int64_t>(PK_T) * 128) PK_PREFETCH_L2(base + b);
+        }
+#endif
         for (int e = tid; e < ne_u; e += PK_T) F[e] = 0.0;
         {
             const PathMember M0 = mem[0];
@@ -203,8 +254,12 @@ PK_DEVICE void front_path_body(const PathArrays pa, double* PK_RESTRICT L, doubl
             PK_SYNC();
             // 4c. rank-w update.  nd = rows of this front that are columns of the next member: that corner is the next
             //     member's diagonal block and belongs to warp 0
+#if PK_OPT & 1
+            const int nd = M.nd;
+#else
             int nd = 0;
             if (!last) { while (w + nd < m && sp[w + nd] < Mn.off + Mn.w) ++nd; }
+#endif
             if (warp == 0 && !last) {
                 const int np = nd * (nd + 1) / 2;
                 if (nd <= 32) {
@@ -238,25 +293,41 @@ PK_DEVICE void front_path_body(const PathArrays pa, double* PK_RESTRICT L, doubl
 #pragma unroll
                     for (int c = 0; c < 4; ++c) { cj[c] = sp[min(j0 + c, m - 1)]; bc[c] = pk_base(cj[c], nu); }
                     const int t_begin = (j0 < w + nd) ? max(j0, w + nd - 3) : j0;      // rows above belong to warp 0's corner
+                    const bool full_cols = j0 + 3 < m;
+                    const int t_full = max(j0 + 3, w + nd);      // from this row on all four entries exist and are ours
                     for (int t = t_begin + lane; t < m; t += 32) {
                         const int r = sp[t];
                         double acc[4];
-                        bool on[4];
+                        if ((PK_OPT & 4) && full_cols && t - lane >= t_full) {   // warp-uniform: the whole 32-row chunk is interior
 #pragma unroll
-                        for (int c = 0; c < 4; ++c) {
-                            // entry (t, j0 + c) exists if t >= j0 + c, and is warp 0's if both indices are below w + nd
-                            on[c] = j0 + c < m && t >= j0 + c && !(t < w + nd && j0 + c < w + nd);
-                            acc[c] = on[c] ? F[bc[c] + r] : 0.0;
+                            for (int c = 0; c < 4; ++c) acc[c] = F[bc[c] + r];
+                            int bk = b0;
+                            for (int k = 0; k < w; ++k) {
+                                const double lr = F[bk + r];
+#pragma unroll
+                                for (int c = 0; c < 4; ++c) acc[c] -= lr * F[bk + cj[c]];
+                                bk += nu - (off + k) - 1;
+                            }
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) F[bc[c] + r] = acc[c];
+                        } else {
+                            bool on[4];
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) {
+                                // entry (t, j0 + c) exists if t >= j0 + c, and is warp 0's if both indices are below w + nd
+                                on[c] = j0 + c < m && t >= j0 + c && !(t < w + nd && j0 + c < w + nd);
+                                acc[c] = on[c] ? F[bc[c] + r] : 0.0;
+                            }
+                            int bk = b0;
+                            for (int k = 0; k < w; ++k) {
+                                const double lr = F[bk + r];
+#pragma unroll
+                                for (int c = 0; c < 4; ++c) acc[c] -= lr * F[bk + cj[c]];
+                                bk += nu - (off + k) - 1;
+                            }
+#pragma unroll
+                            for (int c = 0; c < 4; ++c) if (on[c]) F[bc[c] + r] = acc[c];
                         }
-                        int bk = b0;
-                        for (int k = 0; k < w; ++k) {
-                            const double lr = F[bk + r];
-#pragma unroll
-                            for (int c = 0; c < 4; ++c) acc[c] -= lr * F[bk + cj[c]];
-                            bk += nu - (off + k) - 1;
-                        }
-#pragma unroll
-                        for (int c = 0; c < 4; ++c) if (on[c]) F[bc[c] + r] = acc[c];
                     }
                 }
             }

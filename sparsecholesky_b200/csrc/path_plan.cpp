@@ -172,7 +172,7 @@ bool build_path_program(const HostPlan& P, int level0, int max_nu, int64_t carry
             const int s = mem_ids[i];
             off -= P.w[s];
             PathMember& M = mem[i];
-            M.s = s; M.off = off; M.pad = 0; M.pad2 = 0;
+            M.s = s; M.off = off; M.nd = 0; M.pad2 = 0;
             M.w = P.w[s]; M.m = P.m[s]; M.ld = P.ld[s]; M.first = P.first[s]; M.panel_off = P.panel_off[s];
             M.pos_off = static_cast<int>(out.pos.size());
             pos_of[s] = M.pos_off;
@@ -192,6 +192,13 @@ bool build_path_program(const HostPlan& P, int level0, int max_nu, int64_t carry
             out.max_m = std::max(out.max_m, P.m[s]);
         }
         if (off != 0) throw std::runtime_error("build_path_program: internal offset mismatch");
+        for (int q = 0; q + 1 < nmem; ++q) {            // the corner of member q's update that is the next member's diagonal block
+            const int* ps = out.pos.data() + mem[q].pos_off;
+            const int lim = mem[q + 1].off + mem[q + 1].w;
+            int nd = 0;
+            while (mem[q].w + nd < mem[q].m && ps[mem[q].w + nd] < lim) ++nd;
+            mem[q].nd = nd;
+        }
         out.members.insert(out.members.end(), mem.begin(), mem.end());
         // contribution blocks of the fronts outside the group whose parent is a member
         g.child0 = static_cast<int>(out.children.size());

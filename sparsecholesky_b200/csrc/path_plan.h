@@ -31,7 +31,7 @@ struct alignas(16) PathMember {   // a front eliminated inside a group (self-con
     int pos_off;           // pos[pos_off .. pos_off + m): position in U of every row of the front
     int w, m, ld;          // the front's columns, rows, leading dimension of its panel in the L buffer
     int first;             // global index of its first column
-    int pad;
+    int nd;                // rows of this front that are columns of the NEXT member of the group (0 for the last member)
     int64_t panel_off;     // its panel in the L buffer
     int64_t pad2;
 };

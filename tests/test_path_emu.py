@@ -19,13 +19,13 @@ CSRC = os.path.join(ROOT, "sparsecholesky_b200", "csrc")
 GOLD = os.path.join(ROOT, "tests", "golden")
 
 
-def _build(threads, carry_per_thread):
-    so = SO % threads
+def _build(threads, carry_per_thread, opt=0):
+    so = SO % (f"{threads}_opt{opt}" if opt else threads)
     srcs = [os.path.join(ROOT, "tests", "cpp", "path_emu.cpp")] + [os.path.join(CSRC, f) for f in ("path_plan.cpp", "plan.cpp", "symbolic.cpp")]
     deps = srcs + [os.path.join(CSRC, f) for f in ("path_plan.h", "path_kernel.cuh", "plan.h", "symbolic.h")]
     if not os.path.exists(so) or any(os.path.getmtime(f) > os.path.getmtime(so) for f in deps):
         subprocess.run(["g++", "-std=c++20", "-O2", "-fPIC", "-shared", "-pthread", f"-DPK_THREADS={threads}",
-                        f"-DPK_CARRY_PER_THREAD={carry_per_thread}", "-o", so] + srcs, check=True)
+                        f"-DPK_CARRY_PER_THREAD={carry_per_thread}", f"-DPK_OPT={opt}", "-o", so] + srcs, check=True)
     L = C.CDLL(so)
     L.pathemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_int, C.c_int,
                                  C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_char_p, C.c_int]
@@ -36,6 +36,12 @@ def _build(threads, carry_per_thread):
 def emu():
     """64 host threads per CTA (a barrier of 256 OS threads costs milliseconds), same register budget for carried blocks."""
     return _build(64, 112)
+
+
+@pytest.fixture(scope="module")
+def emu_opt():
+    """every staged compile-time variant switched on (PK_OPT = 15, csrc/path_kernel.cuh)"""
+    return _build(64, 112, opt=15)
 
 
 @pytest.fixture(scope="module")
@@ -140,7 +146,8 @@ def test_front_larger_than_the_group_capacity_is_refused(emu):
     assert rc != 0 and b"max_nu" in err.value
 
 
-def test_kernel_source_has_no_data_race_under_thread_sanitizer(tmp_path):
+@pytest.mark.parametrize("opt", [0, 15])
+def test_kernel_source_has_no_data_race_under_thread_sanitizer(tmp_path, opt):
     """Every shared-memory hand-over in the kernel is separated by a barrier: ThreadSanitizer watches the host threads
     that play the CTA (a barrier removed from path_kernel.cuh is reported as a data race here)."""
     tsan = subprocess.run(["g++", "-print-file-name=libtsan.so"], capture_output=True, text=True).stdout.strip()
@@ -149,7 +156,7 @@ def test_kernel_source_has_no_data_race_under_thread_sanitizer(tmp_path):
     so = str(tmp_path / "libpathemu_tsan.so")
     srcs = [os.path.join(ROOT, "tests", "cpp", "path_emu.cpp")] + [os.path.join(CSRC, f) for f in ("path_plan.cpp", "plan.cpp", "symbolic.cpp")]
     subprocess.run(["g++", "-std=c++20", "-O1", "-g", "-fsanitize=thread", "-fPIC", "-shared", "-pthread", "-DPK_THREADS=64",
-                    "-DPK_CARRY_PER_THREAD=112", "-o", so] + srcs, check=True)
+                    "-DPK_CARRY_PER_THREAD=112", f"-DPK_OPT={opt}", "-o", so] + srcs, check=True)
     code = f"""
 import ctypes as C, numpy as np, sys
 sys.path.insert(0, {ROOT!r})
@@ -172,11 +179,16 @@ print("emu ok")
     assert "ThreadSanitizer: data race" not in r.stderr, r.stderr[:3000]
 
 
-def test_staged_kernel_variant_still_applies():
-    """tools/path_kernel_v3.patch (a kernel variant waiting for GPU time) must keep applying to the tree it is meant for."""
-    import shutil
-    if shutil.which("patch") is None:
-        pytest.skip("patch(1) not available")
-    r = subprocess.run(["patch", "-p1", "--dry-run", "-i", os.path.join("tools", "path_kernel_v3.patch")], cwd=ROOT,
-                       capture_output=True, text=True)
-    assert r.returncode == 0, r.stdout + r.stderr
+
+@pytest.mark.parametrize("mode", [0, 1])
+def test_staged_kernel_variants(emu_opt, mode):
+    # PK_OPT = 15: planner-supplied corner sizes, one warp barrier per pivot, unmasked interior chunks, prefetch (a no-op
+    # on the host) -- same factor to rounding on the batched configuration and on whole trees
+    A, ref = golden("1138_bus")
+    Lx, info, st = run(emu_opt, A, mode=mode)
+    assert info == 0 and relerr(Lx, ref) <= 1e-10
+    for name in ("bcsstk01", "lap2d_24", "lap3d_10"):
+        A, ref = golden(name)
+        mm = int(sc.schol(A, relax=1).panel_layout()["m"].max())
+        Lx, info, st = run(emu_opt, A, relax=1, level0=0, max_nu=mm + 7, mode=mode)
+        assert info == 0 and relerr(Lx, ref) <= 1e-10, (name, st)

@@ -11,11 +11,13 @@ for NU in 128 200 235; do run nu$NU SPCHOL_BATCH_PATH_NU=$NU; done
 run subtree            SPCHOL_BATCH_GROUPS=1
 run subtree_nu200      SPCHOL_BATCH_GROUPS=1 SPCHOL_BATCH_PATH_NU=200
 for L0 in 2 1 0; do run subtree_level$L0 SPCHOL_BATCH_GROUPS=1 SPCHOL_BATCH_LEVEL0=$L0; done
-# v3 of the kernel (host-computed corner size, one warp barrier per pivot, warp-uniform unmasked fast path)
-if patch -p1 --dry-run < tools/path_kernel_v3.patch > /dev/null 2>&1; then
-  patch -p1 < tools/path_kernel_v3.patch > /dev/null && python -m sparsecholesky_b200.build --force > /dev/null && run v3 SPCHOL_BATCH_PATH=1 && run v3_subtree SPCHOL_BATCH_GROUPS=1
-  patch -p1 -R < tools/path_kernel_v3.patch > /dev/null && python -m sparsecholesky_b200.build --force > /dev/null
-fi
+# compile-time variants of k_front_path (csrc/path_kernel.cuh, PK_OPT bits: 1 corner size from the planner, 2 one warp
+# barrier per pivot, 4 unmasked interior chunks, 8 L2 prefetch at group start), one at a time and all together
+for OPT in 1 2 4 8 15; do
+  SPCHOL_NVCC_DEFS="-DPK_OPT=$OPT" python -m sparsecholesky_b200.build --force > /dev/null && run opt$OPT SPCHOL_BATCH_PATH=1
+done
+SPCHOL_NVCC_DEFS="-DPK_OPT=15" python -m sparsecholesky_b200.build --force > /dev/null && run opt15_subtree SPCHOL_BATCH_GROUPS=1
+python -m sparsecholesky_b200.build --force > /dev/null      # back to the shipped build
 # read-back marks (OP_EXPORT, staged): bytes first, then the e2e number with and without
 SPCHOL_TEST_STAGED=1 timeout 300 python -m pytest tests/test_chol_gpu.py -q -k "overlapped_readback" > gpurun_out/staged_marks.log 2>&1; echo "marks test rc=$?"; tail -n 3 gpurun_out/staged_marks.log
 timeout 600 python bench.py --steps 3 --warmup 3 --no-cpu-baseline > gpurun_out/bench_marks_off.json 2> gpurun_out/bench_marks_off.err; echo "marks off rc=$?"
