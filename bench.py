@@ -355,7 +355,7 @@ def main():
                 check(L.spchol_lbuf(plan_h, C.byref(dptr), C.byref(dn)))
 
                 class _Dev:
-                    __cuda_array_interface__ = {"shape": (int(dn.value),), "typestr": "<f8", "data": (int(dptr.value), True), "version": 2}
+                    __cuda_array_interface__ = {"shape": (int(dn.value),), "typestr": "<f8", "data": (int(dptr.value), False), "version": 2}
                 dt = torch.as_tensor(_Dev(), device=f"cuda:{local_rank}")
                 host = np.ctypeslib.as_array(C.cast(hL_, C.POINTER(C.c_double)), shape=(ne_,))
                 chunk = 1 << 20

@@ -692,11 +692,13 @@ int spchol_factor_lbuf(spchol_plan* p, const double* Ax, double* Lbuf_host, int*
     const bool pinned = cudaPointerGetAttributes(&pa, Lbuf_host) == cudaSuccess && pa.type == cudaMemoryTypeHost &&
                         !(getenv("SPCHOL_OVERLAP_D2H") && atoi(getenv("SPCHOL_OVERLAP_D2H")) == 0);
     cudaGetLastError();
-    if (pinned && (rc = export_prepare(p))) return rc;
-    if ((rc = run_numeric(p, p->dAx, pinned ? Lbuf_host : nullptr))) return rc;
+    // (the per-kind profiling replay runs on one stream and does not overlap the read-back: plain copy at the end)
+    const bool overlapped = pinned && !p->profile;
+    if (overlapped && (rc = export_prepare(p))) return rc;
+    if ((rc = run_numeric(p, p->dAx, overlapped ? Lbuf_host : nullptr))) return rc;
     CK(cudaEventRecord(p->ev[2], st));
     CK(cudaEventRecord(p->ev[3], st));
-    if (!pinned)
+    if (!overlapped)
         CK(cudaMemcpyAsync(Lbuf_host, p->dL, static_cast<size_t>(p->H.lbuf_entries) * sizeof(double), cudaMemcpyDeviceToHost, st));
     CK(cudaEventRecord(p->ev[4], st));
     if ((rc = read_info(p, info))) return rc;

@@ -11,7 +11,7 @@ from oracle import pyoracle as po
 from sparsecholesky_b200 import synth
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
-NAMES = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLD, "*.npz")))
+NAMES = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLD, "*.npz")) if not os.path.basename(f).startswith("large_"))
 
 
 @pytest.mark.parametrize("name", NAMES)
@@ -127,3 +127,26 @@ def test_oracle_bitexact_vs_reference_on_amd_permuted_matrices(name):
     rc, _, _, Lx = po.chol(n, B.p, B.i, B.x, parent, Lp)
     rrc, _, _, rLx, _, _ = po.ref_chol(n, B.p, B.i, B.x, int(Lp[n]))
     assert rc == 0 and rrc == 0 and np.array_equal(Lx, rLx)
+
+
+@pytest.mark.parametrize("name", ["lap2d_256", "lap3d_32"])
+def test_oracle_matches_large_reference_fixture(name):
+    """The full-size fixtures (tests/golden/make_golden_large.py: ONE run of the reference's chol()) also pin the plain-C
+    oracle: pattern hashes, sampled values and per-chunk sums of its L on the two cases it finishes in seconds."""
+    import hashlib
+    from sparsecholesky_b200 import synth
+    path = os.path.join(GOLD, "large_" + name + ".npz")
+    if not os.path.exists(path):
+        pytest.skip("fixture not generated")
+    g = np.load(path)
+    dims = tuple(int(v) for v in g["dims"])
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=synth.nd_perm_py(*dims))
+    Ap, Ai, Ax = po.triplet_to_csc(ti, tj, tx, n)
+    assert hashlib.sha256(Ap.tobytes()).hexdigest() == str(g["Ap_sha256"])
+    assert hashlib.sha256(Ai.tobytes()).hexdigest() == str(g["Ai_sha256"])
+    rc, Lp, Li, Lx = po.chol(n, Ap, Ai, Ax)
+    assert rc == 0
+    assert hashlib.sha256(Lp.astype(np.int32).tobytes()).hexdigest() == str(g["Lp_sha256"])
+    assert hashlib.sha256(Li.tobytes()).hexdigest() == str(g["Li_sha256"])
+    pos = np.random.default_rng(int(g["seed"])).integers(0, int(g["nnzL"]), int(g["K"]))
+    assert np.array_equal(Lx[pos], g["sample_x"])           # same arithmetic, same order: bit for bit
