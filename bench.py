@@ -32,7 +32,7 @@ WORKLOADS = {
     "lap3d_32": ((32, 32, 32), "3D 7-point Laplacian 32^3, geometric ND", (32, 32, 32)),
     "lap2d_1024": ((1024, 1024, 1), "2D 5-point Laplacian 1024^2 (1.05M rows), geometric ND", (256, 256, 1)),
     "lap2d_256": ((256, 256, 1), "2D 5-point Laplacian 256^2, geometric ND", (256, 256, 1)),
-    # config 5: handled by sparsecholesky_b200/bench_batched.py
+    # config 5: handled by bench_batched.py (next to this file)
     "batched_1138": (None, "16k SPD matrices over the 1138_bus pattern (batched numeric chol)", None),
 }
 METRIC = "fp64_factor_gflops"
@@ -183,7 +183,7 @@ def main():
         run_reference(args, rank)
         return
     if args.workload == "batched_1138":
-        from sparsecholesky_b200 import bench_batched
+        import bench_batched
         bench_batched.run(args, rank, world, local_rank, ClockSampler, METRIC, UNIT)
         return
 

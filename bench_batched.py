@@ -8,7 +8,7 @@ import time
 
 import numpy as np
 
-ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+ROOT = os.path.dirname(os.path.abspath(__file__))
 MTX = os.path.join(ROOT, "tests", "data", "1138_bus.mtx")
 
 
@@ -91,12 +91,11 @@ def run(args, rank, world, local_rank, ClockSampler, METRIC, UNIT):
         pass
     hbm = float(peaks.get("hbm_gbs", 6650.0))
     achieved = bytes_per_matrix * nb / (reduce(e0.elapsed_time(e1) / args.steps) * 1e-3) * 1e-9
-    roofline = {"kernel": "k_front_path (+ k_assemble, k_front_small of the lower levels, k_export: the whole batched program)", "bound": "hbm",
+    roofline = {"kernel": "k_tree_warp (one warp per matrix walks the whole assembly tree; A read from Ax, L written in CSC order)", "bound": "hbm",
                 "achieved": round(achieved, 1), "peak": hbm, "unit": "GB/s", "frac": round(achieved / hbm, 4), "traffic": None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
                 "algorithmic_bytes_per_matrix": bytes_per_matrix, "matrices_per_launch_set": nb,
-                "traffic_note": "ncu of k_front_path alone (profiles/r1_j_ncu_front_path_v2.txt): 0.70 MB of DRAM traffic per matrix",
-                "note": "per-rank; achieved = algorithmic bytes of this rank's shard / step time; the kernel is issue/barrier bound, not HBM bound"}
+                "note": "per-rank; achieved = algorithmic bytes of this rank's shard / step time (SURVEY 8d: 8 nnz(A) + 24 nnz(L) per matrix)"}
 
     e2e = None
     if not args.no_e2e:

@@ -17,7 +17,7 @@
 #include "../../include/spchol.h"
 #include "capi_internal.h"
 #include "kernels.cuh"
-#include "path_kernel.cuh"
+#include "tree_kernel.cuh"
 #include "residual.cuh"
 #include "solve.cuh"
 
@@ -107,13 +107,13 @@ struct spchol_plan {
     cudaEvent_t ev[5] = {nullptr, nullptr, nullptr, nullptr, nullptr};
     // device buffers
     double* dL = nullptr; double* dW = nullptr; double* dAx = nullptr; double* dLx = nullptr;
-    double *bL = nullptr, *bW = nullptr; int* binfo = nullptr; int b_chunk = 0;   // batched factorization buffers
-    // batched factorization: fronts of the levels >= chain_level0 are walked by one CTA per matrix (k_front_chain)
-    int* d_chain_list = nullptr; int* d_tri_tab = nullptr; int chain_count = 0, chain_level0 = -1, chain_smem = 0; bool chain_ready = false;
-    // ... or (default; SPCHOL_BATCH_PATH=0 falls back to the chain kernel) by the path-group program (k_front_path, path_plan.h),
-    // whose source is also run on host threads by tests/test_path_emu.py
-    PathArrays path{}; int path_smem = 0; bool path_on = false;
-    int64_t b_ws_entries = 0;     // workspace doubles per matrix of the batched buffers (>= H.ws_entries)
+    // warp-per-subtree programs (tree_plan.h / tree_kernel.cuh): `tree` = the bottom subtrees of this matrix (OP_TREE),
+    // `whole` = the whole tree as one task per matrix (batched factorization, BASELINE config 5)
+    struct DevTree { TreeArrays ta{}; double* stash = nullptr; int f_stride = 0; int64_t stash_entries = 0; bool on = false; };
+    DevTree tree, whole;
+    double* bStash = nullptr; int* binfo = nullptr; int b_chunk = 0;              // batched factorization buffers
+    double *hbA = nullptr, *hbL = nullptr; int* hbI = nullptr; int hb_cap = 0;     // device staging of the host-buffer batched call
+    cudaEvent_t hb_ev[2 * 8] = {nullptr}; cudaStream_t stream4 = nullptr;
     double* dWinv = nullptr;      // inverses of the diagonal blocks of one launch (k_potrf_inv -> k_trsm_inv)
     int* dinfo = nullptr;
     int *d_first = nullptr, *d_w = nullptr, *d_m = nullptr, *d_ld = nullptr, *d_parent = nullptr;
@@ -151,6 +151,8 @@ struct spchol_plan {
 };
 
 namespace {
+
+constexpr int kBatchSlices = 8;       // slices of a host-buffer batch in flight (copy in / factor / copy out overlap)
 
 template <class T>
 int upload(spchol_plan* p, const std::vector<T>& v, T** out) {
@@ -293,10 +295,15 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
             continue;
         }
         st = sts[op.stream];
-        const int pk = op.kind == OP_GEMM ? 9 + gemm_k_class(op.threads) : op.kind;   // profile slot
+        const int pk = op.kind == OP_GEMM ? 9 + gemm_k_class(op.threads) : (op.kind == OP_TREE ? 0 : op.kind);   // profile slot (subtree tasks count as small fronts)
         mark(pk);
         const int64_t before = launches;
         switch (op.kind) {
+        case OP_TREE:
+            k_tree_warp<<<op.count, 32, static_cast<size_t>(p->tree.f_stride) * 8 + TW_MAX_M * 4, st>>>(
+                p->tree.ta, dAx, p->dL, p->dW, p->tree.stash, nullptr, p->dinfo, 0, 0, 0, 0, 0, 0, p->tree.f_stride, 0);
+            ++launches;
+            break;
         case OP_SMALL: {
             const int* list = p->d_small_list + op.begin;
             const unsigned g = static_cast<unsigned>(op.count);
@@ -452,6 +459,9 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
         if (const char* la = getenv("SPCHOL_LOOKAHEAD")) opt.lookahead = atoi(la) != 0;
         if (const char* v = getenv("SPCHOL_DEFER_CB")) opt.defer_cb_add = atoi(v) != 0;
         if (const char* v = getenv("SPCHOL_SMALL_MAX_M")) { const int x = atoi(v); if (x >= 16 && x <= 224) opt.small_max_m = x; }   // development switch (A/B timing)
+        if (const char* v = getenv("SPCHOL_TREE")) opt.tree = atoi(v) != 0;
+        if (const char* v = getenv("SPCHOL_TREE_CAP")) { const int x = atoi(v); if (x >= 8 && x <= TW_MAX_M) opt.tree_cap_m = x; }
+        if (const char* v = getenv("SPCHOL_TREE_WORK")) { const double x = atof(v); if (x > 0) opt.tree_work = x; }
         if (const char* v = getenv("SPCHOL_NB")) { const int x = atoi(v); if (x >= 128) opt.NB = x; }
         if (const char* v = getenv("SPCHOL_NB_WIDE")) { const int x = atoi(v); if (x >= 128) opt.NB_wide = x; }
         if (const char* v = getenv("SPCHOL_WIDE_W")) { const int x = atoi(v); if (x >= 1) opt.wide_w = x; }
@@ -501,11 +511,38 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
     UP(H.small_list, p->d_small_list); UP(H.extadd_list, p->d_extadd_list);
     UP(H.zero_tasks, p->d_zero); UP(H.potrf_tasks, p->d_potrf); UP(H.trsm_tasks, p->d_trsm); UP(H.gemm_tasks, p->d_gemm); UP(H.copy_tasks, p->d_copy);
 #undef UP
+    // warp-per-subtree programs
+    {
+        auto up_tree = [&](TreeProgram& T, spchol_plan::DevTree& D, const int* csc_map) -> int {
+            if (T.tasks.empty()) return 0;
+            TwTask* dt = nullptr; TwFront* df = nullptr; TwStash* dsx = nullptr; int* drm = nullptr; int* das = nullptr; unsigned short* dad = nullptr;
+            int r2;
+            if ((r2 = upload(p, T.tasks, &dt)) || (r2 = upload(p, T.fronts, &df)) || (r2 = upload(p, T.stashes, &dsx)) ||
+                (r2 = upload(p, T.rmap, &drm)) || (r2 = upload(p, T.a_src, &das)) || (r2 = upload(p, T.a_dst, &dad))) return r2;
+            D.ta = TreeArrays{dt, static_cast<int>(T.tasks.size()), df, dsx, drm, das, dad, csc_map};
+            D.f_stride = ((T.cap_m * (T.cap_m + 1) / 2) + 1) & ~1;
+            D.stash_entries = (T.stash_entries + 1) & ~int64_t(1);
+            D.on = true;
+            std::vector<TwFront>().swap(T.fronts); std::vector<TwStash>().swap(T.stashes); std::vector<int>().swap(T.rmap);
+            std::vector<int>().swap(T.a_src); std::vector<unsigned short>().swap(T.a_dst);
+            return 0;
+        };
+        if ((rc = up_tree(H.tree, p->tree, nullptr))) return fail(rc);
+        if (p->tree.on && (rc = dalloc(p, p->tree.stash_entries, &p->tree.stash))) return fail(rc);
+        if (!H.tree_whole.tasks.empty() && H.nnzL <= INT_MAX && !H.l_src.empty()) {
+            std::vector<int> inv(static_cast<size_t>(H.lbuf_entries), -1);        // L-buffer offset -> CSC index
+            for (int64_t e = 0; e < H.nnzL; ++e) if (H.l_src[e] >= 0) inv[static_cast<size_t>(H.l_src[e])] = static_cast<int>(e);
+            int* dmap = nullptr;
+            if ((rc = upload(p, inv, &dmap)) || (rc = up_tree(H.tree_whole, p->whole, dmap))) return fail(rc);
+        }
+        if (cudaFuncSetAttribute(k_tree_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) {
+            set_error("cudaFuncSetAttribute (k_tree_warp) failed"); return fail(SPCHOL_ECUDA);
+        }
+    }
     // the big host-side maps are only needed on the device from here on
     std::vector<int64_t>().swap(H.a_dest);
     std::vector<int64_t>().swap(H.l_src);
-    // (plans the batched path accepts keep the relative indices: its group program is built from them on first use)
-    if (H.n_large > 0 || H.world > 1) std::vector<int>().swap(H.rel);
+    std::vector<int>().swap(H.rel);
     if ((rc = dalloc(p, H.lbuf_entries, &p->dL))) return fail(rc);
     if ((rc = dalloc(p, H.ws_entries, &p->dW))) return fail(rc);
     if ((rc = dalloc(p, 1, &p->dinfo))) return fail(rc);
@@ -593,9 +630,10 @@ void spchol_plan_destroy(spchol_plan* p) {
     if (!p) return;
     cudaSetDevice(p->device);
     for (void* d : p->allocs) cudaFree(d);
-    if (p->bL) cudaFree(p->bL);
-    if (p->bW) cudaFree(p->bW);
-    if (p->binfo) cudaFree(p->binfo);
+    for (void* d : {static_cast<void*>(p->bStash), static_cast<void*>(p->binfo), static_cast<void*>(p->hbA), static_cast<void*>(p->hbL),
+                    static_cast<void*>(p->hbI)}) if (d) cudaFree(d);
+    for (auto& e : p->hb_ev) if (e) cudaEventDestroy(e);
+    if (p->stream4) cudaStreamDestroy(p->stream4);
     for (auto& e : p->ev) if (e) cudaEventDestroy(e);
     for (auto& e : p->prof_ev) cudaEventDestroy(e);
     for (auto& e : p->ring) if (e) cudaEventDestroy(e);
@@ -711,84 +749,34 @@ int spchol_factor_lbuf(spchol_plan* p, const double* Ax, double* Lbuf_host, int*
 }
 
 // ---- batched numeric factorization: many value sets over one pattern (config 5) ---------------
-// Every matrix gets its own L buffer and contribution workspace (matrix-major); each launch of the
-// level program covers all matrices of the chunk (grid.y = matrix).  Patterns whose fronts all fit
-// the shared-memory front kernel only (true for 1138_bus-sized problems).
-static int batched_chunk(const spchol_plan* p) {
+// ONE WARP per matrix walks the whole assembly tree (HostPlan::tree_whole, k_tree_warp): the values of A are read
+// straight from Ax, the frontal matrices live in shared memory, the factor is written straight into the CSC order of
+// S -- no L buffer, no assembly pass, no export pass; the only other HBM traffic is the stash of side-branch blocks.
+// Patterns whose fronts all have m <= TW_MAX_M rows (true for 1138_bus-sized problems).
+static int batched_chunk(const spchol_plan* p, int nbatch) {
     size_t fr = 0, tot = 0;
     if (cudaMemGetInfo(&fr, &tot) != cudaSuccess) return 1;
-    const double per = 8.0 * (static_cast<double>(p->H.lbuf_entries) + std::max(p->b_ws_entries, p->H.ws_entries) + p->H.nnzA + p->H.nnzL) + 64;
+    const double per = 8.0 * static_cast<double>(p->whole.stash_entries) + 64;
     const double c = 0.8 * static_cast<double>(fr) / per;
-    return static_cast<int>(std::max(1.0, std::min(c, 65535.0)));
+    return static_cast<int>(std::max(1.0, std::min(c, static_cast<double>(std::max(nbatch, 1)))));
 }
 
 static int batched_reserve(spchol_plan* p, int chunk) {
     if (p->b_chunk >= chunk) return 0;
-    for (void* d : {static_cast<void*>(p->bL), static_cast<void*>(p->bW), static_cast<void*>(p->binfo)}) if (d) cudaFree(d);
-    p->bL = p->bW = nullptr; p->binfo = nullptr; p->b_chunk = 0;
-    CK(cudaMalloc(&p->bL, sizeof(double) * std::max<int64_t>(p->H.lbuf_entries, 1) * chunk));
-    CK(cudaMalloc(&p->bW, sizeof(double) * std::max<int64_t>(p->b_ws_entries, 1) * chunk));
+    if (p->bStash) cudaFree(p->bStash);
+    if (p->binfo) cudaFree(p->binfo);
+    p->bStash = nullptr; p->binfo = nullptr; p->b_chunk = 0;
+    CK(cudaMalloc(&p->bStash, sizeof(double) * std::max<int64_t>(p->whole.stash_entries, 1) * chunk));
     CK(cudaMalloc(&p->binfo, sizeof(int) * chunk));
     p->b_chunk = chunk;
     return 0;
 }
 
-// one-time setup of the batched path: which kernel walks the upper levels, and the per-matrix workspace it needs
-static int batched_prepare(spchol_plan* p) {
+static int batched_check(const spchol_plan* p, const char* who) {
     const HostPlan& H = p->H;
-    int rc;
-    if (!p->chain_ready) {
-        // upper part of the tree = the levels from which on no level has more than 16 fronts: too few fronts per
-        // launch to fill the GPU, and mostly chains whose contribution blocks can stay on the SM
-        p->chain_ready = true;
-        p->b_ws_entries = H.ws_entries;
-        std::vector<int> cnt(H.nlevels + 1, 0);
-        for (int s = 0; s < H.ns; ++s) ++cnt[H.level[s]];
-        int l0 = H.nlevels;
-        while (l0 > 0 && cnt[l0 - 1] <= 16) --l0;
-        // the fronts of those levels in (level, id) order: the order the level-by-level program runs them in, which is
-        // what the lifetimes of the contribution blocks in the workspace arena were planned for.  In the chain part
-        // (one front per level) a front is followed by its parent and its contribution block stays in registers.
-        std::vector<int> lst;
-        int mm = 0;
-        for (int l = l0; l < H.nlevels; ++l)
-            for (int s = 0; s < H.ns; ++s) if (H.level[s] == l) { lst.push_back(s); mm = std::max(mm, H.m[s]); }
-        const int smem = mm * (mm + 1) / 2 * 8;            // packed lower triangle
-        const char* off = getenv("SPCHOL_BATCH_CHAIN");
-        const char* path = getenv("SPCHOL_BATCH_PATH");
-        std::vector<int> tab;
-        for (int ii = 0; static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++ii)
-            for (int jj = 0; jj <= ii && static_cast<int>(tab.size()) < CH_MAXE * CH_T; ++jj) tab.push_back((ii << 16) | jj);
-        static_assert(PK_MAXE * PK_T == CH_MAXE * CH_T, "k_front_path and k_front_chain share the pair table");
-        if (lst.size() >= 8 && !(path && atoi(path) == 0)) {                 // SPCHOL_BATCH_PATH=0: the older chain kernel
-            // path groups: |U| <= 160 rows keeps two CTAs per SM (103 KB each)
-            const int max_nu = getenv("SPCHOL_BATCH_PATH_NU") ? atoi(getenv("SPCHOL_BATCH_PATH_NU")) : 160;
-            PathProgram prog;
-            bool ok = false;
-            // development switches (unmeasured alternatives): SPCHOL_BATCH_GROUPS=1 cuts subtrees instead
-            // of paths, SPCHOL_BATCH_LEVEL0=<l> moves the boundary between the level kernels and the group program
-            const int gmode = getenv("SPCHOL_BATCH_GROUPS") ? atoi(getenv("SPCHOL_BATCH_GROUPS")) : 0;
-            int pl0 = l0;
-            if (getenv("SPCHOL_BATCH_LEVEL0")) pl0 = std::max(0, std::min(H.nlevels, atoi(getenv("SPCHOL_BATCH_LEVEL0"))));
-            try { ok = build_path_program(H, pl0, max_nu, static_cast<int64_t>(PK_MAXE) * PK_T, prog, gmode); }
-            catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
-            const int psmem = prog.max_nu * (prog.max_nu + 1) / 2 * 8;
-            // dynamic + the kernel's static shared arrays (position lists, pivot reciprocals) within the 227 KB of a CTA
-            if (ok && prog.max_m <= PK_SPOS_MAX && psmem + 2 * PK_SPOS_MAX * 4 + PK_SPOS_MAX * 8 + 1024 <= 227 * 1024) {
-                PathGroup* dg = nullptr; PathMember* dm = nullptr; PathChild* dc = nullptr; int* dp = nullptr;
-                if ((rc = upload(p, prog.groups, &dg)) || (rc = upload(p, prog.members, &dm)) || (rc = upload(p, prog.children, &dc)) ||
-                    (rc = upload(p, prog.pos, &dp)) || (rc = upload(p, tab, &p->d_tri_tab))) return rc;
-                p->path = PathArrays{dg, static_cast<int>(prog.groups.size()), dm, dc, dp, p->d_tri_tab};
-                p->path_smem = psmem; p->path_on = true; p->chain_level0 = pl0;
-                p->b_ws_entries = prog.ws_entries;
-                CK(cudaFuncSetAttribute(k_front_path, cudaFuncAttributeMaxDynamicSharedMemorySize, psmem));
-            }
-        }
-        if (!p->path_on && lst.size() >= 8 && smem <= 72 * 1024 && !(off && atoi(off) == 0)) {
-            if ((rc = upload(p, lst, &p->d_chain_list)) || (rc = upload(p, tab, &p->d_tri_tab))) return rc;
-            p->chain_count = static_cast<int>(lst.size()); p->chain_level0 = l0; p->chain_smem = smem;
-            CK(cudaFuncSetAttribute(k_front_chain, cudaFuncAttributeMaxDynamicSharedMemorySize, smem));
-        }
+    if (!p->whole.on || H.world > 1 || H.nnzL > INT_MAX) {
+        set_error(std::string(who) + ": only single-GPU plans whose fronts all fit the warp-per-tree kernel (m <= 128 rows)");
+        return SPCHOL_EINVAL;
     }
     return 0;
 }
@@ -796,50 +784,26 @@ static int batched_prepare(spchol_plan* p) {
 // device-resident: dAx[nbatch][nnzA] -> dLx[nbatch][nnzL] (CSC order of S), dinfo[nbatch] (0 or failing column)
 int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, double* dLx, int* dinfo) {
     if (!p || !dAx || !dLx || !dinfo || nbatch < 0) { set_error("spchol_factor_batched_device: bad argument"); return SPCHOL_EINVAL; }
+    int rc;
+    if ((rc = batched_check(p, "spchol_factor_batched"))) return rc;
     const HostPlan& H = p->H;
-    if (H.n_large > 0 || H.world > 1 || H.nnzL > INT_MAX) {
-        set_error("spchol_factor_batched: only single-GPU plans whose fronts all fit the shared-memory front kernel (m <= 128)");
-        return SPCHOL_EINVAL;
-    }
     CK(cudaSetDevice(p->device));
     cudaStream_t st = p->stream;
-    int rc;
     int64_t launches = 0;
-    if ((rc = batched_prepare(p))) return rc;
-    int chunk = p->b_chunk > 0 ? p->b_chunk : std::min(batched_chunk(p), std::max(nbatch, 1));
-    if ((rc = batched_reserve(p, std::min(chunk, std::max(nbatch, 1))))) return rc;
-    chunk = p->b_chunk;
-    const int64_t wstride = p->b_ws_entries;
+    {
+        const int want = batched_chunk(p, nbatch);
+        if (p->b_chunk < want && (rc = batched_reserve(p, want))) return rc;
+    }
+    const int chunk = p->b_chunk;
+    static const int wpc_env = getenv("SPCHOL_TREE_WPC") ? atoi(getenv("SPCHOL_TREE_WPC")) : 4;
+    const size_t per_warp = static_cast<size_t>(p->whole.f_stride) * 8 + TW_MAX_M * 4;
+    const int wpc = std::max(1, std::min(std::min(wpc_env, 8), static_cast<int>((227 * 1024) / per_warp)));
     for (int b0 = 0; b0 < nbatch; b0 += chunk) {
         const int nb = std::min(chunk, nbatch - b0);
-        CK(cudaMemsetAsync(p->bL, 0, sizeof(double) * H.lbuf_entries * nb, st));
         CK(cudaMemsetAsync(p->binfo, 0x7f, sizeof(int) * nb, st));
-        k_assemble<<<dim3(static_cast<unsigned>((H.nnzA + 255) / 256), nb), 256, 0, st>>>(
-            H.nnzA, p->d_a_dest, dAx + static_cast<int64_t>(b0) * H.nnzA, p->bL, H.lbuf_entries);
-        ++launches;
-        for (const Op& op : H.ops) {
-            if (op.kind != OP_SMALL) continue;
-            if ((p->chain_count || p->path_on) && op.level >= p->chain_level0) continue;      // walked by k_front_chain / k_front_path below
-            const int* list = p->d_small_list + op.begin;
-            const dim3 g(static_cast<unsigned>(op.count), nb);
-            switch (op.threads) {
-            case 32:  k_front_small<32><<<g, 32, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride); break;
-            case 64:  k_front_small<64><<<g, 64, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride); break;
-            case 128: k_front_small<128><<<g, 128, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride); break;
-            default:  k_front_small<256><<<g, 256, op.smem, st>>>(list, p->fa, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride); break;
-            }
-            ++launches;
-        }
-        if (p->path_on) {
-            k_front_path<<<nb, PK_T, p->path_smem, st>>>(p->path, p->bL, p->bW, p->binfo, H.lbuf_entries, wstride);
-            ++launches;
-        } else if (p->chain_count) {
-            k_front_chain<<<nb, CH_T, p->chain_smem, st>>>(p->d_chain_list, p->chain_count, p->fa, p->d_tri_tab, p->bL, p->bW, p->binfo,
-                                                           H.lbuf_entries, wstride);
-            ++launches;
-        }
-        k_export<<<dim3(static_cast<unsigned>((H.nnzL + 255) / 256), nb), 256, 0, st>>>(
-            H.nnzL, p->d_l_src, p->bL, dLx + static_cast<int64_t>(b0) * H.nnzL, H.lbuf_entries);
+        k_tree_warp<<<(nb + wpc - 1) / wpc, 32 * wpc, wpc * per_warp, st>>>(
+            p->whole.ta, dAx + static_cast<int64_t>(b0) * H.nnzA, nullptr, nullptr, p->bStash, dLx + static_cast<int64_t>(b0) * H.nnzL,
+            p->binfo, H.nnzA, 0, 0, p->whole.stash_entries, H.nnzL, nb, p->whole.f_stride, 1);
         k_fix_info<<<(nb + 255) / 256, 256, 0, st>>>(p->binfo, dinfo + b0, nb);
         launches += 2;
     }
@@ -848,35 +812,58 @@ int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, 
     return 0;
 }
 
-// host buffers: Ax[nbatch][nnzA] in, Lx[nbatch][nnzL] and info[nbatch] out; chunks sized to the free HBM
+// host buffers: Ax[nbatch][nnzA] in, Lx[nbatch][nnzL] and info[nbatch] out.  The batch is cut into slices that go
+// through three streams round-robin (H2D -> factor -> D2H per slice), so the copies of one slice overlap the kernel
+// of another; device staging buffers are kept with the plan.
 int spchol_factor_batched(spchol_plan* p, int nbatch, const double* Ax, double* Lx, int* info) {
     if (!p || !Ax || !Lx || !info || nbatch < 0) { set_error("spchol_factor_batched: bad argument"); return SPCHOL_EINVAL; }
+    int rc;
+    if ((rc = batched_check(p, "spchol_factor_batched"))) return rc;
     CK(cudaSetDevice(p->device));
     const HostPlan& H = p->H;
-    if (H.n_large > 0 || H.world > 1 || H.nnzL > INT_MAX) {
-        set_error("spchol_factor_batched: only single-GPU plans whose fronts all fit the shared-memory front kernel (m <= 128)");
-        return SPCHOL_EINVAL;
+    if (nbatch == 0) return 0;
+    // staging for the whole batch when it fits a quarter of the free memory, else slice by slice through the same buffers
+    size_t fr = 0, tot = 0;
+    CK(cudaMemGetInfo(&fr, &tot));
+    const double per = 8.0 * (static_cast<double>(H.nnzA) + H.nnzL) + 4;
+    const int cap = static_cast<int>(std::max(1.0, std::min(static_cast<double>(nbatch), 0.25 * static_cast<double>(fr) / per)));
+    if (p->hb_cap < cap) {
+        for (void* d : {static_cast<void*>(p->hbA), static_cast<void*>(p->hbL), static_cast<void*>(p->hbI)}) if (d) cudaFree(d);
+        p->hbA = p->hbL = nullptr; p->hbI = nullptr; p->hb_cap = 0;
+        CK(cudaMalloc(&p->hbA, sizeof(double) * H.nnzA * cap));
+        CK(cudaMalloc(&p->hbL, sizeof(double) * H.nnzL * cap));
+        CK(cudaMalloc(&p->hbI, sizeof(int) * cap));
+        p->hb_cap = cap;
     }
-    int rc;
-    if ((rc = batched_prepare(p))) return rc;
-    const int chunk = std::min(batched_chunk(p), std::max(nbatch, 1));
-    if ((rc = batched_reserve(p, chunk))) return rc;
-    double *dA = nullptr, *dLx = nullptr; int* dI = nullptr;
-    CK(cudaMalloc(&dA, sizeof(double) * H.nnzA * p->b_chunk));
-    CK(cudaMalloc(&dLx, sizeof(double) * H.nnzL * p->b_chunk));
-    CK(cudaMalloc(&dI, sizeof(int) * p->b_chunk));
-    cudaStream_t st = p->stream;
-    for (int b0 = 0; b0 < nbatch && !rc; b0 += p->b_chunk) {
-        const int nb = std::min(p->b_chunk, nbatch - b0);
-        cudaMemcpyAsync(dA, Ax + static_cast<int64_t>(b0) * H.nnzA, sizeof(double) * H.nnzA * nb, cudaMemcpyHostToDevice, st);
-        rc = spchol_factor_batched_device(p, nb, dA, dLx, dI);
-        cudaMemcpyAsync(Lx + static_cast<int64_t>(b0) * H.nnzL, dLx, sizeof(double) * H.nnzL * nb, cudaMemcpyDeviceToHost, st);
-        cudaMemcpyAsync(info + b0, dI, sizeof(int) * nb, cudaMemcpyDeviceToHost, st);
+    if (!p->hb_ev[0]) for (auto& e : p->hb_ev) CK(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+    if (!p->stream3) CK(cudaStreamCreateWithFlags(&p->stream3, cudaStreamNonBlocking));
+    if (!p->stream4) CK(cudaStreamCreateWithFlags(&p->stream4, cudaStreamNonBlocking));
+    // slices: H2D on stream3, kernels on the plan's stream, D2H on stream4; a slice's buffers are its own part of the staging
+    const int nslice = std::min(kBatchSlices, std::max(1, std::min(nbatch, p->hb_cap) / 256));
+    int64_t launches = 0;
+    for (int c0 = 0; c0 < nbatch; c0 += p->hb_cap) {
+        const int cn = std::min(p->hb_cap, nbatch - c0);
+        if (c0 > 0) CK(cudaStreamSynchronize(p->stream4));       // the staging buffers are reused
+        for (int sl = 0; sl < nslice; ++sl) {
+            const int s0 = static_cast<int>(static_cast<int64_t>(cn) * sl / nslice), s1 = static_cast<int>(static_cast<int64_t>(cn) * (sl + 1) / nslice);
+            if (s1 <= s0) continue;
+            const int ns_ = s1 - s0;
+            CK(cudaMemcpyAsync(p->hbA + static_cast<int64_t>(s0) * H.nnzA, Ax + static_cast<int64_t>(c0 + s0) * H.nnzA,
+                               sizeof(double) * H.nnzA * ns_, cudaMemcpyHostToDevice, p->stream3));
+            CK(cudaEventRecord(p->hb_ev[2 * sl], p->stream3));
+            CK(cudaStreamWaitEvent(p->stream, p->hb_ev[2 * sl], 0));
+            if ((rc = spchol_factor_batched_device(p, ns_, p->hbA + static_cast<int64_t>(s0) * H.nnzA, p->hbL + static_cast<int64_t>(s0) * H.nnzL, p->hbI + s0))) return rc;
+            launches += p->last_launches;
+            CK(cudaEventRecord(p->hb_ev[2 * sl + 1], p->stream));
+            CK(cudaStreamWaitEvent(p->stream4, p->hb_ev[2 * sl + 1], 0));
+            CK(cudaMemcpyAsync(Lx + static_cast<int64_t>(c0 + s0) * H.nnzL, p->hbL + static_cast<int64_t>(s0) * H.nnzL,
+                               sizeof(double) * H.nnzL * ns_, cudaMemcpyDeviceToHost, p->stream4));
+            CK(cudaMemcpyAsync(info + c0 + s0, p->hbI + s0, sizeof(int) * ns_, cudaMemcpyDeviceToHost, p->stream4));
+        }
     }
-    cudaError_t e = cudaStreamSynchronize(st);
-    cudaFree(dA); cudaFree(dLx); cudaFree(dI);
-    if (rc) return rc;
-    if (e != cudaSuccess) { set_error(std::string("spchol_factor_batched: ") + cudaGetErrorString(e)); return SPCHOL_ECUDA; }
+    CK(cudaStreamSynchronize(p->stream4));
+    CK(cudaStreamSynchronize(p->stream));
+    p->last_launches = launches;
     return 0;
 }
 

@@ -173,139 +173,6 @@ __global__ void __launch_bounds__(T) k_front_small(const int* __restrict__ list,
 }
 
 // ---------------------------------------------------------------------------------------------
-// Batched factorization, upper part of the assembly tree: ONE CTA walks a whole list of fronts
-// (ascending ids = children before parents) for ONE matrix.  Near the root the tree of a
-// 1138_bus-like pattern is a chain of fronts with few columns and many rows (w ~ 1..20, m ~ 100):
-// factored level by level, every link writes its whole contribution block to HBM and the next
-// link reads it back -- O(m^2) bytes for O(w m^2) flops, with one front per launch.  Here the
-// contribution block of a front whose parent is the next front of the list never leaves the SM:
-// it is lifted into registers (<= CH_MAXE entries per thread), the shared-memory front is rebuilt
-// for the parent, and the block is added back through the relative indices.
-// ---------------------------------------------------------------------------------------------
-constexpr int CH_T = 256;
-constexpr int CH_CTAS = 3;            // CTAs per SM the kernel is compiled for (register cap 85)
-constexpr int CH_MAXE = 28;           // carried contribution-block entries per thread: mb (mb + 1) / 2 <= 28 * 256
-// tri_tab[e] = (ii << 16) | jj enumerates the pairs ii >= jj row by row (e = ii (ii + 1) / 2 + jj): the entries of
-// an mb x mb lower triangle are exactly the prefix e < mb (mb + 1) / 2, whatever mb is -- one L1-resident table
-// (CH_MAXE * CH_T entries) decodes every carried block, with coalesced loads
-// The front is held packed (lower triangle only, column j at F + j m - j (j - 1) / 2 - j so that col[i] is valid
-// for i >= j): m (m + 1) / 2 doubles, 55 KB at m = 117, which lets three CTAs share an SM.
-__global__ void __launch_bounds__(CH_T, CH_CTAS) k_front_chain(const int* __restrict__ list, int count, FrontArrays fa,
-                                                         const int* __restrict__ tri_tab,
-                                                         double* __restrict__ L, double* __restrict__ W,
-                                                         int* __restrict__ info, int64_t lstride, int64_t wstride) {
-    extern __shared__ double F[];
-    __shared__ int srel[128];                           // relative indices of the carried child (mc <= 119)
-    L += blockIdx.x * lstride; W += blockIdx.x * wstride; info += blockIdx.x;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    constexpr int NW = CH_T / 32;
-    double carry[CH_MAXE];
-    int carried = -1;                                   // front whose contribution block sits in `carry`
-    for (int q = 0; q < count; ++q) {
-        const int s = list[q];
-        const int w = fa.w[s], m = fa.m[s], ld = fa.ld[s];
-        auto colp = [&](int j) { return F + (j * m - j * (j - 1) / 2 - j); };
-        double* __restrict__ P = L + fa.panel_off[s];
-        // 1. the front: A entries in the first w columns, zeros elsewhere
-        for (int j = warp; j < m; j += NW) {
-            double* col = colp(j);
-            if (j < w) {
-                const double* src = P + static_cast<int64_t>(j) * ld;
-                for (int i = j + lane; i < m; i += 32) col[i] = src[i];
-            } else {
-                for (int i = j + lane; i < m; i += 32) col[i] = 0.0;
-            }
-        }
-        __syncthreads();
-        // 2. children in ascending order (the summation order of the level-by-level path): the carried one
-        //    from registers, the others from the workspace
-        for (int cq = fa.child_ptr[s]; cq < fa.child_ptr[s + 1]; ++cq) {
-            const int c = fa.child_idx[cq];
-            const int mc = fa.m[c] - fa.w[c];
-            if (mc == 0) continue;
-            const int* __restrict__ r = fa.rel + fa.rel_off[c];
-            if (c == carried) {
-                const int ne = mc * (mc + 1) / 2;
-                if (tid < mc) srel[tid] = r[tid];
-                __syncthreads();
-#pragma unroll
-                for (int u = 0; u < CH_MAXE; ++u) {
-                    if (u * CH_T >= ne) break;          // uniform: small blocks leave the unrolled loop early
-                    const int e = tid + u * CH_T;
-                    if (e < ne) { const int t = __ldg(tri_tab + e); colp(srel[t & 0xffff])[srel[t >> 16]] += carry[u]; }
-                }
-            } else {
-                const int ldc = even_up_d(mc);
-                const double* __restrict__ C = W + fa.cb_off[c];
-                for (int jj = warp; jj < mc; jj += NW) {
-                    double* col = colp(r[jj]);
-                    const double* src = C + static_cast<int64_t>(jj) * ldc;
-                    for (int ii = jj + lane; ii < mc; ii += 32) col[r[ii]] += src[ii];
-                }
-            }
-            __syncthreads();
-        }
-        carried = -1;
-        // 3a. factor the panel (columns 0..w-1, all rows): right-looking inside the panel only
-        for (int k = 0; k < w; ++k) {
-            double* colk = colp(k);
-            const double d = colk[k];
-            if (d <= 0.0 && tid == 0) atomicMin(info, fa.first[s] + k + 1);     // reference test (chol.hpp:849)
-            const double piv = sqrt(d);
-            __syncthreads();                            // everyone has read the pivot
-            for (int i = k + 1 + tid; i < m; i += CH_T) colk[i] = colk[i] / piv;
-            if (tid == 0) colk[k] = piv;
-            __syncthreads();
-            for (int j = k + 1 + warp; j < w; j += NW) {
-                const double uj = colk[j];
-                double* col = colp(j);
-                for (int i = j + lane; i < m; i += 32) col[i] -= colk[i] * uj;
-            }
-            // (no barrier: the next pivot column k+1 is complete once every warp passed the barrier above of step k+1;
-            //  column k+1 is updated by the warp that owns j = k+1 and read by all after that barrier)
-            __syncthreads();
-        }
-        // 3b. contribution block: F[i][j] -= sum_k F[i][k] F[j][k], the same subtraction order as w rank-1 updates
-        for (int j = w + warp; j < m; j += NW) {
-            double* col = colp(j);
-            for (int i = j + lane; i < m; i += 32) {
-                double acc = col[i];
-                for (int k = 0; k < w; ++k) { const double* ck = colp(k); acc -= ck[i] * ck[j]; }
-                col[i] = acc;
-            }
-        }
-        __syncthreads();
-        // 4. panel -> L buffer; contribution block -> registers if the parent comes next, else -> workspace
-        for (int j = warp; j < w; j += NW) {
-            const double* col = colp(j);
-            double* dst = P + static_cast<int64_t>(j) * ld;
-            for (int i = j + lane; i < m; i += 32) dst[i] = col[i];
-        }
-        const int mb = m - w;
-        if (mb > 0) {
-            const int ne = mb * (mb + 1) / 2;
-            if (q + 1 < count && list[q + 1] == fa.parent[s] && ne <= CH_MAXE * CH_T) {
-#pragma unroll
-                for (int u = 0; u < CH_MAXE; ++u) {
-                    if (u * CH_T >= ne) break;
-                    const int e = tid + u * CH_T;
-                    if (e < ne) { const int t = __ldg(tri_tab + e); carry[u] = colp(w + (t & 0xffff))[w + (t >> 16)]; }
-                }
-                carried = s;
-            } else {
-                const int ldcb = even_up_d(mb);
-                for (int j = w + warp; j < m; j += NW) {
-                    const double* col = colp(j);
-                    double* dst = W + fa.cb_off[s] + static_cast<int64_t>(j - w) * ldcb - w;
-                    for (int i = j + lane; i < m; i += 32) dst[i] = col[i];
-                }
-            }
-        }
-        __syncthreads();                                // F is rebuilt for the next front
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
 // Large fronts, step 1: extend-add one child per parent per launch ("rounds": no two CTAs of a
 // launch touch the same parent, so no atomics and a fixed summation order).
 // grid = (tasks, column slices); each CTA walks child columns jj = blockIdx.y, += gridDim.y.
@@ -817,118 +684,6 @@ __global__ void __launch_bounds__(256) k_gemm_dmma(const GemmTask* __restrict__ 
                 if (col < t.N && row + t.diag >= col) {
                     double* c = C + row + static_cast<int64_t>(col) * ldc;
                     if (beta0) *c = -acc[mi][ni][e]; else *c -= acc[mi][ni][e];
-                }
-            }
-        }
-    }
-}
-
-// ---------------------------------------------------------------------------------------------
-// Same operation as k_gemm_dmma, asynchronous-copy pipeline: operands go global -> shared with
-// cp.async (LDGSTS, no register staging) through ST stages of K step 16, one __syncthreads per
-// step.  Tile and warp grid are template parameters; the shared leading dimensions are == 4
-// (mod 16) doubles so that the 64-bit fragment loads of a half-warp (4 k-rows x 4 consecutive
-// elements) hit 16 distinct 8-byte bank pairs.
-// ---------------------------------------------------------------------------------------------
-__device__ __forceinline__ void cp_async8(double* smem_dst, const double* gsrc, bool valid) {
-    const unsigned d = static_cast<unsigned>(__cvta_generic_to_shared(smem_dst));
-    const int sz = valid ? 8 : 0;      // src-size 0: the 8 destination bytes are zero-filled
-    asm volatile("cp.async.ca.shared.global [%0], [%1], 8, %2;\n" ::"r"(d), "l"(gsrc), "r"(sz));
-}
-__device__ __forceinline__ void cp_async_commit() { asm volatile("cp.async.commit_group;\n" ::); }
-template <int N>
-__device__ __forceinline__ void cp_async_wait() { asm volatile("cp.async.wait_group %0;\n" ::"n"(N)); }
-
-constexpr int G2_BK = 16;
-template <int BM, int BN, int ST>
-constexpr int gemm2_smem() { return ST * G2_BK * (BM + 4 + BN + 4) * 8; }
-
-template <int BM, int BN, int WGM, int WGN, int ST>
-__global__ void __launch_bounds__(WGM * WGN * 32) k_gemm2(const GemmTask* __restrict__ tasks,
-                                                          double* __restrict__ L, double* __restrict__ W) {
-    constexpr int NT = WGM * WGN * 32;
-    constexpr int LDA = BM + 4, LDB = BN + 4;
-    constexpr int STAGE = G2_BK * (LDA + LDB);
-    constexpr int TM = BM / WGM, TN = BN / WGN, MI = TM / 8, NI = TN / 8;
-    static_assert((BM * G2_BK) % NT == 0 && (BN * G2_BK) % NT == 0, "tile / thread mismatch");
-    extern __shared__ double sm[];
-    const GemmTask t = tasks[blockIdx.z];
-    const int i0 = blockIdx.x * BM, j0 = blockIdx.y * BN;
-    if (i0 >= t.M || j0 >= t.N) return;
-    if (i0 + BM - 1 + t.diag < j0) return;            // tile entirely above the wanted trapezoid
-    const double* __restrict__ A = L + t.a_off + i0;
-    const double* __restrict__ B = L + t.b_off + j0;
-    double* __restrict__ C = ((t.c_space & 1) ? W : L) + t.c_off;
-    const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-    const int g = lane >> 2, tq = lane & 3;
-    const int wm = warp % WGM, wn = warp / WGM;
-    const int K = t.K, lda = t.lda, ldb = t.ldb;
-    const int mrows = t.M - i0, nrows = t.N - j0;
-
-    auto issue = [&](int stage, int kt) {
-        double* as = sm + stage * STAGE;
-        double* bs = as + G2_BK * LDA;
-#pragma unroll
-        for (int r = 0; r < (BM * G2_BK) / NT; ++r) {
-            const int e = tid + r * NT, row = e % BM, k = e / BM;
-            const bool ok = row < mrows && kt + k < K;
-            cp_async8(as + k * LDA + row, ok ? A + row + static_cast<int64_t>(kt + k) * lda : A, ok);
-        }
-#pragma unroll
-        for (int r = 0; r < (BN * G2_BK) / NT; ++r) {
-            const int e = tid + r * NT, row = e % BN, k = e / BN;
-            const bool ok = row < nrows && kt + k < K;
-            cp_async8(bs + k * LDB + row, ok ? B + row + static_cast<int64_t>(kt + k) * ldb : B, ok);
-        }
-    };
-
-    double acc[MI][NI][2];
-#pragma unroll
-    for (int mi = 0; mi < MI; ++mi)
-#pragma unroll
-        for (int ni = 0; ni < NI; ++ni) { acc[mi][ni][0] = 0.0; acc[mi][ni][1] = 0.0; }
-
-    const int nk = (K + G2_BK - 1) / G2_BK;
-#pragma unroll
-    for (int s = 0; s < ST - 1; ++s) {
-        if (s < nk) issue(s, s * G2_BK);
-        cp_async_commit();
-    }
-    for (int it = 0; it < nk; ++it) {
-        cp_async_wait<ST - 2>();
-        __syncthreads();                                   // stage `it` has landed; stage it-1 is free
-        if (it + ST - 1 < nk) issue((it + ST - 1) % ST, (it + ST - 1) * G2_BK);
-        cp_async_commit();
-        const double* a = sm + (it % ST) * STAGE + wm * TM + g;
-        const double* b = sm + (it % ST) * STAGE + G2_BK * LDA + wn * TN + g;
-#pragma unroll
-        for (int kk = 0; kk < G2_BK; kk += 4) {
-            double af[MI], bf[NI];
-#pragma unroll
-            for (int mi = 0; mi < MI; ++mi) af[mi] = a[(kk + tq) * LDA + mi * 8];
-#pragma unroll
-            for (int ni = 0; ni < NI; ++ni) bf[ni] = b[(kk + tq) * LDB + ni * 8];
-#pragma unroll
-            for (int mi = 0; mi < MI; ++mi)
-#pragma unroll
-                for (int ni = 0; ni < NI; ++ni) dmma884(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
-        }
-    }
-    cp_async_wait<0>();
-
-    const int ldc = t.ldc;
-#pragma unroll
-    for (int mi = 0; mi < MI; ++mi) {
-        const int row = i0 + wm * TM + mi * 8 + g;
-        if (row >= t.M) continue;
-#pragma unroll
-        for (int ni = 0; ni < NI; ++ni) {
-#pragma unroll
-            for (int e = 0; e < 2; ++e) {
-                const int col = j0 + wn * TN + ni * 8 + 2 * tq + e;
-                if (col < t.N && row + t.diag >= col) {
-                    double* c = C + row + static_cast<int64_t>(col) * ldc;
-                    *c -= acc[mi][ni][e];
                 }
             }
         }

@@ -235,6 +235,9 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     // A scatter map (A is upper CSC: entry (i,j), i <= j, lands at L(j,i)); -1 where the front
     // of column i is not held by this rank
     P.a_dest.resize(S.nnzA);
+    const bool want_tree = opt.tree != 0 && world == 1;
+    std::vector<int> a_front, a_fcol, a_fpos;          // per A entry: front, column inside it, row position inside it (tree programs)
+    if (want_tree) { a_front.resize(S.nnzA); a_fcol.resize(S.nnzA); a_fpos.resize(S.nnzA); }
     for (int j = 0; j < n; ++j) {
         for (int p = S.Ap[j]; p < S.Ap[j + 1]; ++p) {
             const int i = S.Ai[p];
@@ -250,6 +253,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
                 pos = P.w[s] + static_cast<int>(it - b);
             }
             P.a_dest[p] = P.holds(s) ? P.panel_off[s] + static_cast<int64_t>(c) * P.ld[s] + pos : -1;
+            if (want_tree) { a_front[p] = s; a_fcol[p] = c; a_fpos[p] = pos; }
         }
     }
 
@@ -710,10 +714,24 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         }
     };
 
+    // ---- the bottom of the tree: whole subtrees, one warp each (tree_plan.h); the level program starts above them.
+    // The blocks of the subtree roots live in the arena from the start of the factorization until their parents ran.
+    std::vector<char> in_tree(ns, 0);
+    if (want_tree) {
+        if (P.max_m <= TW_MAX_M) build_tree_program(P, {}, true, a_front, a_fcol, a_fpos, P.tree_whole);
+        const std::vector<int> roots = choose_subtrees(P, opt.tree_cap_m, opt.tree_work, in_tree);
+        if (!roots.empty()) {
+            for (int s : roots) if (P.m[s] > P.w[s] && P.parent[s] >= 0) ws_alloc(s);
+            build_tree_program(P, roots, false, a_front, a_fcol, a_fpos, P.tree);
+            Op op{}; op.kind = OP_TREE; op.begin = 0; op.count = static_cast<int>(P.tree.tasks.size()); op.level = 0;
+            P.ops.push_back(op);
+            P.n_tree = static_cast<int64_t>(P.tree.fronts.size());
+        }
+    }
     for (int lv = 0; lv < nlev; ++lv) {
         std::vector<int> local_a, local_b, dists;
         for (int s : by_level[lv]) {
-            if (!P.holds(s)) continue;
+            if (!P.holds(s) || in_tree[s]) continue;
             if (P.m[s] > P.w[s]) ws_alloc(s);
             if (P.own_n[s] > 1) { dists.push_back(s); continue; }
             bool remote = false;

@@ -7,6 +7,7 @@
 #include <vector>
 
 #include "symbolic.h"
+#include "tree_plan.h"
 
 namespace spchol {
 
@@ -53,7 +54,8 @@ struct CopyTask {
 // valid serial order, so a single-stream replay (profiling, the host simulator) is correct.
 enum OpKind : int { OP_SMALL = 0, OP_ZERO = 1, OP_EXTADD = 2, OP_POTRF = 3, OP_TRSM = 4, OP_GEMM = 5, OP_COMM = 6, OP_COPY = 7,
                     OP_EV_RECORD = 8, OP_EV_WAIT = 9,
-                    OP_EXPORT = 10 };   // ranges of the L buffer that are final from here on (read-back of wide fronts, see ExportTask)
+                    OP_EXPORT = 10,     // ranges of the L buffer that are final from here on (read-back of wide fronts, see ExportTask)
+                    OP_TREE = 11 };     // the warp-per-subtree program (HostPlan::tree, tree_plan.h): begin = first task, count = tasks
 constexpr int kEventRing = 64;      // the engine keeps this many CUDA events; event id -> slot id % kEventRing
 struct Op {
     int kind;
@@ -82,6 +84,9 @@ struct PlanOptions {
     int defer_cb_add = 1;      // 1: large fronts never zero their contribution block: the Schur complement is stored (C = -A B^T)
                                // and the children's contributions to it are extend-added afterwards
     int lookahead = 1;         // 1: panel work of large fronts on stream 1, overlapped with the trailing update (see Op)
+    int tree = 1;              // 1: the bottom of the tree goes to the warp-per-subtree kernel (tree_plan.h) instead of one CTA per front and level
+    int tree_cap_m = 117;      // largest front inside a subtree task (117 rows: 55 KB packed, four warps per SM)
+    double tree_work = 2.5e6;  // dense flops of a subtree task (the unit of load balance: ~100 us of one warp)
     int export_mark_w = 0;     // > 0: fronts at least this wide announce every finished block column (OP_EXPORT).  Staged:
                                // checked by the plan simulator, not yet run on a GPU -- SPCHOL_EXPORT_MARK_W=1024 enables it
     // multi-GPU (one plan per rank, every rank builds the same global mapping):
@@ -125,10 +130,12 @@ struct HostPlan {
     std::vector<ExportTask> export_tasks;
     std::vector<char> front_marked;  // per front: 1 if all of its panel is announced by OP_EXPORT ops (not by its level)
     std::vector<Op> ops;
+    TreeProgram tree;                // subtrees at the bottom of the tree, one warp each (single-rank plans; empty: none)
+    TreeProgram tree_whole;          // the whole tree as ONE task (batched factorization; only when every front has m <= TW_MAX_M)
     int n_events = 0;                // event ids handed out (OP_EV_RECORD count)
     int max_potrf_slots = 0;
     // statistics
-    int64_t n_small = 0, n_large = 0;
+    int64_t n_small = 0, n_large = 0, n_tree = 0;     // fronts on the one-CTA-per-front path, the blocked path, inside subtree tasks
     int max_m = 0, max_w = 0;
     double gemm_flops = 0;           // flops of the full M x N x K rectangles of OP_GEMM tasks
     double gemm_flops_alg = 0;       // flops of the wanted (lower-trapezoid) part only

@@ -1,0 +1,68 @@
+// Warp-per-subtree program (host planner) for k_tree_warp (tree_kernel.cuh).
+//
+// ONE WARP factors a whole subtree of the assembly tree, front after front in postorder, with the
+// frontal matrix in shared memory -- no CTA barrier anywhere, parallelism comes from the number of
+// subtrees (single matrix: the bottom of the tree, where 2D 1024^2 has 145 000 fronts with m <= 128)
+// or from the number of matrices (batched factorization over one pattern, BASELINE config 5: one
+// warp per matrix walks the whole tree).  This is the fused dense chain of the reference's
+// factorize_sn + apply_update (include/chol.hpp:1232-1335, :1196-1216) without ever leaving the SM.
+//
+// Layout of a front inside the warp's shared memory: packed lower triangle over REVERSED indices
+// (i' = m-1-i): entry (i, j), i >= j, sits at tri(j') + i' with tri(x) = x (x + 1) / 2.  The position
+// depends on (i', j') only, not on m, so after the w pivot columns (the highest reversed indices)
+// have been eliminated, the contribution block is exactly the standard packed triangle of order
+// m - w at the start of the buffer: handing it to the parent costs nothing when the parent comes
+// next in the program ("carried"); the parent's rows are then spread in place by a monotone map
+// (new position >= old position, processed from the top down).  Contribution blocks of the other
+// children wait in a per-task stack in HBM/L2 ("stash"), in the same packed form.
+#pragma once
+#include <cstdint>
+#include <vector>
+
+namespace spchol {
+
+struct HostPlan;
+
+constexpr int TW_MAX_M = 128;                 // rows of the largest front a program may hold (static position map)
+enum : int { TW_CARRY_IN = 1,                 // the front's first child left its block in shared memory
+             TW_CARRY_OUT = 2,                // this front's block stays in shared memory for the next front (its parent)
+             TW_CB_STD = 4 };                 // block goes to the level program's workspace slot (column-major, ld = even(mb))
+
+struct alignas(16) TwFront {                  // 64 bytes, one descriptor load per front
+    int w, m, ld, first;                      // columns, rows, leading dimension of the panel in the L buffer, first global column
+    int flags, mc, map_off, nstash;           // carried child: order of its block, rmap[map_off .. +mc); stashed children to add
+    int stash0, a0, an, pad;                  // stashes[stash0 .. +nstash); A entries a_src/a_dst[a0 .. +an)
+    int64_t panel_off;                        // panel in the L buffer
+    int64_t cb_out;                           // TW_CB_STD: workspace offset; else (no carry, mb > 0): offset in the stash area
+};
+struct alignas(16) TwStash { int mc, map_off; int64_t src; };     // a stashed child block and its map into the parent
+struct TwTask { int front0, nfront; int64_t stash_base; };         // stash_base: start of the task's private stack in the stash area
+
+struct TreeProgram {
+    int cap_m = 0;                            // largest front (shared memory per warp = tri(cap_m) doubles)
+    int64_t stash_entries = 0;                // doubles of the stash area (all tasks)
+    std::vector<TwTask> tasks;
+    std::vector<TwFront> fronts;
+    std::vector<TwStash> stashes;
+    std::vector<int> rmap;                    // reversed position in the parent of every reversed index of a child's block
+    std::vector<int> a_src;                   // index into Ax
+    std::vector<unsigned short> a_dst;        // packed reversed index inside the front
+    std::vector<char> in_tree;                // per front of the plan: 1 if a task of this program factors it
+    double flops = 0;                         // dense flops of the fronts covered
+    int64_t n_fronts() const { return static_cast<int64_t>(fronts.size()); }
+};
+
+// The subtrees a single-matrix plan hands to k_tree_warp: maximal subtrees whose fronts all have m <= cap_m rows and
+// whose dense flops stay below work_limit (tasks are the unit of load balance).  in_tree[s] marks the fronts covered;
+// returns the roots (ascending).  Subtrees with fewer than min_fronts fronts are not worth a task of their own only if
+// they are single fronts whose parent is not covered either -- those stay with the level program (min_fronts = 1 keeps all).
+std::vector<int> choose_subtrees(const HostPlan& P, int cap_m, double work_limit, std::vector<char>& in_tree);
+
+// Builds the program: one task per root of `roots` (whole = false), or ONE task that walks every tree of the forest
+// (whole = true; roots ignored) -- the batched factorization.  a_front/a_col/a_pos: front, column inside the front and
+// row position inside the front of every stored entry of A (from build_plan).  std_cb: blocks of task roots go to
+// P.cb_off (the level program consumes them).
+void build_tree_program(const HostPlan& P, const std::vector<int>& roots, bool whole, const std::vector<int>& a_front,
+                        const std::vector<int>& a_col, const std::vector<int>& a_pos, TreeProgram& out);
+
+}  // namespace spchol

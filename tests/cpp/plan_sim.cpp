@@ -164,6 +164,7 @@ extern "C" int plansim_factor(int n, const int* Ap, const int* Ai, const double*
         for (int r = 0; r < world; ++r) {
             PlanOptions opt;
             opt.rank = r; opt.world = world;
+            opt.tree = 0;       // the warp-per-subtree tasks have their own host run (tests/cpp/tree_emu.cpp); here every front goes through the level program
             if (dist_NB > 0) opt.dist_NB = dist_NB;
             if (dist_min_w > 0) opt.dist_min_w = dist_min_w;
             if (small_max_m > 0) opt.small_max_m = small_max_m;

@@ -330,8 +330,8 @@ def test_batched_shared_pattern_vs_oracle():
         rc, Lp, Li, ref = po.chol(n, A.p, A.i, Ax[b])
         assert rc == 0
         assert rel_err(Lx[b], ref) <= REL_TOL
-    # the one-matrix path factors front by front, the batched path eliminates runs of fronts in one frontal matrix
-    # (different summation order, division-free pivots): equal to rounding, and reproducible from call to call
+    # the one-matrix path and the batched path (one warp walks the whole tree) sum in different orders: equal to
+    # rounding, and reproducible from call to call
     L1 = sc.chol(sc.CscMatrix(n, A.p, A.i, Ax[5]), S).value()
     assert rel_err(Lx[5], L1.x) <= 1e-11
     Lx2, info2 = sc.chol_batched(S, Ax)
@@ -339,41 +339,66 @@ def test_batched_shared_pattern_vs_oracle():
     assert (Lx2[ok] == Lx[ok]).all() and (info2 == info).all()
 
 
-@pytest.mark.parametrize("relax,max_nu", [(2, 160), (2, 128), (1, 160)])
-def test_batched_path_groups_vs_oracle(monkeypatch, relax, max_nu):
-    # the path-group kernel at several group capacities (its source also runs on host threads: tests/test_path_emu.py)
-    monkeypatch.setenv("SPCHOL_BATCH_PATH_NU", str(max_nu))
+@pytest.mark.parametrize("relax,wpc", [(1, 4), (1, 1), (0, 2), (2, 8)])
+def test_batched_warp_per_tree_vs_oracle(monkeypatch, relax, wpc):
+    # the warp-per-tree kernel (one warp per matrix; its source also runs on host threads: tests/test_tree_emu.py)
+    # at several amalgamation levels and CTA shapes; EVERY matrix of the batch is compared with the oracle
+    monkeypatch.setenv("SPCHOL_TREE_WPC", str(wpc))
     g = np.load(os.path.join(GOLD, "1138_bus.npz"))
     n = int(g["n"])
     A = sc.CscMatrix(n, g["Ap"], g["Ai"], g["Ax"])
-    S = sc.schol(A, relax=relax)                  # a fresh S: the batched setup reads the switches once per plan
-    nbatch = 300                                  # more matrices than CTAs resident at once on half the SMs
+    S = sc.schol(A, relax=relax)
+    nbatch = 700                                  # more matrices than warps resident at once (4 x 148 = 592)
     Ax = np.stack([synth.batch_values(A.p, A.i, A.x, b) for b in range(nbatch)])
     bad = 17
     Ax[bad, (A.p[1:] - 1)[500]] = -1.0
     Lx, info = sc.chol_batched(S, Ax)
     assert info[bad] == 501 and (np.delete(info, bad) == 0).all()
-    for b in (0, 1, 16, 18, 150, 299):
-        rc, Lp, Li, ref = po.chol(n, A.p, A.i, Ax[b])
+    parent, Lp, _ = po.schol(n, A.p, A.i, want_Li=False)
+    for b in range(nbatch):
+        if b == bad:
+            continue
+        rc, _, _, ref = po.chol(n, A.p, A.i, Ax[b], parent, Lp)
         assert rc == 0
-        assert rel_err(Lx[b], ref) <= REL_TOL
+        assert rel_err(Lx[b], ref) <= REL_TOL, b
     Lx2, info2 = sc.chol_batched(S, Ax)           # deterministic: fixed summation order
     assert (Lx2[np.arange(nbatch) != bad] == Lx[np.arange(nbatch) != bad]).all()
 
 
-def test_batched_chain_kernel_fallback(monkeypatch):
-    # SPCHOL_BATCH_PATH=0: the older one-front-at-a-time chain kernel stays available
-    monkeypatch.setenv("SPCHOL_BATCH_PATH", "0")
-    g = np.load(os.path.join(GOLD, "1138_bus.npz"))
+@pytest.mark.parametrize("name", ["bcsstk01", "lap2d_24"])
+def test_batched_other_patterns(name):
+    g = np.load(os.path.join(GOLD, name + ".npz"))
     n = int(g["n"])
     A = sc.CscMatrix(n, g["Ap"], g["Ai"], g["Ax"])
     S = sc.schol(A)
-    Ax = np.stack([synth.batch_values(A.p, A.i, A.x, b) for b in range(8)])
+    Ax = np.stack([synth.batch_values(A.p, A.i, A.x, b) for b in range(40)])
     Lx, info = sc.chol_batched(S, Ax)
     assert (info == 0).all()
-    for b in (0, 7):
-        rc, Lp, Li, ref = po.chol(n, A.p, A.i, Ax[b])
+    for b in range(40):
+        rc, _, _, ref = po.chol(n, A.p, A.i, Ax[b])
         assert rc == 0 and rel_err(Lx[b], ref) <= REL_TOL
+
+
+@pytest.mark.parametrize("dims", [(96, 96, 1), (20, 20, 20)])
+def test_subtree_tasks_on_and_off_agree(monkeypatch, dims):
+    """SPCHOL_TREE=0 keeps every small front on the one-CTA-per-front level kernels; the default hands the bottom
+    subtrees to k_tree_warp.  Same factor to rounding, both within the bar against the oracle."""
+    perm = synth.nd_perm(*dims)
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
+    A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
+    rc, Lp, Li, ref = po.chol(n, A.p, A.i, A.x)
+    assert rc == 0
+    out = {}
+    for tree in ("0", "1"):
+        monkeypatch.setenv("SPCHOL_TREE", tree)
+        S = sc.schol(A)                           # a fresh S: the switch is read when the plan is created
+        L = sc.chol(A, S).value()
+        assert (L.p == Lp).all() and (L.i == Li).all()
+        assert rel_err(L.x, ref) <= REL_TOL
+        assert sc.residual(A, S) <= RES_TOL
+        out[tree] = (L.x, S.plan_stats(0))
+    assert rel_err(out["1"][0], out["0"][0]) <= 1e-11
+    assert out["1"][1]["n_ops"] < out["0"][1]["n_ops"]      # the subtree tasks replaced level launches
 
 
 def test_batched_refuses_large_front_patterns():

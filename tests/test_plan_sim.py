@@ -22,8 +22,8 @@ GOLD = os.path.join(ROOT, "tests", "golden")
 
 @pytest.fixture(scope="module")
 def sim():
-    srcs = [os.path.join(ROOT, "tests", "cpp", "plan_sim.cpp"), os.path.join(CSRC, "plan.cpp"), os.path.join(CSRC, "symbolic.cpp")]
-    deps = srcs + [os.path.join(CSRC, "plan.h"), os.path.join(CSRC, "symbolic.h")]
+    srcs = [os.path.join(ROOT, "tests", "cpp", "plan_sim.cpp"), os.path.join(CSRC, "plan.cpp"), os.path.join(CSRC, "tree_plan.cpp"), os.path.join(CSRC, "symbolic.cpp")]
+    deps = srcs + [os.path.join(CSRC, "plan.h"), os.path.join(CSRC, "tree_plan.h"), os.path.join(CSRC, "symbolic.h")]
     if not os.path.exists(SO) or any(os.path.getmtime(f) > os.path.getmtime(SO) for f in deps):
         subprocess.run(["g++", "-std=c++17", "-O2", "-fPIC", "-shared", "-o", SO] + srcs, check=True)
     L = C.CDLL(SO)
