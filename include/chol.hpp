@@ -17,15 +17,25 @@
 
 #include <algorithm>
 #include <cassert>
+#include <cmath>
 #include <cstddef>
+#include <cstdint>
 #include <expected>
 #include <memory>
+#include <random>
 #include <stdexcept>
 #include <string>
 #include <utility>
 #include <vector>
 
 #include "spchol.h"
+
+// The reference's header declares LAPACK's dpotrf_ (include/chol.hpp:20-22) and its tests call it through that
+// declaration (tests/test_chol.cpp:73,113) as the dense cross-check; callers link their own LAPACK as before.
+// Nothing in this header or in libspchol.so calls it.
+extern "C" {
+void dpotrf_(const char* uplo, const int* n, double* a, const int* lda, int* info);
+}
 
 enum class sym { none, upper, lower };          // reference chol.hpp:26
 
@@ -103,6 +113,19 @@ public:
     }
     csc_matrix(std::size_t n, std::size_t nnz) requires(S != sym::none)
         : internal::csc_storage(n, n, nnz), x_(nnz, T{}) { assert(n > 0 && nnz > 0); }
+    // reference chol.hpp:190-217: the pattern of `schol`, holding A's value wherever A stores that very (row, column)
+    // slot and 0 in the fill-in slots.  As in the reference the look-up is the raw find_index(row, col) -- no swap by
+    // the symmetry tag -- so from an upper-stored A only the diagonal carries over.
+    template <sym S_A>
+    csc_matrix(const csc_matrix<T, S_A>& A, const SChol& schol)
+        : internal::csc_storage(schol.size(), schol.size(), schol.capacity()), x_(schol.capacity(), T(0)) {
+        p_ = schol.p(); i_ = schol.i();
+        for (int j = 0; j < static_cast<int>(A.cols()); ++j)
+            for (int q = p_[j]; q < p_[j + 1]; ++q) {
+                const int at = A.find_index(static_cast<std::size_t>(i_[q]), static_cast<std::size_t>(j));
+                x_[q] = at != -1 ? A.x()[at] : T(0);
+            }
+    }
 
     T& operator[](std::size_t i, std::size_t j) {
         assert(i < m_ && j < n_);
@@ -241,6 +264,8 @@ template <typename T>
 std::expected<csc_matrix<T, sym::none>, std::string> chol(const csc_matrix<T, sym::upper>& A, const SChol& S, int device = 0) {
     static_assert(std::is_same_v<T, double>, "the B200 path is fp64");
     if (!S.symbolic) return std::unexpected(std::string("chol: S was not produced by schol()"));
+    if (A.size() != S.size() || static_cast<std::int64_t>(A.p()[A.size()]) != spchol_symbolic_nnzA(S.symbolic.get()))
+        return std::unexpected(std::string("chol: A does not have the pattern S was built from"));
     if (!S.plan || S.plan_device != device) {
         spchol_plan* p = nullptr;
         if (spchol_plan_create(S.symbolic.get(), device, &p) != SPCHOL_OK) return std::unexpected(std::string(spchol_last_error()));
@@ -261,10 +286,195 @@ std::expected<csc_matrix<T, sym::none>, std::string> chol(const csc_matrix<T, sy
     return chol(A, schol(A));
 }
 
+// reference chol.hpp:1407-1446: the supernodal entry point.  The reference's own body is unfinished (it returns
+// diag(sqrt(a_ii)) scattered into wrong slots); here it is the same supernodal GPU factorization
+// chol() runs -- the thing that function was meant to be -- so tests/test_chol.cpp:99-136 passes.
+template <typename T>
+std::expected<csc_matrix<T, sym::none>, std::string> chol_sn(csc_matrix<T, sym::upper>& A) {
+    return chol(A);
+}
+
+// reference chol.hpp:628-678: pattern of L from one ereach per column.  As in the reference the column's own marker is
+// not preset, so the walk runs on past j and the column also lists the etree ancestors of j (an upper bound of the
+// true pattern: 1172 vs 877 entries on bcsstk01); kept for callers that use it, schol() is the exact one.
+template <typename T>
+SChol schol_etree(const csc_matrix<T, sym::upper>& A) {
+    const int n = static_cast<int>(A.size());
+    SChol S;
+    S.parent = etree(A);
+    auto& Sp = S.p();
+    Sp.assign(n + 1, 0);
+    std::vector<int> s(n), w(n, -1), rows;
+    std::vector<T> x(n, T(0));
+    for (int j = 0; j < n; ++j) {
+        const std::size_t top = ereach(A, static_cast<std::size_t>(j), S.parent, s, w, x, static_cast<std::size_t>(n));
+        const std::size_t start = rows.size();
+        rows.push_back(j);
+        for (std::size_t t = top; t < static_cast<std::size_t>(n); ++t) if (s[t] > j) rows.push_back(s[t]);
+        std::sort(rows.begin() + static_cast<std::ptrdiff_t>(start), rows.end());
+        Sp[j + 1] = static_cast<int>(rows.size());
+    }
+    S.i() = std::move(rows);
+    S.set_capacity(S.i().size());
+    return S;
+}
+
+namespace internal {
+// pcg32 (PCG XSH-RR 64/32, default stream) -- the generator the reference takes from its pcg-cpp submodule
+// (pcg_random.hpp, `pcg32 gen(seed)`): state = (seed + inc) * mult + inc, output from the state before the step.
+class pcg32_engine {
+    std::uint64_t state_;
+    static constexpr std::uint64_t mult = 6364136223846793005ULL, inc = 1442695040888963407ULL;
+public:
+    using result_type = std::uint32_t;
+    explicit pcg32_engine(std::uint64_t seed) : state_((seed + inc) * mult + inc) {}
+    static constexpr result_type min() { return 0u; }
+    static constexpr result_type max() { return 0xffffffffu; }
+    result_type operator()() {
+        const std::uint64_t old = state_;
+        state_ = old * mult + inc;
+        const std::uint32_t xs = static_cast<std::uint32_t>(((old >> 18u) ^ old) >> 27u), rot = static_cast<std::uint32_t>(old >> 59u);
+        return (xs >> rot) | (xs << ((32u - rot) & 31u));
+    }
+};
+}  // namespace internal
+
+// reference chol.hpp:964-996: random symmetric sparse matrix (upper stored), seed 21, diagonal kept and boosted by n.
+template <typename T>
+csc_matrix<T, sym::upper> random_sparse(int n, double density = 0.25, bool positive_definite = true) {
+    internal::pcg32_engine gen(21);
+    std::uniform_real_distribution<double> dist(-n, n);
+    std::vector<int> ti, tj;
+    std::vector<T> tx;
+    for (int i = 0; i < n; ++i)
+        for (int j = i; j < n; ++j) {
+            const double v = dist(gen);
+            if (std::fabs(v) < density * n || i == j) {
+                T val = static_cast<T>(dist(gen));
+                if (i == j && positive_definite) val += static_cast<T>(n);
+                ti.push_back(i); tj.push_back(j); tx.push_back(val);
+            }
+        }
+    return triplet_to_csc_matrix(ti, tj, tx, n);
+}
+
+// reference chol.hpp:1004-1034: random SPD values on the pattern of S (returned lower, callers transpose), seed 42.
+template <typename T>
+csc_matrix<T, sym::lower> random_sparse(const SChol& S, bool positive_definite = true) {
+    const int n = static_cast<int>(S.size());
+    csc_matrix<T, sym::lower> A(S);
+    internal::pcg32_engine gen(42);
+    std::uniform_real_distribution<double> dist(-1.0, 1.0);
+    for (int j = 0; j < n; ++j)
+        for (int q = S.p()[j]; q < S.p()[j + 1]; ++q)
+            A.x()[q] = S.i()[q] == j ? static_cast<T>(1.5 * (std::fabs(dist(gen)) + (positive_definite ? n : 0)))
+                                     : std::fabs(static_cast<T>(dist(gen)) * 10);
+    return A;
+}
+
+// ---- beyond the reference: factors with more than INT_MAX nonzeros --------------------------------
+// The reference's containers are 32-bit (std::vector<int> p_, i_; chol.hpp:52,55; the nnz accumulators at :765, :890
+// overflow at the 128^3 Laplacian, nnz(L) = 2.83e9).  SChol64 is the symbolic handle without the 32-bit pattern
+// arrays, csc_matrix64 the same CSC layout with 64-bit column pointers, chol64 the numeric factorization into it;
+// chol_resident keeps the factor on the device (for chol_solve / chol_residual) when even that is too much to move.
+struct SChol64 {
+    std::size_t n = 0;
+    std::int64_t nnz = 0;
+    std::vector<int> parent;
+    std::shared_ptr<spchol_symbolic> symbolic;
+    mutable std::shared_ptr<spchol_plan> plan;
+    mutable int plan_device = -1;
+    std::size_t size() const { return n; }
+    std::int64_t capacity() const { return nnz; }
+};
+template <typename T>
+class csc_matrix64 {
+    std::size_t n_ = 0;
+    std::vector<std::int64_t> p_;
+    std::vector<int> i_;
+    std::vector<T> x_;
+public:
+    csc_matrix64() = default;
+    csc_matrix64(std::size_t n, std::int64_t nnz) : n_(n), p_(n + 1, 0), i_(static_cast<std::size_t>(nnz)), x_(static_cast<std::size_t>(nnz)) {}
+    std::size_t rows() const { return n_; }
+    std::size_t cols() const { return n_; }
+    std::size_t size() const { return n_; }
+    std::int64_t capacity() const { return static_cast<std::int64_t>(i_.size()); }
+    std::vector<std::int64_t>& p() { return p_; }
+    std::vector<int>& i() { return i_; }
+    std::vector<T>& x() { return x_; }
+    const std::vector<std::int64_t>& p() const { return p_; }
+    const std::vector<int>& i() const { return i_; }
+    const std::vector<T>& x() const { return x_; }
+    std::int64_t find_index(std::size_t i, std::size_t j) const {
+        const auto b = i_.begin() + p_[j], e = i_.begin() + p_[j + 1];
+        const auto it = std::lower_bound(b + 1 <= e ? b + 1 : e, e, static_cast<int>(i));      // diagonal first, then ascending
+        if (b != e && *b == static_cast<int>(i)) return p_[j];
+        return (it != e && *it == static_cast<int>(i)) ? static_cast<std::int64_t>(it - i_.begin()) : -1;
+    }
+    const T operator[](std::size_t i, std::size_t j) const { const auto q = find_index(i, j); return q < 0 ? T(0) : x_[static_cast<std::size_t>(q)]; }
+};
+template <typename T>
+SChol64 schol64(const csc_matrix<T, sym::upper>& A) {
+    spchol_symbolic* h = nullptr;
+    if (spchol_symbolic_create(static_cast<int>(A.size()), A.p().data(), A.i().data(), &h) != SPCHOL_OK) internal::throw_last("schol64");
+    SChol64 S;
+    S.symbolic.reset(h, internal::symbolic_deleter{});
+    S.n = A.size(); S.nnz = spchol_symbolic_nnzL(h);
+    S.parent.resize(S.n);
+    spchol_symbolic_parent(h, S.parent.data());
+    return S;
+}
+namespace internal {
+template <typename T, typename SC>
+std::expected<bool, std::string> ensure_plan(const csc_matrix<T, sym::upper>& A, const SC& S, int device) {
+    if (!S.symbolic) return std::unexpected(std::string("chol: S was not produced by schol()"));
+    if (A.size() != S.size() || static_cast<std::int64_t>(A.p()[A.size()]) != spchol_symbolic_nnzA(S.symbolic.get()))
+        return std::unexpected(std::string("chol: A does not have the pattern S was built from"));
+    if (!S.plan || S.plan_device != device) {
+        spchol_plan* p = nullptr;
+        if (spchol_plan_create(S.symbolic.get(), device, &p) != SPCHOL_OK) return std::unexpected(std::string(spchol_last_error()));
+        S.plan.reset(p, plan_deleter{});
+        S.plan_device = device;
+    }
+    return true;
+}
+}  // namespace internal
+// numeric factorization into the 64-bit CSC: the supernodal panels come back through spchol_factor_lbuf (read back
+// while the upper levels still compute when the buffer is pinned) and are gathered on the host
+template <typename T>
+std::expected<csc_matrix64<T>, std::string> chol64(const csc_matrix<T, sym::upper>& A, const SChol64& S, int device = 0) {
+    static_assert(std::is_same_v<T, double>, "the B200 path is fp64");
+    if (auto ok = internal::ensure_plan(A, S, device); !ok) return std::unexpected(ok.error());
+    std::int64_t entries = 0;
+    spchol_symbolic_panel_layout(S.symbolic.get(), nullptr, nullptr, nullptr, nullptr, &entries);
+    void* host = nullptr;
+    if (spchol_host_alloc(entries * 8, &host) != SPCHOL_OK) return std::unexpected(std::string(spchol_last_error()));
+    std::unique_ptr<void, void (*)(void*)> guard(host, [](void* q) { spchol_host_free(q); });
+    int info = 0;
+    if (spchol_factor_lbuf(S.plan.get(), A.x().data(), static_cast<double*>(host), &info) != SPCHOL_OK)
+        return std::unexpected(std::string(spchol_last_error()));
+    if (info > 0) return std::unexpected(std::string("A is not positive definite."));      // reference chol.hpp:850
+    csc_matrix64<T> L(S.n, S.nnz);
+    if (spchol_symbolic_gather_csc64(S.symbolic.get(), static_cast<const double*>(host), L.p().data(), L.i().data(), L.x().data()) != SPCHOL_OK)
+        return std::unexpected(std::string(spchol_last_error()));
+    return L;
+}
+// the handle-returning form: the factor stays on the device in S's plan; chol_solve / chol_residual consume it
+template <typename T, typename SC>
+std::expected<bool, std::string> chol_resident(const csc_matrix<T, sym::upper>& A, const SC& S, int device = 0) {
+    static_assert(std::is_same_v<T, double>, "the B200 path is fp64");
+    if (auto ok = internal::ensure_plan(A, S, device); !ok) return std::unexpected(ok.error());
+    int info = 0;
+    if (spchol_factor_resident(S.plan.get(), A.x().data(), &info) != SPCHOL_OK) return std::unexpected(std::string(spchol_last_error()));
+    if (info > 0) return std::unexpected(std::string("A is not positive definite."));
+    return true;
+}
+
 // ---- beyond the reference: consumers of the device-resident factor of the last chol(A, S) ----
 // x = A^-1 b: forward and backward substitution on the supernodal panels on the GPU.  b: n x nrhs, column-major.
-template <typename T>
-std::expected<std::vector<T>, std::string> chol_solve(const SChol& S, const std::vector<T>& b, int nrhs = 1) {
+template <typename T, typename SC = SChol>
+std::expected<std::vector<T>, std::string> chol_solve(const SC& S, const std::vector<T>& b, int nrhs = 1) {
     static_assert(std::is_same_v<T, double>, "the B200 path is fp64");
     if (!S.plan) return std::unexpected(std::string("chol_solve: call chol(A, S) first"));
     if (b.size() != S.size() * static_cast<std::size_t>(nrhs)) return std::unexpected(std::string("chol_solve: b must hold n x nrhs values"));
@@ -273,8 +483,8 @@ std::expected<std::vector<T>, std::string> chol_solve(const SChol& S, const std:
     return x;
 }
 // ||A - L L^T||_F / ||A||_F of that factor, estimated on the GPU (what the reference's tests do densely, tests/test_chol.cpp:87)
-template <typename T>
-std::expected<double, std::string> chol_residual(const csc_matrix<T, sym::upper>& A, const SChol& S) {
+template <typename T, typename SC = SChol>
+std::expected<double, std::string> chol_residual(const csc_matrix<T, sym::upper>& A, const SC& S) {
     static_assert(std::is_same_v<T, double>, "the B200 path is fp64");
     if (!S.plan) return std::unexpected(std::string("chol_residual: call chol(A, S) first"));
     double r = 0;

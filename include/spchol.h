@@ -84,6 +84,7 @@ int     spchol_symbolic_create_ex(int n, const int* Ap, const int* Ai, int relax
 void    spchol_symbolic_destroy(spchol_symbolic*);
 int     spchol_symbolic_n(const spchol_symbolic*);
 int64_t spchol_symbolic_nnzL(const spchol_symbolic*);
+int64_t spchol_symbolic_nnzA(const spchol_symbolic*);           /* stored entries of triu(A) the pattern was built from */
 double  spchol_symbolic_flops(const spchol_symbolic*);          /* sum_j colcount_j^2 */
 int     spchol_symbolic_parent(const spchol_symbolic*, int* parent);          /* SChol::parent */
 int     spchol_symbolic_colcount(const spchol_symbolic*, int* colcount);
@@ -104,6 +105,13 @@ int     spchol_symbolic_stats(const spchol_symbolic*, int64_t* stats);
  * relaxed amalgamation added to the pattern are exact zeros. */
 int     spchol_symbolic_panel_layout(const spchol_symbolic*, int* w, int* m, int* ld, int64_t* panel_off, int64_t* lbuf_entries);
 int     spchol_symbolic_front_rows(const spchol_symbolic*, int front, int* rows /* m[front] */);
+
+/* CSC of L with 64-bit column pointers, gathered on the host from a supernodal panel buffer of the layout above:
+ * Lp[n+1] (int64), Li / Lx [nnz(L)] in the reference's order (diagonal first, rows ascending, true pattern only).
+ * The reference's containers are 32-bit (include/chol.hpp:52,55), so this is how a factor with nnz(L) > INT_MAX
+ * (128^3 Laplacian: 2.83e9) reaches a host caller as CSC.  Lp / Li / Lx may be NULL individually (lbuf may be NULL
+ * when Lx is). */
+int     spchol_symbolic_gather_csc64(const spchol_symbolic*, const double* lbuf, int64_t* Lp, int* Li, double* Lx);
 
 /* ---- numeric plan + factorization: replaces chol<T>(A) (include/chol.hpp:750-863) --------- */
 /* device: CUDA ordinal. The plan owns the device L buffer and contribution workspace. */
@@ -148,6 +156,9 @@ int  spchol_map_fronts(const spchol_symbolic*, int world, int dist_min_w, int* o
 /* Host-buffer call (what chol(A,S) binds): H2D of Ax, factor, CSC gather, D2H of Lx.
  * info = 0, or (1-based) a column whose pivot was <= 0 -> "A is not positive definite." (chol.hpp:849-850). */
 int  spchol_factor(spchol_plan*, const double* Ax_host, double* Lx_host, int* info);
+/* Host values in, factor stays on the device (supernodal panels) for spchol_solve / spchol_residual / spchol_lbuf*:
+ * H2D of Ax, factor, info back.  The handle-returning form of chol(A, S) for factors too large to read back. */
+int  spchol_factor_resident(spchol_plan*, const double* Ax_host, int* info);
 /* Batched numeric factorization: nbatch value sets over ONE pattern (BASELINE config 5; the reference
  * would loop chol(A_b), include/chol.hpp:750).  Ax[nbatch][nnzA] -> Lx[nbatch][nnzL] in the CSC order of S,
  * info[nbatch] = 0 or the 1-based failing column of that matrix.  Every launch of the level program covers

@@ -34,6 +34,9 @@ SIGNATURES = {
     "spchol_symbolic_destroy": (None, [_VP]),
     "spchol_symbolic_n": (C.c_int, [_VP]),
     "spchol_symbolic_nnzL": (C.c_int64, [_VP]),
+    "spchol_symbolic_nnzA": (C.c_int64, [_VP]),
+    "spchol_symbolic_gather_csc64": (C.c_int, [_VP, _VP, _VP, _VP, _VP]),
+    "spchol_factor_resident": (C.c_int, [_VP, _VP, C.POINTER(C.c_int)]),
     "spchol_symbolic_flops": (C.c_double, [_VP]),
     "spchol_symbolic_parent": (C.c_int, [_VP, _VP]),
     "spchol_symbolic_colcount": (C.c_int, [_VP, _VP]),

@@ -250,6 +250,50 @@ int spchol_symbolic_front_rows(const spchol_symbolic* s, int front, int* rows) {
     return 0;
 }
 
+int64_t spchol_symbolic_nnzA(const spchol_symbolic* s) { return s ? s->S.nnzA : 0; }
+
+// Supernodal panels (single-GPU layout, spchol_symbolic_panel_layout) -> CSC of L with 64-bit column pointers: the
+// container the reference cannot offer (its p_/i_ are std::vector<int>, include/chol.hpp:52,55, so nnz(L) <= INT_MAX).
+// Layout as the reference's L: diagonal first, rows ascending (:844-855); only the TRUE pattern is emitted, the
+// explicit zeros of relaxed amalgamation are dropped.  Any of Lp / Li / Lx may be NULL.  Host side, one pass.
+int spchol_symbolic_gather_csc64(const spchol_symbolic* sp, const double* lbuf, int64_t* Lp, int* Li, double* Lx) {
+    if (!sp) { set_error("spchol_symbolic_gather_csc64: null symbolic"); return SPCHOL_EINVAL; }
+    if (Lx && !lbuf) { set_error("spchol_symbolic_gather_csc64: values wanted but no panel buffer given"); return SPCHOL_EINVAL; }
+    const Symbolic& S = sp->S;
+    if (Lp) std::memcpy(Lp, S.Lp.data(), sizeof(int64_t) * (static_cast<size_t>(S.n) + 1));
+    if (!Li && !Lx) return 0;
+    try {
+        const std::vector<int>& fbelow = S.fundamental_below();
+        int64_t po = 0;
+        for (int s = 0; s < S.ns; ++s) {
+            const int w = S.w(s), m = S.m(s), ld = (m + 1) & ~1, first = S.sn_start[s];
+            const int* b = S.below(s);
+            const int nbr = m - w, send = first + w;
+            for (int c = 0; c < w; ++c) {
+                const int j = first + c, f = S.fsn_id[j];
+                int64_t q = S.Lp[j];
+                const double* col = lbuf ? lbuf + po + static_cast<int64_t>(c) * ld : nullptr;
+                const int fend = S.fsn_start[f + 1];
+                for (int r = j; r < fend; ++r, ++q) { if (Li) Li[q] = r; if (Lx) Lx[q] = col[r - first]; }
+                const int* fb = fbelow.data() + S.fbelow_ptr[f];
+                const int nfb = static_cast<int>(S.fbelow_ptr[f + 1] - S.fbelow_ptr[f]);
+                int k = 0;
+                for (int t = 0; t < nfb; ++t, ++q) {
+                    const int r = fb[t];
+                    if (Li) Li[q] = r;
+                    if (!Lx) continue;
+                    if (r < send) { Lx[q] = col[r - first]; continue; }
+                    while (k < nbr && b[k] < r) ++k;
+                    if (k >= nbr || b[k] != r) { set_error("spchol_symbolic_gather_csc64: pattern row missing in its front"); return SPCHOL_EINVAL; }
+                    Lx[q] = col[w + k];
+                }
+            }
+            po += static_cast<int64_t>(ld) * w;
+        }
+    } catch (const std::exception& e) { set_error(e.what()); return SPCHOL_EINVAL; }
+    return 0;
+}
+
 static int dryrun_impl(const spchol_symbolic* s, int rank, int world, const int* dist_opts, int64_t* st,
                        int64_t* extra, int nextra, int64_t* comm_sig) {
     if (!s || !st) return SPCHOL_EINVAL;

@@ -183,6 +183,16 @@ int set_small_attr() {
     return 0;
 }
 
+// one CTA (a team of nw warps) per task / per matrix, see tree_kernel.cuh
+constexpr size_t tree_smem(int f_stride) { return (static_cast<size_t>(f_stride) + 2) * 8 + TW_MAX_M * 4; }
+void launch_tree(int nw, int grid, int f_stride, cudaStream_t st, const TreeArrays& ta, const double* Ax, double* L, double* W, double* Stash,
+                 double* Lx, int* info, int64_t axs, int64_t ls, int64_t ws, int64_t ss, int64_t lxs, int nmat, int out_mode) {
+    const size_t sm = tree_smem(f_stride);
+    if (nw >= 4)      k_tree_team<4><<<grid, 128, sm, st>>>(ta, Ax, L, W, Stash, Lx, info, axs, ls, ws, ss, lxs, nmat, f_stride, out_mode);
+    else if (nw >= 2) k_tree_team<2><<<grid, 64, sm, st>>>(ta, Ax, L, W, Stash, Lx, info, axs, ls, ws, ss, lxs, nmat, f_stride, out_mode);
+    else              k_tree_team<1><<<grid, 32, sm, st>>>(ta, Ax, L, W, Stash, Lx, info, axs, ls, ws, ss, lxs, nmat, f_stride, out_mode);
+}
+
 // issue the whole numeric factorization on the plan's stream
 int export_prepare(spchol_plan* p) {
     if (!p->export_runs.empty()) return 0;
@@ -299,11 +309,11 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
         mark(pk);
         const int64_t before = launches;
         switch (op.kind) {
-        case OP_TREE:
-            k_tree_warp<<<op.count, 32, static_cast<size_t>(p->tree.f_stride) * 8 + TW_MAX_M * 4, st>>>(
-                p->tree.ta, dAx, p->dL, p->dW, p->tree.stash, nullptr, p->dinfo, 0, 0, 0, 0, 0, 0, p->tree.f_stride, 0);
+        case OP_TREE: {
+            static const int nw = getenv("SPCHOL_TREE_NW") ? atoi(getenv("SPCHOL_TREE_NW")) : 1;
+            launch_tree(nw, op.count, p->tree.f_stride, st, p->tree.ta, dAx, p->dL, p->dW, p->tree.stash, nullptr, p->dinfo, 0, 0, 0, 0, 0, 0, 0);
             ++launches;
-            break;
+        } break;
         case OP_SMALL: {
             const int* list = p->d_small_list + op.begin;
             const unsigned g = static_cast<unsigned>(op.count);
@@ -520,7 +530,7 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
             if ((r2 = upload(p, T.tasks, &dt)) || (r2 = upload(p, T.fronts, &df)) || (r2 = upload(p, T.stashes, &dsx)) ||
                 (r2 = upload(p, T.rmap, &drm)) || (r2 = upload(p, T.a_src, &das)) || (r2 = upload(p, T.a_dst, &dad))) return r2;
             D.ta = TreeArrays{dt, static_cast<int>(T.tasks.size()), df, dsx, drm, das, dad, csc_map};
-            D.f_stride = ((T.cap_m * (T.cap_m + 1) / 2) + 1) & ~1;
+            D.f_stride = ((T.cap_m * (T.cap_m + 1) / 2) + TK_F_SLACK + 1) & ~1;
             D.stash_entries = (T.stash_entries + 1) & ~int64_t(1);
             D.on = true;
             std::vector<TwFront>().swap(T.fronts); std::vector<TwStash>().swap(T.stashes); std::vector<int>().swap(T.rmap);
@@ -535,8 +545,10 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
             int* dmap = nullptr;
             if ((rc = upload(p, inv, &dmap)) || (rc = up_tree(H.tree_whole, p->whole, dmap))) return fail(rc);
         }
-        if (cudaFuncSetAttribute(k_tree_warp, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) {
-            set_error("cudaFuncSetAttribute (k_tree_warp) failed"); return fail(SPCHOL_ECUDA);
+        if (cudaFuncSetAttribute(k_tree_team<1>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(k_tree_team<2>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess ||
+            cudaFuncSetAttribute(k_tree_team<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, 227 * 1024) != cudaSuccess) {
+            set_error("cudaFuncSetAttribute (k_tree_team) failed"); return fail(SPCHOL_ECUDA);
         }
     }
     // the big host-side maps are only needed on the device from here on
@@ -713,6 +725,16 @@ int spchol_factor(spchol_plan* p, const double* Ax, double* Lx, int* info) {
     return SPCHOL_OK;
 }
 
+int spchol_factor_resident(spchol_plan* p, const double* Ax, int* info) {
+    if (!p || !Ax) { set_error("spchol_factor_resident: null argument"); return SPCHOL_EINVAL; }
+    CK(cudaSetDevice(p->device));
+    int rc;
+    if (!p->dAx && (rc = dalloc(p, p->H.nnzA, &p->dAx))) return rc;
+    CK(cudaMemcpyAsync(p->dAx, Ax, static_cast<size_t>(p->H.nnzA) * sizeof(double), cudaMemcpyHostToDevice, p->stream));
+    if ((rc = run_numeric(p, p->dAx))) return rc;
+    return read_info(p, info);
+}
+
 // H2D of Ax, numeric, D2H of the whole supernodal L buffer (for patterns whose CSC L exceeds
 // the reference's 32-bit indices, e.g. the 128^3 Laplacian).
 int spchol_factor_lbuf(spchol_plan* p, const double* Ax, double* Lbuf_host, int* info) {
@@ -749,7 +771,7 @@ int spchol_factor_lbuf(spchol_plan* p, const double* Ax, double* Lbuf_host, int*
 }
 
 // ---- batched numeric factorization: many value sets over one pattern (config 5) ---------------
-// ONE WARP per matrix walks the whole assembly tree (HostPlan::tree_whole, k_tree_warp): the values of A are read
+// ONE small CTA (a team of warps) per matrix walks the whole assembly tree (HostPlan::tree_whole, k_tree_team): the values of A are read
 // straight from Ax, the frontal matrices live in shared memory, the factor is written straight into the CSC order of
 // S -- no L buffer, no assembly pass, no export pass; the only other HBM traffic is the stash of side-branch blocks.
 // Patterns whose fronts all have m <= TW_MAX_M rows (true for 1138_bus-sized problems).
@@ -795,15 +817,12 @@ int spchol_factor_batched_device(spchol_plan* p, int nbatch, const double* dAx, 
         if (p->b_chunk < want && (rc = batched_reserve(p, want))) return rc;
     }
     const int chunk = p->b_chunk;
-    static const int wpc_env = getenv("SPCHOL_TREE_WPC") ? atoi(getenv("SPCHOL_TREE_WPC")) : 4;
-    const size_t per_warp = static_cast<size_t>(p->whole.f_stride) * 8 + TW_MAX_M * 4;
-    const int wpc = std::max(1, std::min(std::min(wpc_env, 8), static_cast<int>((227 * 1024) / per_warp)));
+    static const int nw = getenv("SPCHOL_BATCH_NW") ? atoi(getenv("SPCHOL_BATCH_NW")) : 4;      // warps of the team that factors one matrix
     for (int b0 = 0; b0 < nbatch; b0 += chunk) {
         const int nb = std::min(chunk, nbatch - b0);
         CK(cudaMemsetAsync(p->binfo, 0x7f, sizeof(int) * nb, st));
-        k_tree_warp<<<(nb + wpc - 1) / wpc, 32 * wpc, wpc * per_warp, st>>>(
-            p->whole.ta, dAx + static_cast<int64_t>(b0) * H.nnzA, nullptr, nullptr, p->bStash, dLx + static_cast<int64_t>(b0) * H.nnzL,
-            p->binfo, H.nnzA, 0, 0, p->whole.stash_entries, H.nnzL, nb, p->whole.f_stride, 1);
+        launch_tree(nw, nb, p->whole.f_stride, st, p->whole.ta, dAx + static_cast<int64_t>(b0) * H.nnzA, nullptr, nullptr, p->bStash,
+                    dLx + static_cast<int64_t>(b0) * H.nnzL, p->binfo, H.nnzA, 0, 0, p->whole.stash_entries, H.nnzL, nb, 1);
         k_fix_info<<<(nb + 255) / 256, 256, 0, st>>>(p->binfo, dinfo + b0, nb);
         launches += 2;
     }

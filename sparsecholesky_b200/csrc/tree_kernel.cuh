@@ -1,12 +1,13 @@
-// k_tree_warp: ONE WARP factors a whole subtree of the assembly tree (or, batched, the whole tree of one
-// matrix), front after front, with the frontal matrix in shared memory; see tree_plan.h for the program and
-// the reversed packed layout that lets a contribution block pass to the parent without moving.
+// k_tree_team: a TEAM of NW warps (one CTA) factors a whole subtree of the assembly tree (or, batched, the whole
+// tree of one matrix), front after front, with the frontal matrix in shared memory; see tree_plan.h for the
+// program and the reversed packed layout that lets a contribution block pass to the parent without moving.
 // Fuses dpotrf_ + dtrsm + dsyrk + apply_update of the reference's supernodal chain
 // (include/chol.hpp:1232-1335, :1196-1216) for every front of the subtree; nothing but the factor
-// (and the blocks of side branches) leaves the SM.  No CTA barrier: only __syncwarp.
+// (and the blocks of side branches) leaves the SM.  The rank-w update of the contribution block runs on the
+// FP64 tensor cores (DMMA m8n8k4) in 8 x 8 tiles dealt to the warps of the team.
 //
 // The body is written against a few macros so that tests/cpp/tree_emu.cpp runs the SAME source on
-// 32 host threads per warp (SPCHOL_HOST_EMU) against the oracle, without a GPU.
+// 32 NW host threads per team (SPCHOL_HOST_EMU) against the oracle, without a GPU.
 #pragma once
 #include <cmath>
 #include <cstdint>
@@ -15,20 +16,24 @@
 
 #ifdef SPCHOL_HOST_EMU
 #define TK_DEVICE inline
-#define TK_LANE (::spchol::emu::tid() & 31)
+#define TK_TID ::spchol::emu::tid()
 #define TK_SYNCWARP() ::spchol::emu::syncwarp()
+#define TK_SYNCTEAM() ::spchol::emu::sync()
 #define TK_LDG(p) (*(p))
 #define TK_ATOMIC_MIN(p, v) ::spchol::emu::atomic_min((p), (v))
 #define TK_RESTRICT
 #define TK_SQRT(x) std::sqrt(x)
+#define TK_DMMA(c0, c1, a, b) ::spchol::emu::dmma884((c0), (c1), (a), (b))
 #else
 #define TK_DEVICE __device__ __forceinline__
-#define TK_LANE static_cast<int>(threadIdx.x & 31)
+#define TK_TID static_cast<int>(threadIdx.x)
 #define TK_SYNCWARP() __syncwarp()
+#define TK_SYNCTEAM() __syncthreads()
 #define TK_LDG(p) __ldg(p)
 #define TK_ATOMIC_MIN(p, v) atomicMin((p), (v))
 #define TK_RESTRICT __restrict__
 #define TK_SQRT(x) sqrt(x)
+#define TK_DMMA(c0, c1, a, b) asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b))
 #endif
 
 namespace spchol {
@@ -43,60 +48,20 @@ struct TreeArrays {                   // device pointers
     const int* csc_map;               // out_mode 1: L-buffer offset of a panel entry -> index into Lx (CSC order), -1 for padding
 };
 
+constexpr int TK_F_SLACK = 8;         // doubles past tri(cap_m): fragment loads of edge tiles may read (never store) there
+
 TK_DEVICE int tk_tri(int x) { return (x * (x + 1)) >> 1; }
 
-// rank-WK update of the contribution block (reversed columns 0..mb-1) by the pivot columns k0..k0+WK-1:
-// 4 target columns per step share the multipliers of a 32-row chunk; every entry is owned by lane (row % 32).
-template <int WK>
-TK_DEVICE void tk_update(double* F, int m, int mb, int k0, int lane) {
-    const double* pc[WK];
-#pragma unroll
-    for (int q = 0; q < WK; ++q) pc[q] = F + tk_tri(m - 1 - k0 - q);
-    for (int c0 = 0; c0 < mb; c0 += 4) {
-        double cm[4][WK];
-        int bc[4];
-#pragma unroll
-        for (int t = 0; t < 4; ++t) {
-            const int cc = c0 + t < mb ? c0 + t : mb - 1;
-            bc[t] = tk_tri(cc);
-#pragma unroll
-            for (int q = 0; q < WK; ++q) cm[t][q] = pc[q][cc];
-        }
-        const int cmax = c0 + 3 < mb ? c0 + 3 : mb - 1;
-        for (int r0 = 0; r0 <= cmax; r0 += 32) {
-            const int ir = r0 + lane;
-            double lr[WK];
-#pragma unroll
-            for (int q = 0; q < WK; ++q) lr[q] = ir <= cmax ? pc[q][ir] : 0.0;
-            if (r0 + 31 <= c0 && c0 + 3 < mb) {           // warp-uniform: the chunk lies inside all four columns
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    double acc = F[bc[t] + ir];
-#pragma unroll
-                    for (int q = 0; q < WK; ++q) acc = fma(-lr[q], cm[t][q], acc);
-                    F[bc[t] + ir] = acc;
-                }
-            } else {
-#pragma unroll
-                for (int t = 0; t < 4; ++t) {
-                    if (c0 + t < mb && ir <= c0 + t) {
-                        double acc = F[bc[t] + ir];
-#pragma unroll
-                        for (int q = 0; q < WK; ++q) acc = fma(-lr[q], cm[t][q], acc);
-                        F[bc[t] + ir] = acc;
-                    }
-                }
-            }
-        }
-    }
-}
-
-// One task = fronts [front0, front0 + nfront) in postorder.  F: tri(cap_m) doubles, sinv: TW_MAX_M ints, both private
-// to the warp.  out_mode 0: panels go to the L buffer; 1: entries go straight to Lx in CSC order through csc_map.
-TK_DEVICE void tree_warp_body(const TreeArrays& ta, const TwTask task, const double* TK_RESTRICT Ax, double* TK_RESTRICT L,
+// One task = fronts [front0, front0 + nfront) in postorder, factored by a team of NW warps (tid = 0 .. 32 NW - 1).
+// F: tri(cap_m) + TK_F_SLACK doubles, sinv: TW_MAX_M ints, spiv: 2 doubles, all private to the team.
+// out_mode 0: panels go to the L buffer; 1: entries go straight to Lx in CSC order through csc_map.
+template <int NW>
+TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const double* TK_RESTRICT Ax, double* TK_RESTRICT L,
                               double* TK_RESTRICT W, double* TK_RESTRICT Stash, double* TK_RESTRICT Lx, int* TK_RESTRICT info,
-                              double* F, int* sinv, int out_mode) {
-    const int lane = TK_LANE;
+                              double* F, int* sinv, double* spiv, int out_mode) {
+    constexpr int NT = 32 * NW;
+    const int tid = TK_TID, lane = tid & 31, warp = tid >> 5;
+    const int g = lane >> 2, tq = lane & 3;                 // DMMA fragment coordinates of the lane
     Stash += task.stash_base;
     for (int f = 0; f < task.nfront; ++f) {
         const TwFront d = ta.fronts[task.front0 + f];
@@ -104,85 +69,113 @@ TK_DEVICE void tree_warp_body(const TreeArrays& ta, const TwTask task, const dou
         // ---- 1. the frontal matrix: spread the carried block in place, or start from zero
         if (d.flags & TW_CARRY_IN) {
             const int* TK_RESTRICT rm = ta.rmap + d.map_off;
-            for (int t = lane; t < m; t += 32) sinv[t] = -1;
-            TK_SYNCWARP();
-            for (int i = lane; i < d.mc; i += 32) sinv[TK_LDG(rm + i)] = i;
-            TK_SYNCWARP();
-            for (int J = m - 1; J >= 0; --J) {
-                const int j = sinv[J];
-                if (j == J) break;                         // the map is the identity from here down: nothing moves
-                double v[4];
-                const int bj = j >= 0 ? tk_tri(j) : 0;
+            for (int t = tid; t < m; t += NT) sinv[t] = -1;
+            TK_SYNCTEAM();
+            for (int i = tid; i < d.mc; i += NT) sinv[TK_LDG(rm + i)] = i;
+            TK_SYNCTEAM();
+            // columns below d.ident are where they belong already (the map is the identity there).  The others move from
+            // the top down, 2 NW columns per round: every warp reads its two columns into registers, the team meets,
+            // every warp writes.  A column's new place never reaches below the old place of a column of a later round.
+            for (int J0 = m - 1; J0 >= d.ident; J0 -= 2 * NW) {
+                double v[2][4];
+                int Jc[2];
 #pragma unroll
-                for (int u = 0; u < 4; ++u) {
-                    const int t = lane + 32 * u;
-                    v[u] = 0.0;
-                    if (t <= J && j >= 0) { const int src = sinv[t]; if (src >= 0) v[u] = F[bj + src]; }
+                for (int h = 0; h < 2; ++h) {
+                    const int J = J0 - (2 * warp + h);
+                    Jc[h] = J;
+                    const int j = J >= d.ident ? sinv[J] : -2;          // -1: a new column (all zero), -2: nothing to do
+                    const int bj = j >= 0 ? tk_tri(j) : 0;
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) {
+                        const int t = lane + 32 * u;
+                        v[h][u] = 0.0;
+                        if (t <= J && j >= 0) { const int src = sinv[t]; if (src >= 0) v[h][u] = F[bj + src]; }
+                    }
                 }
-                TK_SYNCWARP();                             // column j is read before column J (which may overlap it) is written
-                const int bJ = tk_tri(J);
+                TK_SYNCTEAM();
 #pragma unroll
-                for (int u = 0; u < 4; ++u) { const int t = lane + 32 * u; if (t <= J) F[bJ + t] = v[u]; }
+                for (int h = 0; h < 2; ++h) {
+                    const int J = Jc[h];
+                    if (J < d.ident) continue;
+                    const int bJ = tk_tri(J);
+#pragma unroll
+                    for (int u = 0; u < 4; ++u) { const int t = lane + 32 * u; if (t <= J) F[bJ + t] = v[h][u]; }
+                }
             }
         } else {
             const int ne = tk_tri(m);
-            for (int e = lane; e < ne; e += 32) F[e] = 0.0;
+            for (int e = tid; e < ne; e += NT) F[e] = 0.0;
         }
-        TK_SYNCWARP();
+        TK_SYNCTEAM();
         // ---- 2. the front's entries of A (distinct targets)
-        for (int e = lane; e < d.an; e += 32) F[TK_LDG(ta.a_dst + d.a0 + e)] += Ax[TK_LDG(ta.a_src + d.a0 + e)];
-        // ---- 3. blocks of the other children, from the stash (most recent first)
+        for (int e = tid; e < d.an; e += NT) F[TK_LDG(ta.a_dst + d.a0 + e)] += Ax[TK_LDG(ta.a_src + d.a0 + e)];
+        // ---- 3. blocks of the other children, from the stash (most recent first); columns are dealt to the warps
         for (int q = 0; q < d.nstash; ++q) {
-            TK_SYNCWARP();
+            TK_SYNCTEAM();
             const TwStash st = ta.stashes[d.stash0 + q];
             const int* TK_RESTRICT rm = ta.rmap + st.map_off;
-            for (int i = lane; i < st.mc; i += 32) sinv[i] = TK_LDG(rm + i);
-            TK_SYNCWARP();
+            for (int i = tid; i < st.mc; i += NT) sinv[i] = TK_LDG(rm + i);
+            TK_SYNCTEAM();
             const double* TK_RESTRICT src = Stash + st.src;
-            for (int jr = 0; jr < st.mc; ++jr) {
+            for (int jr = warp; jr < st.mc; jr += NW) {
                 const int bJ = tk_tri(sinv[jr]);
                 const double* col = src + tk_tri(jr);
                 for (int ir = lane; ir <= jr; ir += 32) F[bJ + sinv[ir]] += col[ir];
             }
         }
-        TK_SYNCWARP();
+        TK_SYNCTEAM();
         // ---- 4. the w pivot columns (reversed columns m-1 .. m-w), right-looking inside the panel
         for (int k = 0; k < w; ++k) {
             const int Kr = m - 1 - k;
             double* colK = F + tk_tri(Kr);
-            const double dd = colK[Kr];
-            if (dd <= 0.0 && lane == 0) TK_ATOMIC_MIN(info, d.first + k + 1);      // reference test (chol.hpp:849)
-            const double piv = TK_SQRT(dd);
-            const double rinv = 1.0 / piv;
-            TK_SYNCWARP();                                 // every lane has read the pivot
-            for (int i = lane; i < Kr; i += 32) colK[i] *= rinv;
-            if (lane == 0) colK[Kr] = piv;
-            TK_SYNCWARP();
-            for (int Jr = Kr - 1; Jr >= mb; --Jr) {
-                const double uj = colK[Jr];
-                double* colJ = F + tk_tri(Jr);
-                for (int i = lane; i <= Jr; i += 32) colJ[i] = fma(-colK[i], uj, colJ[i]);
+            if (warp == 0) {                               // IEEE sqrt and division, once per pivot
+                const double dd = colK[Kr];
+                if (dd <= 0.0 && lane == 0) TK_ATOMIC_MIN(info, d.first + k + 1);      // reference test (chol.hpp:849)
+                const double piv = TK_SQRT(dd);
+                TK_SYNCWARP();                             // every lane has read the pivot
+                if (lane == 0) { colK[Kr] = piv; spiv[0] = 1.0 / piv; }
             }
-            TK_SYNCWARP();
+            TK_SYNCTEAM();
+            const double rinv = spiv[0];
+            for (int i = tid; i < Kr; i += NT) colK[i] *= rinv;
+            if (k + 1 < w) {
+                TK_SYNCTEAM();
+                for (int Jr = Kr - 1 - warp; Jr >= mb; Jr -= NW) {
+                    const double uj = colK[Jr];
+                    double* colJ = F + tk_tri(Jr);
+                    for (int i = lane; i <= Jr; i += 32) colJ[i] = fma(-colK[i], uj, colJ[i]);
+                }
+            }
+            TK_SYNCTEAM();
         }
-        // ---- 5. contribution block -= L21 L21^T, eight pivots at a time
+        // ---- 5. contribution block -= L21 L21^T on the FP64 tensor cores: 8 x 8 tiles (row block R <= column block C of
+        //         the reversed triangle) dealt to the warps; lane (g, tq) feeds A[g][tq] = -L(8R + g, pivot tq) and
+        //         B[tq][g] = L(8C + g, pivot tq) and owns C(8R + g, 8C + 2 tq) and C(8R + g, 8C + 2 tq + 1)
         if (mb > 0) {
-            for (int k0 = 0; k0 < w; k0 += 8) {
-                switch (w - k0 < 8 ? w - k0 : 8) {
-                case 1: tk_update<1>(F, m, mb, k0, lane); break;
-                case 2: tk_update<2>(F, m, mb, k0, lane); break;
-                case 3: tk_update<3>(F, m, mb, k0, lane); break;
-                case 4: tk_update<4>(F, m, mb, k0, lane); break;
-                case 5: tk_update<5>(F, m, mb, k0, lane); break;
-                case 6: tk_update<6>(F, m, mb, k0, lane); break;
-                case 7: tk_update<7>(F, m, mb, k0, lane); break;
-                default: tk_update<8>(F, m, mb, k0, lane); break;
+            const int nblk = (mb + 7) >> 3;
+            int cnt = 0;
+            for (int Cb = 0; Cb < nblk; ++Cb) {
+                const int c0 = 8 * Cb + 2 * tq, c1 = c0 + 1;
+                const int b0 = tk_tri(c0), b1 = tk_tri(c1);
+                for (int R = 0; R <= Cb; ++R, ++cnt) {
+                    if (NW > 1 && cnt % NW != warp) continue;
+                    const int ir = 8 * R + g;
+                    const bool on0 = ir <= c0 && c0 < mb, on1 = ir <= c1 && c1 < mb;      // entries of the tile inside the triangle
+                    double acc0 = on0 ? F[b0 + ir] : 0.0, acc1 = on1 ? F[b1 + ir] : 0.0;
+                    for (int k0 = 0; k0 < w; k0 += 4) {
+                        const int kk = k0 + tq;
+                        double a = 0.0, b = 0.0;
+                        if (kk < w) { const double* pc = F + tk_tri(m - 1 - kk); a = -pc[ir]; b = pc[8 * Cb + g]; }
+                        TK_DMMA(acc0, acc1, a, b);
+                    }
+                    if (on0) F[b0 + ir] = acc0;
+                    if (on1) F[b1 + ir] = acc1;
                 }
             }
         }
-        TK_SYNCWARP();
-        // ---- 6. the factored columns leave the SM
-        for (int c = 0; c < w; ++c) {
+        TK_SYNCTEAM();
+        // ---- 6. the factored columns leave the SM (columns dealt to the warps)
+        for (int c = warp; c < w; c += NW) {
             const int Jr = m - 1 - c;
             const double* col = F + tk_tri(Jr);
             const int64_t dst0 = d.panel_off + static_cast<int64_t>(c) * d.ld + (m - 1);
@@ -197,7 +190,7 @@ TK_DEVICE void tree_warp_body(const TreeArrays& ta, const TwTask task, const dou
             if (d.flags & TW_CB_STD) {
                 const int ldcb = (mb + 1) & ~1;
                 double* TK_RESTRICT C = W + d.cb_out;
-                for (int jr = 0; jr < mb; ++jr) {
+                for (int jr = warp; jr < mb; jr += NW) {
                     const double* col = F + tk_tri(jr);
                     double* dcol = C + static_cast<int64_t>(mb - 1 - jr) * ldcb + (mb - 1);
                     for (int ir = lane; ir <= jr; ir += 32) dcol[-ir] = col[ir];
@@ -205,34 +198,32 @@ TK_DEVICE void tree_warp_body(const TreeArrays& ta, const TwTask task, const dou
             } else {
                 double* TK_RESTRICT dst = Stash + d.cb_out;
                 const int ne = tk_tri(mb);
-                for (int e = lane; e < ne; e += 32) dst[e] = F[e];
+                for (int e = tid; e < ne; e += NT) dst[e] = F[e];
             }
         }
-        TK_SYNCWARP();
+        TK_SYNCTEAM();
     }
 }
 
 #ifndef SPCHOL_HOST_EMU
-// blockDim.x = 32 * warps per CTA; dynamic shared memory = warps * (f_stride doubles + TW_MAX_M ints).
-// nmat > 0 (batched): warp g factors matrix g with task 0, all pointers advance by their per-matrix strides;
-// nmat == 0: warp g runs task g of a single matrix.
-__global__ void k_tree_warp(TreeArrays ta, const double* __restrict__ Ax, double* __restrict__ L, double* __restrict__ W,
-                            double* __restrict__ Stash, double* __restrict__ Lx, int* __restrict__ info, int64_t ax_stride,
-                            int64_t l_stride, int64_t w_stride, int64_t s_stride, int64_t lx_stride, int nmat, int f_stride,
-                            int out_mode) {
+// One CTA = one team of NW warps.  Dynamic shared memory = (f_stride + 2) doubles + TW_MAX_M ints.
+// nmat > 0 (batched): team b factors matrix b with task 0, all pointers advance by their per-matrix strides;
+// nmat == 0: team b runs task b of a single matrix.
+template <int NW>
+__global__ void __launch_bounds__(32 * NW) k_tree_team(TreeArrays ta, const double* __restrict__ Ax, double* __restrict__ L,
+                                                      double* __restrict__ W, double* __restrict__ Stash, double* __restrict__ Lx,
+                                                      int* __restrict__ info, int64_t ax_stride, int64_t l_stride, int64_t w_stride,
+                                                      int64_t s_stride, int64_t lx_stride, int nmat, int f_stride, int out_mode) {
     extern __shared__ double tk_smem[];
-    const int wpc = blockDim.x >> 5, warp = threadIdx.x >> 5;
-    double* F = tk_smem + static_cast<size_t>(warp) * f_stride;
-    int* sinv = reinterpret_cast<int*>(tk_smem + static_cast<size_t>(wpc) * f_stride) + warp * TW_MAX_M;
-    const int g = blockIdx.x * wpc + warp;
-    if (nmat > 0) {
-        if (g >= nmat) return;
-        tree_warp_body(ta, ta.tasks[0], Ax + g * ax_stride, L + g * l_stride, W + g * w_stride, Stash + g * s_stride, Lx + g * lx_stride,
-                       info + g, F, sinv, out_mode);
-    } else {
-        if (g >= ta.ntasks) return;
-        tree_warp_body(ta, ta.tasks[g], Ax, L, W, Stash, Lx, info, F, sinv, out_mode);
-    }
+    double* F = tk_smem;
+    double* spiv = tk_smem + f_stride;
+    int* sinv = reinterpret_cast<int*>(tk_smem + f_stride + 2);
+    const int64_t b = blockIdx.x;
+    if (nmat > 0)
+        tree_team_body<NW>(ta, ta.tasks[0], Ax + b * ax_stride, L + b * l_stride, W + b * w_stride, Stash + b * s_stride, Lx + b * lx_stride,
+                           info + b, F, sinv, spiv, out_mode);
+    else
+        tree_team_body<NW>(ta, ta.tasks[b], Ax, L, W, Stash, Lx, info, F, sinv, spiv, out_mode);
 }
 #endif
 

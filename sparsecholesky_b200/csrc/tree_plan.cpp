@@ -129,6 +129,8 @@ void build_tree_program(const HostPlan& P, const std::vector<int>& roots_in, boo
                 d.flags |= TW_CARRY_IN;
                 d.mc = P.m[carried] - P.w[carried];
                 d.map_off = push_map(carried);
+                d.ident = 0;
+                while (d.ident < d.mc && out.rmap[d.map_off + d.ident] == d.ident) ++d.ident;
                 out.fronts.back().flags |= TW_CARRY_OUT;
             }
             d.stash0 = static_cast<int>(out.stashes.size());

@@ -1,10 +1,10 @@
-// Warp-per-subtree program (host planner) for k_tree_warp (tree_kernel.cuh).
+// Team-per-subtree program (host planner) for k_tree_team (tree_kernel.cuh).
 //
-// ONE WARP factors a whole subtree of the assembly tree, front after front in postorder, with the
-// frontal matrix in shared memory -- no CTA barrier anywhere, parallelism comes from the number of
+// ONE small CTA (a team of 1..4 warps) factors a whole subtree of the assembly tree, front after front
+// in postorder, with the frontal matrix in shared memory; parallelism comes from the number of
 // subtrees (single matrix: the bottom of the tree, where 2D 1024^2 has 145 000 fronts with m <= 128)
 // or from the number of matrices (batched factorization over one pattern, BASELINE config 5: one
-// warp per matrix walks the whole tree).  This is the fused dense chain of the reference's
+// team per matrix walks the whole tree).  This is the fused dense chain of the reference's
 // factorize_sn + apply_update (include/chol.hpp:1232-1335, :1196-1216) without ever leaving the SM.
 //
 // Layout of a front inside the warp's shared memory: packed lower triangle over REVERSED indices
@@ -31,7 +31,8 @@ enum : int { TW_CARRY_IN = 1,                 // the front's first child left it
 struct alignas(16) TwFront {                  // 64 bytes, one descriptor load per front
     int w, m, ld, first;                      // columns, rows, leading dimension of the panel in the L buffer, first global column
     int flags, mc, map_off, nstash;           // carried child: order of its block, rmap[map_off .. +mc); stashed children to add
-    int stash0, a0, an, pad;                  // stashes[stash0 .. +nstash); A entries a_src/a_dst[a0 .. +an)
+    int stash0, a0, an, ident;                // stashes[stash0 .. +nstash); A entries a_src/a_dst[a0 .. +an); carried child: its first
+                                              // `ident` reversed rows keep their place (the map is the identity there)
     int64_t panel_off;                        // panel in the L buffer
     int64_t cb_out;                           // TW_CB_STD: workspace offset; else (no carry, mb > 0): offset in the stash area
 };

@@ -22,11 +22,25 @@
 
 namespace spchol { namespace emu {
 thread_local int t_tid = 0;
-std::barrier<>* g_warp = nullptr;
+std::barrier<>* g_team = nullptr;
+std::vector<std::barrier<>*> g_warp;
 std::mutex g_mu;
+double g_fa[8][32], g_fb[8][32];      // operand fragments of the emulated tensor-core instruction, per warp
 inline int tid() { return t_tid; }
-inline void syncwarp() { g_warp->arrive_and_wait(); }
+inline void sync() { g_team->arrive_and_wait(); }
+inline void syncwarp() { g_warp[t_tid >> 5]->arrive_and_wait(); }
 inline void atomic_min(int* p, int v) { std::lock_guard<std::mutex> lk(g_mu); if (v < *p) *p = v; }
+// mma.sync.m8n8k4.row.col.f64: lane l holds A[l/4][l%4], B[l%4][l/4] and C[l/4][2 (l%4)], C[l/4][2 (l%4) + 1]
+inline void dmma884(double& c0, double& c1, double a, double b) {
+    const int l = t_tid & 31, wq = t_tid >> 5, gq = l >> 2, q = l & 3;
+    g_fa[wq][l] = a; g_fb[wq][l] = b;
+    syncwarp();
+    for (int k = 0; k < 4; ++k) {
+        c0 = std::fma(g_fa[wq][gq * 4 + k], g_fb[wq][(2 * q) * 4 + k], c0);
+        c1 = std::fma(g_fa[wq][gq * 4 + k], g_fb[wq][(2 * q + 1) * 4 + k], c1);
+    }
+    syncwarp();
+}
 } }
 
 #define SPCHOL_HOST_EMU
@@ -79,7 +93,31 @@ void run_small(const HostPlan& H, std::vector<double>& Lb, std::vector<double>& 
 // whole = 1: the whole tree as one task, factor written in CSC order by the kernel source (batched mode);
 // whole = 0: subtree tasks (cap_m rows, `work` dense flops per task) + plain loops for the fronts above them.
 // stats[6]: #tasks, #fronts in tasks, #stashes, stash doubles, cap_m, #fronts of the plan
-extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double* Ax, int relax, int whole, int cap_m, double work,
+template <int NW>
+static void run_tasks(const TreeArrays& ta, const double* Ax, double* Lb, double* Wb, double* Sb, double* Lx, int* info, int cap_m, int mode) {
+    const double nan = std::numeric_limits<double>::quiet_NaN();
+    std::vector<double> F(static_cast<size_t>(cap_m) * (cap_m + 1) / 2 + TK_F_SLACK, nan);
+    std::vector<int> sinv(TW_MAX_M, -7);
+    double spiv[2] = {nan, nan};
+    std::barrier<> team(32 * NW);
+    emu::g_team = &team;
+    std::vector<std::unique_ptr<std::barrier<>>> wb;
+    emu::g_warp.clear();
+    for (int q = 0; q < NW; ++q) { wb.push_back(std::make_unique<std::barrier<>>(32)); emu::g_warp.push_back(wb.back().get()); }
+    std::vector<std::thread> th;
+    for (int t = 0; t < 32 * NW; ++t)
+        th.emplace_back([&, t] {
+            emu::t_tid = t;
+            for (int q = 0; q < ta.ntasks; ++q) {
+                tree_team_body<NW>(ta, ta.tasks[q], Ax, Lb, Wb, Sb, Lx, info, F.data(), sinv.data(), spiv, mode);
+                emu::sync();
+            }
+        });
+    for (auto& x : th) x.join();
+    emu::g_team = nullptr;
+}
+
+extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double* Ax, int relax, int whole, int cap_m, double work, int nw,
                               double* Lx, int* info_out, int64_t* stats, char* err, int errlen) {
     auto fail = [&](const std::string& msg) { std::snprintf(err, errlen, "%s", msg.c_str()); return -1; };
     try {
@@ -115,21 +153,12 @@ extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double*
             TreeArrays ta{};
             ta.tasks = T.tasks.data(); ta.ntasks = static_cast<int>(T.tasks.size()); ta.fronts = T.fronts.data(); ta.stashes = T.stashes.data();
             ta.rmap = T.rmap.data(); ta.a_src = T.a_src.data(); ta.a_dst = T.a_dst.data(); ta.csc_map = csc_map.data();
-            std::vector<double> F(static_cast<size_t>(T.cap_m) * (T.cap_m + 1) / 2 + 1, nan);
-            std::vector<int> sinv(TW_MAX_M, -7);
-            std::barrier<> bar(32);
-            emu::g_warp = &bar;
-            std::vector<std::thread> th;
-            for (int t = 0; t < 32; ++t)
-                th.emplace_back([&, t] {
-                    emu::t_tid = t;
-                    for (int q = 0; q < ta.ntasks; ++q) {
-                        tree_warp_body(ta, ta.tasks[q], Ax, Lb.data(), Wb.data(), Sb.data(), Lx, &info, F.data(), sinv.data(), whole ? 1 : 0);
-                        emu::syncwarp();
-                    }
-                });
-            for (auto& x : th) x.join();
-            emu::g_warp = nullptr;
+            switch (nw) {
+            case 1: run_tasks<1>(ta, Ax, Lb.data(), Wb.data(), Sb.data(), Lx, &info, T.cap_m, whole ? 1 : 0); break;
+            case 2: run_tasks<2>(ta, Ax, Lb.data(), Wb.data(), Sb.data(), Lx, &info, T.cap_m, whole ? 1 : 0); break;
+            case 4: run_tasks<4>(ta, Ax, Lb.data(), Wb.data(), Sb.data(), Lx, &info, T.cap_m, whole ? 1 : 0); break;
+            default: return fail("nw must be 1, 2 or 4");
+            }
         }
         if (!whole) {
             for (const Op& op : H.ops) {

@@ -339,11 +339,17 @@ def test_batched_shared_pattern_vs_oracle():
     assert (Lx2[ok] == Lx[ok]).all() and (info2 == info).all()
 
 
-@pytest.mark.parametrize("relax,wpc", [(1, 4), (1, 1), (0, 2), (2, 8)])
-def test_batched_warp_per_tree_vs_oracle(monkeypatch, relax, wpc):
-    # the warp-per-tree kernel (one warp per matrix; its source also runs on host threads: tests/test_tree_emu.py)
-    # at several amalgamation levels and CTA shapes; EVERY matrix of the batch is compared with the oracle
-    monkeypatch.setenv("SPCHOL_TREE_WPC", str(wpc))
+@pytest.mark.parametrize("relax,nw", [(1, 4), (1, 1), (0, 2)])
+def test_batched_team_per_tree_vs_oracle(relax, nw):
+    # the team-per-tree kernel (one small CTA per matrix; its source also runs on host threads: tests/test_tree_emu.py)
+    # at several amalgamation levels and team sizes; EVERY matrix of the batch is compared with the oracle
+    import subprocess, sys
+    if nw != 4:          # the team size is read once per process: the other sizes run in a child process
+        code = ("import os, sys; os.environ['SPCHOL_BATCH_NW'] = '%d'; sys.path.insert(0, %r); import tests.test_chol_gpu as t; "
+                "t.test_batched_team_per_tree_vs_oracle(%d, 4)" % (nw, ROOT, relax))
+        r = subprocess.run([sys.executable, "-c", code], capture_output=True, text=True, timeout=900)
+        assert r.returncode == 0, r.stdout[-2000:] + r.stderr[-4000:]
+        return
     g = np.load(os.path.join(GOLD, "1138_bus.npz"))
     n = int(g["n"])
     A = sc.CscMatrix(n, g["Ap"], g["Ai"], g["Ax"])

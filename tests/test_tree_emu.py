@@ -32,18 +32,18 @@ def _build(tsan=False):
 @pytest.fixture(scope="module")
 def emu():
     L = C.CDLL(_build())
-    L.treeemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double,
+    L.treeemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int,
                                  C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_char_p, C.c_int]
     return L
 
 
-def run(L, A, whole, relax=1, cap_m=117, work=2.5e6):
+def run(L, A, whole, relax=1, cap_m=117, work=2.5e6, nw=1):
     S = sc.schol(A, relax=relax)
     Lx = np.empty(S.nnz)
     info = C.c_int(0)
     st = np.zeros(6, np.int64)
     err = C.create_string_buffer(2048)
-    rc = L.treeemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, relax, int(whole), cap_m, work,
+    rc = L.treeemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, relax, int(whole), cap_m, work, nw,
                           Lx.ctypes.data, C.byref(info), st.ctypes.data, err, 2048)
     assert rc == 0, err.value.decode()
     return Lx, info.value, dict(zip(["tasks", "fronts", "stashes", "stash_doubles", "cap_m", "ns"], (int(v) for v in st)))
@@ -59,21 +59,21 @@ def relerr(Lx, ref):
 
 
 @pytest.mark.parametrize("name", ["test3", "bcsstk01", "1138_bus", "lap2d_24", "lap2d_7x5"])      # (lap3d_10 has fronts beyond 128 rows)
-@pytest.mark.parametrize("relax", [0, 1])
-def test_whole_tree_vs_reference_golden(emu, name, relax):
-    # batched mode: one warp walks the whole tree and writes the CSC factor itself
+@pytest.mark.parametrize("relax,nw", [(0, 1), (1, 4), (1, 2)])
+def test_whole_tree_vs_reference_golden(emu, name, relax, nw):
+    # batched mode: one team walks the whole tree and writes the CSC factor itself
     A, ref = golden(name)
-    Lx, info, st = run(emu, A, whole=True, relax=relax)
+    Lx, info, st = run(emu, A, whole=True, relax=relax, nw=nw)
     assert info == 0 and relerr(Lx, ref) <= 1e-10
     assert st["tasks"] == 1 and st["fronts"] == st["ns"]
 
 
 @pytest.mark.parametrize("name", ["bcsstk01", "1138_bus", "lap2d_24", "lap3d_10"])
-@pytest.mark.parametrize("cap_m,work", [(117, 2.5e6), (40, 2e4), (16, 1e3)])
-def test_subtrees_vs_reference_golden(emu, name, cap_m, work):
+@pytest.mark.parametrize("cap_m,work,nw", [(117, 2.5e6, 1), (117, 2.5e6, 4), (40, 2e4, 2), (16, 1e3, 1)])
+def test_subtrees_vs_reference_golden(emu, name, cap_m, work, nw):
     # single-matrix mode: subtree tasks hand their root blocks to the level program in its own layout
     A, ref = golden(name)
-    Lx, info, st = run(emu, A, whole=False, cap_m=cap_m, work=work)
+    Lx, info, st = run(emu, A, whole=False, cap_m=cap_m, work=work, nw=nw)
     assert info == 0 and relerr(Lx, ref) <= 1e-10
     assert st["fronts"] <= st["ns"]
 
@@ -84,8 +84,8 @@ def test_subtrees_on_a_larger_grid(emu):
     A = sc.triplet_to_csc_matrix(ti, tj, tx, n)
     rc, _, _, ref = po.chol(n, A.p, A.i, A.x)
     assert rc == 0
-    for cap_m, work in ((117, 2e5), (64, 2e4)):
-        Lx, info, st = run(emu, A, whole=False, cap_m=cap_m, work=work)
+    for cap_m, work, nw in ((117, 2e5, 4), (64, 2e4, 1)):
+        Lx, info, st = run(emu, A, whole=False, cap_m=cap_m, work=work, nw=nw)
         assert info == 0 and relerr(Lx, ref) <= 1e-10 and st["tasks"] >= 2 and st["stashes"] > 0
 
 
@@ -96,7 +96,7 @@ def test_not_positive_definite_column_is_reported(emu):
     x[A.p[j + 1] - 1] = -1.0                    # diagonal of column j (last entry of an upper-CSC column)
     B = sc.CscMatrix(A.n, A.p, A.i, x)
     rc, _, _, _ = po.chol(B.n, B.p, B.i, B.x)
-    _, info, _ = run(emu, B, whole=True)
+    _, info, _ = run(emu, B, whole=True, nw=4)
     assert rc > 0 and info == rc               # same 1-based column as the oracle (reference test chol.hpp:849)
 
 
@@ -110,10 +110,10 @@ def test_thread_sanitizer_finds_no_race():
         f"g = np.load(os.path.join({GOLD!r}, 'bcsstk01.npz'))\n"
         "A = sc.CscMatrix(int(g['n']), g['Ap'], g['Ai'], g['Ax'])\n"
         f"L = C.CDLL({so!r})\n"
-        "L.treeemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_char_p, C.c_int]\n"
-        "for whole, cap, work in ((1, 117, 2.5e6), (0, 16, 1e3)):\n"
+        "L.treeemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_char_p, C.c_int]\n"
+        "for whole, cap, work, nw in ((1, 117, 2.5e6, 4), (0, 16, 1e3, 2), (1, 117, 2.5e6, 1)):\n"
         "    Lx = np.empty(len(g['Lx'])); info = C.c_int(0); st = np.zeros(6, np.int64); err = C.create_string_buffer(512)\n"
-        "    rc = L.treeemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, 1, whole, cap, work, Lx.ctypes.data, C.byref(info), st.ctypes.data, err, 512)\n"
+        "    rc = L.treeemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, 1, whole, cap, work, nw, Lx.ctypes.data, C.byref(info), st.ctypes.data, err, 512)\n"
         "    assert rc == 0, err.value\n"
         "    assert np.abs(Lx - g['Lx']).max() <= 1e-10 * np.abs(g['Lx']).max()\n"
         "print('TSAN_RUN_OK')\n")
