@@ -150,6 +150,34 @@ void ref_atree(int n, const int* parent, const int* Lp, const int* Li, const int
     auto sp = atree(S, std::vector<int>(sn_id, sn_id + n), sn);
     std::memcpy(super_parent, sp.data(), sizeof(int) * ns);
 }
+// random_sparse<T>(n, density, positive_definite) (include/chol.hpp:964).  Two-call protocol: Ap == NULL -> returns nnz only.
+int ref_random_sparse(int n, double density, int pd, int* Ap, int* Ai, double* Ax) {
+    auto A = random_sparse<double>(n, density, pd != 0);
+    const int nz = A.p()[n];
+    if (Ap) { std::memcpy(Ap, A.p().data(), sizeof(int) * (n + 1)); std::memcpy(Ai, A.i().data(), sizeof(int) * nz); std::memcpy(Ax, A.x().data(), sizeof(double) * nz); }
+    return nz;
+}
+// random_sparse<T>(S, positive_definite) (include/chol.hpp:1004): values on the pattern of S (Lp[n] doubles)
+void ref_random_sparse_S(int n, const int* parent, const int* Lp, const int* Li, int pd, double* x) {
+    SChol S = make_S(n, parent, Lp, Li);
+    auto B = random_sparse<double>(S, pd != 0);
+    std::memcpy(x, B.x().data(), sizeof(double) * Lp[n]);
+}
+// csc_matrix(A, S) constructor (include/chol.hpp:190): values on the pattern of S
+void ref_csc_from_A_S(int n, const int* Ap, const int* Ai, const double* Ax, const int* parent, const int* Lp, const int* Li, double* x) {
+    auto A = make_A(n, Ap, Ai, Ax);
+    SChol S = make_S(n, parent, Lp, Li);
+    csc_matrix<double, sym::upper> W(A, S);
+    std::memcpy(x, W.x().data(), sizeof(double) * Lp[n]);
+}
+// schol_etree (include/chol.hpp:628).  Two-call protocol: Li == NULL -> Lp only; returns nnz.
+int ref_schol_etree(int n, const int* Ap, const int* Ai, int* Lp, int* Li) {
+    auto A = make_A(n, Ap, Ai, nullptr);
+    SChol S = schol_etree(A);
+    std::memcpy(Lp, S.p().data(), sizeof(int) * (n + 1));
+    if (Li) std::memcpy(Li, S.i().data(), sizeof(int) * S.p()[n]);
+    return S.p()[n];
+}
 // csc_to_dense for sym::none (include/chol.hpp:1449).
 void ref_csc_to_dense_none(int n, const int* Lp, const int* Li, const double* Lx, double* dense) {
     csc_matrix<double, sym::none> L(n, n, Lp[n]);

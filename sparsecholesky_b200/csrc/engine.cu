@@ -184,7 +184,7 @@ int set_small_attr() {
 }
 
 // one CTA (a team of nw warps) per task / per matrix, see tree_kernel.cuh
-constexpr size_t tree_smem(int f_stride) { return (static_cast<size_t>(f_stride) + 2) * 8 + TW_MAX_M * 4; }
+constexpr size_t tree_smem(int f_stride) { return (static_cast<size_t>(f_stride) + 2) * 8; }
 void launch_tree(int nw, int grid, int f_stride, cudaStream_t st, const TreeArrays& ta, const double* Ax, double* L, double* W, double* Stash,
                  double* Lx, int* info, int64_t axs, int64_t ls, int64_t ws, int64_t ss, int64_t lxs, int nmat, int out_mode) {
     const size_t sm = tree_smem(f_stride);

@@ -52,50 +52,73 @@ constexpr int TK_F_SLACK = 8;         // doubles past tri(cap_m): fragment loads
 
 TK_DEVICE int tk_tri(int x) { return (x * (x + 1)) >> 1; }
 
+// pull the 128-byte lines of [base + b0, base + b1) towards L1, one line per thread and pass
+TK_DEVICE void tk_prefetch_range(const void* base, int64_t b0, int64_t b1, int tid, int nt) {
+#ifndef SPCHOL_HOST_EMU
+    const char* p = static_cast<const char*>(base);
+    for (int64_t off = (b0 & ~int64_t(127)) + static_cast<int64_t>(tid) * 128; off < b1; off += static_cast<int64_t>(nt) * 128)
+        asm volatile("prefetch.global.L1 [%0];" ::"l"(p + off));
+#else
+    (void)base; (void)b0; (void)b1; (void)tid; (void)nt;
+#endif
+}
+
 // One task = fronts [front0, front0 + nfront) in postorder, factored by a team of NW warps (tid = 0 .. 32 NW - 1).
-// F: tri(cap_m) + TK_F_SLACK doubles, sinv: TW_MAX_M ints, spiv: 2 doubles, all private to the team.
+// F: tri(cap_m) + TK_F_SLACK doubles, spiv: 2 doubles, both private to the team.
 // out_mode 0: panels go to the L buffer; 1: entries go straight to Lx in CSC order through csc_map.
+//
+// Every front starts with a chain of dependent loads (descriptor -> index lists -> values); with four teams per SM there
+// is nothing to hide them behind, so the kernel runs two descriptors ahead: while front f is eliminated, the descriptor
+// of f+2 is in flight and the lists of f+1 (maps, A entry lists, its slice of the CSC map, its values of A) are being
+// pulled into L1.
 template <int NW>
 TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const double* TK_RESTRICT Ax, double* TK_RESTRICT L,
                               double* TK_RESTRICT W, double* TK_RESTRICT Stash, double* TK_RESTRICT Lx, int* TK_RESTRICT info,
-                              double* F, int* sinv, double* spiv, int out_mode) {
+                              double* F, double* spiv, int out_mode) {
     constexpr int NT = 32 * NW;
+    constexpr int MC = 4;                                   // columns a warp moves per round of the in-place spread
     const int tid = TK_TID, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, tq = lane & 3;                 // DMMA fragment coordinates of the lane
     Stash += task.stash_base;
+    const TwFront* TK_RESTRICT fr = ta.fronts + task.front0;
+    TwFront d = fr[0];
+    TwFront dn = fr[task.nfront > 1 ? 1 : 0];
     for (int f = 0; f < task.nfront; ++f) {
-        const TwFront d = ta.fronts[task.front0 + f];
+        const TwFront dnn = fr[f + 2 < task.nfront ? f + 2 : task.nfront - 1];
+        int ax_next = -1;                                   // index of one value of A the next front needs (prefetched further down)
+        if (f + 1 < task.nfront) {
+            tk_prefetch_range(ta.rmap, 4 * static_cast<int64_t>(dn.map_lo), 4 * static_cast<int64_t>(dn.map_lo + dn.map_n), tid, NT);
+            tk_prefetch_range(ta.a_dst, 2 * static_cast<int64_t>(dn.a0), 2 * static_cast<int64_t>(dn.a0 + dn.an), tid, NT);
+            tk_prefetch_range(ta.stashes, 16 * static_cast<int64_t>(dn.stash0), 16 * static_cast<int64_t>(dn.stash0 + dn.nstash), tid, NT);
+            if (out_mode == 1) tk_prefetch_range(ta.csc_map, 4 * dn.panel_off, 4 * (dn.panel_off + static_cast<int64_t>(dn.ld) * dn.w), tid, NT);
+            if (tid < dn.an) ax_next = TK_LDG(ta.a_src + dn.a0 + tid);
+        }
         const int m = d.m, w = d.w, mb = m - w;
         // ---- 1. the frontal matrix: spread the carried block in place, or start from zero
         if (d.flags & TW_CARRY_IN) {
-            const int* TK_RESTRICT rm = ta.rmap + d.map_off;
-            for (int t = tid; t < m; t += NT) sinv[t] = -1;
-            TK_SYNCTEAM();
-            for (int i = tid; i < d.mc; i += NT) sinv[TK_LDG(rm + i)] = i;
-            TK_SYNCTEAM();
-            // columns below d.ident are where they belong already (the map is the identity there).  The others move from
-            // the top down, 2 NW columns per round: every warp reads its two columns into registers, the team meets,
-            // every warp writes.  A column's new place never reaches below the old place of a column of a later round.
-            for (int J0 = m - 1; J0 >= d.ident; J0 -= 2 * NW) {
-                double v[2][4];
-                int Jc[2];
+            // inv[t] = reversed row of the child's block that becomes reversed row t of this front, -1 for a new row.
+            // Columns below d.ident are where they belong already.  The others move from the top down, MC NW columns per
+            // round: every warp reads its columns into registers, the team meets, every warp writes.  A column's new
+            // place never reaches below the old place of a column of a later round, so one barrier per round is enough.
+            const int* TK_RESTRICT inv = ta.rmap + d.map_off;
+            for (int J0 = m - 1; J0 >= d.ident; J0 -= MC * NW) {
+                double v[MC][4];
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int J = J0 - (2 * warp + h);
-                    Jc[h] = J;
-                    const int j = J >= d.ident ? sinv[J] : -2;          // -1: a new column (all zero), -2: nothing to do
+                for (int h = 0; h < MC; ++h) {
+                    const int J = J0 - (MC * warp + h);
+                    const int j = J >= d.ident ? TK_LDG(inv + J) : -2;      // -1: a new column (all zero), -2: nothing to do
                     const int bj = j >= 0 ? tk_tri(j) : 0;
 #pragma unroll
                     for (int u = 0; u < 4; ++u) {
                         const int t = lane + 32 * u;
                         v[h][u] = 0.0;
-                        if (t <= J && j >= 0) { const int src = sinv[t]; if (src >= 0) v[h][u] = F[bj + src]; }
+                        if (t <= J && j >= 0) { const int src = TK_LDG(inv + t); if (src >= 0) v[h][u] = F[bj + src]; }
                     }
                 }
                 TK_SYNCTEAM();
 #pragma unroll
-                for (int h = 0; h < 2; ++h) {
-                    const int J = Jc[h];
+                for (int h = 0; h < MC; ++h) {
+                    const int J = J0 - (MC * warp + h);
                     if (J < d.ident) continue;
                     const int bJ = tk_tri(J);
 #pragma unroll
@@ -111,16 +134,14 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
         for (int e = tid; e < d.an; e += NT) F[TK_LDG(ta.a_dst + d.a0 + e)] += Ax[TK_LDG(ta.a_src + d.a0 + e)];
         // ---- 3. blocks of the other children, from the stash (most recent first); columns are dealt to the warps
         for (int q = 0; q < d.nstash; ++q) {
-            TK_SYNCTEAM();
+            TK_SYNCTEAM();                                 // two sources may hit the same entry from different threads
             const TwStash st = ta.stashes[d.stash0 + q];
             const int* TK_RESTRICT rm = ta.rmap + st.map_off;
-            for (int i = tid; i < st.mc; i += NT) sinv[i] = TK_LDG(rm + i);
-            TK_SYNCTEAM();
             const double* TK_RESTRICT src = Stash + st.src;
             for (int jr = warp; jr < st.mc; jr += NW) {
-                const int bJ = tk_tri(sinv[jr]);
+                const int bJ = tk_tri(TK_LDG(rm + jr));
                 const double* col = src + tk_tri(jr);
-                for (int ir = lane; ir <= jr; ir += 32) F[bJ + sinv[ir]] += col[ir];
+                for (int ir = lane; ir <= jr; ir += 32) F[bJ + TK_LDG(rm + ir)] += col[ir];
             }
         }
         TK_SYNCTEAM();
@@ -148,29 +169,42 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
             }
             TK_SYNCTEAM();
         }
+        if (ax_next >= 0) tk_prefetch_range(Ax, 8 * static_cast<int64_t>(ax_next), 8 * static_cast<int64_t>(ax_next) + 8, 0, 1);
         // ---- 5. contribution block -= L21 L21^T on the FP64 tensor cores: 8 x 8 tiles (row block R <= column block C of
-        //         the reversed triangle) dealt to the warps; lane (g, tq) feeds A[g][tq] = -L(8R + g, pivot tq) and
-        //         B[tq][g] = L(8C + g, pivot tq) and owns C(8R + g, 8C + 2 tq) and C(8R + g, 8C + 2 tq + 1)
+        //         the reversed triangle), tile number C (C + 1) / 2 + R dealt round-robin to the warps; lane (g, tq) feeds
+        //         A[g][tq] = -L(8R + g, pivot tq) and B[tq][g] = L(8C + g, pivot tq) and owns C(8R + g, 8C + 2 tq), (.., + 1)
         if (mb > 0) {
             const int nblk = (mb + 7) >> 3;
-            int cnt = 0;
-            for (int Cb = 0; Cb < nblk; ++Cb) {
-                const int c0 = 8 * Cb + 2 * tq, c1 = c0 + 1;
-                const int b0 = tk_tri(c0), b1 = tk_tri(c1);
-                for (int R = 0; R <= Cb; ++R, ++cnt) {
-                    if (NW > 1 && cnt % NW != warp) continue;
-                    const int ir = 8 * R + g;
-                    const bool on0 = ir <= c0 && c0 < mb, on1 = ir <= c1 && c1 < mb;      // entries of the tile inside the triangle
-                    double acc0 = on0 ? F[b0 + ir] : 0.0, acc1 = on1 ? F[b1 + ir] : 0.0;
-                    for (int k0 = 0; k0 < w; k0 += 4) {
-                        const int kk = k0 + tq;
-                        double a = 0.0, b = 0.0;
-                        if (kk < w) { const double* pc = F + tk_tri(m - 1 - kk); a = -pc[ir]; b = pc[8 * Cb + g]; }
-                        TK_DMMA(acc0, acc1, a, b);
-                    }
-                    if (on0) F[b0 + ir] = acc0;
-                    if (on1) F[b1 + ir] = acc1;
+            const int pb0 = tk_tri(m - 1 - tq);            // the lane's pivot column of the first k-step
+            const bool k_on = tq < w;
+            int Cb = 0, R = warp;
+            while (R > Cb) { R -= Cb + 1; ++Cb; }
+            int Cb_cur = -1, c0 = 0, b0 = 0, b1 = 0;
+            double bf0 = 0.0;
+            while (Cb < nblk) {
+                if (Cb != Cb_cur) {
+                    Cb_cur = Cb;
+                    c0 = 8 * Cb + 2 * tq;
+                    b0 = tk_tri(c0); b1 = b0 + c0 + 1;
+                    bf0 = k_on ? F[pb0 + 8 * Cb + g] : 0.0;
                 }
+                const int ir = 8 * R + g;
+                const bool on0 = ir <= c0 && c0 < mb, on1 = ir <= c0 + 1 && c0 + 1 < mb;      // entries of the tile inside the triangle
+                double acc0 = on0 ? F[b0 + ir] : 0.0, acc1 = on1 ? F[b1 + ir] : 0.0;
+                {
+                    const double a = k_on ? -F[pb0 + ir] : 0.0;
+                    TK_DMMA(acc0, acc1, a, bf0);
+                }
+                for (int k0 = 4; k0 < w; k0 += 4) {
+                    const int kk = k0 + tq;
+                    double a = 0.0, b = 0.0;
+                    if (kk < w) { const double* pc = F + tk_tri(m - 1 - kk); a = -pc[ir]; b = pc[8 * Cb + g]; }
+                    TK_DMMA(acc0, acc1, a, b);
+                }
+                if (on0) F[b0 + ir] = acc0;
+                if (on1) F[b1 + ir] = acc1;
+                R += NW;
+                while (R > Cb) { R -= Cb + 1; ++Cb; }
             }
         }
         TK_SYNCTEAM();
@@ -202,11 +236,12 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
             }
         }
         TK_SYNCTEAM();
+        d = dn; dn = dnn;
     }
 }
 
 #ifndef SPCHOL_HOST_EMU
-// One CTA = one team of NW warps.  Dynamic shared memory = (f_stride + 2) doubles + TW_MAX_M ints.
+// One CTA = one team of NW warps.  Dynamic shared memory = (f_stride + 2) doubles.
 // nmat > 0 (batched): team b factors matrix b with task 0, all pointers advance by their per-matrix strides;
 // nmat == 0: team b runs task b of a single matrix.
 template <int NW>
@@ -217,13 +252,12 @@ __global__ void __launch_bounds__(32 * NW) k_tree_team(TreeArrays ta, const doub
     extern __shared__ double tk_smem[];
     double* F = tk_smem;
     double* spiv = tk_smem + f_stride;
-    int* sinv = reinterpret_cast<int*>(tk_smem + f_stride + 2);
     const int64_t b = blockIdx.x;
     if (nmat > 0)
         tree_team_body<NW>(ta, ta.tasks[0], Ax + b * ax_stride, L + b * l_stride, W + b * w_stride, Stash + b * s_stride, Lx + b * lx_stride,
-                           info + b, F, sinv, spiv, out_mode);
+                           info + b, F, spiv, out_mode);
     else
-        tree_team_body<NW>(ta, ta.tasks[b], Ax, L, W, Stash, Lx, info, F, sinv, spiv, out_mode);
+        tree_team_body<NW>(ta, ta.tasks[b], Ax, L, W, Stash, Lx, info, F, spiv, out_mode);
 }
 #endif
 

@@ -125,12 +125,18 @@ void build_tree_program(const HostPlan& P, const std::vector<int>& roots_in, boo
             };
             int carried = -1;
             if (!kids.empty() && oi > 0 && order[oi - 1] == kids.back() && P.m[kids.back()] > P.w[kids.back()]) carried = kids.back();
+            d.map_lo = static_cast<int>(out.rmap.size());
             if (carried >= 0) {
                 d.flags |= TW_CARRY_IN;
                 d.mc = P.m[carried] - P.w[carried];
-                d.map_off = push_map(carried);
+                const int fwd = push_map(carried);                      // forward map, replaced by its inverse below
+                std::vector<int> inv(d.m, -1);
+                for (int ir = 0; ir < d.mc; ++ir) inv[out.rmap[fwd + ir]] = ir;
                 d.ident = 0;
-                while (d.ident < d.mc && out.rmap[d.map_off + d.ident] == d.ident) ++d.ident;
+                while (d.ident < d.mc && out.rmap[fwd + d.ident] == d.ident) ++d.ident;
+                out.rmap.resize(fwd);
+                d.map_off = fwd;
+                out.rmap.insert(out.rmap.end(), inv.begin(), inv.end());
                 out.fronts.back().flags |= TW_CARRY_OUT;
             }
             d.stash0 = static_cast<int>(out.stashes.size());
@@ -145,6 +151,7 @@ void build_tree_program(const HostPlan& P, const std::vector<int>& roots_in, boo
                 live.pop_back();
             }
             d.nstash = static_cast<int>(out.stashes.size()) - d.stash0;
+            d.map_n = static_cast<int>(out.rmap.size()) - d.map_lo;
             // this front's own block: carried (decided when the parent is emitted), the level program's slot (task
             // roots of a subtree program), or the stash stack
             const int mb = d.m - d.w;

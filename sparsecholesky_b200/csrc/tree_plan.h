@@ -28,15 +28,17 @@ enum : int { TW_CARRY_IN = 1,                 // the front's first child left it
              TW_CARRY_OUT = 2,                // this front's block stays in shared memory for the next front (its parent)
              TW_CB_STD = 4 };                 // block goes to the level program's workspace slot (column-major, ld = even(mb))
 
-struct alignas(16) TwFront {                  // 64 bytes, one descriptor load per front
+struct alignas(16) TwFront {                  // 80 bytes; the kernel keeps two descriptors ahead in registers
     int w, m, ld, first;                      // columns, rows, leading dimension of the panel in the L buffer, first global column
-    int flags, mc, map_off, nstash;           // carried child: order of its block, rmap[map_off .. +mc); stashed children to add
+    int flags, mc, map_off, nstash;           // carried child: order of its block; rmap[map_off .. +m) is the INVERSE map of the spread
+                                              // (source reversed row of every reversed row of this front, -1: a new row); stashed children to add
     int stash0, a0, an, ident;                // stashes[stash0 .. +nstash); A entries a_src/a_dst[a0 .. +an); carried child: its first
                                               // `ident` reversed rows keep their place (the map is the identity there)
+    int map_lo, map_n, pad0, pad1;            // rmap[map_lo .. +map_n): every map this front reads (prefetched one front ahead)
     int64_t panel_off;                        // panel in the L buffer
     int64_t cb_out;                           // TW_CB_STD: workspace offset; else (no carry, mb > 0): offset in the stash area
 };
-struct alignas(16) TwStash { int mc, map_off; int64_t src; };     // a stashed child block and its map into the parent
+struct alignas(16) TwStash { int mc, map_off; int64_t src; };     // a stashed child block and its (forward) map into the parent
 struct TwTask { int front0, nfront; int64_t stash_base; };         // stash_base: start of the task's private stack in the stash area
 
 struct TreeProgram {
@@ -45,7 +47,7 @@ struct TreeProgram {
     std::vector<TwTask> tasks;
     std::vector<TwFront> fronts;
     std::vector<TwStash> stashes;
-    std::vector<int> rmap;                    // reversed position in the parent of every reversed index of a child's block
+    std::vector<int> rmap;                    // maps in reversed indices: forward (child row -> parent row) for stashed blocks, inverse for carried ones
     std::vector<int> a_src;                   // index into Ax
     std::vector<unsigned short> a_dst;        // packed reversed index inside the front
     std::vector<char> in_tree;                // per front of the plan: 1 if a task of this program factors it

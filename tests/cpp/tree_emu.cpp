@@ -97,7 +97,6 @@ template <int NW>
 static void run_tasks(const TreeArrays& ta, const double* Ax, double* Lb, double* Wb, double* Sb, double* Lx, int* info, int cap_m, int mode) {
     const double nan = std::numeric_limits<double>::quiet_NaN();
     std::vector<double> F(static_cast<size_t>(cap_m) * (cap_m + 1) / 2 + TK_F_SLACK, nan);
-    std::vector<int> sinv(TW_MAX_M, -7);
     double spiv[2] = {nan, nan};
     std::barrier<> team(32 * NW);
     emu::g_team = &team;
@@ -109,7 +108,7 @@ static void run_tasks(const TreeArrays& ta, const double* Ax, double* Lb, double
         th.emplace_back([&, t] {
             emu::t_tid = t;
             for (int q = 0; q < ta.ntasks; ++q) {
-                tree_team_body<NW>(ta, ta.tasks[q], Ax, Lb, Wb, Sb, Lx, info, F.data(), sinv.data(), spiv, mode);
+                tree_team_body<NW>(ta, ta.tasks[q], Ax, Lb, Wb, Sb, Lx, info, F.data(), spiv, mode);
                 emu::sync();
             }
         });
