@@ -116,13 +116,28 @@ def cpu_reference_time(dims, repeats=1):
     return kind, best, flops, n, nnzL
 
 
+def make_matrix_checker_only(dims):
+    """The same matrix as make_matrix() built WITHOUT the product library (numpy ND permutation + the checker's own
+    triplet_to_csc): the reference arm maps only oracle/ into its process.  -> (n, Ap, Ai, Ax)"""
+    from oracle import pyoracle as po
+    from sparsecholesky_b200 import synth          # pure numpy helpers; the package does not load libspchol.so on import
+    perm = synth.nd_perm_py(*dims)
+    ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
+    tri = po.ref_triplet_to_csc if po.have_ref() else po.triplet_to_csc
+    Ap, Ai, Ax = tri(ti, tj, tx, n)
+    return n, Ap, Ai, Ax
+
+
 def run_reference(args, rank):
     if rank != 0:
         return
     dims, desc, sample = WORKLOADS[args.workload]
     from oracle import pyoracle as po
-    A = make_matrix(sample)
-    n = A.n
+    n, Ap, Ai, Ax = make_matrix_checker_only(sample)
+
+    class _A:
+        pass
+    A = _A(); A.n, A.p, A.i, A.x = n, Ap, Ai, Ax
     parent, Lp, _ = po.schol(n, A.p, A.i, want_Li=False)
     nnzL = int(Lp[n])
     cc = np.diff(Lp).astype(np.float64)
@@ -151,12 +166,51 @@ def run_reference(args, rank):
         "vs_baseline": None, "dtype": "f64", "data": "synthetic",
         "config": {"workload": args.workload, "description": desc, "reference_sample": smp,
                    "note": "the reference cannot run 128^3 (32-bit nnz overflow) and needs ~10 min for 64^3; "
-                           "its GFLOP/s falls with n (O(n^2) workspace), so this sample flatters it"},
+                           "its GFLOP/s falls with n (O(n^2) workspace), so this sample flatters it.  The SAME-INPUT "
+                           "comparison is in the product arm's line: also.lap3d_32.same_input_speedup (the 32^3 matrix "
+                           "this arm times, factored by the GPU path through the host-buffer call)"},
+        "seconds_per_step": sec,
         "cpu_baseline": {"value": gf, "unit": UNIT, "cores": 1, "kind": "reference" if use_ref else "port", "sample": smp},
         "e2e": {"value": gf, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0},
         "gpu_launches": 0,
     }
     print(json.dumps(line), flush=True)
+
+
+def run_also():
+    """lap2d_1024 (config 3), batched_1138 (config 5), lap3d_32 (the matrix the reference arm times): one child process
+    each, same code path as a direct `bench.py --workload ...` run; returns {workload: summary}."""
+    out = {}
+    jobs = [("lap2d_1024", ["--steps", "10", "--warmup", "3", "--no-cpu-baseline"]),
+            ("batched_1138", ["--steps", "5", "--warmup", "3", "--no-cpu-baseline"]),
+            ("lap3d_32", ["--steps", "10", "--warmup", "3"])]
+    for wl, extra in jobs:
+        t0 = time.time()
+        try:
+            r = subprocess.run([sys.executable, os.path.abspath(__file__), "--workload", wl, "--no-also"] + extra,
+                               capture_output=True, text=True, timeout=600)
+            line = next((l for l in r.stdout.splitlines() if l.startswith("{")), None)
+            if r.returncode != 0 or line is None:
+                out[wl] = {"error": (r.stderr or r.stdout)[-300:]}
+                continue
+            d = json.loads(line)
+            e = d.get("e2e") or {}
+            rf = d.get("roofline") or {}
+            sm = {"ms_per_step": d["ms_per_step"], "value": d["value"], "unit": d["unit"], "steps": d["steps"], "gpu_launches": d["gpu_launches"],
+                  "e2e": {k: e.get(k) for k in ("value", "ms_per_step", "h2d_bytes_per_step", "d2h_bytes_per_step", "result")},
+                  "roofline": {k: rf.get(k) for k in ("kernel", "bound", "achieved", "peak", "unit", "frac", "whole_factor_frac_of_peak")},
+                  "kernel_ms": d.get("kernel_ms"), "residual": (d.get("residual") or {}).get("rel_fro_estimate"),
+                  "parity": d.get("parity"), "clocks": d.get("clocks"), "wall_seconds": round(time.time() - t0, 1)}
+            cpu = d.get("cpu_baseline")
+            if wl == "lap3d_32" and cpu and e.get("ms_per_step"):
+                sm["cpu_baseline"] = cpu
+                sm["same_input_speedup"] = cpu["seconds"] / (e["ms_per_step"] * 1e-3)
+                sm["same_input_note"] = ("reference chol() seconds on this matrix / seconds of the GPU path through the host-buffer "
+                                         "C-ABI call (H2D + factor + CSC export + D2H), same process, same input")
+            out[wl] = sm
+        except Exception as exc:
+            out[wl] = {"error": repr(exc)[:300]}
+    return out
 
 
 def main():
@@ -168,6 +222,7 @@ def main():
     ap.add_argument("--workload", default="lap3d_128", choices=sorted(WORKLOADS))
     ap.add_argument("--no-cpu-baseline", action="store_true")
     ap.add_argument("--no-e2e", action="store_true")
+    ap.add_argument("--no-also", action="store_true", help="default workload only: skip the extra lines for configs 3, 5 and the same-input 32^3 case")
     ap.add_argument("--nbatch", type=int, default=16384, help="batched_1138: matrices in the batch (whole job)")
     ap.add_argument("--dist-nb", type=int, default=0, help="block-column width of distributed fronts (0: library default)")
     ap.add_argument("--dist-min-w", type=int, default=0, help="narrowest front factored by a rank group (0: default)")
@@ -333,9 +388,10 @@ def main():
         tm = np.zeros(4)
         L.spchol_last_timing(plan_h, ptr(tm))
         e2e = {"value": S.flops / e2e_ms * 1e-6, "unit": UNIT, "ms_per_step": e2e_ms, "steps": e2e_steps,
-               "h2d_bytes_per_step": nA * 8 * world, "d2h_bytes_per_step": sum(gather_list(out_entries * 8 + 4)),
+               "h2d_bytes_per_step": nA * 8 * world,
+               "d2h_bytes_per_step": sum(gather_list((ps["readback_entries"] if world > 1 else out_entries) * 8 + 4)),
                "result": "CSC L values (reference layout)" if use_csc else
-                         ("supernodal L panels, each rank reads back the fronts it holds" if world > 1 else
+                         ("supernodal L panels, each rank reads back the fronts it holds alone and the block columns it owns of group fronts" if world > 1 else
                           "supernodal L panels (nnz(L) > INT_MAX: no 32-bit CSC)"),
                "last_step_ms": {"h2d": tm[0], "numeric": tm[1], "export": tm[2], "d2h": tm[3]}}
         L.spchol_host_free(hA)
@@ -366,12 +422,17 @@ def main():
                 e2e["readback_check"] = {"error": repr(exc)[:200]}
     if e2e is not None:
         L.spchol_host_free(e2e_host_L[0])
-    if world == 1:
+    if True:
+        # every rank calls (collective for a multi-GPU plan: each rank multiplies the panels it holds or leads, the probe
+        # products are all-reduced); the factor checked is the one the timed steps produced
         out = C.c_double(0)
+        barrier()
         t0 = time.perf_counter()
         check(L.spchol_residual(plan_h, ptr(np.ascontiguousarray(A.x)), C.byref(out)), "spchol_residual")
         resid = {"rel_fro_estimate": out.value, "bound": 1e-12, "probes": 8, "seconds": round(time.perf_counter() - t0, 3),
-                 "how": "sqrt(mean_k ||(A - L L^T) z_k||^2) / ||A||_F on the device-resident supernodal factor (spchol_residual)"}
+                 "ranks": world,
+                 "how": "sqrt(mean_k ||(A - L L^T) z_k||^2) / ||A||_F on the device-resident supernodal factor (spchol_residual)"
+                        + ("; panels multiplied by the rank that holds or leads each front, probe products summed with ncclAllReduce" if world > 1 else "")}
         assert out.value <= 1e-12, f"residual {out.value} exceeds the 1e-12 bound"
 
     # consumer of the factor: x = A^-1 b on the device-resident panels (spchol_solve), checked end to end
@@ -400,6 +461,12 @@ def main():
                          f"({'32-bit nnz overflow' if S.nnz > 2**31 - 1 else 'O(n^2) workspace: minutes to hours'})",
                "host_cores_available": os.cpu_count()}
 
+    # BASELINE configs 3 and 5 and the same-input case of the reference arm, each a short run of this same script in a
+    # child process AFTER the timed region (so the driver-run line carries them); compact summaries only
+    also = None
+    if world == 1 and rank == 0 and args.workload == "lap3d_128" and not args.no_also:
+        also = run_also()
+
     if rank == 0:
         cfg = {"workload": args.workload, "description": desc, "n": A.n, "nnz_A": A.capacity(), "nnz_L": S.nnz,
                "flops": S.flops, "fronts": ps["ns"], "levels": ps["nlevels"], "l2": "inputs larger than L2 "
@@ -419,6 +486,8 @@ def main():
         }
         if world > 1:
             line["per_rank"] = per_rank
+        if also is not None:
+            line["also"] = also
         print(json.dumps(line), flush=True)
     if dist is not None:
         barrier()

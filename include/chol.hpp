@@ -337,9 +337,13 @@ public:
         return (xs >> rot) | (xs << ((32u - rot) & 31u));
     }
 };
+inline int iabs(double v) { const int t = static_cast<int>(v); return t < 0 ? -t : t; }      // int abs(int) on a double argument
 }  // namespace internal
 
 // reference chol.hpp:964-996: random symmetric sparse matrix (upper stored), seed 21, diagonal kept and boosted by n.
+// The reference writes an unqualified abs(v) here and in the overload below; in its translation units that resolves to the
+// C library's int abs(int), i.e. the value is truncated towards zero first.  Reproduced on purpose (internal::iabs): the
+// matrices come out bit for bit as the reference's (tests/golden/boundary.npz).
 template <typename T>
 csc_matrix<T, sym::upper> random_sparse(int n, double density = 0.25, bool positive_definite = true) {
     internal::pcg32_engine gen(21);
@@ -349,7 +353,7 @@ csc_matrix<T, sym::upper> random_sparse(int n, double density = 0.25, bool posit
     for (int i = 0; i < n; ++i)
         for (int j = i; j < n; ++j) {
             const double v = dist(gen);
-            if (std::fabs(v) < density * n || i == j) {
+            if (internal::iabs(v) < density * n || i == j) {
                 T val = static_cast<T>(dist(gen));
                 if (i == j && positive_definite) val += static_cast<T>(n);
                 ti.push_back(i); tj.push_back(j); tx.push_back(val);
@@ -368,7 +372,7 @@ csc_matrix<T, sym::lower> random_sparse(const SChol& S, bool positive_definite =
     for (int j = 0; j < n; ++j)
         for (int q = S.p()[j]; q < S.p()[j + 1]; ++q)
             A.x()[q] = S.i()[q] == j ? static_cast<T>(1.5 * (std::fabs(dist(gen)) + (positive_definite ? n : 0)))
-                                     : std::fabs(static_cast<T>(dist(gen)) * 10);
+                                     : static_cast<T>(internal::iabs(static_cast<T>(dist(gen)) * 10));
     return A;
 }
 

@@ -148,7 +148,9 @@ int  spchol_comm_world(const spchol_comm*);
  * entry (sum the ranks' vectors); info is already the minimum over all ranks. */
 int  spchol_plan_create_dist(const spchol_symbolic*, spchol_comm*, const int* dist_opts, spchol_plan** out);
 /* dist_stats[0..7] = rank, world, fronts held, fronts factored by a group, #transfers, doubles moved
- * per factorization by this rank, block-column width, 0; rank_load[world] = estimated flops per rank */
+ * per factorization by this rank, block-column width, doubles this rank reads back in spchol_factor_lbuf (the fronts it
+ * holds alone + the block columns it owns of the fronts its group factors; with pinned host memory the other block
+ * columns of such a front are left untouched in Lbuf_host -- their owners deliver them); rank_load[world] = estimated flops per rank */
 int  spchol_plan_dist_stats(const spchol_plan*, int64_t* dist_stats, double* rank_load);
 /* host-only: the mapping a `world`-rank plan would use (no GPU, no NCCL): own_lo/own_n per relaxed front */
 int  spchol_map_fronts(const spchol_symbolic*, int world, int dist_min_w, int* own_lo, int* own_n, double* rank_load);
@@ -204,7 +206,8 @@ int64_t spchol_last_launches(const spchol_plan*);
  * that were factored.  Estimated on the device with 8 Rademacher probes z: sqrt(mean ||(A - L L^T) z||^2) / ||A||_F
  * (E||Rz||^2 = ||R||_F^2), using two panel-times-vectors passes over the supernodal L buffer -- no CSC, so it also
  * works when nnz(L) > INT_MAX (128^3 Laplacian), where the reference's dense comparison (tests/test_chol.cpp:87)
- * cannot run.  Single-GPU plans. */
+ * cannot run.  Multi-GPU plans: collective (every rank calls with the same Ax); each rank multiplies the panels of the
+ * fronts it holds alone or leads, the probe products are summed with ncclAllReduce, every rank gets the same value. */
 int  spchol_residual(spchol_plan*, const double* Ax_host, double* rel_fro);
 
 /* x = A^-1 b with the factor the plan holds: L y = b, then L^T x = y, on the device-resident supernodal panels

@@ -68,6 +68,11 @@ def ref():
         L.ref_compute_supernodes.argtypes = [C.c_int, _VP, _VP, _VP, _VP]
         L.ref_atree.argtypes = [C.c_int, _VP, _VP, _VP, _VP, C.c_int, _VP, _VP]
         L.ref_csc_to_dense_none.argtypes = [C.c_int, _VP, _VP, _VP, _VP]
+        if hasattr(L, "ref_random_sparse"):
+            L.ref_random_sparse.argtypes = [C.c_int, C.c_double, C.c_int, _VP, _VP, _VP]
+            L.ref_random_sparse_S.argtypes = [C.c_int, _VP, _VP, _VP, C.c_int, _VP]
+            L.ref_csc_from_A_S.argtypes = [C.c_int, _VP, _VP, _VP, _VP, _VP, _VP, _VP]
+            L.ref_schol_etree.argtypes = [C.c_int, _VP, _VP, _VP, _VP]
         _ref = L
     return _ref
 

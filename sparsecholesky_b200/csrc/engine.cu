@@ -49,7 +49,7 @@ struct NcclApi {
     int (*GroupEnd)() = nullptr;
     const char* (*GetErrorString)(int) = nullptr;
 };
-constexpr int kNcclInt32 = 2, kNcclFloat64 = 8, kNcclMin = 3, kNcclSplitNoColor = -1;
+constexpr int kNcclInt32 = 2, kNcclFloat64 = 8, kNcclSum = 0, kNcclMin = 3, kNcclSplitNoColor = -1;
 
 NcclApi* nccl_api() {
     static NcclApi api;
@@ -126,6 +126,7 @@ struct spchol_plan {
     // residual check (built on first use): global row index of every below-row, task lists, A coordinates
     int* d_rowidx = nullptr; RTask* d_rt_cols = nullptr; RTask* d_rt_rows = nullptr; int n_rt_cols = 0, n_rt_rows = 0;
     int *d_a_row = nullptr, *d_a_col = nullptr; int* d_level_list = nullptr;
+    FrontArrays fa_r{};               // fa with rel_off replaced by the offsets of d_rowidx (multi-rank plans: HostPlan::ridx_off)
     std::vector<int> level_ptr;
     // overlapped read-back of the supernodal panels (spchol_factor_lbuf with pinned host memory): contiguous runs of
     // the L buffer that are final once a given level has run, copied on a third stream while the upper levels compute
@@ -206,7 +207,19 @@ int export_prepare(spchol_plan* p) {
     for (int s = 0; s < H.ns; ++s) {
         if (!H.holds(s) || H.front_marked[s]) continue;       // marked fronts are read back block column by block column (OP_EXPORT)
         const int bucket = H.level[s] >= cut ? H.level[s] : std::max(cut - 1, 0);
-        raw[bucket].push_back({H.panel_off[s], static_cast<int64_t>(H.ld[s]) * H.w[s]});
+        if (H.own_n[s] > 1) {
+            // a front factored by a rank group: every member holds the whole panel after the broadcasts, but only the
+            // block columns it OWNS are its part of the result -- reading back the rest would move every such panel
+            // own_n times over PCIe (8 GPUs: 53.9 GB instead of 27.6 GB, the round-1 e2e regression)
+            const int DNB = H.dist_NB, G = H.own_n[s], me = H.own_idx[s];
+            for (int c0 = 0, kb = 0; c0 < H.w[s]; c0 += DNB, ++kb) {
+                if (kb % G != me) continue;
+                const int c1 = std::min(c0 + DNB, H.w[s]);
+                raw[bucket].push_back({H.panel_off[s] + static_cast<int64_t>(c0) * H.ld[s], static_cast<int64_t>(c1 - c0) * H.ld[s]});
+            }
+        } else {
+            raw[bucket].push_back({H.panel_off[s], static_cast<int64_t>(H.ld[s]) * H.w[s]});
+        }
     }
     p->export_runs.assign(H.nlevels, {});
     for (int l = 0; l < H.nlevels; ++l) {
@@ -672,7 +685,16 @@ int spchol_plan_dist_stats(const spchol_plan* p, int64_t* st, double* rank_load)
     int64_t held = 0;
     for (int s = 0; s < H.ns; ++s) held += H.holds(s) ? 1 : 0;
     st[0] = H.rank; st[1] = H.world; st[2] = held; st[3] = H.n_dist;
-    st[4] = static_cast<int64_t>(H.comm_tasks.size()); st[5] = H.comm_doubles; st[6] = H.dist_NB; st[7] = 0;
+    st[4] = static_cast<int64_t>(H.comm_tasks.size()); st[5] = H.comm_doubles; st[6] = H.dist_NB;
+    // doubles this rank reads back in spchol_factor_lbuf with pinned memory: its own fronts + the block columns it owns of group fronts
+    int64_t own = 0;
+    for (int s = 0; s < H.ns; ++s) {
+        if (!H.holds(s)) continue;
+        if (H.own_n[s] == 1) { own += static_cast<int64_t>(H.ld[s]) * H.w[s]; continue; }
+        for (int c0 = 0, kb = 0; c0 < H.w[s]; c0 += H.dist_NB, ++kb)
+            if (kb % H.own_n[s] == H.own_idx[s]) own += static_cast<int64_t>(std::min(c0 + H.dist_NB, H.w[s]) - c0) * H.ld[s];
+    }
+    st[7] = own;
     if (rank_load) for (int r = 0; r < H.world; ++r) rank_load[r] = H.rank_load[r];
     return 0;
 }
@@ -1072,26 +1094,40 @@ static int residual_prepare(spchol_plan* p) {
     if (p->d_rowidx) return 0;
     const HostPlan& H = p->H;
     int rc;
-    std::vector<int> order(H.ns);
-    p->level_ptr.assign(H.nlevels + 1, 0);
-    for (int s = 0; s < H.ns; ++s) ++p->level_ptr[H.level[s] + 1];
-    for (int l = 0; l < H.nlevels; ++l) p->level_ptr[l + 1] += p->level_ptr[l];
-    { std::vector<int> cur(p->level_ptr.begin(), p->level_ptr.end() - 1);
-      for (int s = 0; s < H.ns; ++s) order[cur[H.level[s]]++] = s; }
     std::vector<RTask> tc, tr;
-    for (int s = 0; s < H.ns; ++s) {
-        for (int c0 = 0; c0 < H.w[s]; c0 += 32) tc.push_back({s, c0});
-        for (int r0 = 0; r0 < H.m[s]; r0 += 256) tr.push_back({s, r0});
+    if (H.world > 1) {
+        // the rows come from the host plan; only the fronts this rank multiplies (ridx_off >= 0) get tasks
+        int64_t* d_off = nullptr;
+        for (int s = 0; s < H.ns; ++s) {
+            if (H.ridx_off[s] < 0) continue;
+            for (int c0 = 0; c0 < H.w[s]; c0 += 32) tc.push_back({s, c0});
+            for (int r0 = 0; r0 < H.m[s]; r0 += 256) tr.push_back({s, r0});
+        }
+        if ((rc = upload(p, H.ridx, &p->d_rowidx)) || (rc = upload(p, H.ridx_off, &d_off))) return rc;
+        p->fa_r = p->fa; p->fa_r.rel_off = d_off;
+        std::vector<int>().swap(p->H.ridx);
+    } else {
+        std::vector<int> order(H.ns);
+        p->level_ptr.assign(H.nlevels + 1, 0);
+        for (int s = 0; s < H.ns; ++s) ++p->level_ptr[H.level[s] + 1];
+        for (int l = 0; l < H.nlevels; ++l) p->level_ptr[l + 1] += p->level_ptr[l];
+        { std::vector<int> cur(p->level_ptr.begin(), p->level_ptr.end() - 1);
+          for (int s = 0; s < H.ns; ++s) order[cur[H.level[s]]++] = s; }
+        for (int s = 0; s < H.ns; ++s) {
+            for (int c0 = 0; c0 < H.w[s]; c0 += 32) tc.push_back({s, c0});
+            for (int r0 = 0; r0 < H.m[s]; r0 += 256) tr.push_back({s, r0});
+        }
+        if ((rc = upload(p, order, &p->d_level_list)) || (rc = dalloc(p, H.rel_off[H.ns], &p->d_rowidx))) return rc;
+        p->fa_r = p->fa;
+        for (int l = H.nlevels - 1; l >= 0; --l) {           // parents before children
+            const int cnt = p->level_ptr[l + 1] - p->level_ptr[l];
+            if (cnt) k_rowidx_level<<<std::min(cnt, 4096), 128, 0, p->stream>>>(p->d_level_list + p->level_ptr[l], cnt, p->fa, p->d_rowidx);
+        }
     }
     p->n_rt_cols = static_cast<int>(tc.size()); p->n_rt_rows = static_cast<int>(tr.size());
-    if ((rc = upload(p, order, &p->d_level_list)) || (rc = upload(p, tc, &p->d_rt_cols)) || (rc = upload(p, tr, &p->d_rt_rows)) ||
-        (rc = upload(p, p->H.a_row, &p->d_a_row)) || (rc = upload(p, p->H.a_col, &p->d_a_col)) ||
-        (rc = dalloc(p, H.rel_off[H.ns], &p->d_rowidx))) return rc;
+    if ((rc = upload(p, tc, &p->d_rt_cols)) || (rc = upload(p, tr, &p->d_rt_rows)) ||
+        (rc = upload(p, p->H.a_row, &p->d_a_row)) || (rc = upload(p, p->H.a_col, &p->d_a_col))) return rc;
     std::vector<int>().swap(p->H.a_row); std::vector<int>().swap(p->H.a_col);
-    for (int l = H.nlevels - 1; l >= 0; --l) {           // parents before children
-        const int cnt = p->level_ptr[l + 1] - p->level_ptr[l];
-        if (cnt) k_rowidx_level<<<std::min(cnt, 4096), 128, 0, p->stream>>>(p->d_level_list + p->level_ptr[l], cnt, p->fa, p->d_rowidx);
-    }
     CK(cudaGetLastError());
     return 0;
 }
@@ -1099,10 +1135,14 @@ static int residual_prepare(spchol_plan* p) {
 int spchol_residual(spchol_plan* p, const double* Ax, double* rel_fro) {
     if (!p || !Ax || !rel_fro) { set_error("spchol_residual: null argument"); return SPCHOL_EINVAL; }
     const HostPlan& H = p->H;
-    if (H.world > 1) { set_error("spchol_residual: single-GPU plans only"); return SPCHOL_EINVAL; }
     CK(cudaSetDevice(p->device));
     int rc;
     if ((rc = residual_prepare(p))) return rc;
+    // multi-rank plans (collective: every rank calls with the same Ax): each rank multiplies the panels of the fronts it
+    // holds alone or leads, the probe products y = L^T z and u = L y are summed over the ranks (every column of L belongs
+    // to exactly one multiplying rank), r = A z is formed by everybody -- the estimate is identical on all ranks
+    NcclApi* nc = H.world > 1 ? nccl_api() : nullptr;
+    if (H.world > 1 && (!nc || !p->comm)) { set_error("spchol_residual: multi-rank plan without a communicator"); return SPCHOL_EINVAL; }
     cudaStream_t st = p->stream;
     const int64_t nv = static_cast<int64_t>(H.n) * NPROBE;
     double *z = nullptr, *dA = nullptr;                  // z, y, u, r, 2 scalars
@@ -1112,8 +1152,12 @@ int spchol_residual(spchol_plan* p, const double* Ax, double* rel_fro) {
     cudaMemcpyAsync(dA, Ax, sizeof(double) * H.nnzA, cudaMemcpyHostToDevice, st);
     cudaMemsetAsync(scal, 0, 2 * sizeof(double), st);
     k_probe_init<<<static_cast<unsigned>((nv + 255) / 256), 256, 0, st>>>(H.n, z, y, u, r);
-    if (p->n_rt_cols) k_lt_mult<<<p->n_rt_cols, 256, 0, st>>>(p->d_rt_cols, p->fa, p->d_rowidx, p->dL, z, y);
-    if (p->n_rt_rows) k_l_mult<<<p->n_rt_rows, 256, 0, st>>>(p->d_rt_rows, p->fa, p->d_rowidx, p->dL, y, u);
+    if (p->n_rt_cols) k_lt_mult<<<p->n_rt_cols, 256, 0, st>>>(p->d_rt_cols, p->fa_r, p->d_rowidx, p->dL, z, y);
+    if (nc && nc->AllReduce(y, y, static_cast<size_t>(nv), kNcclFloat64, kNcclSum, p->comm->world_comm, st) != 0) {
+        cudaFree(z); cudaFree(dA); set_error("spchol_residual: ncclAllReduce failed"); return SPCHOL_ENCCL; }
+    if (p->n_rt_rows) k_l_mult<<<p->n_rt_rows, 256, 0, st>>>(p->d_rt_rows, p->fa_r, p->d_rowidx, p->dL, y, u);
+    if (nc && nc->AllReduce(u, u, static_cast<size_t>(nv), kNcclFloat64, kNcclSum, p->comm->world_comm, st) != 0) {
+        cudaFree(z); cudaFree(dA); set_error("spchol_residual: ncclAllReduce failed"); return SPCHOL_ENCCL; }
     k_sym_mult<<<static_cast<unsigned>((H.nnzA + 255) / 256), 256, 0, st>>>(H.nnzA, p->d_a_row, p->d_a_col, dA, z, r, scal);
     k_diff_norm<<<1184, 256, 0, st>>>(nv, r, u, scal);
     double h[2] = {0, 0};

@@ -257,10 +257,15 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         }
     }
 
-    if (world == 1) {
-        P.a_row.assign(S.Ai.begin(), S.Ai.end());
-        P.a_col.resize(S.nnzA);
-        for (int j = 0; j < n; ++j) for (int p = S.Ap[j]; p < S.Ap[j + 1]; ++p) P.a_col[p] = j;
+    P.a_row.assign(S.Ai.begin(), S.Ai.end());
+    P.a_col.resize(S.nnzA);
+    for (int j = 0; j < n; ++j) for (int p = S.Ap[j]; p < S.Ap[j + 1]; ++p) P.a_col[p] = j;
+    if (world > 1) {
+        P.ridx_off.assign(ns, -1);
+        int64_t o = 0;
+        for (int s = 0; s < ns; ++s) if (P.holds(s) && P.own_idx[s] == 0) { P.ridx_off[s] = o; o += P.m[s] - P.w[s]; }
+        P.ridx.resize(o);
+        for (int s = 0; s < ns; ++s) if (P.ridx_off[s] >= 0) std::copy(S.below(s), S.below(s) + (P.m[s] - P.w[s]), P.ridx.begin() + P.ridx_off[s]);
     }
 
     // CSC export map; a panel replicated over a rank group is exported by the group's first rank

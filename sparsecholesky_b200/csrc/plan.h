@@ -117,7 +117,12 @@ struct HostPlan {
     // maps
     std::vector<int64_t> a_dest;     // nnzA  : L-buffer offset of each stored A entry
     std::vector<int64_t> l_src;      // nnzL  : L-buffer offset of each CSC entry of L (want_csc)
-    std::vector<int> a_row, a_col;   // nnzA  : coordinates of the stored entries of triu(A) (residual check; single-rank plans)
+    std::vector<int> a_row, a_col;   // nnzA  : coordinates of the stored entries of triu(A) (residual check)
+    // multi-rank plans: global row index of every below-row of the fronts whose panel THIS rank multiplies in the residual
+    // check (fronts it holds alone, and group fronts where it is the group's first rank), ridx_off[s] = -1 elsewhere.
+    // (Single-rank plans rebuild the same thing on the device from the relative indices.)
+    std::vector<int64_t> ridx_off;
+    std::vector<int> ridx;
     // schedule
     std::vector<int> small_list;
     std::vector<int> extadd_list;    // child front ids

@@ -59,7 +59,7 @@ class DistPlan:
         check(lib().spchol_plan_dist_stats(self.h, ptr(ds), ptr(load)))
         keys = ["ns", "nlevels", "n_small", "n_large", "lbuf_entries", "ws_entries", "n_ops", "max_m", "max_w", "device_bytes"]
         d = dict(zip(keys, (int(v) for v in st)))
-        d.update(dict(zip(["rank", "world", "fronts_held", "fronts_dist", "transfers", "doubles_moved", "dist_NB"], (int(v) for v in ds[:7]))))
+        d.update(dict(zip(["rank", "world", "fronts_held", "fronts_dist", "transfers", "doubles_moved", "dist_NB", "readback_entries"], (int(v) for v in ds[:8]))))
         d["rank_load"] = load.tolist()
         return d
 

@@ -19,9 +19,47 @@ static void dense_cholesky(std::vector<double>& a, int n) {      // stand-in for
     }
 }
 
+extern "C" void dpotrf_(const char*, const int* n, double* a, const int* lda, int* info) {   // the header only declares LAPACK's
+    std::vector<double> t(a, a + static_cast<std::size_t>(*lda) * *n);
+    dense_cholesky(t, *n);
+    std::copy(t.begin(), t.end(), a);
+    *info = 0;
+}
+
+template <class V>
+static void dump(std::FILE* f, const char* name, const V& v) {
+    std::fprintf(f, "%s %zu", name, v.size());
+    for (const auto& e : v) std::fprintf(f, " %.17g", static_cast<double>(e));
+    std::fprintf(f, "\n");
+}
+
 int main(int argc, char** argv) {
     const std::string data = argc > 1 ? argv[1] : "tests/data";
     const bool gpu = argc > 2 && !std::strcmp(argv[2], "gpu");
+    if (argc > 3 && !std::strcmp(argv[2], "dump")) {
+        // the remaining public helpers of the reference header, written out for a bit-for-bit comparison with what the
+        // reference itself produced (tests/golden/boundary.npz, generated from oracle/_ref/libref.so)
+        std::FILE* f = std::fopen(argv[3], "w");
+        CHECK(f != nullptr);
+        for (auto [n, dens] : {std::pair<int, double>{10, 0.25}, {37, 0.1}}) {
+            auto R = random_sparse<double>(n, dens);                       // reference chol.hpp:964
+            const std::string tag = "rs" + std::to_string(n);
+            dump(f, (tag + "_p").c_str(), R.p()); dump(f, (tag + "_i").c_str(), R.i()); dump(f, (tag + "_x").c_str(), R.x());
+        }
+        auto A = load_matrix_market_to_csc<double>(data + "/bcsstk01.mtx");
+        auto S = schol(A);
+        auto B = random_sparse<double>(S);                                 // :1004 (lower, on the pattern of S)
+        dump(f, "rsS_x", B.x());
+        auto Bt = B.transpose();                                           // usage of reference main.cpp:323
+        CHECK(Bt.p()[Bt.size()] == B.p()[B.size()]);
+        csc_matrix<double, sym::upper> Wk(A, S);                           // :190 (only the diagonal carries over from an upper A)
+        dump(f, "ctor_x", Wk.x());
+        auto E = schol_etree(A);                                           // :628
+        dump(f, "se_p", E.p()); dump(f, "se_i", E.i());
+        std::fclose(f);
+        std::printf("test_dropin dump OK\n");
+        return 0;
+    }
     const std::vector<std::vector<int>> pattern = {{0}, {1}, {0, 2}, {3}, {0, 2, 4}, {0, 1, 3, 5}, {0, 2, 5, 6}};
     {   // CholeskyTest.EliminationTree (reference tests/test_chol.cpp:6-25)
         auto A = build_csc_matrix_from_pattern<double>(pattern);
@@ -90,6 +128,36 @@ int main(int argc, char** argv) {
             auto x = chol_solve(S, b);
             CHECK(x.has_value());
             for (int i = 0; i < n; ++i) CHECK(std::fabs((*x)[i] - 1.0) < 1e-8);
+        }
+        {   // CholeskyTest.SupernodalCholesky (:99-136): chol_sn is the same supernodal GPU factorization
+            std::vector<int> ti = {0, 0, 0, 1, 1, 2}, tj = {0, 1, 2, 1, 2, 2};
+            std::vector<double> tx = {4.0, 1.0, 1.0, 3.0, 0.0, 2.0}, expected = {4.0, 1.0, 1.0, 1.0, 3.0, 0.0, 1.0, 0.0, 2.0};
+            dense_cholesky(expected, 3);
+            auto A = triplet_to_csc_matrix(ti, tj, tx, 3);
+            auto L = chol_sn(A);
+            CHECK(L.has_value());
+            auto result = csc_to_dense(*L);
+            for (int j = 0; j < 3; ++j) for (int i = j; i < 3; ++i) CHECK(std::fabs(result[i + j * 3] - expected[i + j * 3]) < 1e-9);
+        }
+        {   // 64-bit container: same factor as the 32-bit path, entry for entry; resident factor + solve
+            auto A = load_matrix_market_to_csc<double>(data + "/1138_bus.mtx");
+            auto S = schol(A);
+            auto L = chol(A, S).value();
+            auto S64 = schol64(A);
+            CHECK(S64.nnz == static_cast<std::int64_t>(S.capacity()) && S64.parent == S.parent);
+            auto L64 = chol64(A, S64);
+            CHECK(L64.has_value());
+            CHECK(L64->p().size() == L.p().size() && L64->i() == L.i());
+            for (std::size_t j = 0; j < L.p().size(); ++j) CHECK(L64->p()[j] == L.p()[j]);
+            CHECK(L64->x() == L.x());
+            CHECK(((*L64)[5, 5] == L.x()[L.p()[5]]));
+            auto ok = chol_resident(A, S64);
+            CHECK(ok.has_value());
+            auto res = chol_residual(A, S64);
+            CHECK(res.has_value() && *res <= 1e-12);
+            // a matrix with another pattern is refused instead of being read out of bounds
+            auto A2 = load_matrix_market_to_csc<double>(data + "/bcsstk01.mtx");
+            CHECK(!chol(A2, S).has_value());
         }
         {   // error path (reference chol.hpp:850)
             auto A = triplet_to_csc_matrix<double>({0, 0, 1}, {0, 1, 1}, {1.0, 2.0, 1.0}, 2);

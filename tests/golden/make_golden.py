@@ -81,5 +81,36 @@ def main():
         golden_for(nm, n, *po.ref_triplet_to_csc(ti, tj, tx, n))
 
 
+def boundary_golden():
+    """outputs of the reference's remaining public helpers (random_sparse x2, csc_matrix(A, S), schol_etree) for the
+    drop-in header test (tests/test_dropin_cpp.py)"""
+    import ctypes as C
+    R = po.ref()
+    out = {}
+    for n, dens in ((10, 0.25), (37, 0.1)):
+        nz = R.ref_random_sparse(n, dens, 1, None, None, None)
+        Ap = np.empty(n + 1, np.int32); Ai = np.empty(nz, np.int32); Ax = np.empty(nz)
+        R.ref_random_sparse(n, dens, 1, Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data)
+        out[f"rs{n}_p"] = Ap; out[f"rs{n}_i"] = Ai; out[f"rs{n}_x"] = Ax
+    n, Ap, Ai, Ax = po.ref_load_mtx(os.path.join(ROOT, "tests", "data", "bcsstk01.mtx"))
+    parent, Lp, Li, _ = po.ref_schol(n, Ap, Ai)
+    x = np.empty(int(Lp[n]))
+    R.ref_random_sparse_S(n, parent.ctypes.data, Lp.ctypes.data, Li.ctypes.data, 1, x.ctypes.data)
+    out["rsS_x"] = x.copy()
+    R.ref_csc_from_A_S(n, Ap.ctypes.data, Ai.ctypes.data, Ax.ctypes.data, parent.ctypes.data, Lp.ctypes.data, Li.ctypes.data, x.ctypes.data)
+    out["ctor_x"] = x.copy()
+    Ep = np.empty(n + 1, np.int32)
+    nz = R.ref_schol_etree(n, Ap.ctypes.data, Ai.ctypes.data, Ep.ctypes.data, None)
+    Ei = np.empty(nz, np.int32)
+    R.ref_schol_etree(n, Ap.ctypes.data, Ai.ctypes.data, Ep.ctypes.data, Ei.ctypes.data)
+    out["se_p"] = Ep; out["se_i"] = Ei
+    np.savez_compressed(os.path.join(OUT, "boundary.npz"), **out)
+    print("boundary: random_sparse(10) nnz", len(out["rs10_i"]), "schol_etree(bcsstk01) nnz", nz)
+
+
 if __name__ == "__main__":
-    main()
+    if len(sys.argv) > 1 and sys.argv[1] == "boundary":
+        boundary_golden()
+    else:
+        main()
+        boundary_golden()

@@ -44,6 +44,12 @@ def main():
             err = float((np.abs(L.x - Lx) / np.abs(Lx)).max())
             assert err <= 1e-10, (name, err)
             worst = max(worst, err)
+            # the distributed residual check (every rank multiplies the panels it holds or leads, ncclAllReduce of the probes)
+            import ctypes as C
+            from sparsecholesky_b200._lib import check, lib, ptr
+            out = C.c_double(0)
+            check(lib().spchol_residual(plan.h, ptr(np.ascontiguousarray(A.x)), C.byref(out)), "spchol_residual")
+            assert out.value <= 1e-12, (name, out.value)
         if rank == 0:
             print(f"mgpu {name}: world={world} dist fronts={st['fronts_dist']} transfers={st['transfers']} max rel err={err:.2e}", flush=True)
         plan.close()

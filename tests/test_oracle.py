@@ -11,7 +11,7 @@ from oracle import pyoracle as po
 from sparsecholesky_b200 import synth
 
 GOLD = os.path.join(os.path.dirname(__file__), "golden")
-NAMES = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLD, "*.npz")) if not os.path.basename(f).startswith("large_"))
+NAMES = sorted(os.path.basename(f)[:-4] for f in glob.glob(os.path.join(GOLD, "*.npz")) if not os.path.basename(f).startswith(("large_", "boundary")))
 
 
 @pytest.mark.parametrize("name", NAMES)
