@@ -17,6 +17,7 @@
 #include "../../include/spchol.h"
 #include "capi_internal.h"
 #include "kernels.cuh"
+#include "gemm_tma.cuh"
 #include "tree_kernel.cuh"
 #include "residual.cuh"
 #include "solve.cuh"
@@ -123,6 +124,8 @@ struct spchol_plan {
     int *d_small_list = nullptr, *d_extadd_list = nullptr;
     ZeroTask* d_zero = nullptr; PotrfTask* d_potrf = nullptr; TrsmTask* d_trsm = nullptr; GemmTask* d_gemm = nullptr;
     CopyTask* d_copy = nullptr;
+    CUtensorMap* d_tmaps = nullptr;                 // one per front with update tasks (k_gemm_tma)
+    bool gemm_tma = true;                           // SPCHOL_GEMM_TMA=0: the register-staged k_gemm_dmma (A/B timing)
     // residual check (built on first use): global row index of every below-row, task lists, A coordinates
     int* d_rowidx = nullptr; RTask* d_rt_cols = nullptr; RTask* d_rt_rows = nullptr; int n_rt_cols = 0, n_rt_rows = 0;
     int *d_a_row = nullptr, *d_a_col = nullptr; int* d_level_list = nullptr;
@@ -365,8 +368,12 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
         case OP_GEMM:
             for (int b = 0; b < op.count; b += 65535) {
                 const int c = std::min(op.count - b, 65535);
-                k_gemm_dmma<<<dim3((op.gx + G_BM - 1) / G_BM, (op.gy + G_BN - 1) / G_BN, c), 256, G_SMEM, st>>>(
-                    p->d_gemm + op.begin + b, p->dL, p->dW, gemm_swizzle);
+                if (p->gemm_tma)
+                    k_gemm_tma<<<dim3((op.gx + G3_BM - 1) / G3_BM, (op.gy + G3_BN - 1) / G3_BN, c), 256, G3_SMEM, st>>>(
+                        p->d_gemm + op.begin + b, p->d_tmaps, p->dL, p->dW, gemm_swizzle);
+                else
+                    k_gemm_dmma<<<dim3((op.gx + G_BM - 1) / G_BM, (op.gy + G_BN - 1) / G_BN, c), 256, G_SMEM, st>>>(
+                        p->d_gemm + op.begin + b, p->dL, p->dW, gemm_swizzle);
                 ++launches;
             }
             break;
@@ -571,6 +578,34 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
     if ((rc = dalloc(p, H.lbuf_entries, &p->dL))) return fail(rc);
     if ((rc = dalloc(p, H.ws_entries, &p->dW))) return fail(rc);
     if ((rc = dalloc(p, 1, &p->dinfo))) return fail(rc);
+    if (const char* v = getenv("SPCHOL_GEMM_TMA")) p->gemm_tma = atoi(v) != 0;
+    if (!H.tmap_fronts.empty()) {
+        // TMA tensor maps of the panels the update kernel reads: m rows x w columns of doubles with row pitch ld, boxes of
+        // 16 rows x G3_BK columns, 128-byte swizzle, zeros out of bounds (encoded by the driver, used straight from HBM)
+        using EncodeFn = CUresult (*)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*, const cuuint64_t*,
+                                      const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave, CUtensorMapSwizzle,
+                                      CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+        void* fn = nullptr;
+        cudaDriverEntryPointQueryResult qr;
+        if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &fn, cudaEnableDefault, &qr) != cudaSuccess || !fn) {
+            cudaGetLastError();
+            set_error("spchol: cuTensorMapEncodeTiled is not available from this driver (needed by the TMA-staged update kernel)");
+            return fail(SPCHOL_ECUDA);
+        }
+        std::vector<CUtensorMap> maps(H.tmap_fronts.size());
+        for (size_t i = 0; i < maps.size(); ++i) {
+            const int s = H.tmap_fronts[i];
+            const cuuint64_t dims[2] = {static_cast<cuuint64_t>(H.m[s]), static_cast<cuuint64_t>(H.w[s])};
+            const cuuint64_t strides[1] = {static_cast<cuuint64_t>(H.ld[s]) * 8};
+            const cuuint32_t box[2] = {16, static_cast<cuuint32_t>(G3_BK)};
+            const cuuint32_t estr[2] = {1, 1};
+            const CUresult cr = reinterpret_cast<EncodeFn>(fn)(&maps[i], CU_TENSOR_MAP_DATA_TYPE_FLOAT64, 2, p->dL + H.panel_off[s], dims, strides, box, estr,
+                                                               CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                                                               CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+            if (cr != CUDA_SUCCESS) { set_error("spchol: cuTensorMapEncodeTiled failed (code " + std::to_string(static_cast<int>(cr)) + ")"); return fail(SPCHOL_ECUDA); }
+        }
+        if ((rc = upload(p, maps, &p->d_tmaps))) return fail(rc);
+    }
     if ((rc = dalloc(p, static_cast<int64_t>(std::max(H.max_potrf_slots, 1)) * PB_MAX * PB_MAX, &p->dWinv))) return fail(rc);
     p->fa = FrontArrays{p->d_first, p->d_w, p->d_m, p->d_ld, p->d_parent, p->d_panel_off, p->d_cb_off,
                         p->d_rel_off, p->d_rel, p->d_child_ptr, p->d_child_idx, p->d_own_n, p->d_own_idx, H.dist_NB};
@@ -590,7 +625,9 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
             set_error("cudaFuncSetAttribute (shared memory carve-out) failed"); return fail(SPCHOL_ECUDA);
         }
     }
-    if (cudaFuncSetAttribute(k_gemm_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM) != cudaSuccess ||
+    if (cudaFuncSetAttribute(k_gemm_tma, cudaFuncAttributeMaxDynamicSharedMemorySize, G3_SMEM) != cudaSuccess ||
+        cudaFuncSetAttribute(k_gemm_tma, cudaFuncAttributePreferredSharedMemoryCarveout, cudaSharedmemCarveoutMaxShared) != cudaSuccess ||
+        cudaFuncSetAttribute(k_gemm_dmma, cudaFuncAttributeMaxDynamicSharedMemorySize, G_SMEM) != cudaSuccess ||
         cudaFuncSetAttribute(k_potrf_inv<32>, cudaFuncAttributeMaxDynamicSharedMemorySize, potrf_inv_smem(32)) != cudaSuccess ||
         cudaFuncSetAttribute(k_potrf_inv<64>, cudaFuncAttributeMaxDynamicSharedMemorySize, potrf_inv_smem(64)) != cudaSuccess ||
         cudaFuncSetAttribute(k_potrf_inv<128>, cudaFuncAttributeMaxDynamicSharedMemorySize, potrf_inv_smem(128)) != cudaSuccess ||

@@ -311,7 +311,23 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         ws_size[s] = even_up64(cb_entries(s));
         P.cb_off[s] = arena.alloc(ws_size[s]);
     };
-    auto add_gemm = [&](Op& op, const GemmTask& ge) {
+    // panels in address order, to find the front an operand offset belongs to
+    std::vector<std::pair<int64_t, int>> pan;
+    for (int s = 0; s < ns; ++s) if (P.holds(s)) pan.push_back({P.panel_off[s], s});
+    std::sort(pan.begin(), pan.end());
+    std::vector<int> front_tmap(ns, -1);
+    auto add_gemm = [&](Op& op, GemmTask ge) {
+        {   // TMA view: both operands are row ranges of one front's panel
+            auto it = std::upper_bound(pan.begin(), pan.end(), std::make_pair(ge.a_off, ns));
+            if (it == pan.begin()) throw std::runtime_error("spchol: update operand outside every panel");
+            const int s = std::prev(it)->second;
+            const int64_t po = P.panel_off[s], ea = ge.a_off - po, eb = ge.b_off - po;
+            const int ld = P.ld[s];
+            if (eb < 0 || ea / ld != eb / ld || ea / ld + ge.K > P.w[s] || ge.lda != ld || ge.ldb != ld)
+                throw std::runtime_error("spchol: update operands are not row ranges of one panel");
+            if (front_tmap[s] < 0) { front_tmap[s] = static_cast<int>(P.tmap_fronts.size()); P.tmap_fronts.push_back(s); }
+            ge.tmap = front_tmap[s]; ge.ra = static_cast<int>(ea % ld); ge.rb = static_cast<int>(eb % ld); ge.kc = static_cast<int>(ea / ld);
+        }
         P.gemm_tasks.push_back(ge);
         op.gx = std::max(op.gx, ge.M); op.gy = std::max(op.gy, ge.N);
         op.threads = std::max(op.threads, ge.K);                    // OP_GEMM: largest K of the launch (profiling classes)

@@ -19,6 +19,9 @@ struct GemmTask {
     int diag;        // element (i,j) of C is wanted iff i + diag >= j   (lower-trapezoid mask)
     int c_space;     // bit 0: C lives in the L buffer (0) / the contribution workspace (1); bit 1: C = -A B^T (the target
                      // holds no data yet: Schur complement into a fresh contribution block) instead of C -= A B^T
+    // TMA view of the operands (k_gemm_tma): A and B are row ranges of ONE front's panel, described by that front's tensor
+    // map (HostPlan::tmap_fronts[tmap]: m rows x w columns, leading dimension ld); A starts at row ra, B at row rb, both at column kc
+    int tmap, ra, rb, kc;
 };
 struct PotrfTask { int64_t d_off; int ld; int nb; int col0; int slot; };         // diag block in L buffer; slot: scratch for its inverse
 struct TrsmTask  { int64_t b_off; int ld; int nb; int rows; int64_t d_off; int slot; };  // rows below the block
@@ -130,6 +133,7 @@ struct HostPlan {
     std::vector<PotrfTask> potrf_tasks;
     std::vector<TrsmTask> trsm_tasks;
     std::vector<GemmTask> gemm_tasks;
+    std::vector<int> tmap_fronts;    // fronts whose panel needs a TMA tensor map (GemmTask::tmap indexes this list)
     std::vector<CommTask> comm_tasks;
     std::vector<CopyTask> copy_tasks;
     std::vector<ExportTask> export_tasks;

@@ -96,3 +96,30 @@ def batch_values(Ap, Ai, Ax, b):
     d = batch_scaling(b, n)
     col = np.repeat(np.arange(n), np.diff(Ap))
     return (d[Ai] * Ax) * d[col]
+
+
+def graded_laplacian_triplets(nx, ny=1, nz=1, perm=None, decades=10.0, shift=1e-9, seed=7):
+    """Ill-conditioned SPD test matrix with the pattern of laplacian_triplets: a weighted graph Laplacian whose edge
+    weights span `decades` orders of magnitude (10^U(-decades/2, decades/2), seeded), free boundary, plus
+    shift * (largest diagonal) on the diagonal so that it is (barely) positive definite.  cond(A) ~ 1e10 and more with
+    the defaults -- the case the explicit-inverse panel solve of the wide fronts has to survive."""
+    n = nx * ny * nz
+    ids = np.arange(n, dtype=np.int64)
+    x = ids % nx; y = (ids // nx) % ny; z = ids // (nx * ny)
+    rng = np.random.default_rng(seed)
+    rows, cols, vals = [], [], []
+    diag = np.zeros(n)
+    for mask, step in ((x + 1 < nx, 1), (y + 1 < ny, nx), (z + 1 < nz, nx * ny)):
+        a = ids[mask]
+        if a.size == 0:
+            continue
+        w = 10.0 ** rng.uniform(-decades / 2, decades / 2, a.size)
+        rows.append(a); cols.append(a + step); vals.append(-w)
+        np.add.at(diag, a, w); np.add.at(diag, a + step, w)
+    diag += shift * diag.max()
+    ti = np.concatenate([ids] + rows); tj = np.concatenate([ids] + cols); tx = np.concatenate([diag] + vals)
+    if perm is not None:
+        inv = np.empty(n, np.int64)
+        inv[perm] = np.arange(n, dtype=np.int64)
+        ti = inv[ti]; tj = inv[tj]
+    return ti.astype(np.int32), tj.astype(np.int32), tx, n
