@@ -49,6 +49,15 @@ int spchol_triplet_to_csc(int64_t nz, const int* ti, const int* tj, const double
  * Two-call protocol: with ti == NULL only *n_out / *nz_out are written. */
 int spchol_mtx_read(const char* path, int* n_out, int64_t* nz_out, int* ti, int* tj, double* tx);
 
+/* The same on the GPU: triplets and outputs in DEVICE memory (d_Ap[n+1], d_Ai / d_Ax[nz]); a stable 64-bit
+ * radix sort by (column, row) + segmented sum, duplicates added in input order, explicit zeros kept.  The CSC stays on the
+ * device (d_Ax feeds spchol_factor_device).  stream: a cudaStream_t or NULL; synchronous on return. */
+int spchol_triplet_to_csc_device(int64_t nz, const int* d_ti, const int* d_tj, const double* d_tx, int n,
+                                 int* d_Ap, int* d_Ai, double* d_Ax, int64_t* nnz_out, void* stream);
+/* host-pointer convenience around it (H2D, device ingest, D2H); *device_ms (optional) = CUDA-event time of the device part */
+int spchol_triplet_to_csc_gpu(int64_t nz, const int* ti, const int* tj, const double* tx, int n,
+                              int* Ap, int* Ai, double* Ax, int64_t* nnz_out, double* device_ms);
+
 /* ---- orderings (host; additive: the reference has no ordering code) -------- */
 /* geometric nested dissection of an nx*ny*nz grid, the fixed permutation of the benchmark Laplacians
  * (SURVEY.md 8d): perm[new] = old grid id, id = x + nx*(y + ny*z) */

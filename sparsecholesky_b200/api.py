@@ -192,6 +192,18 @@ def triplet_to_csc_matrix(ti, tj, tx, n):
     return CscMatrix(n, Ap, Ai[: m.value].copy(), Ax[: m.value].copy(), Sym.upper)
 
 
+def triplet_to_csc_matrix_gpu(ti, tj, tx, n, return_ms=False):
+    """triplet_to_csc_matrix on the GPU (spchol_triplet_to_csc_gpu: stable radix sort by (column, row) + segmented sum of
+    duplicates in input order); same result as the host path / the reference (chol.hpp:309-369)."""
+    ti = np.ascontiguousarray(ti, np.int32); tj = np.ascontiguousarray(tj, np.int32); tx = np.ascontiguousarray(tx, np.float64)
+    nz = len(ti)
+    Ap = np.empty(n + 1, np.int32); Ai = np.empty(max(nz, 1), np.int32); Ax = np.empty(max(nz, 1), np.float64)
+    m = C.c_int64(0); ms = C.c_double(0)
+    check(lib().spchol_triplet_to_csc_gpu(nz, ptr(ti), ptr(tj), ptr(tx), n, ptr(Ap), ptr(Ai), ptr(Ax), C.byref(m), C.byref(ms)), "triplet_to_csc_matrix_gpu")
+    A = CscMatrix(n, Ap, Ai[: m.value].copy(), Ax[: m.value].copy())
+    return (A, ms.value) if return_ms else A
+
+
 def load_matrix_market_to_csc(filename):
     L = lib()
     n = C.c_int(0); nz = C.c_int64(0)

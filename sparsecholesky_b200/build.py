@@ -7,7 +7,7 @@ HERE = os.path.dirname(os.path.abspath(__file__))
 CSRC = os.path.join(HERE, "csrc")
 OUT = os.path.join(HERE, "libspchol.so")
 SOURCES = ["symbolic.cpp", "ordering.cpp", "plan.cpp", "tree_plan.cpp", "capi_host.cpp", "engine.cu"]
-HEADERS = ["symbolic.h", "ordering.h", "plan.h", "capi_internal.h", "kernels.cuh", "gemm_tma.cuh", "tree_plan.h", "tree_kernel.cuh", "residual.cuh", "solve.cuh", "../../include/spchol.h"]
+HEADERS = ["symbolic.h", "ordering.h", "plan.h", "capi_internal.h", "kernels.cuh", "gemm_tma.cuh", "ingest.cuh", "tree_plan.h", "tree_kernel.cuh", "residual.cuh", "solve.cuh", "../../include/spchol.h"]
 
 
 def needs_build() -> bool:

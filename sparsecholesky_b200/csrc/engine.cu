@@ -18,6 +18,7 @@
 #include "capi_internal.h"
 #include "kernels.cuh"
 #include "gemm_tma.cuh"
+#include "ingest.cuh"
 #include "tree_kernel.cuh"
 #include "residual.cuh"
 #include "solve.cuh"
@@ -369,7 +370,7 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
             for (int b = 0; b < op.count; b += 65535) {
                 const int c = std::min(op.count - b, 65535);
                 if (p->gemm_tma)
-                    k_gemm_tma<<<dim3((op.gx + G3_BM - 1) / G3_BM, (op.gy + G3_BN - 1) / G3_BN, c), 256, G3_SMEM, st>>>(
+                    k_gemm_tma<<<dim3((op.gx + 1 + G3_BM - 1) / G3_BM, (op.gy + 1 + G3_BN - 1) / G3_BN, c), 256, G3_SMEM, st>>>(      // (+1: odd-row shift)
                         p->d_gemm + op.begin + b, p->d_tmaps, p->dL, p->dW, gemm_swizzle);
                 else
                     k_gemm_dmma<<<dim3((op.gx + G_BM - 1) / G_BM, (op.gy + G_BN - 1) / G_BN, c), 256, G_SMEM, st>>>(
@@ -943,6 +944,118 @@ int spchol_factor_batched(spchol_plan* p, int nbatch, const double* Ax, double* 
     CK(cudaStreamSynchronize(p->stream));
     p->last_launches = launches;
     return 0;
+}
+
+// ---- device-side ingest: COO -> upper CSC on the GPU, see ingest.cuh ------------------------------
+namespace {
+int ingest_scan(int64_t n, const unsigned* in, unsigned* out, unsigned* sums, cudaStream_t st) {
+    const int nb = static_cast<int>((n + IN_SCAN_BLOCK - 1) / IN_SCAN_BLOCK);
+    if (nb <= 0) return 0;
+    k_in_scan_block<<<nb, 256, 0, st>>>(n, in, out, sums);
+    if (nb > 1) {
+        k_in_scan_sums<<<1, 256, 0, st>>>(nb, sums);
+        k_in_scan_add<<<nb, 256, 0, st>>>(n, out, sums);
+    }
+    return 0;
+}
+}  // namespace
+
+// d_ti / d_tj / d_tx: nz triplets in device memory; d_Ap [n+1], d_Ai / d_Ax [nz] device outputs; *nnz_out = merged entries.
+// Synchronous on return (the count comes back to the host); stream = a cudaStream_t or NULL.
+int spchol_triplet_to_csc_device(int64_t nz, const int* d_ti, const int* d_tj, const double* d_tx, int n,
+                                 int* d_Ap, int* d_Ai, double* d_Ax, int64_t* nnz_out, void* stream) {
+    if (nz < 0 || n < 1 || !d_Ap || !nnz_out || (nz > 0 && (!d_ti || !d_tj || !d_tx || !d_Ai || !d_Ax))) { set_error("spchol_triplet_to_csc_device: bad argument"); return SPCHOL_EINVAL; }
+    if (nz > INT_MAX) { set_error("spchol_triplet_to_csc_device: more than INT_MAX triplets"); return SPCHOL_ERANGE; }
+    if (spchol_device_count() <= 0) { set_error("spchol_triplet_to_csc_device: no CUDA device"); return SPCHOL_ENOGPU; }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    *nnz_out = 0;
+    if (nz == 0) { CK(cudaMemsetAsync(d_Ap, 0, sizeof(int) * (static_cast<size_t>(n) + 1), st)); CK(cudaStreamSynchronize(st)); return 0; }
+    const int nwarps = static_cast<int>((nz + IN_WARP_ITEMS - 1) / IN_WARP_ITEMS);
+    const int64_t nh = static_cast<int64_t>(256) * nwarps;
+    const int64_t nscan = std::max<int64_t>(std::max<int64_t>(nh, nz), n + 1);
+    const int nbs = static_cast<int>((nscan + IN_SCAN_BLOCK - 1) / IN_SCAN_BLOCK);
+    // one arena: 2 key buffers, 2 payload buffers, histogram, head flags, slots, column counts, scan sums, flag
+    auto up = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t bK = up(sizeof(unsigned long long) * nz), bI = up(sizeof(unsigned) * nz), bH = up(sizeof(unsigned) * nh),
+                 bC = up(sizeof(unsigned) * (static_cast<size_t>(n) + 1)), bS = up(sizeof(unsigned) * nbs);
+    unsigned char* arena = nullptr;
+    CK(cudaMalloc(&arena, 2 * bK + 4 * bI + bH + bC + bS + 256));
+    unsigned char* q = arena;
+    auto take = [&](size_t b) { unsigned char* r = q; q += b; return r; };
+    unsigned long long* key[2] = {reinterpret_cast<unsigned long long*>(take(bK)), reinterpret_cast<unsigned long long*>(take(bK))};
+    unsigned* idx[2] = {reinterpret_cast<unsigned*>(take(bI)), reinterpret_cast<unsigned*>(take(bI))};
+    unsigned* head = reinterpret_cast<unsigned*>(take(bI));
+    unsigned* slot = reinterpret_cast<unsigned*>(take(bI));
+    unsigned* hist = reinterpret_cast<unsigned*>(take(bH));
+    unsigned* colc = reinterpret_cast<unsigned*>(take(bC));
+    unsigned* sums = reinterpret_cast<unsigned*>(take(bS));
+    int* bad = reinterpret_cast<int*>(take(256));
+    auto done = [&](int code) { cudaFree(arena); return code; };
+    if (cudaMemsetAsync(bad, 0, sizeof(int), st) != cudaSuccess || cudaMemsetAsync(colc, 0, sizeof(unsigned) * (static_cast<size_t>(n) + 1), st) != cudaSuccess)
+        { set_error("spchol_triplet_to_csc_device: cudaMemsetAsync failed"); return done(SPCHOL_ECUDA); }
+    const unsigned gb = static_cast<unsigned>((nz + 255) / 256);
+    k_in_keys<<<gb, 256, 0, st>>>(nz, d_ti, d_tj, n, key[0], idx[0], bad);
+    int bits = 1;
+    while ((int64_t(1) << bits) < n) ++bits;
+    const int nbytes = (bits + 7) / 8;
+    int cur = 0;
+    for (int half = 0; half < 2; ++half)
+        for (int b = 0; b < nbytes; ++b) {
+            const int shift = 32 * half + 8 * b;
+            k_in_hist<<<(nwarps + 7) / 8, 256, 0, st>>>(nz, key[cur], shift, nwarps, hist);
+            ingest_scan(nh, hist, hist, sums, st);
+            k_in_scatter<<<(nwarps + 7) / 8, 256, 0, st>>>(nz, key[cur], idx[cur], shift, nwarps, hist, key[cur ^ 1], idx[cur ^ 1]);
+            cur ^= 1;
+        }
+    k_in_heads<<<gb, 256, 0, st>>>(nz, key[cur], head, colc);
+    ingest_scan(nz, head, slot, sums, st);
+    k_in_emit<<<gb, 256, 0, st>>>(nz, key[cur], idx[cur], head, slot, d_tx, d_Ai, d_Ax);
+    unsigned last[2] = {0, 0};
+    cudaMemcpyAsync(&last[0], slot + (nz - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(&last[1], head + (nz - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, st);
+    int hbad = 0;
+    cudaMemcpyAsync(&hbad, bad, sizeof(int), cudaMemcpyDeviceToHost, st);
+    ingest_scan(static_cast<int64_t>(n) + 1, colc, colc, sums, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) { set_error("spchol_triplet_to_csc_device: kernel failure"); return done(SPCHOL_ECUDA); }
+    if (hbad) { set_error("spchol_triplet_to_csc_device: index outside [0, n)"); return done(SPCHOL_EINVAL); }
+    const unsigned total = last[0] + last[1];
+    k_in_ap<<<(n + 1 + 255) / 256, 256, 0, st>>>(n, colc, total, d_Ap);
+    if (cudaStreamSynchronize(st) != cudaSuccess) { set_error("spchol_triplet_to_csc_device: kernel failure"); return done(SPCHOL_ECUDA); }
+    *nnz_out = total;
+    return done(0);
+}
+
+// host-pointer convenience around the device ingest (tests / callers without device buffers): H2D, ingest, D2H;
+// *device_ms (optional) = time of the device part alone (CUDA events).
+int spchol_triplet_to_csc_gpu(int64_t nz, const int* ti, const int* tj, const double* tx, int n, int* Ap, int* Ai, double* Ax,
+                              int64_t* nnz_out, double* device_ms) {
+    if (nz < 0 || n < 1 || !Ap || !nnz_out) { set_error("spchol_triplet_to_csc_gpu: bad argument"); return SPCHOL_EINVAL; }
+    if (spchol_device_count() <= 0) { set_error("spchol_triplet_to_csc_gpu: no CUDA device"); return SPCHOL_ENOGPU; }
+    int *dti = nullptr, *dtj = nullptr, *dAp = nullptr, *dAi = nullptr; double *dtx = nullptr, *dAx = nullptr;
+    const size_t z = static_cast<size_t>(std::max<int64_t>(nz, 1));
+    auto freeall = [&] { cudaFree(dti); cudaFree(dtj); cudaFree(dtx); cudaFree(dAp); cudaFree(dAi); cudaFree(dAx); };
+    if (cudaMalloc(&dti, 4 * z) != cudaSuccess || cudaMalloc(&dtj, 4 * z) != cudaSuccess || cudaMalloc(&dtx, 8 * z) != cudaSuccess ||
+        cudaMalloc(&dAp, 4 * (static_cast<size_t>(n) + 1)) != cudaSuccess || cudaMalloc(&dAi, 4 * z) != cudaSuccess || cudaMalloc(&dAx, 8 * z) != cudaSuccess) {
+        freeall(); set_error("spchol_triplet_to_csc_gpu: out of device memory"); return SPCHOL_ENOMEM;
+    }
+    cudaMemcpy(dti, ti, 4 * static_cast<size_t>(nz), cudaMemcpyHostToDevice);
+    cudaMemcpy(dtj, tj, 4 * static_cast<size_t>(nz), cudaMemcpyHostToDevice);
+    cudaMemcpy(dtx, tx, 8 * static_cast<size_t>(nz), cudaMemcpyHostToDevice);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, nullptr);
+    const int rc = spchol_triplet_to_csc_device(nz, dti, dtj, dtx, n, dAp, dAi, dAx, nnz_out, nullptr);
+    cudaEventRecord(e1, nullptr);
+    cudaEventSynchronize(e1);
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (device_ms) *device_ms = ms;
+    if (rc == 0) {
+        cudaMemcpy(Ap, dAp, 4 * (static_cast<size_t>(n) + 1), cudaMemcpyDeviceToHost);
+        if (*nnz_out > 0) { cudaMemcpy(Ai, dAi, 4 * static_cast<size_t>(*nnz_out), cudaMemcpyDeviceToHost); cudaMemcpy(Ax, dAx, 8 * static_cast<size_t>(*nnz_out), cudaMemcpyDeviceToHost); }
+    }
+    freeall();
+    return rc;
 }
 
 int spchol_host_alloc(int64_t bytes, void** out) {

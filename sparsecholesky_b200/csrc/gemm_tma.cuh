@@ -68,7 +68,10 @@ __global__ void __launch_bounds__(256, 2) k_gemm_tma(const GemmTask* __restrict_
         bx = band * G3_SWZ + within % rows;
         by = within / rows;
     }
-    const int i0 = bx * G3_BM, j0 = by * G3_BN;
+    // TMA moves 16-byte granules along the contiguous dimension: the first row of a box must be even.  A range that
+    // starts at an odd panel row (w odd: the Schur complement starts at row w) is tiled from the row above instead -- the
+    // tile grid is shifted by one, the extra leading row (-1) is computed and never stored.
+    const int i0 = bx * G3_BM - (t.ra & 1), j0 = by * G3_BN - (t.rb & 1);
     if (i0 >= t.M || j0 >= t.N) return;
     if (i0 + G3_BM - 1 + t.diag < j0) return;          // tile entirely above the wanted trapezoid
     // stages: 1024-byte aligned (the 128B swizzle pattern repeats every 8 lines); barriers behind them
@@ -102,7 +105,7 @@ __global__ void __launch_bounds__(256, 2) k_gemm_tma(const GemmTask* __restrict_
     if ((swizzle & 2) && K <= 1024 && !(t.c_space & 2)) {
         // short K: the read-modify-write of the C tile at the end is a visible part of the CTA's life -- pull it towards L2 now
         const int pc = tid >> 2, pr = (tid & 3) * 32;
-        if (j0 + pc < t.N && i0 + pr < t.M) {
+        if (j0 + pc >= 0 && j0 + pc < t.N && i0 + pr >= 0 && i0 + pr < t.M) {
             const double* cp = C + (i0 + pr) + static_cast<int64_t>(j0 + pc) * t.ldc;
             asm volatile("prefetch.global.L2 [%0];" ::"l"(cp));
             if (i0 + pr + 16 < t.M) asm volatile("prefetch.global.L2 [%0];" ::"l"(cp + 16));
@@ -155,13 +158,13 @@ __global__ void __launch_bounds__(256, 2) k_gemm_tma(const GemmTask* __restrict_
 #pragma unroll
     for (int mi = 0; mi < 4; ++mi) {
         const int row = i0 + wm * 32 + (mi >> 1) * 16 + g3_box_row(mi & 1, g);
-        if (row >= t.M) continue;
+        if (row < 0 || row >= t.M) continue;
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) {
 #pragma unroll
             for (int e = 0; e < 2; ++e) {
                 const int col = j0 + wn * 32 + (ni >> 1) * 16 + g3_box_row(ni & 1, 2 * tq + e);
-                if (col < t.N && row + t.diag >= col) {
+                if (col >= 0 && col < t.N && row + t.diag >= col) {
                     double* c = C + row + static_cast<int64_t>(col) * ldc;
                     if (beta0) *c = -acc[mi][ni][e]; else *c -= acc[mi][ni][e];
                 }

@@ -122,7 +122,7 @@ int main(int argc, char** argv) {
                    s.name, s.M, s.N, s.K, s.ntask, vname, ms, fl / ms * 1e-9, diff);
             fflush(stdout);
         };
-        const dim3 g1((s.M + G_BM - 1) / G_BM, (s.N + G_BN - 1) / G_BN, s.ntask), g3((s.M + G3_BM - 1) / G3_BM, (s.N + G3_BN - 1) / G3_BN, s.ntask);
+        const dim3 g1((s.M + G_BM - 1) / G_BM, (s.N + G_BN - 1) / G_BN, s.ntask), g3((s.M + 1 + G3_BM - 1) / G3_BM, (s.N + 1 + G3_BN - 1) / G3_BN, s.ntask);
         run("r1_regstage", [&] { k_gemm_dmma<<<g1, 256, G_SMEM>>>(dt, L, W, 3); });
         run("r2_tma", [&] { k_gemm_tma<<<g3, 256, G3_SMEM>>>(dt, dm, L, W, 3); });
         cudaFree(L); cudaFree(W); cudaFree(W0); cudaFree(Wref); cudaFree(dmax); cudaFree(dt); cudaFree(dm);
