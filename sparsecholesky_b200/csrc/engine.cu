@@ -143,6 +143,7 @@ struct spchol_plan {
     std::vector<SolveStep> solve_steps;        // forward order; the backward solve walks it in reverse
     SBlock* d_sblocks = nullptr; SChunk* d_supd = nullptr; SChunk* d_sgat = nullptr;
     bool solve_ready = false;
+    double* d_solve_v = nullptr;               // work vectors of spchol_solve (3 n SOLVE_NR doubles, allocated on first use)
     int64_t device_bytes = 0;
     int64_t last_launches = 0;
     double last_ms[4] = {0, 0, 0, 0};
@@ -327,7 +328,7 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
         const int64_t before = launches;
         switch (op.kind) {
         case OP_TREE: {
-            static const int nw = getenv("SPCHOL_TREE_NW") ? atoi(getenv("SPCHOL_TREE_NW")) : 1;
+            static const int nw = getenv("SPCHOL_TREE_NW") ? atoi(getenv("SPCHOL_TREE_NW")) : 2;
             launch_tree(nw, op.count, p->tree.f_stride, st, p->tree.ta, dAx, p->dL, p->dW, p->tree.stash, nullptr, p->dinfo, 0, 0, 0, 0, 0, 0, 0);
             ++launches;
         } break;
@@ -1205,17 +1206,17 @@ int spchol_solve(spchol_plan* p, const double* b, double* x, int nrhs) {
     if ((rc = solve_prepare(p))) return rc;
     cudaStream_t st = p->stream;
     const int64_t nv = static_cast<int64_t>(H.n) * SOLVE_NR;
-    double* dv = nullptr;                               // [0, nv): right-hand sides / solution, [nv, 2 nv): gather sums
-    CK(cudaMalloc(&dv, sizeof(double) * 2 * nv));
-    std::vector<double> hv(static_cast<size_t>(nv));
+    // work vectors live with the plan: [0, nv) right-hand sides / solution interleaved [n][SOLVE_NR], [nv, 2 nv) gather sums,
+    // [2 nv, 3 nv) the caller's columns as they arrive / leave (column-major); packing and unpacking run on the device
+    if (!p->d_solve_v && (rc = dalloc(p, 3 * nv, &p->d_solve_v))) return rc;
+    double* dv = p->d_solve_v;
+    double* stage = dv + 2 * nv;
     int64_t launches = 0;
     cudaError_t e = cudaSuccess;
     for (int k0 = 0; k0 < nrhs && e == cudaSuccess; k0 += SOLVE_NR) {
         const int nr = std::min(SOLVE_NR, nrhs - k0);
-        for (int64_t i = 0; i < H.n; ++i)
-            for (int k = 0; k < SOLVE_NR; ++k) hv[i * SOLVE_NR + k] = k < nr ? b[static_cast<int64_t>(k0 + k) * H.n + i] : 0.0;
-        cudaMemcpyAsync(dv, hv.data(), sizeof(double) * nv, cudaMemcpyHostToDevice, st);
-        cudaMemsetAsync(dv + nv, 0, sizeof(double) * nv, st);
+        cudaMemcpyAsync(stage, b + static_cast<int64_t>(k0) * H.n, sizeof(double) * H.n * nr, cudaMemcpyHostToDevice, st);
+        k_solve_pack<<<static_cast<unsigned>((nv + 255) / 256), 256, 0, st>>>(H.n, nr, stage, dv, dv + nv);
         for (const auto& sp : p->solve_steps) {         // L y = b
             k_solve_diag<false><<<sp.bn, 256, sp.smem, st>>>(p->d_sblocks + sp.b0, p->fa, p->dL, dv, nullptr);
             if (sp.un) k_solve_update<<<sp.un, 256, 0, st>>>(p->d_supd + sp.u0, p->fa, p->d_rowidx, p->dL, dv);
@@ -1226,13 +1227,12 @@ int spchol_solve(spchol_plan* p, const double* b, double* x, int nrhs) {
             k_solve_diag<true><<<it->bn, 256, it->smem, st>>>(p->d_sblocks + it->b0, p->fa, p->dL, dv, dv + nv);
             launches += 1 + (it->gn ? 1 : 0);
         }
-        cudaMemcpyAsync(hv.data(), dv, sizeof(double) * nv, cudaMemcpyDeviceToHost, st);
+        k_solve_unpack<<<static_cast<unsigned>((static_cast<int64_t>(H.n) * nr + 255) / 256), 256, 0, st>>>(H.n, nr, dv, stage);
+        cudaMemcpyAsync(x + static_cast<int64_t>(k0) * H.n, stage, sizeof(double) * H.n * nr, cudaMemcpyDeviceToHost, st);
+        launches += 2;
         e = cudaStreamSynchronize(st);
         if (e == cudaSuccess) e = cudaGetLastError();
-        for (int64_t i = 0; i < H.n && e == cudaSuccess; ++i)
-            for (int k = 0; k < nr; ++k) x[static_cast<int64_t>(k0 + k) * H.n + i] = hv[i * SOLVE_NR + k];
     }
-    cudaFree(dv);
     p->last_launches = launches;
     if (e != cudaSuccess) { set_error(std::string("spchol_solve: ") + cudaGetErrorString(e)); return SPCHOL_ECUDA; }
     return SPCHOL_OK;

@@ -88,8 +88,9 @@ struct PlanOptions {
                                // and the children's contributions to it are extend-added afterwards
     int lookahead = 1;         // 1: panel work of large fronts on stream 1, overlapped with the trailing update (see Op)
     int tree = 1;              // 1: the bottom of the tree goes to the warp-per-subtree kernel (tree_plan.h) instead of one CTA per front and level
-    int tree_cap_m = 117;      // largest front inside a subtree task (117 rows: 55 KB packed, four warps per SM)
-    double tree_work = 2.5e6;  // dense flops of a subtree task (the unit of load balance: ~100 us of one warp)
+    int tree_cap_m = 64;       // largest front inside a subtree task (64 rows: 16.7 KB packed, 13 teams per SM; measured on 2D 1024^2:
+                               // small-front time 2.25 ms at 64 rows / 2 warps against 2.5-5.1 ms at 96-117 rows and 3.03 ms without subtree tasks)
+    double tree_work = 2.5e6;  // dense flops of a subtree task (the unit of load balance)
     int export_mark_w = 0;     // > 0: fronts at least this wide announce every finished block column (OP_EXPORT).  Staged:
                                // checked by the plan simulator, not yet run on a GPU -- SPCHOL_EXPORT_MARK_W=1024 enables it
     // multi-GPU (one plan per rank, every rank builds the same global mapping):

@@ -23,6 +23,21 @@ struct SBlock { int s, c0; };         // front, first column of the block
 struct SChunk { int s, c0, r0; };     // + first row of a chunk of 256 rows (forward update) / unused (backward)
 constexpr int solve_diag_smem(int nb) { return (nb * (nb | 1) + nb * SOLVE_NR) * 8; }
 
+// column-major right-hand sides (n x nr) -> interleaved [n][SOLVE_NR] (missing columns zero), gather sums cleared; and back
+__global__ void k_solve_pack(int n, int nr, const double* __restrict__ cols, double* __restrict__ v, double* __restrict__ tsum) {
+    const int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    if (e >= static_cast<int64_t>(n) * SOLVE_NR) return;
+    const int64_t i = e / SOLVE_NR; const int k = static_cast<int>(e % SOLVE_NR);
+    v[e] = k < nr ? cols[static_cast<int64_t>(k) * n + i] : 0.0;
+    tsum[e] = 0.0;
+}
+__global__ void k_solve_unpack(int n, int nr, const double* __restrict__ v, double* __restrict__ cols) {
+    const int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    if (e >= static_cast<int64_t>(n) * nr) return;
+    const int64_t i = e % n; const int k = static_cast<int>(e / n);
+    cols[e] = v[i * SOLVE_NR + k];
+}
+
 // diagonal block solve, forward (TRANS = false): y = L_jj^-1 x   or backward (TRANS = true): x = L_jj^-T (y - t)
 template <bool TRANS>
 __global__ void __launch_bounds__(256) k_solve_diag(const SBlock* __restrict__ tasks, FrontArrays fa, const double* __restrict__ L,
