@@ -190,7 +190,7 @@ int set_small_attr() {
 }
 
 // one CTA (a team of nw warps) per task / per matrix, see tree_kernel.cuh
-constexpr size_t tree_smem(int f_stride) { return (static_cast<size_t>(f_stride) + 2) * 8; }
+constexpr size_t tree_smem(int f_stride) { return (static_cast<size_t>(f_stride) + 2 + 64) * 8; }
 void launch_tree(int nw, int grid, int f_stride, cudaStream_t st, const TreeArrays& ta, const double* Ax, double* L, double* W, double* Stash,
                  double* Lx, int* info, int64_t axs, int64_t ls, int64_t ws, int64_t ss, int64_t lxs, int nmat, int out_mode) {
     const size_t sm = tree_smem(f_stride);
@@ -493,6 +493,7 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
         if (const char* v = getenv("SPCHOL_SMALL_MAX_M")) { const int x = atoi(v); if (x >= 16 && x <= 224) opt.small_max_m = x; }   // development switch (A/B timing)
         if (const char* v = getenv("SPCHOL_TREE")) opt.tree = atoi(v) != 0;
         if (const char* v = getenv("SPCHOL_TREE_CAP")) { const int x = atoi(v); if (x >= 8 && x <= TW_MAX_M) opt.tree_cap_m = x; }
+        if (const char* v = getenv("SPCHOL_BATCH_GROUP_M")) { const int x = atoi(v); if (x >= 0 && x <= TW_MAX_M) opt.batch_group_m = x; }
         if (const char* v = getenv("SPCHOL_TREE_WORK")) { const double x = atof(v); if (x > 0) opt.tree_work = x; }
         if (const char* v = getenv("SPCHOL_NB")) { const int x = atoi(v); if (x >= 128) opt.NB = x; }
         if (const char* v = getenv("SPCHOL_NB_WIDE")) { const int x = atoi(v); if (x >= 128) opt.NB_wide = x; }
@@ -551,7 +552,10 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
             int r2;
             if ((r2 = upload(p, T.tasks, &dt)) || (r2 = upload(p, T.fronts, &df)) || (r2 = upload(p, T.stashes, &dsx)) ||
                 (r2 = upload(p, T.rmap, &drm)) || (r2 = upload(p, T.a_src, &das)) || (r2 = upload(p, T.a_dst, &dad))) return r2;
-            D.ta = TreeArrays{dt, static_cast<int>(T.tasks.size()), df, dsx, drm, das, dad, csc_map};
+            unsigned short* dos = nullptr; int* dod = nullptr; int* dgc = nullptr;
+            if ((r2 = upload(p, T.out_src, &dos)) || (r2 = upload(p, T.out_dst, &dod)) || (r2 = upload(p, T.gcol, &dgc))) return r2;
+            D.ta = TreeArrays{dt, static_cast<int>(T.tasks.size()), df, dsx, drm, das, dad, csc_map, dos, dod, dgc};
+            std::vector<unsigned short>().swap(T.out_src); std::vector<int>().swap(T.out_dst); std::vector<int>().swap(T.gcol);
             D.f_stride = ((T.cap_m * (T.cap_m + 1) / 2) + TK_F_SLACK + 1) & ~1;
             D.stash_entries = (T.stash_entries + 1) & ~int64_t(1);
             D.on = true;

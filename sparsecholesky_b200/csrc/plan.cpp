@@ -739,7 +739,10 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     // The blocks of the subtree roots live in the arena from the start of the factorization until their parents ran.
     std::vector<char> in_tree(ns, 0);
     if (want_tree) {
-        if (P.max_m <= TW_MAX_M) build_tree_program(P, {}, true, a_front, a_fcol, a_fpos, P.tree_whole);
+        if (P.max_m <= TW_MAX_M) {
+            if (opt.batch_group_m > 0 && opt.want_csc) build_group_program(P, std::max(opt.batch_group_m, P.max_m), a_front, a_fcol, a_fpos, P.tree_whole);
+            else build_tree_program(P, {}, true, a_front, a_fcol, a_fpos, P.tree_whole);
+        }
         const std::vector<int> roots = choose_subtrees(P, opt.tree_cap_m, opt.tree_work, in_tree);
         if (!roots.empty()) {
             for (int s : roots) if (P.m[s] > P.w[s] && P.parent[s] >= 0) ws_alloc(s);

@@ -91,6 +91,8 @@ struct PlanOptions {
     int tree_cap_m = 64;       // largest front inside a subtree task (64 rows: 16.7 KB packed, 13 teams per SM; measured on 2D 1024^2:
                                // small-front time 2.25 ms at 64 rows / 2 warps against 2.5-5.1 ms at 96-117 rows and 3.03 ms without subtree tasks)
     double tree_work = 2.5e6;  // dense flops of a subtree task (the unit of load balance)
+    int batch_group_m = 117;   // batched whole-tree program: fronts are amalgamated into groups of up to this many rows (tree_plan.h,
+                               // build_group_program; 117 rows = 55 KB packed = four teams per SM); 0: one step per front of the plan
     int export_mark_w = 0;     // > 0: fronts at least this wide announce every finished block column (OP_EXPORT).  Staged:
                                // checked by the plan simulator, not yet run on a GPU -- SPCHOL_EXPORT_MARK_W=1024 enables it
     // multi-GPU (one plan per rank, every rank builds the same global mapping):

@@ -23,6 +23,7 @@
 #define TK_ATOMIC_MIN(p, v) ::spchol::emu::atomic_min((p), (v))
 #define TK_RESTRICT
 #define TK_SQRT(x) std::sqrt(x)
+#define TK_RSQRT(x) (1.0 / std::sqrt(x))
 #define TK_DMMA(c0, c1, a, b) ::spchol::emu::dmma884((c0), (c1), (a), (b))
 #else
 #define TK_DEVICE __device__ __forceinline__
@@ -33,6 +34,7 @@
 #define TK_ATOMIC_MIN(p, v) atomicMin((p), (v))
 #define TK_RESTRICT __restrict__
 #define TK_SQRT(x) sqrt(x)
+#define TK_RSQRT(x) rsqrt(x)
 #define TK_DMMA(c0, c1, a, b) asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b))
 #endif
 
@@ -46,6 +48,9 @@ struct TreeArrays {                   // device pointers
     const int* a_src;
     const unsigned short* a_dst;
     const int* csc_map;               // out_mode 1: L-buffer offset of a panel entry -> index into Lx (CSC order), -1 for padding
+    const unsigned short* out_src;    // amalgamated groups (TW_GROUP): packed position in F of every true entry of L ...
+    const int* out_dst;               // ... and its index in the CSC values of L
+    const int* gcol;                  // ... global column of every column of a group (reporting a non-positive pivot)
 };
 
 constexpr int TK_F_SLACK = 8;         // doubles past tri(cap_m): fragment loads of edge tiles may read (never store) there
@@ -64,7 +69,7 @@ TK_DEVICE void tk_prefetch_range(const void* base, int64_t b0, int64_t b1, int t
 }
 
 // One task = fronts [front0, front0 + nfront) in postorder, factored by a team of NW warps (tid = 0 .. 32 NW - 1).
-// F: tri(cap_m) + TK_F_SLACK doubles, spiv: 2 doubles, both private to the team.
+// F: tri(cap_m) + TK_F_SLACK doubles, spiv: 2 doubles, sT: 64 doubles (inverse of a micro block), all private to the team.
 // out_mode 0: panels go to the L buffer; 1: entries go straight to Lx in CSC order through csc_map.
 //
 // Every front starts with a chain of dependent loads (descriptor -> index lists -> values); with four teams per SM there
@@ -74,7 +79,7 @@ TK_DEVICE void tk_prefetch_range(const void* base, int64_t b0, int64_t b1, int t
 template <int NW>
 TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const double* TK_RESTRICT Ax, double* TK_RESTRICT L,
                               double* TK_RESTRICT W, double* TK_RESTRICT Stash, double* TK_RESTRICT Lx, int* TK_RESTRICT info,
-                              double* F, double* spiv, int out_mode) {
+                              double* F, double* spiv, double* sT, int out_mode) {
     constexpr int NT = 32 * NW;
     constexpr int MC = 4;                                   // columns a warp moves per round of the in-place spread
     const int tid = TK_TID, lane = tid & 31, warp = tid >> 5;
@@ -145,70 +150,118 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
             }
         }
         TK_SYNCTEAM();
-        // ---- 4. the w pivot columns (reversed columns m-1 .. m-w), right-looking inside the panel
-        for (int k = 0; k < w; ++k) {
-            const int Kr = m - 1 - k;
-            double* colK = F + tk_tri(Kr);
-            if (warp == 0) {                               // IEEE sqrt and division, once per pivot
-                const double dd = colK[Kr];
-                if (dd <= 0.0 && lane == 0) TK_ATOMIC_MIN(info, d.first + k + 1);      // reference test (chol.hpp:849)
-                const double piv = TK_SQRT(dd);
-                TK_SYNCWARP();                             // every lane has read the pivot
-                if (lane == 0) { colK[Kr] = piv; spiv[0] = 1.0 / piv; }
-            }
-            TK_SYNCTEAM();
-            const double rinv = spiv[0];
-            for (int i = tid; i < Kr; i += NT) colK[i] *= rinv;
-            if (k + 1 < w) {
-                TK_SYNCTEAM();
-                for (int Jr = Kr - 1 - warp; Jr >= mb; Jr -= NW) {
-                    const double uj = colK[Jr];
-                    double* colJ = F + tk_tri(Jr);
-                    for (int i = lane; i <= Jr; i += 32) colJ[i] = fma(-colK[i], uj, colJ[i]);
-                }
-            }
-            TK_SYNCTEAM();
-        }
         if (ax_next >= 0) tk_prefetch_range(Ax, 8 * static_cast<int64_t>(ax_next), 8 * static_cast<int64_t>(ax_next) + 8, 0, 1);
-        // ---- 5. contribution block -= L21 L21^T on the FP64 tensor cores: 8 x 8 tiles (row block R <= column block C of
-        //         the reversed triangle), tile number C (C + 1) / 2 + R dealt round-robin to the warps; lane (g, tq) feeds
-        //         A[g][tq] = -L(8R + g, pivot tq) and B[tq][g] = L(8C + g, pivot tq) and owns C(8R + g, 8C + 2 tq), (.., + 1)
-        if (mb > 0) {
-            const int nblk = (mb + 7) >> 3;
-            const int pb0 = tk_tri(m - 1 - tq);            // the lane's pivot column of the first k-step
-            const bool k_on = tq < w;
-            int Cb = 0, R = warp;
-            while (R > Cb) { R -= Cb + 1; ++Cb; }
-            int Cb_cur = -1, c0 = 0, b0 = 0, b1 = 0;
-            double bf0 = 0.0;
-            while (Cb < nblk) {
-                if (Cb != Cb_cur) {
-                    Cb_cur = Cb;
-                    c0 = 8 * Cb + 2 * tq;
-                    b0 = tk_tri(c0); b1 = b0 + c0 + 1;
-                    bf0 = k_on ? F[pb0 + 8 * Cb + g] : 0.0;
+        // ---- 4. elimination of the w pivot columns, right-looking in micro-panels of 8 columns over the WHOLE front (the rest
+        //         of the panel and the contribution block alike).  Per micro-panel: (a) warp 0 factors the 8 x 8 diagonal block in
+        //         registers and inverts it, (b) one thread per row below multiplies the row by the inverse (no division, no
+        //         dependence between rows), (c) rank-8 update of everything behind it on the FP64 tensor cores: 8 x 8 tiles (row
+        //         block R <= column block C of the reversed triangle), tile number C (C + 1) / 2 + R dealt round-robin to the
+        //         warps; lane (g, tq) feeds A[g][k] = -L(8R + g, pivot k) and B[k][g] = L(8C + g, pivot k) for k = tq, 4 + tq and
+        //         owns C(8R + g, 8C + 2 tq) and C(8R + g, 8C + 2 tq + 1).  Three team barriers per 8 pivots.
+        for (int k0 = 0; k0 < w; k0 += 8) {
+            const int nk = w - k0 < 8 ? w - k0 : 8;
+            const int Kt = m - 1 - k0;                     // reversed index of the micro-panel's first pivot
+            const int mt = m - k0 - nk;                    // order of what remains behind the micro-panel
+            if (warp == 0) {
+                double l[8][8], rinv[8];
+#pragma unroll
+                for (int i = 0; i < 8; ++i)
+#pragma unroll
+                    for (int j = 0; j <= i; ++j) l[i][j] = (i < nk && j < nk) ? F[tk_tri(Kt - j) + (Kt - i)] : (i == j ? 1.0 : 0.0);
+#pragma unroll
+                for (int k = 0; k < 8; ++k) {
+                    const double dd = l[k][k];
+                    if (dd <= 0.0 && lane == 0 && k < nk)      // reference test (chol.hpp:849)
+                        TK_ATOMIC_MIN(info, ((d.flags & TW_GROUP) ? TK_LDG(ta.gcol + d.ld + k0 + k) : d.first + k0 + k) + 1);
+                    const double piv = TK_SQRT(dd);            // IEEE square root: the diagonal of L as the reference stores it
+                    double y = TK_RSQRT(dd);                   // 1 / piv: reciprocal square root seed, two Newton steps against piv
+                    y = fma(fma(-piv, y, 1.0), y, y);
+                    y = fma(fma(-piv, y, 1.0), y, y);
+                    rinv[k] = y;
+                    l[k][k] = piv;
+#pragma unroll
+                    for (int i = k + 1; i < 8; ++i) l[i][k] *= y;
+#pragma unroll
+                    for (int j = k + 1; j < 8; ++j)
+#pragma unroll
+                        for (int i = j; i < 8; ++i) l[i][j] = fma(-l[i][k], l[j][k], l[i][j]);
                 }
-                const int ir = 8 * R + g;
-                const bool on0 = ir <= c0 && c0 < mb, on1 = ir <= c0 + 1 && c0 + 1 < mb;      // entries of the tile inside the triangle
-                double acc0 = on0 ? F[b0 + ir] : 0.0, acc1 = on1 ? F[b1 + ir] : 0.0;
-                {
-                    const double a = k_on ? -F[pb0 + ir] : 0.0;
-                    TK_DMMA(acc0, acc1, a, bf0);
+                TK_SYNCWARP();                                 // every lane has read the block before it is overwritten
+                // column j of the inverse: L t = e_j; lane j (< 8) computes and stores it, and writes row j of the factor
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    double tcol[8];
+#pragma unroll
+                    for (int i = 0; i < 8; ++i) {
+                        if (i < j) { tcol[i] = 0.0; continue; }
+                        double acc = (i == j) ? 1.0 : 0.0;
+#pragma unroll
+                        for (int k = j; k < i; ++k) acc = fma(-l[i][k], tcol[k], acc);
+                        tcol[i] = acc * rinv[i];
+                    }
+                    if (lane == j) {
+#pragma unroll
+                        for (int i = 0; i < 8; ++i) sT[i * 8 + j] = tcol[i];
+#pragma unroll
+                        for (int c = 0; c <= j; ++c) if (j < nk) F[tk_tri(Kt - c) + (Kt - j)] = l[j][c];
+                    }
                 }
-                for (int k0 = 4; k0 < w; k0 += 4) {
-                    const int kk = k0 + tq;
-                    double a = 0.0, b = 0.0;
-                    if (kk < w) { const double* pc = F + tk_tri(m - 1 - kk); a = -pc[ir]; b = pc[8 * Cb + g]; }
-                    TK_DMMA(acc0, acc1, a, b);
-                }
-                if (on0) F[b0 + ir] = acc0;
-                if (on1) F[b1 + ir] = acc1;
-                R += NW;
-                while (R > Cb) { R -= Cb + 1; ++Cb; }
             }
+            TK_SYNCTEAM();
+            for (int ir = tid; ir < mt; ir += NT) {            // (b) x <- x T^T, one row per thread
+                double x[8], yv[8];
+#pragma unroll
+                for (int q = 0; q < 8; ++q) x[q] = q < nk ? F[tk_tri(Kt - q) + ir] : 0.0;
+#pragma unroll
+                for (int j = 0; j < 8; ++j) {
+                    double acc = 0.0;
+#pragma unroll
+                    for (int q = 0; q <= j; ++q) acc = fma(x[q], sT[j * 8 + q], acc);
+                    yv[j] = acc;
+                }
+#pragma unroll
+                for (int q = 0; q < 8; ++q) if (q < nk) F[tk_tri(Kt - q) + ir] = yv[q];
+            }
+            TK_SYNCTEAM();
+            if (mt > 0) {                                      // (c)
+                const int nblk = (mt + 7) >> 3;
+                const int pbA = tk_tri(Kt - tq), pbB = tk_tri(Kt - 4 - tq);      // the lane's pivot columns of the two k-steps
+                const bool onA = tq < nk, onB = 4 + tq < nk;
+                int Cb = 0, R = warp;
+                while (R > Cb) { R -= Cb + 1; ++Cb; }
+                int Cb_cur = -1, c0 = 0, b0 = 0, b1 = 0;
+                double bfA = 0.0, bfB = 0.0;
+                while (Cb < nblk) {
+                    if (Cb != Cb_cur) {
+                        Cb_cur = Cb;
+                        c0 = 8 * Cb + 2 * tq;
+                        b0 = tk_tri(c0); b1 = b0 + c0 + 1;
+                        bfA = onA ? F[pbA + 8 * Cb + g] : 0.0;
+                        bfB = onB ? F[pbB + 8 * Cb + g] : 0.0;
+                    }
+                    const int ir = 8 * R + g;
+                    const bool on0 = ir <= c0 && c0 < mt, on1 = ir <= c0 + 1 && c0 + 1 < mt;      // entries of the tile inside the triangle
+                    double acc0 = on0 ? F[b0 + ir] : 0.0, acc1 = on1 ? F[b1 + ir] : 0.0;
+                    const double aA = onA ? -F[pbA + ir] : 0.0;
+                    TK_DMMA(acc0, acc1, aA, bfA);
+                    if (nk > 4) {
+                        const double aB = onB ? -F[pbB + ir] : 0.0;
+                        TK_DMMA(acc0, acc1, aB, bfB);
+                    }
+                    if (on0) F[b0 + ir] = acc0;
+                    if (on1) F[b1 + ir] = acc1;
+                    R += NW;
+                    while (R > Cb) { R -= Cb + 1; ++Cb; }
+                }
+            }
+            TK_SYNCTEAM();
         }
-        TK_SYNCTEAM();
         // ---- 6. the factored columns leave the SM (columns dealt to the warps)
+        if (d.flags & TW_GROUP) {
+            // an amalgamated group of fronts (batched whole-tree program): the TRUE entries of its columns by list,
+            // (packed position in F, index in the CSC values of L); the explicit zeros of the amalgamation are skipped
+            for (int e = tid; e < d.pad1; e += NT) Lx[TK_LDG(ta.out_dst + d.pad0 + e)] = F[TK_LDG(ta.out_src + d.pad0 + e)];
+        } else
         for (int c = warp; c < w; c += NW) {
             const int Jr = m - 1 - c;
             const double* col = F + tk_tri(Jr);
@@ -241,23 +294,24 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
 }
 
 #ifndef SPCHOL_HOST_EMU
-// One CTA = one team of NW warps.  Dynamic shared memory = (f_stride + 2) doubles.
+// One CTA = one team of NW warps.  Dynamic shared memory = (f_stride + 2 + 64) doubles.
 // nmat > 0 (batched): team b factors matrix b with task 0, all pointers advance by their per-matrix strides;
 // nmat == 0: team b runs task b of a single matrix.
 template <int NW>
-__global__ void __launch_bounds__(32 * NW) k_tree_team(TreeArrays ta, const double* __restrict__ Ax, double* __restrict__ L,
+__global__ void __launch_bounds__(32 * NW, 16 / NW) k_tree_team(TreeArrays ta, const double* __restrict__ Ax, double* __restrict__ L,
                                                       double* __restrict__ W, double* __restrict__ Stash, double* __restrict__ Lx,
                                                       int* __restrict__ info, int64_t ax_stride, int64_t l_stride, int64_t w_stride,
                                                       int64_t s_stride, int64_t lx_stride, int nmat, int f_stride, int out_mode) {
     extern __shared__ double tk_smem[];
     double* F = tk_smem;
     double* spiv = tk_smem + f_stride;
+    double* sT = spiv + 2;
     const int64_t b = blockIdx.x;
     if (nmat > 0)
         tree_team_body<NW>(ta, ta.tasks[0], Ax + b * ax_stride, L + b * l_stride, W + b * w_stride, Stash + b * s_stride, Lx + b * lx_stride,
-                           info + b, F, spiv, out_mode);
+                           info + b, F, spiv, sT, out_mode);
     else
-        tree_team_body<NW>(ta, ta.tasks[b], Ax, L, W, Stash, Lx, info, F, spiv, out_mode);
+        tree_team_body<NW>(ta, ta.tasks[b], Ax, L, W, Stash, Lx, info, F, spiv, sT, out_mode);
 }
 #endif
 

@@ -197,4 +197,124 @@ void build_tree_program(const HostPlan& P, const std::vector<int>& roots_in, boo
     (void)even_up;
 }
 
+void build_group_program(const HostPlan& P, int cap_m, const std::vector<int>& a_front, const std::vector<int>& a_col,
+                         const std::vector<int>& a_pos, TreeProgram& out) {
+    const int ns = P.ns;
+    cap_m = std::min(cap_m, TW_MAX_M);
+    if (P.l_src.empty() && P.nnzL > 0) throw std::runtime_error("spchol: the group program needs the CSC export map");
+    // ---- 1. grouping, bottom-up: a front absorbs the groups of its children (largest block first) while |U| <= cap_m
+    std::vector<int> gw(ns), top(ns);                 // columns of the group whose top is s; group top of every front
+    std::vector<std::vector<int>> members(ns);
+    for (int s = 0; s < ns; ++s) { gw[s] = P.w[s]; top[s] = s; members[s].push_back(s); }
+    std::vector<int> kids;
+    for (int p = 0; p < ns; ++p) {
+        if (P.m[p] > cap_m) throw std::runtime_error("spchol: front too large for the group program");
+        kids.assign(P.child_idx.begin() + P.child_ptr[p], P.child_idx.begin() + P.child_ptr[p + 1]);
+        std::stable_sort(kids.begin(), kids.end(), [&](int a, int b) { return (P.m[a] - P.w[a]) > (P.m[b] - P.w[b]); });
+        for (int c : kids) {
+            if (gw[p] + gw[c] + (P.m[p] - P.w[p]) > cap_m) continue;
+            gw[p] += gw[c];
+            members[p].insert(members[p].end(), members[c].begin(), members[c].end());
+            std::vector<int>().swap(members[c]);
+        }
+    }
+    std::vector<int> gid(ns, -1), tops;
+    for (int s = 0; s < ns; ++s) if (!members[s].empty()) {
+        std::sort(members[s].begin(), members[s].end(), [&](int a, int b) { return P.first[a] < P.first[b]; });      // elimination order
+        for (int q : members[s]) { top[q] = s; gid[q] = static_cast<int>(tops.size()); }
+        tops.push_back(s);
+    }
+    const int ng = static_cast<int>(tops.size());
+    // ---- 2. position in U of every row of every member front (columns: members in elimination order; then the top's below rows)
+    std::vector<int> colbase(ns, 0);
+    std::vector<int64_t> pos_off(ns + 1, 0);
+    for (int s = 0; s < ns; ++s) pos_off[s + 1] = pos_off[s] + P.m[s];
+    std::vector<int> posU(static_cast<size_t>(pos_off[ns]));
+    for (int g = 0; g < ng; ++g) {
+        const int t = tops[g];
+        int cb = 0;
+        for (int q : members[t]) { colbase[q] = cb; cb += P.w[q]; }
+        // members top-down (parents before children): descending id works, children have smaller ids
+        std::vector<int> ord(members[t]);
+        std::sort(ord.begin(), ord.end(), std::greater<int>());
+        for (int q : ord) {
+            int* pq = posU.data() + pos_off[q];
+            for (int c = 0; c < P.w[q]; ++c) pq[c] = colbase[q] + c;
+            const int nb = P.m[q] - P.w[q];
+            if (q == t) { for (int i = 0; i < nb; ++i) pq[P.w[q] + i] = gw[t] + i; continue; }
+            const int par = P.parent[q];
+            const int* r = P.rel.data() + P.rel_off[q];
+            const int* pp = posU.data() + pos_off[par];
+            for (int i = 0; i < nb; ++i) pq[P.w[q] + i] = pp[r[i]];
+        }
+    }
+    // ---- 3. the groups as the fronts of a virtual plan (only the fields the program builder reads)
+    HostPlan V;
+    V.ns = ng; V.n = P.n; V.rank = 0; V.world = 1;
+    V.w.resize(ng); V.m.resize(ng); V.ld.assign(ng, 0); V.first.resize(ng); V.parent.assign(ng, -1);
+    V.panel_off.assign(ng, 0); V.cb_off.assign(ng, -1); V.own_lo.assign(ng, 0); V.own_n.assign(ng, 1); V.own_idx.assign(ng, 0);
+    V.rel_off.assign(ng + 1, 0);
+    for (int g = 0; g < ng; ++g) {
+        const int t = tops[g];
+        V.w[g] = gw[t]; V.m[g] = gw[t] + (P.m[t] - P.w[t]); V.first[g] = g;      // `first` carries the group id through the builder
+        V.parent[g] = P.parent[t] >= 0 ? gid[P.parent[t]] : -1;
+        V.rel_off[g + 1] = V.rel_off[g] + (P.m[t] - P.w[t]);
+        out.padded_flops += front_flops(V.w[g], V.m[g]);
+    }
+    V.rel.resize(static_cast<size_t>(V.rel_off[ng]));
+    for (int g = 0; g < ng; ++g) {
+        const int t = tops[g], par = P.parent[t];
+        if (par < 0) continue;
+        const int nb = P.m[t] - P.w[t];
+        const int* r = P.rel.data() + P.rel_off[t];
+        const int* pp = posU.data() + pos_off[par];
+        for (int i = 0; i < nb; ++i) V.rel[V.rel_off[g] + i] = pp[r[i]];
+        // the rows below a group's top must come out ascending in the parent group for the in-place spread (monotone map)
+        for (int i = 1; i < nb; ++i) if (V.rel[V.rel_off[g] + i] <= V.rel[V.rel_off[g] + i - 1]) throw std::runtime_error("spchol: group map is not monotone");
+    }
+    V.child_ptr.assign(ng + 1, 0);
+    for (int g = 0; g < ng; ++g) if (V.parent[g] >= 0) ++V.child_ptr[V.parent[g] + 1];
+    for (int g = 0; g < ng; ++g) V.child_ptr[g + 1] += V.child_ptr[g];
+    V.child_idx.resize(V.child_ptr[ng]);
+    { std::vector<int> cur(V.child_ptr.begin(), V.child_ptr.end() - 1);
+      for (int g = 0; g < ng; ++g) if (V.parent[g] >= 0) V.child_idx[cur[V.parent[g]]++] = g; }
+    std::vector<int> af(a_front.size()), ac(a_front.size()), ap(a_front.size());
+    for (size_t e = 0; e < a_front.size(); ++e) {
+        const int s = a_front[e];
+        af[e] = gid[s]; ac[e] = colbase[s] + a_col[e]; ap[e] = posU[pos_off[s] + a_pos[e]];
+    }
+    build_tree_program(V, {}, true, af, ac, ap, out);
+    // ---- 4. output lists (true entries of L only) and the columns' global indices, attached to the emitted fronts
+    std::vector<std::pair<int64_t, int>> pan;
+    for (int s = 0; s < ns; ++s) pan.push_back({P.panel_off[s], s});
+    std::sort(pan.begin(), pan.end());
+    std::vector<std::vector<std::pair<unsigned short, int>>> lists(ng);
+    for (int64_t e = 0; e < P.nnzL; ++e) {
+        const int64_t off = P.l_src[e];
+        if (off < 0) throw std::runtime_error("spchol: export map hole in a single-rank plan");
+        const int s = std::prev(std::upper_bound(pan.begin(), pan.end(), std::make_pair(off, ns)))->second;
+        const int64_t rel = off - P.panel_off[s];
+        const int c = static_cast<int>(rel / P.ld[s]), t = static_cast<int>(rel % P.ld[s]);
+        const int g = gid[s], mg = V.m[g];
+        const int jr = mg - 1 - (colbase[s] + c), ir = mg - 1 - posU[pos_off[s] + t];
+        lists[g].push_back({static_cast<unsigned short>(tri64(jr) + ir), static_cast<int>(e)});
+    }
+    std::vector<int> gcol0(ng), out0(ng);
+    for (int g = 0; g < ng; ++g) {
+        gcol0[g] = static_cast<int>(out.gcol.size());
+        for (int q : members[tops[g]]) for (int c = 0; c < P.w[q]; ++c) out.gcol.push_back(P.first[q] + c);
+        out0[g] = static_cast<int>(out.out_src.size());
+        for (const auto& pr : lists[g]) { out.out_src.push_back(pr.first); out.out_dst.push_back(pr.second); }
+    }
+    for (TwFront& d : out.fronts) {
+        const int g = d.first;
+        d.flags |= TW_GROUP;
+        d.ld = gcol0[g]; d.pad0 = out0[g]; d.pad1 = static_cast<int>(lists[g].size());
+    }
+    out.n_groups = ng;
+    out.in_tree.assign(ns, 1);
+    out.flops = 0;
+    for (int s = 0; s < ns; ++s) out.flops += front_flops(P.w[s], P.m[s]);
+}
+
 }  // namespace spchol

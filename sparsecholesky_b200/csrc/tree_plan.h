@@ -26,7 +26,9 @@ struct HostPlan;
 constexpr int TW_MAX_M = 128;                 // rows of the largest front a program may hold (static position map)
 enum : int { TW_CARRY_IN = 1,                 // the front's first child left its block in shared memory
              TW_CARRY_OUT = 2,                // this front's block stays in shared memory for the next front (its parent)
-             TW_CB_STD = 4 };                 // block goes to the level program's workspace slot (column-major, ld = even(mb))
+             TW_CB_STD = 4,                   // block goes to the level program's workspace slot (column-major, ld = even(mb))
+             TW_GROUP = 8 };                  // an amalgamated group of fronts (batched whole-tree program): columns are not one
+                                              // contiguous range -- `ld` indexes gcol[], (pad0, pad1) = (first, count) of its output list
 
 struct alignas(16) TwFront {                  // 80 bytes; the kernel keeps two descriptors ahead in registers
     int w, m, ld, first;                      // columns, rows, leading dimension of the panel in the L buffer, first global column
@@ -50,6 +52,11 @@ struct TreeProgram {
     std::vector<int> rmap;                    // maps in reversed indices: forward (child row -> parent row) for stashed blocks, inverse for carried ones
     std::vector<int> a_src;                   // index into Ax
     std::vector<unsigned short> a_dst;        // packed reversed index inside the front
+    std::vector<unsigned short> out_src;      // groups: packed position in F of every TRUE entry of L of the group's columns ...
+    std::vector<int> out_dst;                 // ... and its index in the CSC values of L (ascending per group)
+    std::vector<int> gcol;                    // groups: global column of every column of a group
+    int n_groups = 0;                         // 0: the fronts of the program are the fronts of the plan
+    double padded_flops = 0;                  // groups: dense flops including the explicit zeros of the amalgamation
     std::vector<char> in_tree;                // per front of the plan: 1 if a task of this program factors it
     double flops = 0;                         // dense flops of the fronts covered
     int64_t n_fronts() const { return static_cast<int64_t>(fronts.size()); }
@@ -67,5 +74,15 @@ std::vector<int> choose_subtrees(const HostPlan& P, int cap_m, double work_limit
 // P.cb_off (the level program consumes them).
 void build_tree_program(const HostPlan& P, const std::vector<int>& roots, bool whole, const std::vector<int>& a_front,
                         const std::vector<int>& a_col, const std::vector<int>& a_pos, TreeProgram& out);
+
+// The batched whole-tree program over AMALGAMATED GROUPS: a group is a connected piece of the assembly tree (a top front
+// plus descendants, grown bottom-up while its row set U = columns of the members ++ rows below the top stays within cap_m
+// rows) that is factored as ONE dense front over U.  Entries of U x U outside the members' true fronts are explicit zeros
+// and stay exact zeros through the elimination (no true entry of L depends on them), so the factor is the same; what is
+// bought with the extra flops -- cheap on the tensor cores -- is a program of ~50 big regular steps instead of ~500 small
+// ones (1138_bus: 529 fronts -> 52 groups at 117 rows, 2.6x the flops).  Needs P.l_src (the CSC export map): the TRUE
+// entries of every group leave through an explicit (position in F, CSC index) list.
+void build_group_program(const HostPlan& P, int cap_m, const std::vector<int>& a_front, const std::vector<int>& a_col,
+                         const std::vector<int>& a_pos, TreeProgram& out);
 
 }  // namespace spchol

@@ -98,6 +98,7 @@ static void run_tasks(const TreeArrays& ta, const double* Ax, double* Lb, double
     const double nan = std::numeric_limits<double>::quiet_NaN();
     std::vector<double> F(static_cast<size_t>(cap_m) * (cap_m + 1) / 2 + TK_F_SLACK, nan);
     double spiv[2] = {nan, nan};
+    std::vector<double> sT(64, nan);
     std::barrier<> team(32 * NW);
     emu::g_team = &team;
     std::vector<std::unique_ptr<std::barrier<>>> wb;
@@ -108,7 +109,7 @@ static void run_tasks(const TreeArrays& ta, const double* Ax, double* Lb, double
         th.emplace_back([&, t] {
             emu::t_tid = t;
             for (int q = 0; q < ta.ntasks; ++q) {
-                tree_team_body<NW>(ta, ta.tasks[q], Ax, Lb, Wb, Sb, Lx, info, F.data(), spiv, mode);
+                tree_team_body<NW>(ta, ta.tasks[q], Ax, Lb, Wb, Sb, Lx, info, F.data(), spiv, sT.data(), mode);
                 emu::sync();
             }
         });
@@ -116,6 +117,7 @@ static void run_tasks(const TreeArrays& ta, const double* Ax, double* Lb, double
     emu::g_team = nullptr;
 }
 
+// whole = 2: the whole-tree program over amalgamated groups of up to cap_m rows (build_group_program), else as whole = 1
 extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double* Ax, int relax, int whole, int cap_m, double work, int nw,
                               double* Lx, int* info_out, int64_t* stats, char* err, int errlen) {
     auto fail = [&](const std::string& msg) { std::snprintf(err, errlen, "%s", msg.c_str()); return -1; };
@@ -127,6 +129,7 @@ extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double*
         PlanOptions opt;
         opt.small_max_m = 1 << 20;          // everything above the subtrees on the whole-front path
         opt.tree = 1; opt.tree_cap_m = cap_m; opt.tree_work = work;
+        opt.batch_group_m = whole == 2 ? cap_m : 0;
         build_plan(S, opt, H);
         if (H.n_large > 0) return fail("pattern has fronts beyond the shared-memory front kernel");
         const TreeProgram& T = whole ? H.tree_whole : H.tree;
@@ -134,6 +137,7 @@ extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double*
         if (stats) {
             stats[0] = static_cast<int64_t>(T.tasks.size()); stats[1] = static_cast<int64_t>(T.fronts.size());
             stats[2] = static_cast<int64_t>(T.stashes.size()); stats[3] = T.stash_entries; stats[4] = T.cap_m; stats[5] = H.ns;
+            stats[6] = T.n_groups; stats[7] = static_cast<int64_t>(T.padded_flops);
         }
         const double nan = std::numeric_limits<double>::quiet_NaN();
         std::vector<double> Lb(static_cast<size_t>(H.lbuf_entries), 0.0);
@@ -152,6 +156,7 @@ extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double*
             TreeArrays ta{};
             ta.tasks = T.tasks.data(); ta.ntasks = static_cast<int>(T.tasks.size()); ta.fronts = T.fronts.data(); ta.stashes = T.stashes.data();
             ta.rmap = T.rmap.data(); ta.a_src = T.a_src.data(); ta.a_dst = T.a_dst.data(); ta.csc_map = csc_map.data();
+            ta.out_src = T.out_src.data(); ta.out_dst = T.out_dst.data(); ta.gcol = T.gcol.data();
             switch (nw) {
             case 1: run_tasks<1>(ta, Ax, Lb.data(), Wb.data(), Sb.data(), Lx, &info, T.cap_m, whole ? 1 : 0); break;
             case 2: run_tasks<2>(ta, Ax, Lb.data(), Wb.data(), Sb.data(), Lx, &info, T.cap_m, whole ? 1 : 0); break;

@@ -41,12 +41,12 @@ def run(L, A, whole, relax=1, cap_m=117, work=2.5e6, nw=1):
     S = sc.schol(A, relax=relax)
     Lx = np.empty(S.nnz)
     info = C.c_int(0)
-    st = np.zeros(6, np.int64)
+    st = np.zeros(8, np.int64)
     err = C.create_string_buffer(2048)
     rc = L.treeemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, relax, int(whole), cap_m, work, nw,
                           Lx.ctypes.data, C.byref(info), st.ctypes.data, err, 2048)
     assert rc == 0, err.value.decode()
-    return Lx, info.value, dict(zip(["tasks", "fronts", "stashes", "stash_doubles", "cap_m", "ns"], (int(v) for v in st)))
+    return Lx, info.value, dict(zip(["tasks", "fronts", "stashes", "stash_doubles", "cap_m", "ns", "groups", "padded_flops"], (int(v) for v in st)))
 
 
 def golden(name):
@@ -66,6 +66,20 @@ def test_whole_tree_vs_reference_golden(emu, name, relax, nw):
     Lx, info, st = run(emu, A, whole=True, relax=relax, nw=nw)
     assert info == 0 and relerr(Lx, ref) <= 1e-10
     assert st["tasks"] == 1 and st["fronts"] == st["ns"]
+
+
+@pytest.mark.parametrize("name", ["test3", "bcsstk01", "1138_bus", "lap2d_24", "lap2d_7x5"])
+@pytest.mark.parametrize("cap_m,nw", [(117, 4), (128, 1), (64, 2), (0, 4)])
+def test_group_program_vs_reference_golden(emu, name, cap_m, nw):
+    # the batched program over amalgamated groups: fewer, bigger dense steps with explicit zeros that must stay exact zeros
+    A, ref = golden(name)
+    S = sc.schol(A)
+    cap = max(cap_m, S.stats()["max_m"])            # (cap 0: every front its own group)
+    Lx, info, st = run(emu, A, whole=2, cap_m=cap, nw=nw)
+    assert info == 0 and relerr(Lx, ref) <= 1e-10
+    assert st["tasks"] == 1 and 1 <= st["groups"] <= st["ns"] and st["fronts"] == st["groups"]
+    if name == "1138_bus" and cap_m == 117:
+        assert st["groups"] <= 60                    # 529 fronts -> ~52 groups
 
 
 @pytest.mark.parametrize("name", ["bcsstk01", "1138_bus", "lap2d_24", "lap3d_10"])
@@ -98,6 +112,8 @@ def test_not_positive_definite_column_is_reported(emu):
     rc, _, _, _ = po.chol(B.n, B.p, B.i, B.x)
     _, info, _ = run(emu, B, whole=True, nw=4)
     assert rc > 0 and info == rc               # same 1-based column as the oracle (reference test chol.hpp:849)
+    _, info, _ = run(emu, B, whole=2, nw=4)    # ... also through the column table of an amalgamated group
+    assert info == rc
 
 
 def test_thread_sanitizer_finds_no_race():
@@ -111,8 +127,8 @@ def test_thread_sanitizer_finds_no_race():
         "A = sc.CscMatrix(int(g['n']), g['Ap'], g['Ai'], g['Ax'])\n"
         f"L = C.CDLL({so!r})\n"
         "L.treeemu_factor.argtypes = [C.c_int, C.c_void_p, C.c_void_p, C.c_void_p, C.c_int, C.c_int, C.c_int, C.c_double, C.c_int, C.c_void_p, C.POINTER(C.c_int), C.c_void_p, C.c_char_p, C.c_int]\n"
-        "for whole, cap, work, nw in ((1, 117, 2.5e6, 4), (0, 16, 1e3, 2), (1, 117, 2.5e6, 1)):\n"
-        "    Lx = np.empty(len(g['Lx'])); info = C.c_int(0); st = np.zeros(6, np.int64); err = C.create_string_buffer(512)\n"
+        "for whole, cap, work, nw in ((2, 117, 2.5e6, 4), (1, 117, 2.5e6, 4), (0, 16, 1e3, 2), (1, 117, 2.5e6, 1)):\n"
+        "    Lx = np.empty(len(g['Lx'])); info = C.c_int(0); st = np.zeros(8, np.int64); err = C.create_string_buffer(512)\n"
         "    rc = L.treeemu_factor(A.n, A.p.ctypes.data, A.i.ctypes.data, A.x.ctypes.data, 1, whole, cap, work, nw, Lx.ctypes.data, C.byref(info), st.ctypes.data, err, 512)\n"
         "    assert rc == 0, err.value\n"
         "    assert np.abs(Lx - g['Lx']).max() <= 1e-10 * np.abs(g['Lx']).max()\n"
