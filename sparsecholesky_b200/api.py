@@ -311,6 +311,8 @@ def chol(A, S=None, device=0):
     non-positive pivot is the reference's "A is not positive definite." (chol.hpp:850)."""
     if S is None:
         S = schol(A)
+    if A.n != S.n or A.capacity() != int(lib().spchol_symbolic_nnzA(S._sym.h)):
+        return Expected(error="chol: A does not have the pattern S was built from")
     plan = S.plan(device)
     Lx = np.empty(S.nnz, np.float64)
     info = C.c_int(0)

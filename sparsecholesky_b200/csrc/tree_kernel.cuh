@@ -155,30 +155,40 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
         //         of the panel and the contribution block alike).  Per micro-panel: (a) warp 0 factors the 8 x 8 diagonal block in
         //         registers and inverts it, (b) one thread per row below multiplies the row by the inverse (no division, no
         //         dependence between rows), (c) rank-8 update of everything behind it on the FP64 tensor cores: 8 x 8 tiles (row
-        //         block R <= column block C of the reversed triangle), tile number C (C + 1) / 2 + R dealt round-robin to the
-        //         warps; lane (g, tq) feeds A[g][k] = -L(8R + g, pivot k) and B[k][g] = L(8C + g, pivot k) for k = tq, 4 + tq and
-        //         owns C(8R + g, 8C + 2 tq) and C(8R + g, 8C + 2 tq + 1).  Three team barriers per 8 pivots.
-        for (int k0 = 0; k0 < w; k0 += 8) {
-            const int nk = w - k0 < 8 ? w - k0 : 8;
-            const int Kt = m - 1 - k0;                     // reversed index of the micro-panel's first pivot
-            const int mt = m - k0 - nk;                    // order of what remains behind the micro-panel
-            if (warp == 0) {
-                double l[8][8], rinv[8];
+        //         block R <= column block C of the reversed triangle) dealt round-robin to the warps; lane (g, tq) feeds
+        //         A[g][k] = -L(8R + g, pivot k) and B[k][g] = L(8C + g, pivot k) for k = tq, 4 + tq and owns C(8R + g, 8C + 2 tq)
+        //         and C(8R + g, 8C + 2 tq + 1).  Look-ahead: the tiles that hold the NEXT micro-panel's columns go first (all
+        //         warps), then warp 0 factors that micro-panel while the other warps finish the update -- the serial 8-pivot chain
+        //         hides behind tensor-core work.  Three team barriers per 8 pivots.
+        auto micro_factor = [&](int k0, int nk) {              // warp 0 only
+            const int Kt = m - 1 - k0;
+            double l[8][8], rinv[8];
 #pragma unroll
-                for (int i = 0; i < 8; ++i)
+            for (int i = 0; i < 8; ++i)
 #pragma unroll
-                    for (int j = 0; j <= i; ++j) l[i][j] = (i < nk && j < nk) ? F[tk_tri(Kt - j) + (Kt - i)] : (i == j ? 1.0 : 0.0);
+                for (int j = 0; j <= i; ++j) l[i][j] = (i < nk && j < nk) ? F[tk_tri(Kt - j) + (Kt - i)] : (i == j ? 1.0 : 0.0);
 #pragma unroll
-                for (int k = 0; k < 8; ++k) {
+            for (int k = 0; k < 8; ++k) {
+                rinv[k] = 1.0;
+                if (k < nk) {
                     const double dd = l[k][k];
-                    if (dd <= 0.0 && lane == 0 && k < nk)      // reference test (chol.hpp:849)
+                    if (dd <= 0.0 && lane == 0)                // reference test (chol.hpp:849)
                         TK_ATOMIC_MIN(info, ((d.flags & TW_GROUP) ? TK_LDG(ta.gcol + d.ld + k0 + k) : d.first + k0 + k) + 1);
-                    const double piv = TK_SQRT(dd);            // IEEE square root: the diagonal of L as the reference stores it
-                    double y = TK_RSQRT(dd);                   // 1 / piv: reciprocal square root seed, two Newton steps against piv
-                    y = fma(fma(-piv, y, 1.0), y, y);
-                    y = fma(fma(-piv, y, 1.0), y, y);
+                    // sqrt(d) and 1/sqrt(d) together (Goldschmidt from the reciprocal-square-root seed, then one residual
+                    // correction each): the square root comes out correctly rounded except for rare last-bit cases, the
+                    // reciprocal within one ulp -- six dependent FMAs instead of a software sqrt followed by a division
+                    double y = TK_RSQRT(dd);
+                    double gq = dd * y, hq = 0.5 * y;
+                    double r = fma(-gq, hq, 0.5);
+                    gq = fma(gq, r, gq); hq = fma(hq, r, hq);
+                    r = fma(-gq, hq, 0.5);
+                    gq = fma(gq, r, gq); hq = fma(hq, r, hq);
+                    const double piv = fma(fma(-gq, gq, dd), hq, gq);          // g + (d - g^2) / (2 g)
+                    y = hq + hq;
+                    y = fma(fma(-piv, y, 1.0), y, y);                          // 1 / piv
+                    if (!(dd > 0.0)) { y = 1.0 / TK_SQRT(dd); }                // non-positive pivot: the reference's sqrt / division semantics (NaN / inf)
                     rinv[k] = y;
-                    l[k][k] = piv;
+                    l[k][k] = (dd > 0.0) ? piv : TK_SQRT(dd);
 #pragma unroll
                     for (int i = k + 1; i < 8; ++i) l[i][k] *= y;
 #pragma unroll
@@ -186,29 +196,31 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
 #pragma unroll
                         for (int i = j; i < 8; ++i) l[i][j] = fma(-l[i][k], l[j][k], l[i][j]);
                 }
-                TK_SYNCWARP();                                 // every lane has read the block before it is overwritten
-                // column j of the inverse: L t = e_j; lane j (< 8) computes and stores it, and writes row j of the factor
+            }
+            TK_SYNCWARP();                                     // every lane has read the block before it is overwritten
+            // column j of the inverse: L t = e_j; lane j (< 8) computes and stores it, and writes row j of the factor
 #pragma unroll
-                for (int j = 0; j < 8; ++j) {
-                    double tcol[8];
+            for (int j = 0; j < 8; ++j) {
+                double tcol[8];
 #pragma unroll
-                    for (int i = 0; i < 8; ++i) {
-                        if (i < j) { tcol[i] = 0.0; continue; }
-                        double acc = (i == j) ? 1.0 : 0.0;
+                for (int i = 0; i < 8; ++i) {
+                    if (i < j) { tcol[i] = 0.0; continue; }
+                    double acc = (i == j) ? 1.0 : 0.0;
 #pragma unroll
-                        for (int k = j; k < i; ++k) acc = fma(-l[i][k], tcol[k], acc);
-                        tcol[i] = acc * rinv[i];
-                    }
-                    if (lane == j) {
+                    for (int k = j; k < i; ++k) acc = fma(-l[i][k], tcol[k], acc);
+                    tcol[i] = acc * rinv[i];
+                }
+                if (lane == j) {
 #pragma unroll
-                        for (int i = 0; i < 8; ++i) sT[i * 8 + j] = tcol[i];
+                    for (int i = 0; i < 8; ++i) sT[i * 8 + j] = tcol[i];
 #pragma unroll
-                        for (int c = 0; c <= j; ++c) if (j < nk) F[tk_tri(Kt - c) + (Kt - j)] = l[j][c];
-                    }
+                    for (int c = 0; c <= j; ++c) if (j < nk) F[tk_tri(Kt - c) + (Kt - j)] = l[j][c];
                 }
             }
-            TK_SYNCTEAM();
-            for (int ir = tid; ir < mt; ir += NT) {            // (b) x <- x T^T, one row per thread
+        };
+        auto rows_below = [&](int k0, int nk) {                // x <- x T^T, one row per thread
+            const int Kt = m - 1 - k0, mt = m - k0 - nk;
+            for (int ir = tid; ir < mt; ir += NT) {
                 double x[8], yv[8];
 #pragma unroll
                 for (int q = 0; q < 8; ++q) x[q] = q < nk ? F[tk_tri(Kt - q) + ir] : 0.0;
@@ -222,37 +234,62 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
 #pragma unroll
                 for (int q = 0; q < 8; ++q) if (q < nk) F[tk_tri(Kt - q) + ir] = yv[q];
             }
-            TK_SYNCTEAM();
-            if (mt > 0) {                                      // (c)
-                const int nblk = (mt + 7) >> 3;
-                const int pbA = tk_tri(Kt - tq), pbB = tk_tri(Kt - 4 - tq);      // the lane's pivot columns of the two k-steps
-                const bool onA = tq < nk, onB = 4 + tq < nk;
-                int Cb = 0, R = warp;
-                while (R > Cb) { R -= Cb + 1; ++Cb; }
-                int Cb_cur = -1, c0 = 0, b0 = 0, b1 = 0;
-                double bfA = 0.0, bfB = 0.0;
-                while (Cb < nblk) {
-                    if (Cb != Cb_cur) {
-                        Cb_cur = Cb;
-                        c0 = 8 * Cb + 2 * tq;
-                        b0 = tk_tri(c0); b1 = b0 + c0 + 1;
-                        bfA = onA ? F[pbA + 8 * Cb + g] : 0.0;
-                        bfB = onB ? F[pbB + 8 * Cb + g] : 0.0;
-                    }
-                    const int ir = 8 * R + g;
-                    const bool on0 = ir <= c0 && c0 < mt, on1 = ir <= c0 + 1 && c0 + 1 < mt;      // entries of the tile inside the triangle
-                    double acc0 = on0 ? F[b0 + ir] : 0.0, acc1 = on1 ? F[b1 + ir] : 0.0;
-                    const double aA = onA ? -F[pbA + ir] : 0.0;
-                    TK_DMMA(acc0, acc1, aA, bfA);
-                    if (nk > 4) {
-                        const double aB = onB ? -F[pbB + ir] : 0.0;
-                        TK_DMMA(acc0, acc1, aB, bfB);
-                    }
-                    if (on0) F[b0 + ir] = acc0;
-                    if (on1) F[b1 + ir] = acc1;
-                    R += NW;
-                    while (R > Cb) { R -= Cb + 1; ++Cb; }
+        };
+        // rank-nk update by the micro-panel at k0 of the tiles with column block in [cb_lo, cb_hi), tile `first`, `first + step`, ... of them
+        auto update_tiles = [&](int k0, int nk, int cb_lo, int cb_hi, int first, int step) {
+            const int Kt = m - 1 - k0, mt = m - k0 - nk;
+            const int pbA = tk_tri(Kt - tq), pbB = tk_tri(Kt - 4 - tq);      // the lane's pivot columns of the two k-steps
+            const bool onA = tq < nk, onB = 4 + tq < nk;
+            int Cb = cb_lo, R = first;
+            while (Cb < cb_hi && R > Cb) { R -= Cb + 1; ++Cb; }
+            int Cb_cur = -1, c0 = 0, b0 = 0, b1 = 0;
+            double bfA = 0.0, bfB = 0.0;
+            while (Cb < cb_hi) {
+                if (Cb != Cb_cur) {
+                    Cb_cur = Cb;
+                    c0 = 8 * Cb + 2 * tq;
+                    b0 = tk_tri(c0); b1 = b0 + c0 + 1;
+                    bfA = onA ? F[pbA + 8 * Cb + g] : 0.0;
+                    bfB = onB ? F[pbB + 8 * Cb + g] : 0.0;
                 }
+                const int ir = 8 * R + g;
+                const bool on0 = ir <= c0 && c0 < mt, on1 = ir <= c0 + 1 && c0 + 1 < mt;      // entries of the tile inside the triangle
+                double acc0 = on0 ? F[b0 + ir] : 0.0, acc1 = on1 ? F[b1 + ir] : 0.0;
+                const double aA = onA ? -F[pbA + ir] : 0.0;
+                TK_DMMA(acc0, acc1, aA, bfA);
+                if (nk > 4) {
+                    const double aB = onB ? -F[pbB + ir] : 0.0;
+                    TK_DMMA(acc0, acc1, aB, bfB);
+                }
+                if (on0) F[b0 + ir] = acc0;
+                if (on1) F[b1 + ir] = acc1;
+                R += step;
+                while (Cb < cb_hi && R > Cb) { R -= Cb + 1; ++Cb; }
+            }
+        };
+        if (w > 0) {
+            if (warp == 0) micro_factor(0, w < 8 ? w : 8);
+            TK_SYNCTEAM();
+            rows_below(0, w < 8 ? w : 8);
+            TK_SYNCTEAM();
+        }
+        for (int k0 = 0; k0 < w; k0 += 8) {
+            const int nk = w - k0 < 8 ? w - k0 : 8;
+            const int mt = m - k0 - nk;                    // order of what remains behind the micro-panel
+            const int nblk = (mt + 7) >> 3;
+            const int kn = k0 + 8;                         // next micro-panel (if any)
+            if (kn < w) {
+                const int nkn = w - kn < 8 ? w - kn : 8;
+                const int cbA = (mt - nkn) >> 3;           // column blocks from here up hold the next micro-panel's columns
+                update_tiles(k0, nk, cbA, nblk, warp, NW);
+                TK_SYNCTEAM();
+                if (NW == 1) { update_tiles(k0, nk, 0, cbA, 0, 1); micro_factor(kn, nkn); }
+                else if (warp == 0) micro_factor(kn, nkn);
+                else update_tiles(k0, nk, 0, cbA, warp - 1, NW - 1);
+                TK_SYNCTEAM();
+                rows_below(kn, nkn);
+            } else if (mt > 0) {
+                update_tiles(k0, nk, 0, nblk, warp, NW);
             }
             TK_SYNCTEAM();
         }
