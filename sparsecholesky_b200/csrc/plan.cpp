@@ -740,7 +740,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
     std::vector<char> in_tree(ns, 0);
     if (want_tree) {
         if (P.max_m <= TW_MAX_M) {
-            if (opt.batch_group_m > 0 && opt.want_csc) build_group_program(P, std::max(opt.batch_group_m, P.max_m), a_front, a_fcol, a_fpos, P.tree_whole);
+            if (opt.batch_group_m > 0 && opt.want_csc) build_group_program(P, opt.batch_group_m, a_front, a_fcol, a_fpos, P.tree_whole);
             else build_tree_program(P, {}, true, a_front, a_fcol, a_fpos, P.tree_whole);
         }
         const std::vector<int> roots = choose_subtrees(P, opt.tree_cap_m, opt.tree_work, in_tree);

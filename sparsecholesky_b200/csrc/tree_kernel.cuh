@@ -25,6 +25,7 @@
 #define TK_SQRT(x) std::sqrt(x)
 #define TK_RSQRT(x) (1.0 / std::sqrt(x))
 #define TK_DMMA(c0, c1, a, b) ::spchol::emu::dmma884((c0), (c1), (a), (b))
+#define TK_TEAM_ID ::spchol::emu::g_team_id
 #else
 #define TK_DEVICE __device__ __forceinline__
 #define TK_TID static_cast<int>(threadIdx.x)
@@ -35,6 +36,7 @@
 #define TK_RESTRICT __restrict__
 #define TK_SQRT(x) sqrt(x)
 #define TK_RSQRT(x) rsqrt(x)
+#define TK_TEAM_ID static_cast<int>(blockIdx.x)
 #define TK_DMMA(c0, c1, a, b) asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n" : "+d"(c0), "+d"(c1) : "d"(a), "d"(b))
 #endif
 
@@ -69,7 +71,7 @@ TK_DEVICE void tk_prefetch_range(const void* base, int64_t b0, int64_t b1, int t
 }
 
 // One task = fronts [front0, front0 + nfront) in postorder, factored by a team of NW warps (tid = 0 .. 32 NW - 1).
-// F: tri(cap_m) + TK_F_SLACK doubles, spiv: 2 doubles, sT: 64 doubles (inverse of a micro block), all private to the team.
+// F: tri(cap_m) + TK_F_SLACK doubles, spiv: 2 doubles, sT: 64 doubles (reciprocal pivots of a micro block), all private to the team.
 // out_mode 0: panels go to the L buffer; 1: entries go straight to Lx in CSC order through csc_map.
 //
 // Every front starts with a chain of dependent loads (descriptor -> index lists -> values); with four teams per SM there
@@ -84,6 +86,10 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
     constexpr int MC = 4;                                   // columns a warp moves per round of the in-place spread
     const int tid = TK_TID, lane = tid & 31, warp = tid >> 5;
     const int g = lane >> 2, tq = lane & 3;                 // DMMA fragment coordinates of the lane
+    // the warp that runs the serial 8 x 8 factorizations: rotated over the teams of an SM, so that the serial chains of the
+    // resident teams do not all land on the same scheduler (warp w of every CTA sits on scheduler w mod 4)
+    const int sw = NW > 1 ? (TK_TEAM_ID % NW) : 0;
+    const int ow = NW > 1 ? (warp - sw - 1 + NW) % NW : 0;  // index of this warp among the other NW - 1
     Stash += task.stash_base;
     const TwFront* TK_RESTRICT fr = ta.fronts + task.front0;
     TwFront d = fr[0];
@@ -160,7 +166,7 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
         //         and C(8R + g, 8C + 2 tq + 1).  Look-ahead: the tiles that hold the NEXT micro-panel's columns go first (all
         //         warps), then warp 0 factors that micro-panel while the other warps finish the update -- the serial 8-pivot chain
         //         hides behind tensor-core work.  Three team barriers per 8 pivots.
-        auto micro_factor = [&](int k0, int nk) {              // warp 0 only
+        auto micro_factor = [&](int k0, int nk) {              // one warp (sw) only
             const int Kt = m - 1 - k0;
             double l[8][8], rinv[8];
 #pragma unroll
@@ -198,41 +204,39 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
                 }
             }
             TK_SYNCWARP();                                     // every lane has read the block before it is overwritten
-            // column j of the inverse: L t = e_j; lane j (< 8) computes and stores it, and writes row j of the factor
+            if (lane < 8) {                                    // lane j writes row j of the factor and its reciprocal pivot
 #pragma unroll
-            for (int j = 0; j < 8; ++j) {
-                double tcol[8];
+                for (int j = 0; j < 8; ++j)
+                    if (lane == j) {
+                        sT[j] = rinv[j];
 #pragma unroll
-                for (int i = 0; i < 8; ++i) {
-                    if (i < j) { tcol[i] = 0.0; continue; }
-                    double acc = (i == j) ? 1.0 : 0.0;
-#pragma unroll
-                    for (int k = j; k < i; ++k) acc = fma(-l[i][k], tcol[k], acc);
-                    tcol[i] = acc * rinv[i];
-                }
-                if (lane == j) {
-#pragma unroll
-                    for (int i = 0; i < 8; ++i) sT[i * 8 + j] = tcol[i];
-#pragma unroll
-                    for (int c = 0; c <= j; ++c) if (j < nk) F[tk_tri(Kt - c) + (Kt - j)] = l[j][c];
-                }
+                        for (int c = 0; c <= j; ++c) if (j < nk) F[tk_tri(Kt - c) + (Kt - j)] = l[j][c];
+                    }
             }
         };
-        auto rows_below = [&](int k0, int nk) {                // x <- x T^T, one row per thread
+        auto rows_below = [&](int k0, int nk) {                // x L11^T = b by substitution, one row per thread (rows are independent)
             const int Kt = m - 1 - k0, mt = m - k0 - nk;
+            if (tid >= mt && NT >= mt) return;
+            double l[8][8], ri[8];                             // the factored diagonal block and the reciprocal pivots (shared-memory broadcasts)
+#pragma unroll
+            for (int i = 0; i < 8; ++i) {
+                ri[i] = sT[i];
+#pragma unroll
+                for (int j = 0; j < i; ++j) l[i][j] = (i < nk) ? F[tk_tri(Kt - j) + (Kt - i)] : 0.0;
+            }
             for (int ir = tid; ir < mt; ir += NT) {
-                double x[8], yv[8];
+                double x[8];
 #pragma unroll
                 for (int q = 0; q < 8; ++q) x[q] = q < nk ? F[tk_tri(Kt - q) + ir] : 0.0;
 #pragma unroll
                 for (int j = 0; j < 8; ++j) {
-                    double acc = 0.0;
+                    double acc = x[j];
 #pragma unroll
-                    for (int q = 0; q <= j; ++q) acc = fma(x[q], sT[j * 8 + q], acc);
-                    yv[j] = acc;
+                    for (int q = 0; q < j; ++q) acc = fma(-x[q], l[j][q], acc);
+                    x[j] = acc * ri[j];
                 }
 #pragma unroll
-                for (int q = 0; q < 8; ++q) if (q < nk) F[tk_tri(Kt - q) + ir] = yv[q];
+                for (int q = 0; q < 8; ++q) if (q < nk) F[tk_tri(Kt - q) + ir] = x[q];
             }
         };
         // rank-nk update by the micro-panel at k0 of the tiles with column block in [cb_lo, cb_hi), tile `first`, `first + step`, ... of them
@@ -268,7 +272,7 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
             }
         };
         if (w > 0) {
-            if (warp == 0) micro_factor(0, w < 8 ? w : 8);
+            if (warp == sw) micro_factor(0, w < 8 ? w : 8);
             TK_SYNCTEAM();
             rows_below(0, w < 8 ? w : 8);
             TK_SYNCTEAM();
@@ -284,8 +288,8 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
                 update_tiles(k0, nk, cbA, nblk, warp, NW);
                 TK_SYNCTEAM();
                 if (NW == 1) { update_tiles(k0, nk, 0, cbA, 0, 1); micro_factor(kn, nkn); }
-                else if (warp == 0) micro_factor(kn, nkn);
-                else update_tiles(k0, nk, 0, cbA, warp - 1, NW - 1);
+                else if (warp == sw) micro_factor(kn, nkn);
+                else update_tiles(k0, nk, 0, cbA, ow, NW - 1);
                 TK_SYNCTEAM();
                 rows_below(kn, nkn);
             } else if (mt > 0) {

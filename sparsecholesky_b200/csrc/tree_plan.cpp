@@ -200,7 +200,8 @@ void build_tree_program(const HostPlan& P, const std::vector<int>& roots_in, boo
 void build_group_program(const HostPlan& P, int cap_m, const std::vector<int>& a_front, const std::vector<int>& a_col,
                          const std::vector<int>& a_pos, TreeProgram& out) {
     const int ns = P.ns;
-    cap_m = std::min(cap_m, TW_MAX_M);
+    cap_m = std::min(cap_m, TW_MAX_M);      // a front absorbs children only while the group stays within cap_m rows; fronts of
+                                            // the plan that are larger than that stand alone (the caller checked them against TW_MAX_M)
     if (P.l_src.empty() && P.nnzL > 0) throw std::runtime_error("spchol: the group program needs the CSC export map");
     // ---- 1. grouping, bottom-up: a front absorbs the groups of its children (largest block first) while |U| <= cap_m
     std::vector<int> gw(ns), top(ns);                 // columns of the group whose top is s; group top of every front
@@ -208,7 +209,7 @@ void build_group_program(const HostPlan& P, int cap_m, const std::vector<int>& a
     for (int s = 0; s < ns; ++s) { gw[s] = P.w[s]; top[s] = s; members[s].push_back(s); }
     std::vector<int> kids;
     for (int p = 0; p < ns; ++p) {
-        if (P.m[p] > cap_m) throw std::runtime_error("spchol: front too large for the group program");
+        if (P.m[p] > TW_MAX_M) throw std::runtime_error("spchol: front too large for the group program");
         kids.assign(P.child_idx.begin() + P.child_ptr[p], P.child_idx.begin() + P.child_ptr[p + 1]);
         std::stable_sort(kids.begin(), kids.end(), [&](int a, int b) { return (P.m[a] - P.w[a]) > (P.m[b] - P.w[b]); });
         for (int c : kids) {

@@ -13,6 +13,7 @@
 #include <cmath>
 #include <cstdint>
 #include <cstdio>
+#include <cstdlib>
 #include <limits>
 #include <memory>
 #include <mutex>
@@ -25,6 +26,7 @@ thread_local int t_tid = 0;
 std::barrier<>* g_team = nullptr;
 std::vector<std::barrier<>*> g_warp;
 std::mutex g_mu;
+int g_team_id = 0;                     // stands in for blockIdx.x (which warp of a team runs the serial part)
 double g_fa[8][32], g_fb[8][32];      // operand fragments of the emulated tensor-core instruction, per warp
 inline int tid() { return t_tid; }
 inline void sync() { g_team->arrive_and_wait(); }
@@ -121,6 +123,7 @@ static void run_tasks(const TreeArrays& ta, const double* Ax, double* Lb, double
 extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double* Ax, int relax, int whole, int cap_m, double work, int nw,
                               double* Lx, int* info_out, int64_t* stats, char* err, int errlen) {
     auto fail = [&](const std::string& msg) { std::snprintf(err, errlen, "%s", msg.c_str()); return -1; };
+    emu::g_team_id = std::getenv("TREEEMU_TEAM") ? std::atoi(std::getenv("TREEEMU_TEAM")) : 0;
     try {
         Symbolic S;
         RelaxParams rp; rp.enable = relax != 0;

@@ -73,8 +73,7 @@ def test_whole_tree_vs_reference_golden(emu, name, relax, nw):
 def test_group_program_vs_reference_golden(emu, name, cap_m, nw):
     # the batched program over amalgamated groups: fewer, bigger dense steps with explicit zeros that must stay exact zeros
     A, ref = golden(name)
-    S = sc.schol(A)
-    cap = max(cap_m, S.stats()["max_m"])            # (cap 0: every front its own group)
+    cap = max(cap_m, 1)                              # (cap 1: nothing is absorbed, every front its own group)
     Lx, info, st = run(emu, A, whole=2, cap_m=cap, nw=nw)
     assert info == 0 and relerr(Lx, ref) <= 1e-10
     assert st["tasks"] == 1 and 1 <= st["groups"] <= st["ns"] and st["fronts"] == st["groups"]
@@ -90,6 +89,18 @@ def test_subtrees_vs_reference_golden(emu, name, cap_m, work, nw):
     Lx, info, st = run(emu, A, whole=False, cap_m=cap_m, work=work, nw=nw)
     assert info == 0 and relerr(Lx, ref) <= 1e-10
     assert st["fronts"] <= st["ns"]
+
+
+@pytest.mark.parametrize("team", [1, 2, 3])
+def test_serial_warp_rotation(emu, team, monkeypatch):
+    # on the GPU the warp that runs the serial 8 x 8 factorizations is blockIdx.x mod NW; the host run picks it by hand
+    monkeypatch.setenv("TREEEMU_TEAM", str(team))
+    A, ref = golden("1138_bus")
+    Lx, info, st = run(emu, A, whole=2, cap_m=117, nw=4)
+    assert info == 0 and relerr(Lx, ref) <= 1e-10
+    A, ref = golden("lap2d_24")
+    Lx, info, st = run(emu, A, whole=False, cap_m=40, work=2e4, nw=2)
+    assert info == 0 and relerr(Lx, ref) <= 1e-10
 
 
 def test_subtrees_on_a_larger_grid(emu):
