@@ -93,8 +93,8 @@ struct PlanOptions {
     double tree_work = 2.5e6;  // dense flops of a subtree task (the unit of load balance)
     int batch_group_m = 117;   // batched whole-tree program: fronts are amalgamated into groups of up to this many rows (tree_plan.h,
                                // build_group_program; 117 rows = 55 KB packed = four teams per SM); 0: one step per front of the plan
-    int export_mark_w = 0;     // > 0: fronts at least this wide announce every finished block column (OP_EXPORT).  Staged:
-                               // checked by the plan simulator, not yet run on a GPU -- SPCHOL_EXPORT_MARK_W=1024 enables it
+    int export_mark_w = 1024;  // > 0: fronts at least this wide announce every finished block column (OP_EXPORT): spchol_factor_lbuf reads
+                               // them back while the front's trailing update still runs (128^3 e2e 1146 -> 1073 ms); 0: read-back by levels only
     // multi-GPU (one plan per rank, every rank builds the same global mapping):
     int rank = 0, world = 1;
     int dist_NB = 256;         // block-column width of a front that is factored by a rank group

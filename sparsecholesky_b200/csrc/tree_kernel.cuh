@@ -98,10 +98,15 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
         const TwFront dnn = fr[f + 2 < task.nfront ? f + 2 : task.nfront - 1];
         int ax_next = -1;                                   // index of one value of A the next front needs (prefetched further down)
         if (f + 1 < task.nfront) {
-            tk_prefetch_range(ta.rmap, 4 * static_cast<int64_t>(dn.map_lo), 4 * static_cast<int64_t>(dn.map_lo + dn.map_n), tid, NT);
-            tk_prefetch_range(ta.a_dst, 2 * static_cast<int64_t>(dn.a0), 2 * static_cast<int64_t>(dn.a0 + dn.an), tid, NT);
-            tk_prefetch_range(ta.stashes, 16 * static_cast<int64_t>(dn.stash0), 16 * static_cast<int64_t>(dn.stash0 + dn.nstash), tid, NT);
-            if (out_mode == 1) tk_prefetch_range(ta.csc_map, 4 * dn.panel_off, 4 * (dn.panel_off + static_cast<int64_t>(dn.ld) * dn.w), tid, NT);
+            if (warp == NW - 1) {                           // one warp issues the prefetches (a line per lane and pass)
+                tk_prefetch_range(ta.rmap, 4 * static_cast<int64_t>(dn.map_lo), 4 * static_cast<int64_t>(dn.map_lo + dn.map_n), lane, 32);
+                tk_prefetch_range(ta.a_dst, 2 * static_cast<int64_t>(dn.a0), 2 * static_cast<int64_t>(dn.a0 + dn.an), lane, 32);
+                tk_prefetch_range(ta.stashes, 16 * static_cast<int64_t>(dn.stash0), 16 * static_cast<int64_t>(dn.stash0 + dn.nstash), lane, 32);
+                if (dn.flags & TW_GROUP) {
+                    tk_prefetch_range(ta.out_src, 2 * static_cast<int64_t>(dn.pad0), 2 * static_cast<int64_t>(dn.pad0 + dn.pad1), lane, 32);
+                    tk_prefetch_range(ta.out_dst, 4 * static_cast<int64_t>(dn.pad0), 4 * static_cast<int64_t>(dn.pad0 + dn.pad1), lane, 32);
+                } else if (out_mode == 1) tk_prefetch_range(ta.csc_map, 4 * dn.panel_off, 4 * (dn.panel_off + static_cast<int64_t>(dn.ld) * dn.w), lane, 32);
+            }
             if (tid < dn.an) ax_next = TK_LDG(ta.a_src + dn.a0 + tid);
         }
         const int m = d.m, w = d.w, mb = m - w;
@@ -239,13 +244,15 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
                 for (int q = 0; q < 8; ++q) if (q < nk) F[tk_tri(Kt - q) + ir] = x[q];
             }
         };
-        // rank-nk update by the micro-panel at k0 of the tiles with column block in [cb_lo, cb_hi), tile `first`, `first + step`, ... of them
+        // rank-nk update by the micro-panel at k0 of the tiles with column block in [cb_lo, cb_hi).  The unit of work is a PAIR of
+        // row tiles (2U, 2U + 1) of one column block -- they share the B fragments and the column bases; units `first`,
+        // `first + step`, ... of the range are this warp's
         auto update_tiles = [&](int k0, int nk, int cb_lo, int cb_hi, int first, int step) {
             const int Kt = m - 1 - k0, mt = m - k0 - nk;
             const int pbA = tk_tri(Kt - tq), pbB = tk_tri(Kt - 4 - tq);      // the lane's pivot columns of the two k-steps
             const bool onA = tq < nk, onB = 4 + tq < nk;
-            int Cb = cb_lo, R = first;
-            while (Cb < cb_hi && R > Cb) { R -= Cb + 1; ++Cb; }
+            int Cb = cb_lo, U = first;
+            while (Cb < cb_hi && U > (Cb >> 1)) { U -= (Cb >> 1) + 1; ++Cb; }
             int Cb_cur = -1, c0 = 0, b0 = 0, b1 = 0;
             double bfA = 0.0, bfB = 0.0;
             while (Cb < cb_hi) {
@@ -256,19 +263,28 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
                     bfA = onA ? F[pbA + 8 * Cb + g] : 0.0;
                     bfB = onB ? F[pbB + 8 * Cb + g] : 0.0;
                 }
-                const int ir = 8 * R + g;
-                const bool on0 = ir <= c0 && c0 < mt, on1 = ir <= c0 + 1 && c0 + 1 < mt;      // entries of the tile inside the triangle
-                double acc0 = on0 ? F[b0 + ir] : 0.0, acc1 = on1 ? F[b1 + ir] : 0.0;
-                const double aA = onA ? -F[pbA + ir] : 0.0;
-                TK_DMMA(acc0, acc1, aA, bfA);
+                const int ir0 = 16 * U + g, ir1 = ir0 + 8;
+                const bool two = 2 * U + 1 <= Cb;              // the second row tile of the pair exists (warp-uniform)
+                const bool on00 = ir0 <= c0 && c0 < mt, on01 = ir0 <= c0 + 1 && c0 + 1 < mt;      // entries inside the triangle
+                const bool on10 = two && ir1 <= c0 && c0 < mt, on11 = two && ir1 <= c0 + 1 && c0 + 1 < mt;
+                double a00 = on00 ? F[b0 + ir0] : 0.0, a01 = on01 ? F[b1 + ir0] : 0.0;
+                double a10 = on10 ? F[b0 + ir1] : 0.0, a11 = on11 ? F[b1 + ir1] : 0.0;
+                const double fA0 = onA ? -F[pbA + ir0] : 0.0;
+                const double fA1 = (onA && two) ? -F[pbA + ir1] : 0.0;
+                TK_DMMA(a00, a01, fA0, bfA);
+                if (two) TK_DMMA(a10, a11, fA1, bfA);
                 if (nk > 4) {
-                    const double aB = onB ? -F[pbB + ir] : 0.0;
-                    TK_DMMA(acc0, acc1, aB, bfB);
+                    const double fB0 = onB ? -F[pbB + ir0] : 0.0;
+                    const double fB1 = (onB && two) ? -F[pbB + ir1] : 0.0;
+                    TK_DMMA(a00, a01, fB0, bfB);
+                    if (two) TK_DMMA(a10, a11, fB1, bfB);
                 }
-                if (on0) F[b0 + ir] = acc0;
-                if (on1) F[b1 + ir] = acc1;
-                R += step;
-                while (Cb < cb_hi && R > Cb) { R -= Cb + 1; ++Cb; }
+                if (on00) F[b0 + ir0] = a00;
+                if (on01) F[b1 + ir0] = a01;
+                if (on10) F[b0 + ir1] = a10;
+                if (on11) F[b1 + ir1] = a11;
+                U += step;
+                while (Cb < cb_hi && U > (Cb >> 1)) { U -= (Cb >> 1) + 1; ++Cb; }
             }
         };
         if (w > 0) {
