@@ -351,11 +351,15 @@ def main():
             traffic, traffic_src = tj["dram_bytes_per_launch"], tj["source"]
     except Exception:
         pass
+    gb = C.c_double(0); gt = C.c_int64(0)
+    check(L.spchol_plan_gemm_bytes(plan_h, C.byref(gb), C.byref(gt)))
+    kname = "k_gemm_dmma" if os.environ.get("SPCHOL_GEMM_TMA") == "0" else "k_gemm_tma"
     roofline = {
-        "kernel": "k_gemm_dmma", "bound": "tensor", "achieved": round(achieved, 3), "peak": round(peak.value, 3),
+        "kernel": kname, "bound": "tensor", "achieved": round(achieved, 3), "peak": round(peak.value, 3),
         "unit": "TFLOP/s", "frac": round(achieved / peak.value, 4) if peak.value else None, "traffic": traffic,
         "traffic_source": traffic_src,
-        "peak_source": "measured live: register-resident mma.sync.m8n8k4.f64 chains on this GPU (MEASURED_PEAKS.json has no FP64 entry)",
+        "operand_bytes_per_launch_if_moved_once": round(gb.value / max(gemm_launches, 1), 1),
+        "peak_source": "measured live: register-resident mma.sync.m8n8k4.f64 chains on this GPU (MEASURED_PEAKS.json has no FP64 entry: fallback)",
         "launches": gemm_launches, "avg_launch_ms": round(gemm_ms / max(gemm_launches, 1), 4),
         "algorithmic_flops_per_step": fl2[0], "share_of_step": round(gemm_ms / max(float(kms[:9].sum()), 1e-9), 3),
         "by_K_class": gemm_classes,

@@ -206,6 +206,8 @@ int  spchol_set_profile(spchol_plan*, int on);
 int  spchol_get_profile(const spchol_plan*, double* kind_ms12, int64_t* kind_launches12, double* flops2);
 /* algorithmic flops of the DMMA update tasks by K class (K <= 128, <= 256, larger); their times are profile slots 9..11 */
 int  spchol_get_gemm_classes(const spchol_plan*, double* flops3);
+/* operand bytes of the update tasks of one factorization if every operand moved exactly once, and the number of tasks */
+int  spchol_plan_gemm_bytes(const spchol_plan*, double* bytes_min, int64_t* tasks);
 /* stream handle (cudaStream_t) the plan launches on, for CUDA-event timing by the caller */
 void* spchol_stream(spchol_plan*);
 /* number of kernel launches the last factorization issued */

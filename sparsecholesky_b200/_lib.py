@@ -76,6 +76,7 @@ SIGNATURES = {
     "spchol_set_profile": (C.c_int, [_VP, C.c_int]),
     "spchol_get_profile": (C.c_int, [_VP, _VP, _VP, _VP]),
     "spchol_get_gemm_classes": (C.c_int, [_VP, _VP]),
+    "spchol_plan_gemm_bytes": (C.c_int, [_VP, C.POINTER(C.c_double), C.POINTER(C.c_int64)]),
     "spchol_stream": (_VP, [_VP]),
     "spchol_last_launches": (C.c_int64, [_VP]),
     "spchol_symbolic_panel_layout": (C.c_int, [_VP, _VP, _VP, _VP, _VP, C.POINTER(C.c_int64)]),

@@ -328,7 +328,7 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
         const int64_t before = launches;
         switch (op.kind) {
         case OP_TREE: {
-            static const int nw = getenv("SPCHOL_TREE_NW") ? atoi(getenv("SPCHOL_TREE_NW")) : 2;
+            static const int nw = getenv("SPCHOL_TREE_NW") ? atoi(getenv("SPCHOL_TREE_NW")) : 1;
             launch_tree(nw, op.count, p->tree.f_stride, st, p->tree.ta, dAx, p->dL, p->dW, p->tree.stash, nullptr, p->dinfo, 0, 0, 0, 0, 0, 0, 0);
             ++launches;
         } break;
@@ -1151,6 +1151,14 @@ int spchol_get_profile(const spchol_plan* p, double* kind_ms12, int64_t* kind_la
     if (!p) return SPCHOL_EINVAL;
     for (int k = 0; k < 12; ++k) { if (kind_ms12) kind_ms12[k] = p->kind_ms[k]; if (kind_launches12) kind_launches12[k] = p->kind_launches[k]; }
     if (flops2) { flops2[0] = p->H.gemm_flops_alg; flops2[1] = p->H.gemm_flops; }
+    return 0;
+}
+// operand bytes of the update tasks of one factorization if every operand moved exactly once (the floor the DRAM traffic of
+// the update kernel is compared with) and the number of update tasks
+int spchol_plan_gemm_bytes(const spchol_plan* p, double* bytes_min, int64_t* tasks) {
+    if (!p) return SPCHOL_EINVAL;
+    if (bytes_min) *bytes_min = p->H.gemm_bytes_min;
+    if (tasks) *tasks = static_cast<int64_t>(p->H.gemm_tasks.size());
     return 0;
 }
 // algorithmic flops of the update tasks by K class (K <= 128, <= 256, larger): profile slots 9, 10, 11

@@ -344,6 +344,7 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
         }
         P.gemm_flops_alg += 2.0 * cnt * ge.K;
         P.gemm_flops_alg_k[gemm_k_class(ge.K)] += 2.0 * cnt * ge.K;
+        P.gemm_bytes_min += 8.0 * ((static_cast<double>(ge.M) + ge.N) * ge.K + ((ge.c_space & 2) ? 1.0 : 2.0) * cnt);
     };
     auto add_comm = [&](int kind, int lo, int cn, int root, int space, int64_t coff, int64_t count, int lv) {
         Op op{}; op.kind = OP_COMM; op.begin = static_cast<int>(P.comm_tasks.size()); op.count = 1; op.level = lv;

@@ -88,8 +88,9 @@ struct PlanOptions {
                                // and the children's contributions to it are extend-added afterwards
     int lookahead = 1;         // 1: panel work of large fronts on stream 1, overlapped with the trailing update (see Op)
     int tree = 1;              // 1: the bottom of the tree goes to the warp-per-subtree kernel (tree_plan.h) instead of one CTA per front and level
-    int tree_cap_m = 64;       // largest front inside a subtree task (64 rows: 16.7 KB packed, 13 teams per SM; measured on 2D 1024^2:
-                               // small-front time 2.25 ms at 64 rows / 2 warps against 2.5-5.1 ms at 96-117 rows and 3.03 ms without subtree tasks)
+    int tree_cap_m = 48;       // largest front inside a subtree task (48 rows: 9.4 KB packed; the teams are register-limited to 16 per SM).
+                               // Measured on 2D 1024^2 (small-front time, final kernel): 2.71 ms at 48 rows / 1 warp, 2.97 at 64 / 1, 3.05 at 64 / 2,
+                               // 3.03 ms without subtree tasks
     double tree_work = 2.5e6;  // dense flops of a subtree task (the unit of load balance)
     int batch_group_m = 117;   // batched whole-tree program: fronts are amalgamated into groups of up to this many rows (tree_plan.h,
                                // build_group_program; 117 rows = 55 KB packed = four teams per SM); 0: one step per front of the plan
@@ -152,6 +153,7 @@ struct HostPlan {
     double gemm_flops = 0;           // flops of the full M x N x K rectangles of OP_GEMM tasks
     double gemm_flops_alg = 0;       // flops of the wanted (lower-trapezoid) part only
     double gemm_flops_alg_k[3] = {0, 0, 0};   // the same split by K class of the task (gemm_k_class)
+    double gemm_bytes_min = 0;       // operand bytes of the update tasks if every operand moved once: (M + N) K read, wanted C entries read + written (stored only: written)
     int64_t n_dist = 0;              // fronts factored by a rank group
     int64_t comm_doubles = 0;        // doubles this rank sends or receives per factorization
     bool holds(int s) const { return own_idx[s] >= 0; }

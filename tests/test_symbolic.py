@@ -171,3 +171,32 @@ def test_numeric_path_fails_loudly_without_gpu():
     A = sc.triplet_to_csc_matrix([0, 0, 1], [0, 1, 1], [4.0, 1.0, 3.0], 2)
     with pytest.raises(sc.api.SpcholError, match="no CUDA device"):
         sc.chol(A)
+
+
+@pytest.mark.parametrize("name", ["bcsstk01", "1138_bus", "lap3d_10"])
+def test_gather_csc64_from_panels(name):
+    """spchol_symbolic_gather_csc64 (the 64-bit CSC behind chol64 in the C++ header): pattern == the reference's S.p / S.i,
+    values gathered from a supernodal panel buffer filled with the reference's L through the documented export layout."""
+    import ctypes as C
+    from sparsecholesky_b200._lib import check, lib, ptr
+    g = np.load(os.path.join(GOLD, name + ".npz"))
+    A = sc.CscMatrix(int(g["n"]), g["Ap"], g["Ai"], g["Ax"])
+    S = sc.schol(A)
+    n, nnz = A.n, S.nnz
+    lay = S.panel_layout()
+    st, _ = S.supernodes(relaxed=True)
+    lbuf = np.full(lay["lbuf_entries"], np.nan)
+    Lp, Li, Lx = g["Lp"], g["Li"], g["Lx"]
+    for k in range(len(lay["w"])):                       # scatter the reference's L into the panels (padding stays NaN)
+        rows = S.front_rows(k, lay["m"][k])
+        for c in range(int(lay["w"][k])):
+            j = int(st[k]) + c
+            a, b = int(Lp[j]), int(Lp[j + 1])
+            pos = np.searchsorted(rows, Li[a:b])
+            lbuf[int(lay["panel_off"][k]) + c * int(lay["ld"][k]) + pos] = Lx[a:b]
+    p64 = np.empty(n + 1, np.int64); i32 = np.empty(nnz, np.int32); x = np.empty(nnz)
+    check(lib().spchol_symbolic_gather_csc64(S._sym.h, ptr(lbuf), ptr(p64), ptr(i32), ptr(x)), "gather_csc64")
+    assert np.array_equal(p64, Lp.astype(np.int64)) and np.array_equal(i32, Li)
+    assert np.array_equal(x, Lx)                           # only true entries were read: no NaN came through
+    check(lib().spchol_symbolic_gather_csc64(S._sym.h, None, ptr(p64), ptr(i32), None), "gather_csc64 pattern only")
+    assert int(lib().spchol_symbolic_nnzA(S._sym.h)) == A.capacity()

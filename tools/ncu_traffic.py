@@ -1,55 +1,40 @@
-"""Reduce an `ncu --set full` report of k_gemm_dmma launches to profiles/ncu_gemm_traffic.json + a text summary.
-Usage: python tools/ncu_traffic.py <report.ncu-rep> <workload> <summary.txt> "<command line that was profiled>" """
+"""DRAM traffic of the update kernel per launch, from an ncu metrics-only pass over EVERY launch of the kernel in one bench
+command:
+    ncu --metrics dram__bytes_read.sum,dram__bytes_write.sum,gpu__time_duration.sum --clock-control none -k regex:k_gemm_tma \
+        --csv --log-file <csv> python bench.py --steps 1 --warmup 3 --no-e2e --no-cpu-baseline --no-also
+Writes profiles/ncu_gemm_traffic.json (read by bench.py -> roofline.traffic) and a text summary.
+Usage: python tools/ncu_traffic.py <csv> <workload> <summary.txt> <launches per factorization> <operand bytes per factorization>"""
 import csv
 import io
 import json
-import subprocess
 import sys
 
-rep, workload, out_txt, cmdline = sys.argv[1:5]
-raw = subprocess.run(["ncu", "-i", rep, "--page", "raw", "--csv"], capture_output=True, text=True).stdout
-rows = list(csv.reader(io.StringIO(raw)))
-hdr, units, data = rows[0], rows[1], rows[2:]
-col = {k: i for i, k in enumerate(hdr)}
-
-
-def f(row, key):
-    v = row[col[key]].replace(",", "")
-    return float(v) if v else 0.0
-
-
-def to_bytes(v, unit):
-    return v * {"byte": 1, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9}[unit]
-
-
-keys = ["gpu__time_duration.sum", "dram__bytes_read.sum", "dram__bytes_write.sum", "smsp__cycles_active.avg",
-        "smsp__inst_executed.sum", "sm__throughput.avg.pct_of_peak_sustained_elapsed", "launch__registers_per_thread",
-        "l1tex__data_pipe_lsu_wavefronts_mem_shared_op_ld.sum", "l1tex__data_bank_conflicts_pipe_lsu_mem_shared_op_ld.sum",
-        "lts__t_sector_hit_rate.pct", "sm__warps_active.avg.pct_of_peak_sustained_active",
-        "smsp__average_warps_issue_stalled_math_pipe_throttle_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_barrier_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_long_scoreboard_per_issue_active.ratio",
-        "smsp__average_warps_issue_stalled_short_scoreboard_per_issue_active.ratio"]
-dm = [k for k in hdr if "subpipe_dmma_cycles_active" in k]
-lines = [f"# ncu --set full --clock-control none --import-source on -k regex:k_gemm_dmma ({cmdline}), 1 B200",
-         f"# report: {rep} (scratch); per-launch values of the {len(data)} captured launches"]
-tot_bytes, tot_ms = 0.0, 0.0
-for k in ["Kernel Name", "Grid Size", "Block Size"] + keys + dm:
-    if k not in col:
-        continue
-    lines.append(f"{k} [{units[col[k]]}]: {[r[col[k]] for r in data]}")
-per = []
-for r in data:
-    b = to_bytes(f(r, "dram__bytes_read.sum"), units[col["dram__bytes_read.sum"]]) + \
-        to_bytes(f(r, "dram__bytes_write.sum"), units[col["dram__bytes_write.sum"]])
-    per.append(b)
-if dm:
-    lines.append("DMMA sub-pipe active / SMSP active cycles: " +
-                 str([round(f(r, dm[0]) / max(f(r, "smsp__cycles_active.avg"), 1), 3) for r in data]))
-lines.append(f"traffic per launch (dram read+write) [MB]: {[round(b / 1e6, 1) for b in per]}")
-open(out_txt, "w").write("\n".join(lines) + "\n")
-json.dump({"workload": workload, "kernel": "k_gemm_dmma", "launches_captured": len(data),
-           "dram_bytes_per_launch": sum(per) / max(len(per), 1),
-           "source": f"{out_txt} (ncu --set full, mean of {len(data)} captured launches of the bench command)"},
+src, workload, out_txt, per_step, operand = sys.argv[1], sys.argv[2], sys.argv[3], int(sys.argv[4]), float(sys.argv[5])
+lines = [l for l in open(src) if not l.startswith("==")]
+rd = wr = ms = 0.0
+n = 0
+mult = {"byte": 1.0, "Kbyte": 1e3, "Mbyte": 1e6, "Gbyte": 1e9, "Tbyte": 1e12}
+tmul = {"ns": 1e-6, "us": 1e-3, "usecond": 1e-3, "ms": 1.0, "msecond": 1.0, "s": 1e3, "second": 1e3}
+for row in csv.DictReader(io.StringIO("".join(lines))):
+    name, unit = row.get("Metric Name"), row.get("Metric Unit")
+    v = float(row["Metric Value"].replace(",", ""))
+    if name == "dram__bytes_read.sum":
+        rd += v * mult[unit]; n += 1
+    elif name == "dram__bytes_write.sum":
+        wr += v * mult[unit]
+    elif name == "gpu__time_duration.sum":
+        ms += v * tmul[unit]
+steps = n / per_step
+per_launch = (rd + wr) / max(n, 1)
+txt = [f"# {src}: ncu metrics-only pass over every launch of the update kernel ({workload})",
+       f"launches captured: {n} = {steps:.2f} factorizations x {per_step} launches",
+       f"DRAM read {rd / 1e9:.2f} GB + write {wr / 1e9:.2f} GB = {(rd + wr) / 1e9:.2f} GB -> {(rd + wr) / max(steps, 1e-9) / 1e9:.2f} GB per factorization, {per_launch / 1e6:.2f} MB per launch",
+       f"operand bytes if every operand moved exactly once: {operand / 1e9:.2f} GB per factorization ({operand / per_step / 1e6:.2f} MB per launch)",
+       f"traffic / that floor: {(rd + wr) / max(steps, 1e-9) / operand:.2f}x",
+       f"kernel time under ncu (cold cache, serialised): {ms / max(steps, 1e-9):.1f} ms per factorization"]
+open(out_txt, "w").write("\n".join(txt) + "\n")
+json.dump({"workload": workload, "kernel": "k_gemm_tma", "launches_captured": n, "dram_bytes_per_launch": per_launch,
+           "operand_bytes_per_launch_if_moved_once": operand / per_step, "ratio": (rd + wr) / max(steps, 1e-9) / operand,
+           "source": f"{out_txt} (ncu metrics-only pass over all {n} launches of the bench command, mean per launch)"},
           open("profiles/ncu_gemm_traffic.json", "w"), indent=1)
-print("\n".join(lines)[:3000])
+print("\n".join(txt))

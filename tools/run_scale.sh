@@ -1,19 +1,25 @@
 #!/bin/bash
-# final round-1 numbers on N GPUs: 128^3 (and the batched config) through bench.py exactly as the driver launches it
+# N-GPU bench lines of the headline workload on the final code (run once per N: gpurun --gpus N -- bash tools/run_scale.sh N)
 mkdir -p gpurun_out
 N=${1:-8}
 export NCCL_DEBUG=WARN
 timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 \
-    bench.py --gpus $N --steps 3 --warmup 3 > gpurun_out/final_lap3d_128_n$N.json 2> gpurun_out/final_lap3d_128_n$N.err
-echo "128 rc=$?"; python -c "
+    bench.py --gpus $N --steps 5 --warmup 3 --workload lap3d_128 > gpurun_out/r2z_bench_lap3d_128_n$N.json 2> gpurun_out/r2z_bench_n$N.err
+echo "bench rc=$?"; python - <<PY
 import json
-for l in open('gpurun_out/final_lap3d_128_n$N.json'):
+for l in open('gpurun_out/r2z_bench_lap3d_128_n$N.json'):
     if l.startswith('{'):
-        d=json.loads(l); print('n=$N', round(d['ms_per_step'],1), round(d['value']), d['roofline']['whole_factor_frac_of_peak'], 'e2e', d['e2e'] and round(d['e2e']['ms_per_step'],1))
-        for r in d.get('per_rank',[]): print('   ', r['ms'], r['kernel_ms'])
-"; tail -n 2 gpurun_out/final_lap3d_128_n$N.err | cut -c1-300
-if [ "$2" = "batched" ]; then
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29513 \
-    bench.py --gpus $N --steps 3 --warmup 3 --workload batched_1138 > gpurun_out/final_batched_n$N.json 2> gpurun_out/final_batched_n$N.err
-echo "batched rc=$?"; grep '^{' gpurun_out/final_batched_n$N.json | cut -c1-400; tail -n 2 gpurun_out/final_batched_n$N.err | cut -c1-300
+        d=json.loads(l); print('N=$N', round(d['ms_per_step'],1), round(d['value']), 'e2e', round(d['e2e']['ms_per_step'],1), 'd2h GB', round(d['e2e']['d2h_bytes_per_step']/1e9,1), 'residual', d['residual']['rel_fro_estimate'])
+        for r in d['per_rank']: print('   ', r['ms'], r['kernel_ms'])
+PY
+tail -n 2 gpurun_out/r2z_bench_n$N.err | cut -c1-300
+if [ "$N" = "8" ]; then
+  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29513 \
+    bench.py --gpus 8 --steps 3 --warmup 3 --workload batched_1138 > gpurun_out/r2z_bench_batched_1138_n8.json 2> gpurun_out/r2z_bench_batched_n8.err
+  echo "batched n8 rc=$? $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2z_bench_batched_1138_n8.json | head -2 | tr '\n' ' ')"
+  for D in 128 512; do
+    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 2951$((D/128)) \
+      bench.py --gpus 8 --steps 3 --warmup 3 --workload lap3d_128 --dist-nb $D --no-e2e > gpurun_out/r2z_bench_lap3d_128_n8_dnb$D.json 2> /dev/null
+    echo "dnb$D rc=$? $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2z_bench_lap3d_128_n8_dnb$D.json | head -1)"
+  done
 fi
