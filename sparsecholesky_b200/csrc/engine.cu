@@ -141,7 +141,7 @@ struct spchol_plan {
     // triangular solves (built on first use): per (level, block step) slices of the task arrays
     struct SolveStep { int b0, bn, u0, un, g0, gn, smem; };
     std::vector<SolveStep> solve_steps;        // forward order; the backward solve walks it in reverse
-    SBlock* d_sblocks = nullptr; SChunk* d_supd = nullptr; SChunk* d_sgat = nullptr;
+    SBlock* d_sblocks = nullptr; SChunk* d_supd = nullptr; SGat* d_sgat = nullptr;
     bool solve_ready = false;
     double* d_solve_v = nullptr;               // work vectors of spchol_solve (3 n SOLVE_NR doubles, allocated on first use)
     int64_t device_bytes = 0;
@@ -1179,7 +1179,7 @@ static int solve_prepare(spchol_plan* p) {
     const HostPlan& H = p->H;
     std::vector<std::vector<int>> by_level(H.nlevels);
     for (int s = 0; s < H.ns; ++s) by_level[H.level[s]].push_back(s);
-    std::vector<SBlock> blocks; std::vector<SChunk> upd, gat;
+    std::vector<SBlock> blocks; std::vector<SChunk> upd; std::vector<SGat> gat;
     for (int l = 0; l < H.nlevels; ++l) {
         int maxJ = 0;
         for (int s : by_level[l]) maxJ = std::max(maxJ, (H.w[s] + SOLVE_NB - 1) / SOLVE_NB);
@@ -1193,7 +1193,7 @@ static int solve_prepare(spchol_plan* p) {
                 mnb = std::max(mnb, nb);
                 blocks.push_back({s, c0});
                 for (int r0 = end; r0 < H.m[s]; r0 += 256) upd.push_back({s, c0, r0});
-                if (end < H.m[s]) for (int cs = c0; cs < end; cs += 32) gat.push_back({s, cs, end});
+                if (end < H.m[s]) for (int cs = c0; cs < end; cs += 32) for (int i0 = end; i0 < H.m[s]; i0 += SOLVE_GROWS) gat.push_back({s, cs, end, i0});
             }
             st.bn = static_cast<int>(blocks.size()) - st.b0; st.un = static_cast<int>(upd.size()) - st.u0;
             st.gn = static_cast<int>(gat.size()) - st.g0; st.smem = solve_diag_smem(mnb);

@@ -166,7 +166,9 @@ __global__ void __launch_bounds__(256, 2) k_gemm_tma(const GemmTask* __restrict_
                 const int col = j0 + wn * 32 + (ni >> 1) * 16 + g3_box_row(ni & 1, 2 * tq + e);
                 if (col >= 0 && col < t.N && row + t.diag >= col) {
                     double* c = C + row + static_cast<int64_t>(col) * ldc;
-                    if (beta0) *c = -acc[mi][ni][e]; else *c -= acc[mi][ni][e];
+                    if (beta0) *c = -acc[mi][ni][e];
+                    else if (swizzle & 4) atomicAdd(c, -acc[mi][ni][e]);      // result unused: RED.ADD.F64 at the L2, no load to wait for
+                    else *c -= acc[mi][ni][e];                                  // (every element has exactly one writer per launch: same value either way)
                 }
             }
         }

@@ -280,7 +280,7 @@ __global__ void __launch_bounds__(PI_THREADS, 2) k_potrf_inv(const PotrfTask* __
 
     // 8x8 micro Cholesky + inverse of the diagonal micro block at p, entirely in registers of ONE
     // warp (operands are shared-memory broadcasts, no shuffles); results go to S (factor) and T
-    // (inverse).  sqrt and reciprocal of a pivot come from one rsqrt refined by a Newton step each.
+    // (inverse).  sqrt and reciprocal of a pivot come from one rsqrt seed refined by Goldschmidt steps (see below).
     auto micro_factor = [&](int mp) {
         const int p = mp * 8;
         double l[8][8], tm[8][8], rinv[8];
@@ -292,10 +292,18 @@ __global__ void __launch_bounds__(PI_THREADS, 2) k_potrf_inv(const PotrfTask* __
         for (int k = 0; k < 8; ++k) {
             const double d = l[k][k];
             if (d <= 0.0 && lane == 0 && p + k < nb) atomicMin(info, t.col0 + p + k + 1);   // reference test (chol.hpp:849)
+            // sqrt(d) and 1/sqrt(d) together: Goldschmidt iteration from the reciprocal-square-root seed, then one residual
+            // correction each (square root correctly rounded up to rare last-bit cases, reciprocal within one ulp) -- no
+            // software sqrt / division on the serial path of the block
             double y = rsqrt(d);
-            double piv = d * y;
-            piv = fma(fma(-piv, piv, d), 0.5 * y, piv);  // sqrt(d), Newton-corrected
-            y = fma(fma(-piv, y, 1.0), y, y);            // 1/piv, Newton-corrected
+            double gq = d * y, hq = 0.5 * y;
+            double r = fma(-gq, hq, 0.5);
+            gq = fma(gq, r, gq); hq = fma(hq, r, hq);
+            r = fma(-gq, hq, 0.5);
+            gq = fma(gq, r, gq); hq = fma(hq, r, hq);
+            const double piv = fma(fma(-gq, gq, d), hq, gq);
+            y = hq + hq;
+            y = fma(fma(-piv, y, 1.0), y, y);
             rinv[k] = y;
             l[k][k] = piv;
 #pragma unroll

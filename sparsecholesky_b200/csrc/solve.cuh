@@ -20,8 +20,11 @@ namespace spchol {
 constexpr int SOLVE_NR = NPROBE;      // 8 right-hand sides per pass
 constexpr int SOLVE_NB = 128;         // column block
 struct SBlock { int s, c0; };         // front, first column of the block
-struct SChunk { int s, c0, r0; };     // + first row of a chunk of 256 rows (forward update) / unused (backward)
-constexpr int solve_diag_smem(int nb) { return (nb * (nb | 1) + nb * SOLVE_NR) * 8; }
+struct SChunk { int s, c0, r0; };     // + first row of a chunk of 256 rows (forward update)
+struct SGat { int s, c0, r0, i0; };   // backward gather: 32 columns from c0 of the block ending at r0, rows [i0, i0 + SOLVE_GROWS)
+constexpr int SOLVE_GROWS = 2048;     // rows per gather CTA: a tall front (16 447 rows at the root of 128^3) is cut into chunks whose
+                                      // partial sums meet in tsum by atomicAdd -- one CTA per 32 columns streamed the whole panel (1.3 ms a launch)
+constexpr int solve_diag_smem(int nb) { return (nb * (nb | 1) + nb * SOLVE_NR + nb) * 8; }
 
 // column-major right-hand sides (n x nr) -> interleaved [n][SOLVE_NR] (missing columns zero), gather sums cleared; and back
 __global__ void k_solve_pack(int n, int nr, const double* __restrict__ cols, double* __restrict__ v, double* __restrict__ tsum) {
@@ -48,6 +51,8 @@ __global__ void __launch_bounds__(256) k_solve_diag(const SBlock* __restrict__ t
     const int nb = min(SOLVE_NB, w - t.c0), lds = nb | 1;
     double* S = sm;                       // S[i + j*lds] = L[c0 + i][c0 + j], i >= j
     double* X = sm + nb * lds;            // X[i*SOLVE_NR + k]
+    double* RD = X + nb * SOLVE_NR;       // reciprocals of the diagonal (one IEEE division per column, all in parallel, instead of
+                                          // four divisions on the serial path of every column)
     const double* __restrict__ D = L + fa.panel_off[s] + t.c0 + static_cast<int64_t>(t.c0) * ld;
     const int tid = threadIdx.x;
     for (int idx = tid; idx < nb * nb; idx += 256) {
@@ -56,6 +61,7 @@ __global__ void __launch_bounds__(256) k_solve_diag(const SBlock* __restrict__ t
     }
     const int64_t g0 = static_cast<int64_t>(fa.first[s] + t.c0) * SOLVE_NR;
     for (int idx = tid; idx < nb * SOLVE_NR; idx += 256) X[idx] = b[g0 + idx] - (TRANS ? tsum[g0 + idx] : 0.0);
+    for (int c = tid; c < nb; c += 256) RD[c] = 1.0 / D[c + static_cast<int64_t>(c) * ld];
     __syncthreads();
     // thread (i, h): row i of the block, right-hand sides 4h .. 4h+3
     const int i = tid >> 1, h = (tid & 1) * 4;
@@ -65,9 +71,9 @@ __global__ void __launch_bounds__(256) k_solve_diag(const SBlock* __restrict__ t
     if (!TRANS) {
         for (int c = 0; c < nb; ++c) {
             if (i == c) {
-                const double d = S[c + c * lds];
+                const double rd = RD[c];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) { x[k] = x[k] / d; X[c * SOLVE_NR + h + k] = x[k]; }
+                for (int k = 0; k < 4; ++k) { x[k] = x[k] * rd; X[c * SOLVE_NR + h + k] = x[k]; }
             }
             __syncthreads();
             if (i > c && i < nb) {
@@ -79,9 +85,9 @@ __global__ void __launch_bounds__(256) k_solve_diag(const SBlock* __restrict__ t
     } else {
         for (int c = nb - 1; c >= 0; --c) {
             if (i == c) {
-                const double d = S[c + c * lds];
+                const double rd = RD[c];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) { x[k] = x[k] / d; X[c * SOLVE_NR + h + k] = x[k]; }
+                for (int k = 0; k < 4; ++k) { x[k] = x[k] * rd; X[c * SOLVE_NR + h + k] = x[k]; }
             }
             __syncthreads();
             if (i < c) {
@@ -135,10 +141,10 @@ __global__ void __launch_bounds__(256) k_solve_update(const SChunk* __restrict__
 
 // backward gather: tsum[first + c] = sum_{i >= block end} L[i][c] x[row(i)]   for 32 columns c0 .. c0+31 of a block
 // (task.r0 = end of the SOLVE_NB block the columns belong to)
-__global__ void __launch_bounds__(256) k_solve_gather(const SChunk* __restrict__ tasks, FrontArrays fa, const int* __restrict__ rowidx,
+__global__ void __launch_bounds__(256) k_solve_gather(const SGat* __restrict__ tasks, FrontArrays fa, const int* __restrict__ rowidx,
                                                       const double* __restrict__ L, const double* __restrict__ x, double* __restrict__ tsum) {
     __shared__ double Z[128][SOLVE_NR + 1];
-    const SChunk t = tasks[blockIdx.x];
+    const SGat t = tasks[blockIdx.x];
     const int s = t.s, w = fa.w[s], m = fa.m[s], ld = fa.ld[s];
     const double* __restrict__ P = L + fa.panel_off[s];
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -148,16 +154,17 @@ __global__ void __launch_bounds__(256) k_solve_gather(const SChunk* __restrict__
     for (int a = 0; a < 4; ++a)
 #pragma unroll
         for (int k = 0; k < SOLVE_NR; ++k) acc[a][k] = 0.0;
-    for (int i0 = t.r0; i0 < m; i0 += 128) {
+    const int iend = min(m, t.i0 + SOLVE_GROWS);
+    for (int i0 = t.i0; i0 < iend; i0 += 128) {
         __syncthreads();
         for (int e = tid; e < 128 * SOLVE_NR; e += 256) {
             const int i = i0 + e / SOLVE_NR;
-            Z[e / SOLVE_NR][e % SOLVE_NR] = i < m ? x[static_cast<int64_t>(front_row(fa, rowidx, s, w, i)) * SOLVE_NR + e % SOLVE_NR] : 0.0;
+            Z[e / SOLVE_NR][e % SOLVE_NR] = i < iend ? x[static_cast<int64_t>(front_row(fa, rowidx, s, w, i)) * SOLVE_NR + e % SOLVE_NR] : 0.0;
         }
         __syncthreads();
         for (int ii = lane; ii < 128; ii += 32) {
             const int i = i0 + ii;
-            if (i >= m) break;
+            if (i >= iend) break;
 #pragma unroll
             for (int a = 0; a < 4; ++a) {
                 const int c = cb + a;
@@ -175,7 +182,7 @@ __global__ void __launch_bounds__(256) k_solve_gather(const SChunk* __restrict__
         for (int k = 0; k < SOLVE_NR; ++k) {
             double v = acc[a][k];
             for (int o = 16; o; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
-            if (lane == 0 && cb + a < w && cb + a < t.r0) tsum[static_cast<int64_t>(fa.first[s] + cb + a) * SOLVE_NR + k] = v;
+            if (lane == 0 && cb + a < w && cb + a < t.r0) atomicAdd(tsum + static_cast<int64_t>(fa.first[s] + cb + a) * SOLVE_NR + k, v);
         }
 }
 

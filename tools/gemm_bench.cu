@@ -125,6 +125,7 @@ int main(int argc, char** argv) {
         const dim3 g1((s.M + G_BM - 1) / G_BM, (s.N + G_BN - 1) / G_BN, s.ntask), g3((s.M + 1 + G3_BM - 1) / G3_BM, (s.N + 1 + G3_BN - 1) / G3_BN, s.ntask);
         run("r1_regstage", [&] { k_gemm_dmma<<<g1, 256, G_SMEM>>>(dt, L, W, 3); });
         run("r2_tma", [&] { k_gemm_tma<<<g3, 256, G3_SMEM>>>(dt, dm, L, W, 3); });
+        run("r2_tma_red", [&] { k_gemm_tma<<<g3, 256, G3_SMEM>>>(dt, dm, L, W, 7); });
         cudaFree(L); cudaFree(W); cudaFree(W0); cudaFree(Wref); cudaFree(dmax); cudaFree(dt); cudaFree(dm);
     }
     return 0;
