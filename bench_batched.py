@@ -91,7 +91,7 @@ def run(args, rank, world, local_rank, ClockSampler, METRIC, UNIT):
         pass
     hbm = float(peaks.get("hbm_gbs", 6650.0))
     achieved = bytes_per_matrix * nb / (reduce(e0.elapsed_time(e1) / args.steps) * 1e-3) * 1e-9
-    roofline = {"kernel": "k_tree_warp (one warp per matrix walks the whole assembly tree; A read from Ax, L written in CSC order)", "bound": "hbm",
+    roofline = {"kernel": "k_tree_team (one 4-warp team per matrix walks the whole assembly tree in amalgamated groups; A read from Ax, L written in CSC order)", "bound": "hbm",
                 "achieved": round(achieved, 1), "peak": hbm, "unit": "GB/s", "frac": round(achieved / hbm, 4), "traffic": None,
                 "peak_source": "MEASURED_PEAKS.json hbm_gbs (of measured)" if peaks else "fallback 6650 GB/s (of fallback)",
                 "algorithmic_bytes_per_matrix": bytes_per_matrix, "matrices_per_launch_set": nb,

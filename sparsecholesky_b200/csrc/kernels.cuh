@@ -207,16 +207,17 @@ __global__ void __launch_bounds__(128) k_extend_add(const int* __restrict__ list
         }
         const double* src = C + static_cast<int64_t>(jj) * ldc;
         double* dst = cj < wp ? Pp + static_cast<int64_t>(cj) * ldp : Cp + static_cast<int64_t>(cj - wp) * ldcb - wp;
-        // four independent gather / scatter-add chains per thread (the loop is latency bound otherwise)
+        // the additions go out as RED.ADD.F64 (atomicAdd with the result unused): performed at the L2, nothing to wait for on
+        // the SM side; every target has exactly one writer per launch (one child per parent and round), so the sums and
+        // their order are the same as with a read-modify-write
         const int T = blockDim.x;
         int ii = jj + threadIdx.x;
         for (; ii + 3 * T < mc; ii += 4 * T) {
             const int r0 = r[ii], r1 = r[ii + T], r2 = r[ii + 2 * T], r3 = r[ii + 3 * T];
             const double s0 = src[ii], s1 = src[ii + T], s2 = src[ii + 2 * T], s3 = src[ii + 3 * T];
-            const double d0 = dst[r0], d1 = dst[r1], d2 = dst[r2], d3 = dst[r3];
-            dst[r0] = d0 + s0; dst[r1] = d1 + s1; dst[r2] = d2 + s2; dst[r3] = d3 + s3;
+            atomicAdd(dst + r0, s0); atomicAdd(dst + r1, s1); atomicAdd(dst + r2, s2); atomicAdd(dst + r3, s3);
         }
-        for (; ii < mc; ii += T) dst[r[ii]] += src[ii];
+        for (; ii < mc; ii += T) atomicAdd(dst + r[ii], src[ii]);
     }
 }
 

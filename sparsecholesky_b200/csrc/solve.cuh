@@ -68,32 +68,61 @@ __global__ void __launch_bounds__(256) k_solve_diag(const SBlock* __restrict__ t
     double x[4];
 #pragma unroll
     for (int k = 0; k < 4; ++k) x[k] = i < nb ? X[i * SOLVE_NR + h + k] : 0.0;
+    // Columns in micro blocks of 8: the 8 rows of a micro block sit in 16 consecutive threads of ONE warp (tid = 2 i + h), so
+    // the substitution inside a micro block needs warp barriers only; the CTA meets once per micro block, before the rows
+    // outside it take their update (16 CTA barriers per 128 columns instead of 128).
     if (!TRANS) {
-        for (int c = 0; c < nb; ++c) {
-            if (i == c) {
-                const double rd = RD[c];
+        for (int c0 = 0; c0 < nb; c0 += 8) {
+            const int c1 = min(c0 + 8, nb);
+            if (i >= c0 && i < c0 + 8) {                       // warp-uniform per half warp; both halves of the warp take the barriers
+                for (int c = c0; c < c1; ++c) {
+                    if (i == c) {
+                        const double rd = RD[c];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) { x[k] = x[k] * rd; X[c * SOLVE_NR + h + k] = x[k]; }
+                        for (int k = 0; k < 4; ++k) { x[k] = x[k] * rd; X[c * SOLVE_NR + h + k] = x[k]; }
+                    }
+                    __syncwarp(0xffffu << (threadIdx.x & 16));
+                    if (i > c && i < c1) {
+                        const double l = S[i + c * lds];
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) x[k] = fma(-l, X[c * SOLVE_NR + h + k], x[k]);
+                    }
+                }
             }
             __syncthreads();
-            if (i > c && i < nb) {
-                const double l = S[i + c * lds];
+            if (i >= c1 && i < nb) {
+                for (int c = c0; c < c1; ++c) {
+                    const double l = S[i + c * lds];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) x[k] = fma(-l, X[c * SOLVE_NR + h + k], x[k]);
+                    for (int k = 0; k < 4; ++k) x[k] = fma(-l, X[c * SOLVE_NR + h + k], x[k]);
+                }
             }
         }
     } else {
-        for (int c = nb - 1; c >= 0; --c) {
-            if (i == c) {
-                const double rd = RD[c];
+        for (int lo = (nb - 1) & ~7; lo >= 0; lo -= 8) {       // micro blocks aligned to 8 from the left, last one first
+            const int hi = min(lo + 8, nb);
+            if (i >= lo && i < lo + 8) {
+                for (int c = hi - 1; c >= lo; --c) {
+                    if (i == c) {
+                        const double rd = RD[c];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) { x[k] = x[k] * rd; X[c * SOLVE_NR + h + k] = x[k]; }
+                        for (int k = 0; k < 4; ++k) { x[k] = x[k] * rd; X[c * SOLVE_NR + h + k] = x[k]; }
+                    }
+                    __syncwarp(0xffffu << (threadIdx.x & 16));
+                    if (i < c && i >= lo) {
+                        const double l = S[c + i * lds];          // L[c][i]
+#pragma unroll
+                        for (int k = 0; k < 4; ++k) x[k] = fma(-l, X[c * SOLVE_NR + h + k], x[k]);
+                    }
+                }
             }
             __syncthreads();
-            if (i < c) {
-                const double l = S[c + i * lds];          // L[c][i]
+            if (i < lo) {
+                for (int c = hi - 1; c >= lo; --c) {
+                    const double l = S[c + i * lds];
 #pragma unroll
-                for (int k = 0; k < 4; ++k) x[k] = fma(-l, X[c * SOLVE_NR + h + k], x[k]);
+                    for (int k = 0; k < 4; ++k) x[k] = fma(-l, X[c * SOLVE_NR + h + k], x[k]);
+                }
             }
         }
     }
