@@ -983,8 +983,21 @@ int spchol_triplet_to_csc_device(int64_t nz, const int* d_ti, const int* d_tj, c
     auto up = [](size_t b) { return (b + 255) & ~size_t(255); };
     const size_t bK = up(sizeof(unsigned long long) * nz), bI = up(sizeof(unsigned) * nz), bH = up(sizeof(unsigned) * nh),
                  bC = up(sizeof(unsigned) * (static_cast<size_t>(n) + 1)), bS = up(sizeof(unsigned) * nbs);
-    unsigned char* arena = nullptr;
-    CK(cudaMalloc(&arena, 2 * bK + 4 * bI + bH + bC + bS + 256));
+    // work space: kept between calls (grow-only, per process; cudaMalloc / cudaFree of ~40 bytes per triplet would cost more than
+    // the sort itself).  Not thread-safe: one ingest at a time per process.
+    static unsigned char* s_arena = nullptr;
+    static size_t s_arena_bytes = 0;
+    static int s_arena_dev = -1;
+    const size_t need = 2 * bK + 4 * bI + bH + bC + bS + 256;
+    int dev = 0;
+    CK(cudaGetDevice(&dev));
+    if (need > s_arena_bytes || dev != s_arena_dev) {
+        if (s_arena) { cudaSetDevice(s_arena_dev); cudaFree(s_arena); cudaSetDevice(dev); }
+        s_arena = nullptr; s_arena_bytes = 0;
+        CK(cudaMalloc(&s_arena, need));
+        s_arena_bytes = need; s_arena_dev = dev;
+    }
+    unsigned char* arena = s_arena;
     unsigned char* q = arena;
     auto take = [&](size_t b) { unsigned char* r = q; q += b; return r; };
     unsigned long long* key[2] = {reinterpret_cast<unsigned long long*>(take(bK)), reinterpret_cast<unsigned long long*>(take(bK))};
@@ -995,7 +1008,7 @@ int spchol_triplet_to_csc_device(int64_t nz, const int* d_ti, const int* d_tj, c
     unsigned* colc = reinterpret_cast<unsigned*>(take(bC));
     unsigned* sums = reinterpret_cast<unsigned*>(take(bS));
     int* bad = reinterpret_cast<int*>(take(256));
-    auto done = [&](int code) { cudaFree(arena); return code; };
+    auto done = [&](int code) { return code; };
     if (cudaMemsetAsync(bad, 0, sizeof(int), st) != cudaSuccess || cudaMemsetAsync(colc, 0, sizeof(unsigned) * (static_cast<size_t>(n) + 1), st) != cudaSuccess)
         { set_error("spchol_triplet_to_csc_device: cudaMemsetAsync failed"); return done(SPCHOL_ECUDA); }
     const unsigned gb = static_cast<unsigned>((nz + 255) / 256);

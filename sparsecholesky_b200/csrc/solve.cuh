@@ -22,7 +22,7 @@ constexpr int SOLVE_NB = 128;         // column block
 struct SBlock { int s, c0; };         // front, first column of the block
 struct SChunk { int s, c0, r0; };     // + first row of a chunk of 256 rows (forward update)
 struct SGat { int s, c0, r0, i0; };   // backward gather: 32 columns from c0 of the block ending at r0, rows [i0, i0 + SOLVE_GROWS)
-constexpr int SOLVE_GROWS = 2048;     // rows per gather CTA: a tall front (16 447 rows at the root of 128^3) is cut into chunks whose
+constexpr int SOLVE_GROWS = 256;      // rows per gather CTA: a tall front (16 447 rows at the root of 128^3) is cut into chunks whose
                                       // partial sums meet in tsum by atomicAdd -- one CTA per 32 columns streamed the whole panel (1.3 ms a launch)
 constexpr int solve_diag_smem(int nb) { return (nb * (nb | 1) + nb * SOLVE_NR + nb) * 8; }
 

@@ -46,7 +46,7 @@ def test_laplacians_and_speed(dims):
     perm = synth.nd_perm(*dims)
     ti, tj, tx, n = synth.laplacian_triplets(*dims, perm=perm)
     A, ms = sc.triplet_to_csc_matrix_gpu(ti, tj, tx, n, return_ms=True)
-    A, ms = sc.triplet_to_csc_matrix_gpu(ti, tj, tx, n, return_ms=True)     # second call: no first-launch costs
+    A, ms = sc.triplet_to_csc_matrix_gpu(ti, tj, tx, n, return_ms=True)     # second call: work space allocated, kernels loaded
     H = sc.triplet_to_csc_matrix(ti, tj, tx, n)
     same(A, H.p, H.i, H.x)
     print(f"device ingest {dims}: {len(ti)} triplets in {ms:.2f} ms")
