@@ -223,7 +223,10 @@ int  spchol_residual(spchol_plan*, const double* Ax_host, double* rel_fro);
 
 /* x = A^-1 b with the factor the plan holds: L y = b, then L^T x = y, on the device-resident supernodal panels
  * (level by level; L is streamed once per direction).  b, x: n x nrhs column-major host arrays (may alias).
- * The reference stops at the factor (it has no solve); single-GPU plans. */
+ * The reference stops at the factor (it has no solve).  Multi-GPU plans: collective (every rank calls
+ * with the same b and receives the whole x); a front is solved by the rank that holds it alone or leads its group, the
+ * subtrees below the split need no communication, the columns of the shared top of the tree are exchanged once per
+ * level (ncclAllReduce of a packed buffer), the pieces of x are summed at the end. */
 int  spchol_solve(spchol_plan*, const double* b_host, double* x_host, int nrhs);
 
 #ifdef __cplusplus

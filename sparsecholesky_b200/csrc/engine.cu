@@ -112,7 +112,7 @@ struct spchol_plan {
     // warp-per-subtree programs (tree_plan.h / tree_kernel.cuh): `tree` = the bottom subtrees of this matrix (OP_TREE),
     // `whole` = the whole tree as one task per matrix (batched factorization, BASELINE config 5)
     struct DevTree { TreeArrays ta{}; double* stash = nullptr; int f_stride = 0; int64_t stash_entries = 0; bool on = false; };
-    DevTree tree, whole;
+    DevTree tree, tree2, whole;
     double* bStash = nullptr; int* binfo = nullptr; int b_chunk = 0;              // batched factorization buffers
     double *hbA = nullptr, *hbL = nullptr; int* hbI = nullptr; int hb_cap = 0;     // device staging of the host-buffer batched call
     cudaEvent_t hb_ev[2 * 8] = {nullptr}; cudaStream_t stream4 = nullptr;
@@ -141,6 +141,11 @@ struct spchol_plan {
     // triangular solves (built on first use): per (level, block step) slices of the task arrays
     struct SolveStep { int b0, bn, u0, un, g0, gn, smem; };
     std::vector<SolveStep> solve_steps;        // forward order; the backward solve walks it in reverse
+    std::vector<int> solve_level_ptr;          // steps of level l: solve_steps[solve_level_ptr[l] .. solve_level_ptr[l + 1])
+    // multi-rank solve: columns more than one rank touches (k_top_*), the exchange buffer, the columns this rank solves,
+    // the first level with such a front
+    int* d_top_idx = nullptr; double* d_top_buf = nullptr; unsigned char* d_solve_mine = nullptr;
+    int64_t n_top = 0; int solve_shared_level = 0;
     SBlock* d_sblocks = nullptr; SChunk* d_supd = nullptr; SGat* d_sgat = nullptr;
     bool solve_ready = false;
     double* d_solve_v = nullptr;               // work vectors of spchol_solve (3 n SOLVE_NR doubles, allocated on first use)
@@ -328,8 +333,10 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
         const int64_t before = launches;
         switch (op.kind) {
         case OP_TREE: {
-            static const int nw = getenv("SPCHOL_TREE_NW") ? atoi(getenv("SPCHOL_TREE_NW")) : 1;
-            launch_tree(nw, op.count, p->tree.f_stride, st, p->tree.ta, dAx, p->dL, p->dW, p->tree.stash, nullptr, p->dinfo, 0, 0, 0, 0, 0, 0, 0);
+            static const int nw1 = getenv("SPCHOL_TREE_NW") ? atoi(getenv("SPCHOL_TREE_NW")) : 1;
+            static const int nw2 = getenv("SPCHOL_TREE2_NW") ? atoi(getenv("SPCHOL_TREE2_NW")) : 4;
+            const spchol_plan::DevTree& T = op.begin ? p->tree2 : p->tree;
+            launch_tree(op.begin ? nw2 : nw1, op.count, T.f_stride, st, T.ta, dAx, p->dL, p->dW, T.stash, nullptr, p->dinfo, 0, 0, 0, 0, 0, 0, 0);
             ++launches;
         } break;
         case OP_SMALL: {
@@ -495,6 +502,8 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
         if (const char* v = getenv("SPCHOL_TREE_CAP")) { const int x = atoi(v); if (x >= 8 && x <= TW_MAX_M) opt.tree_cap_m = x; }
         if (const char* v = getenv("SPCHOL_BATCH_GROUP_M")) { const int x = atoi(v); if (x >= 0 && x <= TW_MAX_M) opt.batch_group_m = x; }
         if (const char* v = getenv("SPCHOL_TREE_WORK")) { const double x = atof(v); if (x > 0) opt.tree_work = x; }
+        if (const char* v = getenv("SPCHOL_TREE2_CAP")) { const int x = atoi(v); if (x >= 0 && x <= TW_MAX_M) opt.tree2_cap_m = x; }
+        if (const char* v = getenv("SPCHOL_TREE2_WORK")) { const double x = atof(v); if (x > 0) opt.tree2_work = x; }
         if (const char* v = getenv("SPCHOL_NB")) { const int x = atoi(v); if (x >= 128) opt.NB = x; }
         if (const char* v = getenv("SPCHOL_NB_WIDE")) { const int x = atoi(v); if (x >= 128) opt.NB_wide = x; }
         if (const char* v = getenv("SPCHOL_WIDE_W")) { const int x = atoi(v); if (x >= 1) opt.wide_w = x; }
@@ -565,6 +574,8 @@ static int plan_create_impl(const spchol_symbolic* sym, int device, spchol_comm*
         };
         if ((rc = up_tree(H.tree, p->tree, nullptr))) return fail(rc);
         if (p->tree.on && (rc = dalloc(p, p->tree.stash_entries, &p->tree.stash))) return fail(rc);
+        if ((rc = up_tree(H.tree2, p->tree2, nullptr))) return fail(rc);
+        if (p->tree2.on && (rc = dalloc(p, p->tree2.stash_entries, &p->tree2.stash))) return fail(rc);
         if (!H.tree_whole.tasks.empty() && H.nnzL <= INT_MAX && !H.l_src.empty()) {
             std::vector<int> inv(static_cast<size_t>(H.lbuf_entries), -1);        // L-buffer offset -> CSC index
             for (int64_t e = 0; e < H.nnzL; ++e) if (H.l_src[e] >= 0) inv[static_cast<size_t>(H.l_src[e])] = static_cast<int>(e);
@@ -1193,15 +1204,20 @@ static int solve_prepare(spchol_plan* p) {
     std::vector<std::vector<int>> by_level(H.nlevels);
     for (int s = 0; s < H.ns; ++s) by_level[H.level[s]].push_back(s);
     std::vector<SBlock> blocks; std::vector<SChunk> upd; std::vector<SGat> gat;
+    // multi-rank plans: a front is solved by the rank that holds it alone or leads its group (that rank has the whole panel
+    // and the row list, ridx_off >= 0)
+    const bool multi = H.world > 1;
+    auto mine = [&](int s) { return !multi || H.ridx_off[s] >= 0; };
+    p->solve_level_ptr.assign(H.nlevels + 1, 0);
     for (int l = 0; l < H.nlevels; ++l) {
         int maxJ = 0;
-        for (int s : by_level[l]) maxJ = std::max(maxJ, (H.w[s] + SOLVE_NB - 1) / SOLVE_NB);
+        for (int s : by_level[l]) if (mine(s)) maxJ = std::max(maxJ, (H.w[s] + SOLVE_NB - 1) / SOLVE_NB);
         for (int j = 0; j < maxJ; ++j) {
             spchol_plan::SolveStep st{static_cast<int>(blocks.size()), 0, static_cast<int>(upd.size()), 0, static_cast<int>(gat.size()), 0, 0};
             int mnb = 0;
             for (int s : by_level[l]) {
                 const int c0 = j * SOLVE_NB;
-                if (c0 >= H.w[s]) continue;
+                if (c0 >= H.w[s] || !mine(s)) continue;
                 const int nb = std::min(SOLVE_NB, H.w[s] - c0), end = c0 + nb;
                 mnb = std::max(mnb, nb);
                 blocks.push_back({s, c0});
@@ -1212,6 +1228,29 @@ static int solve_prepare(spchol_plan* p) {
             st.gn = static_cast<int>(gat.size()) - st.g0; st.smem = solve_diag_smem(mnb);
             p->solve_steps.push_back(st);
         }
+        p->solve_level_ptr[l + 1] = static_cast<int>(p->solve_steps.size());
+    }
+    if (multi) {
+        // shared[s]: some descendant of s is solved by another rank -- its columns receive updates from (forward) and are read
+        // by (backward) more than one rank
+        std::vector<char> shared(H.ns, 0);
+        for (int s = 0; s < H.ns; ++s) {                 // children before parents
+            const int q = H.parent[s];
+            if (q >= 0 && (shared[s] || H.own_lo[s] != H.own_lo[q])) shared[q] = 1;
+        }
+        std::vector<int> top;
+        std::vector<unsigned char> keep(static_cast<size_t>(H.n), 0);
+        p->solve_shared_level = H.nlevels;
+        for (int s = 0; s < H.ns; ++s) {
+            if (shared[s]) {
+                p->solve_shared_level = std::min(p->solve_shared_level, H.level[s]);
+                for (int c = 0; c < H.w[s]; ++c) top.push_back(H.first[s] + c);
+            }
+            if (H.own_lo[s] == H.rank) for (int c = 0; c < H.w[s]; ++c) keep[H.first[s] + c] = 1;
+        }
+        p->n_top = static_cast<int64_t>(top.size());
+        if ((rc = upload(p, top, &p->d_top_idx)) || (rc = upload(p, keep, &p->d_solve_mine)) ||
+            (rc = dalloc(p, std::max<int64_t>(p->n_top, 1) * SOLVE_NR, &p->d_top_buf))) return rc;
     }
     if ((rc = upload(p, blocks, &p->d_sblocks)) || (rc = upload(p, upd, &p->d_supd)) || (rc = upload(p, gat, &p->d_sgat))) return rc;
     CK(cudaFuncSetAttribute(k_solve_diag<false>, cudaFuncAttributeMaxDynamicSharedMemorySize, solve_diag_smem(SOLVE_NB)));
@@ -1221,11 +1260,17 @@ static int solve_prepare(spchol_plan* p) {
 }
 
 // x = A^-1 b with the factor the plan holds (last spchol_factor* call): L y = b, L^T x = y on the supernodal panels.
-// b, x: n x nrhs column-major host arrays (may alias).  Single-GPU plans.
+// b, x: n x nrhs column-major host arrays (may alias).
+// Multi-rank plans: collective -- every rank calls with the same b and receives the whole x.  Every front is solved by ONE
+// rank (the holder, or the leader of the group that factored it: it has the whole panel).  The subtrees below the split need
+// no communication; from the first level with a front whose descendants sit on several ranks upwards, the ranks exchange
+// the columns of those fronts once per level (k_top_gather, ncclAllReduce, k_top_store): updates summed on the way up,
+// solved values handed out on the way down.  The pieces of x are summed at the end.
 int spchol_solve(spchol_plan* p, const double* b, double* x, int nrhs) {
     if (!p || !b || !x || nrhs < 1) { set_error("spchol_solve: bad argument"); return SPCHOL_EINVAL; }
     const HostPlan& H = p->H;
-    if (H.world > 1) { set_error("spchol_solve: single-GPU plans only"); return SPCHOL_EINVAL; }
+    NcclApi* nc = H.world > 1 ? nccl_api() : nullptr;
+    if (H.world > 1 && (!nc || !p->comm)) { set_error("spchol_solve: multi-rank plan without a communicator"); return SPCHOL_EINVAL; }
     CK(cudaSetDevice(p->device));
     int rc;
     if ((rc = solve_prepare(p))) return rc;
@@ -1238,19 +1283,50 @@ int spchol_solve(spchol_plan* p, const double* b, double* x, int nrhs) {
     double* stage = dv + 2 * nv;
     int64_t launches = 0;
     cudaError_t e = cudaSuccess;
-    for (int k0 = 0; k0 < nrhs && e == cudaSuccess; k0 += SOLVE_NR) {
+    bool nccl_failed = false;
+    const int64_t ne_top = p->n_top * SOLVE_NR;
+    const unsigned top_grid = static_cast<unsigned>((ne_top + 255) / 256);
+    auto exchange = [&](bool down) {
+        if (!nc || ne_top == 0) return;
+        // up: every copy of the shared columns is summed, the solving rank keeps the sum, the others start again from zero;
+        // down: the value of every shared column from the rank that solves it, stored everywhere (solve.cuh)
+        if (down) k_top_gather<true><<<top_grid, 256, 0, st>>>(ne_top, p->d_top_idx, p->d_solve_mine, dv, p->d_top_buf);
+        else k_top_gather<false><<<top_grid, 256, 0, st>>>(ne_top, p->d_top_idx, p->d_solve_mine, dv, p->d_top_buf);
+        if (nc->AllReduce(p->d_top_buf, p->d_top_buf, static_cast<size_t>(ne_top), kNcclFloat64, kNcclSum, p->comm->world_comm, st) != 0)
+            nccl_failed = true;
+        if (down) k_top_store<false><<<top_grid, 256, 0, st>>>(ne_top, p->d_top_idx, p->d_solve_mine, dv, p->d_top_buf);
+        else k_top_store<true><<<top_grid, 256, 0, st>>>(ne_top, p->d_top_idx, p->d_solve_mine, dv, p->d_top_buf);
+        launches += 2;
+    };
+    for (int k0 = 0; k0 < nrhs && e == cudaSuccess && !nccl_failed; k0 += SOLVE_NR) {
         const int nr = std::min(SOLVE_NR, nrhs - k0);
         cudaMemcpyAsync(stage, b + static_cast<int64_t>(k0) * H.n, sizeof(double) * H.n * nr, cudaMemcpyHostToDevice, st);
         k_solve_pack<<<static_cast<unsigned>((nv + 255) / 256), 256, 0, st>>>(H.n, nr, stage, dv, dv + nv);
-        for (const auto& sp : p->solve_steps) {         // L y = b
-            k_solve_diag<false><<<sp.bn, 256, sp.smem, st>>>(p->d_sblocks + sp.b0, p->fa, p->dL, dv, nullptr);
-            if (sp.un) k_solve_update<<<sp.un, 256, 0, st>>>(p->d_supd + sp.u0, p->fa, p->d_rowidx, p->dL, dv);
-            launches += 1 + (sp.un ? 1 : 0);
+        if (nc && ne_top) { k_top_clear_others<<<top_grid, 256, 0, st>>>(ne_top, p->d_top_idx, p->d_solve_mine, dv); ++launches; }
+        for (int l = 0; l < H.nlevels; ++l) {            // L y = b
+            if (nc && l >= p->solve_shared_level) exchange(false);
+            for (int q = p->solve_level_ptr[l]; q < p->solve_level_ptr[l + 1]; ++q) {
+                const auto& sp = p->solve_steps[q];
+                if (!sp.bn) continue;
+                k_solve_diag<false><<<sp.bn, 256, sp.smem, st>>>(p->d_sblocks + sp.b0, p->fa_r, p->dL, dv, nullptr);
+                if (sp.un) k_solve_update<<<sp.un, 256, 0, st>>>(p->d_supd + sp.u0, p->fa_r, p->d_rowidx, p->dL, dv);
+                launches += 1 + (sp.un ? 1 : 0);
+            }
         }
-        for (auto it = p->solve_steps.rbegin(); it != p->solve_steps.rend(); ++it) {     // L^T x = y
-            if (it->gn) k_solve_gather<<<it->gn, 256, 0, st>>>(p->d_sgat + it->g0, p->fa, p->d_rowidx, p->dL, dv, dv + nv);
-            k_solve_diag<true><<<it->bn, 256, it->smem, st>>>(p->d_sblocks + it->b0, p->fa, p->dL, dv, dv + nv);
-            launches += 1 + (it->gn ? 1 : 0);
+        for (int l = H.nlevels - 1; l >= 0; --l) {       // L^T x = y
+            for (int q = p->solve_level_ptr[l + 1] - 1; q >= p->solve_level_ptr[l]; --q) {
+                const auto& sp = p->solve_steps[q];
+                if (!sp.bn) continue;
+                if (sp.gn) k_solve_gather<<<sp.gn, 256, 0, st>>>(p->d_sgat + sp.g0, p->fa_r, p->d_rowidx, p->dL, dv, dv + nv);
+                k_solve_diag<true><<<sp.bn, 256, sp.smem, st>>>(p->d_sblocks + sp.b0, p->fa_r, p->dL, dv, dv + nv);
+                launches += 1 + (sp.gn ? 1 : 0);
+            }
+            if (nc && l >= p->solve_shared_level) exchange(true);
+        }
+        if (nc) {                                        // every row of x was computed by exactly one rank
+            k_solve_mask<<<static_cast<unsigned>((nv + 255) / 256), 256, 0, st>>>(nv, p->d_solve_mine, dv);
+            if (nc->AllReduce(dv, dv, static_cast<size_t>(nv), kNcclFloat64, kNcclSum, p->comm->world_comm, st) != 0) nccl_failed = true;
+            ++launches;
         }
         k_solve_unpack<<<static_cast<unsigned>((static_cast<int64_t>(H.n) * nr + 255) / 256), 256, 0, st>>>(H.n, nr, dv, stage);
         cudaMemcpyAsync(x + static_cast<int64_t>(k0) * H.n, stage, sizeof(double) * H.n * nr, cudaMemcpyDeviceToHost, st);
@@ -1259,6 +1335,7 @@ int spchol_solve(spchol_plan* p, const double* b, double* x, int nrhs) {
         if (e == cudaSuccess) e = cudaGetLastError();
     }
     p->last_launches = launches;
+    if (nccl_failed) { set_error("spchol_solve: ncclAllReduce failed"); return SPCHOL_ENCCL; }
     if (e != cudaSuccess) { set_error(std::string("spchol_solve: ") + cudaGetErrorString(e)); return SPCHOL_ECUDA; }
     return SPCHOL_OK;
 }

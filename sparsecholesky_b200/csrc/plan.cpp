@@ -752,6 +752,20 @@ void build_plan(const Symbolic& S, const PlanOptions& opt, HostPlan& P) {
             P.ops.push_back(op);
             P.n_tree = static_cast<int64_t>(P.tree.fronts.size());
         }
+        // second tier: the subtrees of fronts up to tree2_cap_m rows that sit on top of the first tier, one 4-warp team each.
+        // These fronts (2D 1024^2: 6 000 of them on ~8 levels) would otherwise take one launch per level of one CTA per front.
+        if (opt.tree2_cap_m > opt.tree_cap_m) {
+            std::vector<char> in2;
+            const std::vector<int> roots2 = choose_subtrees(P, opt.tree2_cap_m, opt.tree2_work, in2, &in_tree);
+            if (!roots2.empty()) {
+                for (int s : roots2) if (P.m[s] > P.w[s] && P.parent[s] >= 0) ws_alloc(s);
+                build_tree_program(P, roots2, false, a_front, a_fcol, a_fpos, P.tree2, &in_tree);
+                Op op{}; op.kind = OP_TREE; op.begin = 1; op.count = static_cast<int>(P.tree2.tasks.size()); op.level = 0;
+                P.ops.push_back(op);
+                P.n_tree += static_cast<int64_t>(P.tree2.fronts.size());
+                for (int s = 0; s < ns; ++s) if (in2[s]) in_tree[s] = 1;
+            }
+        }
     }
     for (int lv = 0; lv < nlev; ++lv) {
         std::vector<int> local_a, local_b, dists;

@@ -58,7 +58,7 @@ struct CopyTask {
 enum OpKind : int { OP_SMALL = 0, OP_ZERO = 1, OP_EXTADD = 2, OP_POTRF = 3, OP_TRSM = 4, OP_GEMM = 5, OP_COMM = 6, OP_COPY = 7,
                     OP_EV_RECORD = 8, OP_EV_WAIT = 9,
                     OP_EXPORT = 10,     // ranges of the L buffer that are final from here on (read-back of wide fronts, see ExportTask)
-                    OP_TREE = 11 };     // the warp-per-subtree program (HostPlan::tree, tree_plan.h): begin = first task, count = tasks
+                    OP_TREE = 11 };     // the warp-per-subtree program (HostPlan::tree, tree_plan.h): begin = tier (0: HostPlan::tree, 1: tree2), count = tasks
 constexpr int kEventRing = 64;      // the engine keeps this many CUDA events; event id -> slot id % kEventRing
 struct Op {
     int kind;
@@ -92,6 +92,8 @@ struct PlanOptions {
                                // Measured on 2D 1024^2 (small-front time, final kernel): 2.71 ms at 48 rows / 1 warp, 2.97 at 64 / 1, 3.05 at 64 / 2,
                                // 3.03 ms without subtree tasks
     double tree_work = 2.5e6;  // dense flops of a subtree task (the unit of load balance)
+    int tree2_cap_m = 128;     // second tier of subtree tasks on top of the first (4-warp teams; 0: none): fronts up to this many rows
+    double tree2_work = 3e7;   // dense flops of a second-tier task
     int batch_group_m = 117;   // batched whole-tree program: fronts are amalgamated into groups of up to this many rows (tree_plan.h,
                                // build_group_program; 117 rows = 55 KB packed = four teams per SM); 0: one step per front of the plan
     int export_mark_w = 1024;  // > 0: fronts at least this wide announce every finished block column (OP_EXPORT): spchol_factor_lbuf reads
@@ -144,6 +146,7 @@ struct HostPlan {
     std::vector<char> front_marked;  // per front: 1 if all of its panel is announced by OP_EXPORT ops (not by its level)
     std::vector<Op> ops;
     TreeProgram tree;                // subtrees at the bottom of the tree, one warp each (single-rank plans; empty: none)
+    TreeProgram tree2;               // second tier: subtrees of mid-size fronts on top of `tree` (their leaves read the first tier's blocks)
     TreeProgram tree_whole;          // the whole tree as ONE task (batched factorization; only when every front has m <= TW_MAX_M)
     int n_events = 0;                // event ids handed out (OP_EV_RECORD count)
     int max_potrf_slots = 0;

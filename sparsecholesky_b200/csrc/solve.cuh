@@ -34,6 +34,41 @@ __global__ void k_solve_pack(int n, int nr, const double* __restrict__ cols, dou
     v[e] = k < nr ? cols[static_cast<int64_t>(k) * n + i] : 0.0;
     tsum[e] = 0.0;
 }
+// Multi-rank solve (engine.cu, spchol_solve): the entries of the work vector that more than one rank touches -- the columns of
+// the fronts at the top of the tree that have descendants on another rank -- are listed in idx[]; mine[i] != 0 where this
+// rank solves column i.  On the way up only the solving rank holds the VALUE of such a column (b minus the updates that
+// have arrived), the other ranks hold the updates they have produced since the last exchange, starting from zero: an
+// exchange sums the copies (ncclAllReduce between k_top_gather and k_top_store), the solver keeps the sum, the others
+// start again from zero -- the same terms as the sequential substitution, added in another order, no differences taken.
+// On the way down a column is REPLACED everywhere by the value its solver holds (k_top_gather with mine: the others
+// contribute zero).
+__global__ void k_top_clear_others(int64_t ne, const int* __restrict__ idx, const unsigned char* __restrict__ mine, double* __restrict__ v) {
+    const int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    if (e >= ne) return;
+    const int i = idx[e / SOLVE_NR];
+    if (!mine[i]) v[static_cast<int64_t>(i) * SOLVE_NR + e % SOLVE_NR] = 0.0;
+}
+template <bool ONLY_MINE>
+__global__ void k_top_gather(int64_t ne, const int* __restrict__ idx, const unsigned char* __restrict__ mine,
+                             const double* __restrict__ v, double* __restrict__ out) {
+    const int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    if (e >= ne) return;
+    const int i = idx[e / SOLVE_NR];
+    out[e] = (!ONLY_MINE || mine[i]) ? v[static_cast<int64_t>(i) * SOLVE_NR + e % SOLVE_NR] : 0.0;
+}
+template <bool ONLY_MINE>
+__global__ void k_top_store(int64_t ne, const int* __restrict__ idx, const unsigned char* __restrict__ mine, double* __restrict__ v,
+                            const double* __restrict__ in) {
+    const int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    if (e >= ne) return;
+    const int i = idx[e / SOLVE_NR];
+    v[static_cast<int64_t>(i) * SOLVE_NR + e % SOLVE_NR] = (!ONLY_MINE || mine[i]) ? in[e] : 0.0;
+}
+// keeps the rows of the solution this rank computed (mine[i] != 0), clears the others: the sum over the ranks is the solution
+__global__ void k_solve_mask(int64_t ne, const unsigned char* __restrict__ mine, double* __restrict__ v) {
+    const int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
+    if (e < ne && !mine[e / SOLVE_NR]) v[e] = 0.0;
+}
 __global__ void k_solve_unpack(int n, int nr, const double* __restrict__ v, double* __restrict__ cols) {
     const int64_t e = blockIdx.x * static_cast<int64_t>(blockDim.x) + threadIdx.x;
     if (e >= static_cast<int64_t>(n) * nr) return;

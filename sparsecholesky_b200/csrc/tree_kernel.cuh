@@ -153,6 +153,16 @@ TK_DEVICE void tree_team_body(const TreeArrays& ta, const TwTask task, const dou
             TK_SYNCTEAM();                                 // two sources may hit the same entry from different threads
             const TwStash st = ta.stashes[d.stash0 + q];
             const int* TK_RESTRICT rm = ta.rmap + st.map_off;
+            if (st.mc < 0) {                               // left in the workspace by an earlier tier: column-major lower, ld = even(mc)
+                const int mc = -st.mc, ldc = (mc + 1) & ~1;
+                const double* src = W + st.src;
+                for (int jr = warp; jr < mc; jr += NW) {
+                    const int bJ = tk_tri(TK_LDG(rm + jr));
+                    const double* col = src + static_cast<int64_t>(mc - 1 - jr) * ldc + (mc - 1);     // reversed row ir sits at col[-ir]
+                    for (int ir = lane; ir <= jr; ir += 32) F[bJ + TK_LDG(rm + ir)] += col[-ir];
+                }
+                continue;
+            }
             const double* TK_RESTRICT src = Stash + st.src;
             for (int jr = warp; jr < st.mc; jr += NW) {
                 const int bJ = tk_tri(TK_LDG(rm + jr));

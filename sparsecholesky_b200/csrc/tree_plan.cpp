@@ -12,19 +12,22 @@ inline int even_up(int v) { return (v + 1) & ~1; }
 inline double front_flops(double w, double m) { return w * m * m - m * w * (w - 1) + (w - 1) * w * (2 * w - 1) / 6.0; }
 }  // namespace
 
-std::vector<int> choose_subtrees(const HostPlan& P, int cap_m, double work_limit, std::vector<char>& in_tree) {
+std::vector<int> choose_subtrees(const HostPlan& P, int cap_m, double work_limit, std::vector<char>& in_tree,
+                                 const std::vector<char>* below) {
     const int ns = P.ns;
     cap_m = std::min(cap_m, TW_MAX_M);
     std::vector<double> sub(ns);
     std::vector<int> submax(ns);
+    auto gone = [&](int s) { return below && (*below)[s]; };      // factored by an earlier tier: not part of this forest
     for (int s = 0; s < ns; ++s) { sub[s] = front_flops(P.w[s], P.m[s]); submax[s] = P.m[s]; }
     for (int s = 0; s < ns; ++s) {                    // children have smaller ids than parents
         const int p = P.parent[s];
-        if (p >= 0) { sub[p] += sub[s]; submax[p] = std::max(submax[p], submax[s]); }
+        if (p >= 0 && !gone(s)) { sub[p] += sub[s]; submax[p] = std::max(submax[p], submax[s]); }
     }
     in_tree.assign(ns, 0);
     std::vector<int> roots;
-    for (int s = 0; s < ns; ++s) in_tree[s] = (submax[s] <= cap_m && sub[s] <= work_limit && P.holds(s) && P.own_n[s] == 1) ? 1 : 0;
+    for (int s = 0; s < ns; ++s)
+        in_tree[s] = (!gone(s) && submax[s] <= cap_m && sub[s] <= work_limit && P.holds(s) && P.own_n[s] == 1) ? 1 : 0;
     for (int s = 0; s < ns; ++s) {
         if (!in_tree[s]) continue;
         const int p = P.parent[s];
@@ -36,9 +39,11 @@ std::vector<int> choose_subtrees(const HostPlan& P, int cap_m, double work_limit
 }
 
 void build_tree_program(const HostPlan& P, const std::vector<int>& roots_in, bool whole, const std::vector<int>& a_front,
-                        const std::vector<int>& a_col, const std::vector<int>& a_pos, TreeProgram& out) {
+                        const std::vector<int>& a_col, const std::vector<int>& a_pos, TreeProgram& out,
+                        const std::vector<char>* below) {
     out = TreeProgram();
     const int ns = P.ns;
+    auto gone = [&](int s) { return below && (*below)[s]; };
     std::vector<int> roots = roots_in;
     if (whole) {
         roots.clear();
@@ -71,7 +76,7 @@ void build_tree_program(const HostPlan& P, const std::vector<int>& roots_in, boo
         std::vector<int> lidx;                                  // stack frame -> index into local
         auto ordered_children = [&](int s) {
             kids.clear();
-            for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) kids.push_back(P.child_idx[q]);
+            for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) if (!gone(P.child_idx[q])) kids.push_back(P.child_idx[q]);
             std::stable_sort(kids.begin(), kids.end(), [&](int a, int b) { return (P.m[a] - P.w[a]) < (P.m[b] - P.w[b]); });
             return kids;
         };
@@ -114,7 +119,7 @@ void build_tree_program(const HostPlan& P, const std::vector<int>& roots_in, boo
             d.an = static_cast<int>(out.a_src.size()) - d.a0;
             // children: the last one in visiting order was factored just before s and is carried (if it has a block)
             kids.clear();
-            for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) kids.push_back(P.child_idx[q]);
+            for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) if (!gone(P.child_idx[q])) kids.push_back(P.child_idx[q]);
             std::stable_sort(kids.begin(), kids.end(), [&](int a, int b) { return (P.m[a] - P.w[a]) < (P.m[b] - P.w[b]); });
             auto push_map = [&](int c) {
                 const int mc = P.m[c] - P.w[c];
@@ -149,6 +154,14 @@ void build_tree_program(const HostPlan& P, const std::vector<int>& roots_in, boo
                 out.stashes.push_back(st);
                 sp = live.back().second;              // pop
                 live.pop_back();
+            }
+            // children an earlier tier factored: their blocks wait in the level program's workspace (column-major, ld = even(mc));
+            // a negative order tells the kernel
+            for (int q = P.child_ptr[s]; q < P.child_ptr[s + 1]; ++q) {
+                const int c = P.child_idx[q];
+                if (!gone(c) || P.m[c] == P.w[c]) continue;
+                if (P.cb_off[c] < 0) throw std::runtime_error("spchol: block of a lower-tier subtree root has no workspace slot");
+                out.stashes.push_back(TwStash{-(P.m[c] - P.w[c]), push_map(c), P.cb_off[c]});
             }
             d.nstash = static_cast<int>(out.stashes.size()) - d.stash0;
             d.map_n = static_cast<int>(out.rmap.size()) - d.map_lo;

@@ -40,7 +40,9 @@ struct alignas(16) TwFront {                  // 80 bytes; the kernel keeps two 
     int64_t panel_off;                        // panel in the L buffer
     int64_t cb_out;                           // TW_CB_STD: workspace offset; else (no carry, mb > 0): offset in the stash area
 };
-struct alignas(16) TwStash { int mc, map_off; int64_t src; };     // a stashed child block and its (forward) map into the parent
+struct alignas(16) TwStash { int mc, map_off; int64_t src; };     // a stashed child block and its (forward) map into the parent;
+                                                                  // mc < 0: a block of order -mc in the level program's workspace
+                                                                  // (column-major lower, ld = even(-mc)) left by an earlier tier
 struct TwTask { int front0, nfront; int64_t stash_base; };         // stash_base: start of the task's private stack in the stash area
 
 struct TreeProgram {
@@ -66,14 +68,18 @@ struct TreeProgram {
 // whose dense flops stay below work_limit (tasks are the unit of load balance).  in_tree[s] marks the fronts covered;
 // returns the roots (ascending).  Subtrees with fewer than min_fronts fronts are not worth a task of their own only if
 // they are single fronts whose parent is not covered either -- those stay with the level program (min_fronts = 1 keeps all).
-std::vector<int> choose_subtrees(const HostPlan& P, int cap_m, double work_limit, std::vector<char>& in_tree);
+// below (optional): fronts an earlier tier of subtree tasks factors -- they are left out of the forest, so the subtrees chosen
+// here sit on top of them (their blocks come in through the level program's workspace).
+std::vector<int> choose_subtrees(const HostPlan& P, int cap_m, double work_limit, std::vector<char>& in_tree,
+                                 const std::vector<char>* below = nullptr);
 
 // Builds the program: one task per root of `roots` (whole = false), or ONE task that walks every tree of the forest
 // (whole = true; roots ignored) -- the batched factorization.  a_front/a_col/a_pos: front, column inside the front and
 // row position inside the front of every stored entry of A (from build_plan).  std_cb: blocks of task roots go to
 // P.cb_off (the level program consumes them).
 void build_tree_program(const HostPlan& P, const std::vector<int>& roots, bool whole, const std::vector<int>& a_front,
-                        const std::vector<int>& a_col, const std::vector<int>& a_pos, TreeProgram& out);
+                        const std::vector<int>& a_col, const std::vector<int>& a_pos, TreeProgram& out,
+                        const std::vector<char>* below = nullptr);
 
 // The batched whole-tree program over AMALGAMATED GROUPS: a group is a connected piece of the assembly tree (a top front
 // plus descendants, grown bottom-up while its row set U = columns of the members ++ rows below the top stays within cap_m

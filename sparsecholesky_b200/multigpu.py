@@ -106,6 +106,16 @@ def chol_dist(A, plan):
     return Expected(value=CscMatrix(A.n, S.p, S.i, Lx, Sym.none))
 
 
+def solve_dist(plan, b):
+    """Collective x = A^-1 b with the factor the plan holds after chol_dist (spchol_solve on a multi-rank plan): every rank
+    passes the same b (n,) or (n, nrhs) and receives the whole x.  Each front is solved by the rank that holds or leads it;
+    the ranks exchange their contributions to the shared top of the tree once per level (ncclAllReduce)."""
+    B = np.asfortranarray(np.asarray(b, np.float64).reshape(plan.S.n, -1))
+    X = np.empty_like(B, order="F")
+    check(lib().spchol_solve(plan.h, B.ctypes.data, X.ctypes.data, B.shape[1]), "solve_dist")
+    return X.reshape(np.shape(b))
+
+
 def batch_shard(nbatch, rank, world):
     """[b0, b1) of the batch index this rank factors (config 5: no collective on the data path)."""
     base, rem = divmod(nbatch, world)

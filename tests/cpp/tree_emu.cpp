@@ -133,6 +133,10 @@ extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double*
         opt.small_max_m = 1 << 20;          // everything above the subtrees on the whole-front path
         opt.tree = 1; opt.tree_cap_m = cap_m; opt.tree_work = work;
         opt.batch_group_m = whole == 2 ? cap_m : 0;
+        // second tier of subtree tasks (whole = 0 only): TREEEMU_TIER2 = "cap_m,work,nw"
+        int cap2 = 0, nw2 = 4; double work2 = 3e7;
+        if (const char* v = std::getenv("TREEEMU_TIER2")) std::sscanf(v, "%d,%lf,%d", &cap2, &work2, &nw2);
+        opt.tree2_cap_m = whole ? 0 : cap2; opt.tree2_work = work2;
         build_plan(S, opt, H);
         if (H.n_large > 0) return fail("pattern has fronts beyond the shared-memory front kernel");
         const TreeProgram& T = whole ? H.tree_whole : H.tree;
@@ -141,11 +145,11 @@ extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double*
             stats[0] = static_cast<int64_t>(T.tasks.size()); stats[1] = static_cast<int64_t>(T.fronts.size());
             stats[2] = static_cast<int64_t>(T.stashes.size()); stats[3] = T.stash_entries; stats[4] = T.cap_m; stats[5] = H.ns;
             stats[6] = T.n_groups; stats[7] = static_cast<int64_t>(T.padded_flops);
+            if (!whole) { stats[6] = static_cast<int64_t>(H.tree2.tasks.size()); stats[7] = static_cast<int64_t>(H.tree2.fronts.size()); }
         }
         const double nan = std::numeric_limits<double>::quiet_NaN();
         std::vector<double> Lb(static_cast<size_t>(H.lbuf_entries), 0.0);
         std::vector<double> Wb(static_cast<size_t>(std::max<int64_t>(H.ws_entries, 1)), nan);      // poison: read-before-write shows
-        std::vector<double> Sb(static_cast<size_t>(std::max<int64_t>(T.stash_entries, 1)), nan);
         std::vector<int> csc_map;
         if (whole) {
             csc_map.assign(static_cast<size_t>(H.lbuf_entries), -1);
@@ -155,18 +159,23 @@ extern "C" int treeemu_factor(int n, const int* Ap, const int* Ai, const double*
             for (int64_t i = 0; i < H.nnzA; ++i) if (H.a_dest[i] >= 0) Lb[H.a_dest[i]] = Ax[i];
         }
         int info = 0x7f7f7f7f;
-        if (!T.tasks.empty()) {
+        auto run_prog = [&](const TreeProgram& Q, int teams) -> bool {
+            if (Q.tasks.empty()) return true;
+            std::vector<double> Sq(static_cast<size_t>(std::max<int64_t>(Q.stash_entries, 1)), nan);
             TreeArrays ta{};
-            ta.tasks = T.tasks.data(); ta.ntasks = static_cast<int>(T.tasks.size()); ta.fronts = T.fronts.data(); ta.stashes = T.stashes.data();
-            ta.rmap = T.rmap.data(); ta.a_src = T.a_src.data(); ta.a_dst = T.a_dst.data(); ta.csc_map = csc_map.data();
-            ta.out_src = T.out_src.data(); ta.out_dst = T.out_dst.data(); ta.gcol = T.gcol.data();
-            switch (nw) {
-            case 1: run_tasks<1>(ta, Ax, Lb.data(), Wb.data(), Sb.data(), Lx, &info, T.cap_m, whole ? 1 : 0); break;
-            case 2: run_tasks<2>(ta, Ax, Lb.data(), Wb.data(), Sb.data(), Lx, &info, T.cap_m, whole ? 1 : 0); break;
-            case 4: run_tasks<4>(ta, Ax, Lb.data(), Wb.data(), Sb.data(), Lx, &info, T.cap_m, whole ? 1 : 0); break;
-            default: return fail("nw must be 1, 2 or 4");
+            ta.tasks = Q.tasks.data(); ta.ntasks = static_cast<int>(Q.tasks.size()); ta.fronts = Q.fronts.data(); ta.stashes = Q.stashes.data();
+            ta.rmap = Q.rmap.data(); ta.a_src = Q.a_src.data(); ta.a_dst = Q.a_dst.data(); ta.csc_map = csc_map.data();
+            ta.out_src = Q.out_src.data(); ta.out_dst = Q.out_dst.data(); ta.gcol = Q.gcol.data();
+            switch (teams) {
+            case 1: run_tasks<1>(ta, Ax, Lb.data(), Wb.data(), Sq.data(), Lx, &info, Q.cap_m, whole ? 1 : 0); break;
+            case 2: run_tasks<2>(ta, Ax, Lb.data(), Wb.data(), Sq.data(), Lx, &info, Q.cap_m, whole ? 1 : 0); break;
+            case 4: run_tasks<4>(ta, Ax, Lb.data(), Wb.data(), Sq.data(), Lx, &info, Q.cap_m, whole ? 1 : 0); break;
+            default: return false;
             }
-        }
+            return true;
+        };
+        if (!run_prog(T, nw)) return fail("nw must be 1, 2 or 4");
+        if (!whole && !run_prog(H.tree2, nw2)) return fail("nw of the second tier must be 1, 2 or 4");
         if (!whole) {
             for (const Op& op : H.ops) {
                 if (op.kind == OP_TREE) continue;

@@ -31,6 +31,7 @@ def main():
         g = np.load(os.path.join(gold, name + ".npz"))
         cases.append((name, sc.CscMatrix(int(g["n"]), g["Ap"], g["Ai"], g["Ax"]), 4, 4))
     worst = 0.0
+    worst_solve = 0.0
     for name, A, nb, mw in cases:
         S = sc.schol(A, relax=3)                  # tree-parallel amalgamation, as bench.py uses for world > 1
         plan = multigpu.DistPlan(S, comm, dist_NB=nb, dist_min_w=mw)
@@ -50,6 +51,18 @@ def main():
             out = C.c_double(0)
             check(lib().spchol_residual(plan.h, ptr(np.ascontiguousarray(A.x)), C.byref(out)), "spchol_residual")
             assert out.value <= 1e-12, (name, out.value)
+            # the distributed solve: every front is solved by one rank, contributions to the shared top of the tree are
+            # exchanged once per level; every rank gets the whole x (1 and 11 right-hand sides: two passes of 8)
+            rng = np.random.default_rng(11 + rep)
+            for nrhs in (1, 11):
+                import scipy.sparse as sp
+                Au = sp.csc_matrix((A.x, A.i, A.p), shape=(A.n, A.n))
+                Af = Au + sp.triu(Au, 1).T
+                bb = Af @ rng.standard_normal((A.n, nrhs))
+                xs = multigpu.solve_dist(plan, bb if nrhs > 1 else bb[:, 0]).reshape(A.n, nrhs)
+                serr = float(np.linalg.norm(Af @ xs - bb) / np.linalg.norm(bb))     # solution of order one: rounding level whatever the condition number
+                assert serr <= 1e-13, (name, "solve", nrhs, serr)
+                worst_solve = max(worst_solve, serr)
         if rank == 0:
             print(f"mgpu {name}: world={world} dist fronts={st['fronts_dist']} transfers={st['transfers']} max rel err={err:.2e}", flush=True)
         plan.close()
@@ -64,7 +77,7 @@ def main():
     plan.close()
     dist.barrier()
     if rank == 0:
-        print(f"MGPU OK world={world} worst={worst:.2e}", flush=True)
+        print(f"MGPU OK world={world} worst={worst:.2e} solve residual={worst_solve:.2e}", flush=True)
     comm.close()
     dist.destroy_process_group()
 

@@ -237,6 +237,10 @@ def test_solve_on_device_factor(name):
         assert np.abs(X - Xref).max() <= 1e-9 * max(np.abs(Xref).max(), 1e-300)
         # backward stable solve: ||A x - b|| <~ eps * cond(A) * ||b|| (cond ~ 1e6..1e7 for the two Harwell-Boeing matrices)
         assert np.linalg.norm(_sym_matvec(A, X) - B) <= 1e-8 * np.linalg.norm(B)
+        # a right-hand side with a solution of order one: the residual is at rounding level whatever the condition number
+        B2 = _sym_matvec(A, rng.standard_normal((A.n, nrhs)))
+        X2 = sc.solve(S, B2 if nrhs > 1 else B2[:, 0]).reshape(A.n, -1)
+        assert np.linalg.norm(_sym_matvec(A, X2) - B2) <= 1e-13 * np.linalg.norm(B2)
 
 
 def test_solve_large_fronts_end_to_end():

@@ -91,6 +91,20 @@ def test_subtrees_vs_reference_golden(emu, name, cap_m, work, nw):
     assert st["fronts"] <= st["ns"]
 
 
+@pytest.mark.parametrize("name", ["bcsstk01", "1138_bus", "lap2d_24", "lap3d_10"])
+@pytest.mark.parametrize("cap1,work1,nw1,tier2", [(16, 1e3, 1, "117,3e7,4"), (24, 2e4, 1, "64,1e5,2"), (8, 1e3, 2, "40,2e4,1")])
+def test_two_tiers_vs_reference_golden(emu, name, cap1, work1, nw1, tier2, monkeypatch):
+    # a second tier of subtree tasks on top of the first: its leaves read the first tier's root blocks from the level
+    # program's workspace (column-major), everything above it stays with the level program
+    monkeypatch.setenv("TREEEMU_TIER2", tier2)
+    A, ref = golden(name)
+    Lx, info, st = run(emu, A, whole=False, cap_m=cap1, work=work1, nw=nw1)
+    assert info == 0 and relerr(Lx, ref) <= 1e-10
+    if tier2.startswith("117"):
+        assert st["groups"] >= 1 and st["padded_flops"] >= 1      # (tasks, fronts) of the second tier
+    assert st["fronts"] + st["padded_flops"] <= st["ns"]
+
+
 @pytest.mark.parametrize("team", [1, 2, 3])
 def test_serial_warp_rotation(emu, team, monkeypatch):
     # on the GPU the warp that runs the serial 8 x 8 factorizations is blockIdx.x mod NW; the host run picks it by hand
@@ -112,6 +126,12 @@ def test_subtrees_on_a_larger_grid(emu):
     for cap_m, work, nw in ((117, 2e5, 4), (64, 2e4, 1)):
         Lx, info, st = run(emu, A, whole=False, cap_m=cap_m, work=work, nw=nw)
         assert info == 0 and relerr(Lx, ref) <= 1e-10 and st["tasks"] >= 2 and st["stashes"] > 0
+    os.environ["TREEEMU_TIER2"] = "64,2e5,4"
+    try:
+        Lx, info, st = run(emu, A, whole=False, cap_m=32, work=2e4, nw=1)
+    finally:
+        del os.environ["TREEEMU_TIER2"]
+    assert info == 0 and relerr(Lx, ref) <= 1e-10 and st["groups"] >= 2
 
 
 def test_not_positive_definite_column_is_reported(emu):
@@ -148,7 +168,7 @@ def test_thread_sanitizer_finds_no_race():
     tsan = sorted(glob.glob("/usr/lib/gcc/x86_64-linux-gnu/*/libtsan.so")) + sorted(glob.glob("/usr/lib/x86_64-linux-gnu/libtsan.so*"))
     if not tsan:
         pytest.skip("libtsan not installed")
-    env = dict(os.environ, LD_PRELOAD=tsan[0], TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 exitcode=66")
+    env = dict(os.environ, LD_PRELOAD=tsan[0], TREEEMU_TIER2="117,3e7,4", TSAN_OPTIONS="halt_on_error=0 report_signal_unsafe=0 exitcode=66")
     r = subprocess.run(["python", "-c", code], capture_output=True, text=True, env=env, timeout=600)
     assert "TSAN_RUN_OK" in r.stdout, r.stdout[-2000:] + r.stderr[-4000:]
     assert "data race" not in r.stderr, r.stderr[-6000:]
