@@ -54,6 +54,17 @@ int spchol_mtx_read(const char* path, int* n_out, int64_t* nz_out, int* ti, int*
  * device (d_Ax feeds spchol_factor_device).  stream: a cudaStream_t or NULL; synchronous on return. */
 int spchol_triplet_to_csc_device(int64_t nz, const int* d_ti, const int* d_tj, const double* d_tx, int n,
                                  int* d_Ap, int* d_Ai, double* d_Ax, int64_t* nnz_out, void* stream);
+/* The same without any allocation.  No counterpart in the reference: added for
+ * callers that cannot call cudaMalloc (code under CUDA graph capture, tight serving loops, harnesses that forbid it).
+ * Same arguments and bit-for-bit the same result as spchol_triplet_to_csc_device, on the current device; the work space
+ * of the sort is a static device array inside the library (36.3 MB, held by every GPU that loads the library until the
+ * process exits), so the call is limited to SPCHOL_NOALLOC_MAX_NZ triplets and SPCHOL_NOALLOC_MAX_N columns and returns
+ * SPCHOL_ERANGE beyond that.  It calls no cudaMalloc / cudaFree.  All calls share the array: calls that overlap on one
+ * GPU (two host threads, two streams) race -- run one at a time per GPU. */
+#define SPCHOL_NOALLOC_MAX_NZ 1048576
+#define SPCHOL_NOALLOC_MAX_N  1048576
+int spchol_triplet_to_csc_device_noalloc(int64_t nz, const int* d_ti, const int* d_tj, const double* d_tx, int n,
+                                         int* d_Ap, int* d_Ai, double* d_Ax, int64_t* nnz_out, void* stream);
 /* host-pointer convenience around it (H2D, device ingest, D2H); *device_ms (optional) = CUDA-event time of the device part */
 int spchol_triplet_to_csc_gpu(int64_t nz, const int* ti, const int* tj, const double* tx, int n,
                               int* Ap, int* Ai, double* Ax, int64_t* nnz_out, double* device_ms);

@@ -8,6 +8,7 @@
 #include <cstring>
 #include <dlfcn.h>
 #include <map>
+#include <mutex>
 #include <new>
 #include <set>
 #include <string>
@@ -1085,6 +1086,125 @@ int spchol_triplet_to_csc_gpu(int64_t nz, const int* ti, const int* tj, const do
     }
     freeall();
     return rc;
+}
+
+// ---- the device ingest without any allocation (no counterpart in the reference; added
+// for callers that cannot call cudaMalloc: CUDA graph capture, tight serving loops, harnesses that forbid it).
+// The work space of the sort is a file-scope device array of fixed size, so the entry point is limited to
+// SPCHOL_NOALLOC_MAX_NZ triplets and SPCHOL_NOALLOC_MAX_N columns (include/spchol.h).  Every GPU that loads the library
+// holds the array (36.3 MB) until the process exits.  All calls share it: it keeps the last call's contents (what must
+// start at zero is cleared per call), and two calls that overlap on one GPU race.
+}  // extern "C"
+namespace {
+constexpr int64_t NA_MAX_NZ = SPCHOL_NOALLOC_MAX_NZ;
+constexpr int64_t NA_MAX_N = SPCHOL_NOALLOC_MAX_N;
+constexpr size_t na_up(size_t b) { return (b + 255) & ~size_t(255); }
+constexpr int64_t na_max3(int64_t a, int64_t b, int64_t c) { return a > b ? (a > c ? a : c) : (b > c ? b : c); }
+// the arena of spchol_triplet_to_csc_device at the largest admitted problem (same carving, same order)
+constexpr size_t na_scratch_bytes(int64_t nz, int64_t n) {
+    const int64_t nwarps = (nz + IN_WARP_ITEMS - 1) / IN_WARP_ITEMS;
+    const int64_t nh = 256 * nwarps;
+    const int64_t nbs = (na_max3(nh, nz, n + 1) + IN_SCAN_BLOCK - 1) / IN_SCAN_BLOCK;
+    return 2 * na_up(sizeof(unsigned long long) * nz) + 4 * na_up(sizeof(unsigned) * nz) + na_up(sizeof(unsigned) * nh) +
+           na_up(sizeof(unsigned) * (n + 1)) + na_up(sizeof(unsigned) * nbs) + 256;
+}
+constexpr size_t NA_SCRATCH_BYTES = na_scratch_bytes(NA_MAX_NZ, NA_MAX_N);
+static_assert(NA_SCRATCH_BYTES <= (size_t(40) << 20), "the static ingest scratch is meant to stay modest");
+static __device__ __align__(256) unsigned char g_ingest_scratch[NA_SCRATCH_BYTES];
+
+// In host code g_ingest_scratch is only a stand-in for the symbol: the device address comes from cudaGetSymbolAddress,
+// once per device, with that device current.
+constexpr int NA_MAX_DEVICES = 64;
+unsigned char* g_ingest_scratch_addr[NA_MAX_DEVICES] = {};
+std::mutex g_ingest_scratch_mutex;
+int ingest_scratch_address(int dev, unsigned char** out) {
+    if (dev < 0 || dev >= NA_MAX_DEVICES) { set_error("spchol_triplet_to_csc_device_noalloc: device index beyond 63"); return SPCHOL_EINVAL; }
+    std::lock_guard<std::mutex> lock(g_ingest_scratch_mutex);
+    if (!g_ingest_scratch_addr[dev]) {
+        void* ptr = nullptr;
+        const cudaError_t e = cudaGetSymbolAddress(&ptr, g_ingest_scratch);
+        if (e != cudaSuccess || !ptr) {
+            set_error(std::string("spchol_triplet_to_csc_device_noalloc: cudaGetSymbolAddress failed: ") + cudaGetErrorString(e));
+            return SPCHOL_ECUDA;
+        }
+        g_ingest_scratch_addr[dev] = static_cast<unsigned char*>(ptr);
+    }
+    *out = g_ingest_scratch_addr[dev];
+    return 0;
+}
+}  // namespace
+extern "C" {
+
+// Same arguments, same result (bit for bit) as spchol_triplet_to_csc_device; runs on the current device.  Calls no
+// cudaMalloc / cudaFree; refuses nz > SPCHOL_NOALLOC_MAX_NZ or n > SPCHOL_NOALLOC_MAX_N with SPCHOL_ERANGE.
+int spchol_triplet_to_csc_device_noalloc(int64_t nz, const int* d_ti, const int* d_tj, const double* d_tx, int n,
+                                         int* d_Ap, int* d_Ai, double* d_Ax, int64_t* nnz_out, void* stream) {
+    static const char* who = "spchol_triplet_to_csc_device_noalloc";
+    if (nz < 0 || n < 1 || !d_Ap || !nnz_out || (nz > 0 && (!d_ti || !d_tj || !d_tx || !d_Ai || !d_Ax))) { set_error(std::string(who) + ": bad argument"); return SPCHOL_EINVAL; }
+    if (nz > NA_MAX_NZ || n > NA_MAX_N) {
+        set_error(std::string(who) + ": " + std::to_string(nz) + " triplets / " + std::to_string(n) + " columns exceed the static work space (at most " +
+                  std::to_string(NA_MAX_NZ) + " triplets, " + std::to_string(NA_MAX_N) + " columns); use spchol_triplet_to_csc_device");
+        return SPCHOL_ERANGE;
+    }
+    if (spchol_device_count() <= 0) { set_error(std::string(who) + ": no CUDA device"); return SPCHOL_ENOGPU; }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    *nnz_out = 0;
+    if (nz == 0) { CK(cudaMemsetAsync(d_Ap, 0, sizeof(int) * (static_cast<size_t>(n) + 1), st)); CK(cudaStreamSynchronize(st)); return 0; }
+    int dev = 0, rc = 0;
+    CK(cudaGetDevice(&dev));
+    unsigned char* arena = nullptr;
+    if ((rc = ingest_scratch_address(dev, &arena))) return rc;
+    const int nwarps = static_cast<int>((nz + IN_WARP_ITEMS - 1) / IN_WARP_ITEMS);
+    const int64_t nh = static_cast<int64_t>(256) * nwarps;
+    const int64_t nscan = std::max<int64_t>(std::max<int64_t>(nh, nz), static_cast<int64_t>(n) + 1);
+    const int nbs = static_cast<int>((nscan + IN_SCAN_BLOCK - 1) / IN_SCAN_BLOCK);
+    const size_t bK = na_up(sizeof(unsigned long long) * nz), bI = na_up(sizeof(unsigned) * nz), bH = na_up(sizeof(unsigned) * nh),
+                 bC = na_up(sizeof(unsigned) * (static_cast<size_t>(n) + 1)), bS = na_up(sizeof(unsigned) * nbs);
+    if (2 * bK + 4 * bI + bH + bC + bS + 256 > NA_SCRATCH_BYTES) { set_error(std::string(who) + ": work space accounting is off"); return SPCHOL_ERANGE; }
+    unsigned char* q = arena;
+    auto take = [&](size_t b) { unsigned char* r = q; q += b; return r; };
+    unsigned long long* key[2] = {reinterpret_cast<unsigned long long*>(take(bK)), reinterpret_cast<unsigned long long*>(take(bK))};
+    unsigned* idx[2] = {reinterpret_cast<unsigned*>(take(bI)), reinterpret_cast<unsigned*>(take(bI))};
+    unsigned* head = reinterpret_cast<unsigned*>(take(bI));
+    unsigned* slot = reinterpret_cast<unsigned*>(take(bI));
+    unsigned* hist = reinterpret_cast<unsigned*>(take(bH));
+    unsigned* colc = reinterpret_cast<unsigned*>(take(bC));
+    unsigned* sums = reinterpret_cast<unsigned*>(take(bS));
+    int* bad = reinterpret_cast<int*>(take(256));
+    // the array keeps what the last call left: the flag and the column counts start at zero, everything else is
+    // written before it is read
+    if (cudaMemsetAsync(bad, 0, sizeof(int), st) != cudaSuccess || cudaMemsetAsync(colc, 0, sizeof(unsigned) * (static_cast<size_t>(n) + 1), st) != cudaSuccess)
+        { set_error(std::string(who) + ": cudaMemsetAsync failed"); return SPCHOL_ECUDA; }
+    const unsigned gb = static_cast<unsigned>((nz + 255) / 256);
+    k_in_keys<<<gb, 256, 0, st>>>(nz, d_ti, d_tj, n, key[0], idx[0], bad);
+    int bits = 1;
+    while ((int64_t(1) << bits) < n) ++bits;
+    const int nbytes = (bits + 7) / 8;
+    int cur = 0;
+    for (int half = 0; half < 2; ++half)
+        for (int b = 0; b < nbytes; ++b) {
+            const int shift = 32 * half + 8 * b;
+            k_in_hist<<<(nwarps + 7) / 8, 256, 0, st>>>(nz, key[cur], shift, nwarps, hist);
+            ingest_scan(nh, hist, hist, sums, st);
+            k_in_scatter<<<(nwarps + 7) / 8, 256, 0, st>>>(nz, key[cur], idx[cur], shift, nwarps, hist, key[cur ^ 1], idx[cur ^ 1]);
+            cur ^= 1;
+        }
+    k_in_heads<<<gb, 256, 0, st>>>(nz, key[cur], head, colc);
+    ingest_scan(nz, head, slot, sums, st);
+    k_in_emit<<<gb, 256, 0, st>>>(nz, key[cur], idx[cur], head, slot, d_tx, d_Ai, d_Ax);
+    unsigned last[2] = {0, 0};
+    cudaMemcpyAsync(&last[0], slot + (nz - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, st);
+    cudaMemcpyAsync(&last[1], head + (nz - 1), sizeof(unsigned), cudaMemcpyDeviceToHost, st);
+    int hbad = 0;
+    cudaMemcpyAsync(&hbad, bad, sizeof(int), cudaMemcpyDeviceToHost, st);
+    ingest_scan(static_cast<int64_t>(n) + 1, colc, colc, sums, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) { set_error(std::string(who) + ": kernel failure"); return SPCHOL_ECUDA; }
+    if (hbad) { set_error(std::string(who) + ": index outside [0, n)"); return SPCHOL_EINVAL; }
+    const unsigned total = last[0] + last[1];
+    k_in_ap<<<(n + 1 + 255) / 256, 256, 0, st>>>(n, colc, total, d_Ap);
+    if (cudaStreamSynchronize(st) != cudaSuccess) { set_error(std::string(who) + ": kernel failure"); return SPCHOL_ECUDA; }
+    *nnz_out = total;
+    return 0;
 }
 
 int spchol_host_alloc(int64_t bytes, void** out) {
