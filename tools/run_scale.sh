@@ -9,7 +9,7 @@ echo "bench rc=$?"; python - <<PY
 import json
 for l in open('gpurun_out/r2z_bench_lap3d_128_n$N.json'):
     if l.startswith('{'):
-        d=json.loads(l); print('N=$N', round(d['ms_per_step'],1), round(d['value']), 'e2e', round(d['e2e']['ms_per_step'],1), 'd2h GB', round(d['e2e']['d2h_bytes_per_step']/1e9,1), 'residual', d['residual']['rel_fro_estimate'])
+        d=json.loads(l); print('N=$N', round(d['ms_per_step'],1), round(d['value']), 'e2e', round(d['e2e']['ms_per_step'],1), 'solve', d['solve']['seconds_host_to_host'], d['solve']['rel_residual'], 'd2h GB', round(d['e2e']['d2h_bytes_per_step']/1e9,1), 'residual', d['residual']['rel_fro_estimate'])
         for r in d['per_rank']: print('   ', r['ms'], r['kernel_ms'])
 PY
 tail -n 2 gpurun_out/r2z_bench_n$N.err | cut -c1-300
@@ -17,9 +17,7 @@ if [ "$N" = "8" ]; then
   timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29513 \
     bench.py --gpus 8 --steps 3 --warmup 3 --workload batched_1138 > gpurun_out/r2z_bench_batched_1138_n8.json 2> gpurun_out/r2z_bench_batched_n8.err
   echo "batched n8 rc=$? $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2z_bench_batched_1138_n8.json | head -2 | tr '\n' ' ')"
-  for D in 128 512; do
-    timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 2951$((D/128)) \
-      bench.py --gpus 8 --steps 3 --warmup 3 --workload lap3d_128 --dist-nb $D --no-e2e > gpurun_out/r2z_bench_lap3d_128_n8_dnb$D.json 2> /dev/null
-    echo "dnb$D rc=$? $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2z_bench_lap3d_128_n8_dnb$D.json | head -1)"
-  done
+  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29514 \
+    tests/mgpu_worker.py > gpurun_out/r2z_mgpu_worker_n8.log 2>&1
+  echo "worker rc=$?"; grep "MGPU OK" gpurun_out/r2z_mgpu_worker_n8.log
 fi
