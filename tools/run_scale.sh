@@ -3,7 +3,7 @@
 mkdir -p gpurun_out
 N=${1:-8}
 export NCCL_DEBUG=WARN
-timeout 900 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 \
+timeout 200 python -m torch.distributed.run --nnodes=1 --nproc-per-node $N --master-addr 127.0.0.1 --master-port 29512 \
     bench.py --gpus $N --steps 5 --warmup 3 --workload lap3d_128 > gpurun_out/r2z_bench_lap3d_128_n$N.json 2> gpurun_out/r2z_bench_n$N.err
 echo "bench rc=$?"; python - <<PY
 import json
@@ -14,10 +14,10 @@ for l in open('gpurun_out/r2z_bench_lap3d_128_n$N.json'):
 PY
 tail -n 2 gpurun_out/r2z_bench_n$N.err | cut -c1-300
 if [ "$N" = "8" ]; then
-  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29513 \
+  timeout 90 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29513 \
     bench.py --gpus 8 --steps 3 --warmup 3 --workload batched_1138 > gpurun_out/r2z_bench_batched_1138_n8.json 2> gpurun_out/r2z_bench_batched_n8.err
   echo "batched n8 rc=$? $(grep -o '"ms_per_step": [0-9.]*' gpurun_out/r2z_bench_batched_1138_n8.json | head -2 | tr '\n' ' ')"
-  timeout 600 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29514 \
+  timeout 100 python -m torch.distributed.run --nnodes=1 --nproc-per-node 8 --master-addr 127.0.0.1 --master-port 29514 \
     tests/mgpu_worker.py > gpurun_out/r2z_mgpu_worker_n8.log 2>&1
   echo "worker rc=$?"; grep "MGPU OK" gpurun_out/r2z_mgpu_worker_n8.log
 fi
