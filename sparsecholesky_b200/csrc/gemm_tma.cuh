@@ -12,6 +12,7 @@
 // choice the 16 lanes of a half-warp (4 rows x 4 k) hit 16 distinct 8-byte bank pairs -- conflict-free without padding.
 #pragma once
 #include <cstdint>
+#include <type_traits>
 #include <cuda.h>
 #include <cuda_runtime.h>
 
@@ -50,6 +51,13 @@ __device__ __forceinline__ void g3_tma_load_2d(unsigned dst, const CUtensorMap* 
 __device__ __forceinline__ void g3_dmma(double& c0, double& c1, double a, double b) {
     asm volatile("mma.sync.aligned.m8n8k4.row.col.f64.f64.f64.f64 {%0,%1}, {%2}, {%3}, {%0,%1};\n"
                  : "+d"(c0), "+d"(c1) : "d"(a), "d"(b));
+}
+// fragment element from a stage: an explicit ld.shared with a 32-bit address (a plain dereference compiles to generic
+// 64-bit loads here: the compiler does not see through the ring arithmetic that the pointer is shared memory)
+__device__ __forceinline__ double g3_lds(unsigned addr) {
+    double v;
+    asm volatile("ld.shared.f64 %0, [%1];" : "=d"(v) : "r"(addr));
+    return v;
 }
 // row (0..15) inside a box of fragment row g (0..7) of the h-th (0/1) 8-row fragment
 __device__ __forceinline__ int g3_box_row(int h, int g) { return 4 * h + (g & 1) + 2 * (g >> 2) + 8 * ((g >> 1) & 1); }
@@ -130,20 +138,23 @@ __global__ void __launch_bounds__(256, 2) k_gemm_tma(const GemmTask* __restrict_
 #pragma unroll
         for (int ni = 0; ni < 4; ++ni) { acc[mi][ni][0] = 0.0; acc[mi][ni][1] = 0.0; }
 
-    for (int kt = 0; kt < nk; ++kt) {
+    // one K-slab of the ring: TAIL = the last slab of a K that is not a multiple of G3_BK (the panel goes on beyond K, so
+    // the surplus columns are masked; full slabs carry no predicates)
+    auto slab = [&](int kt, auto tail_c) {
+        constexpr bool TAIL = decltype(tail_c)::value;
         const int s = kt % G3_ST;
         g3_mbar_wait(bar0 + 8 * s, (kt / G3_ST) & 1);
-        const unsigned char* as = stage0 + s * G3_STAGE + (wm * 2) * G3_BOX;
-        const unsigned char* bs = stage0 + s * G3_STAGE + (G3_BM / 16 + wn * 2) * G3_BOX;
-        const int krem = K - kt * G3_BK;               // columns of this slab inside the task (the panel goes on beyond K)
+        const unsigned as = sbase + s * G3_STAGE + (wm * 2) * G3_BOX;
+        const unsigned bs = sbase + s * G3_STAGE + (G3_BM / 16 + wn * 2) * G3_BOX;
+        const int krem = K - kt * G3_BK;
 #pragma unroll
         for (int q = 0; q < G3_BK / 4; ++q) {
             double af[4], bf[4];
-            const bool kon = 4 * q + tq < krem;
+            const bool kon = !TAIL || 4 * q + tq < krem;
 #pragma unroll
-            for (int mi = 0; mi < 4; ++mi) af[mi] = kon ? *reinterpret_cast<const double*>(as + (mi >> 1) * G3_BOX + foff[mi & 1][q]) : 0.0;
+            for (int mi = 0; mi < 4; ++mi) af[mi] = kon ? g3_lds(as + (mi >> 1) * G3_BOX + foff[mi & 1][q]) : 0.0;
 #pragma unroll
-            for (int ni = 0; ni < 4; ++ni) bf[ni] = kon ? *reinterpret_cast<const double*>(bs + (ni >> 1) * G3_BOX + foff[ni & 1][q]) : 0.0;
+            for (int ni = 0; ni < 4; ++ni) bf[ni] = kon ? g3_lds(bs + (ni >> 1) * G3_BOX + foff[ni & 1][q]) : 0.0;
 #pragma unroll
             for (int mi = 0; mi < 4; ++mi)
 #pragma unroll
@@ -151,7 +162,10 @@ __global__ void __launch_bounds__(256, 2) k_gemm_tma(const GemmTask* __restrict_
         }
         __syncthreads();                               // everyone is done with stage s: refill it with the slab G3_ST ahead
         if (tid == 0 && kt + G3_ST < nk) issue(s, kt + G3_ST);
-    }
+    };
+    const int nk_full = K / G3_BK;
+    for (int kt = 0; kt < nk_full; ++kt) slab(kt, std::false_type{});
+    if (nk_full < nk) slab(nk_full, std::true_type{});
 
     const int ldc = t.ldc;
     const bool beta0 = (t.c_space & 2) != 0;
