@@ -280,7 +280,7 @@ int run_numeric(spchol_plan* p, const double* dAx, double* host_out = nullptr) {
     }
     // profiling replays the program on one stream (program order is a valid serial order)
     cudaStream_t sts[2] = {p->stream, prof ? p->stream : p->stream2};
-    static const int gemm_swizzle = getenv("SPCHOL_GEMM_SWIZZLE") ? atoi(getenv("SPCHOL_GEMM_SWIZZLE")) : 7;     // banded tiles + C prefetch + RED epilogue
+    static const int gemm_swizzle = getenv("SPCHOL_GEMM_SWIZZLE") ? atoi(getenv("SPCHOL_GEMM_SWIZZLE")) : 15;    // banded tiles + C prefetch + RED epilogue + per-stage free barriers
     if (prof) host_out = nullptr;
     int level_next = 0;                  // levels below this one have been handed to the copy stream
     size_t n_mark = 0;                   // OP_EXPORT ops seen so far

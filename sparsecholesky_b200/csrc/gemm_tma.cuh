@@ -23,7 +23,7 @@ namespace spchol {
 constexpr int G3_BM = 128, G3_BN = 64, G3_BK = 16, G3_ST = 4;      // CTA tile, K-slab, pipeline stages
 constexpr int G3_BOX = 16 * G3_BK * 8;                             // bytes of one 16-row box
 constexpr int G3_STAGE = (G3_BM + G3_BN) / 16 * G3_BOX;            // bytes per stage (A boxes, then B boxes)
-constexpr int G3_SMEM = G3_ST * G3_STAGE + 1024 + 64;              // + alignment slack + barriers
+constexpr int G3_SMEM = G3_ST * G3_STAGE + 1024 + 64;              // + alignment slack + barriers (full and empty per stage)
 constexpr int G3_SWZ = 8;                                          // banded tile order, as k_gemm_dmma
 
 __device__ __forceinline__ unsigned g3_smem_u32(const void* p) { return static_cast<unsigned>(__cvta_generic_to_shared(p)); }
@@ -32,6 +32,9 @@ __device__ __forceinline__ void g3_mbar_init(unsigned bar, unsigned count) {
 }
 __device__ __forceinline__ void g3_mbar_expect_tx(unsigned bar, unsigned bytes) {
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void g3_mbar_arrive(unsigned bar) {
+    asm volatile("mbarrier.arrive.shared::cta.b64 _, [%0];" ::"r"(bar) : "memory");
 }
 __device__ __forceinline__ void g3_mbar_wait(unsigned bar, unsigned parity) {
     asm volatile(
@@ -86,6 +89,8 @@ __global__ void __launch_bounds__(256, 2) k_gemm_tma(const GemmTask* __restrict_
     unsigned char* stage0 = reinterpret_cast<unsigned char*>((reinterpret_cast<uintptr_t>(g3_raw) + 1023) & ~uintptr_t(1023));
     const unsigned sbase = g3_smem_u32(stage0);
     const unsigned bar0 = sbase + G3_ST * G3_STAGE;
+    const unsigned ebar0 = bar0 + 8 * G3_ST;           // "stage is free again" barriers (swizzle & 8), one arrival per warp
+    const bool free_bars = (swizzle & 8) != 0;
     const CUtensorMap* map = tmaps + t.tmap;
     double* __restrict__ C = ((t.c_space & 1) ? W : L) + t.c_off;
     const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -105,7 +110,7 @@ __global__ void __launch_bounds__(256, 2) k_gemm_tma(const GemmTask* __restrict_
     };
     if (tid == 0) {
 #pragma unroll
-        for (int s = 0; s < G3_ST; ++s) g3_mbar_init(bar0 + 8 * s, 1);
+        for (int s = 0; s < G3_ST; ++s) { g3_mbar_init(bar0 + 8 * s, 1); g3_mbar_init(ebar0 + 8 * s, 8); }
         asm volatile("fence.mbarrier_init.release.cluster;" ::: "memory");
         asm volatile("fence.proxy.async.shared::cta;" ::: "memory");
         for (int s = 0; s < G3_ST && s < nk; ++s) issue(s, s);
@@ -160,8 +165,21 @@ __global__ void __launch_bounds__(256, 2) k_gemm_tma(const GemmTask* __restrict_
 #pragma unroll
                 for (int ni = 0; ni < 4; ++ni) g3_dmma(acc[mi][ni][0], acc[mi][ni][1], af[mi], bf[ni]);
         }
-        __syncthreads();                               // everyone is done with stage s: refill it with the slab G3_ST ahead
-        if (tid == 0 && kt + G3_ST < nk) issue(s, kt + G3_ST);
+        if (!free_bars) {
+            __syncthreads();                           // everyone is done with stage s: refill it with the slab G3_ST ahead
+            if (tid == 0 && kt + G3_ST < nk) issue(s, kt + G3_ST);
+        } else {
+            // no CTA-wide barrier in the loop: every warp reports the stage free, and the refill runs ONE slab behind (the
+            // stage of slab kt - 1, which the other warps left long ago), so the issuing thread hardly ever waits and the
+            // warps may drift up to two slabs apart
+            __syncwarp();
+            if (lane == 0) g3_mbar_arrive(ebar0 + 8 * s);
+            if (tid == 0 && kt >= 1 && kt - 1 + G3_ST < nk) {
+                const int p = kt - 1, sp = p % G3_ST;
+                g3_mbar_wait(ebar0 + 8 * sp, (p / G3_ST) & 1);
+                issue(sp, p + G3_ST);
+            }
+        }
     };
     const int nk_full = K / G3_BK;
     for (int kt = 0; kt < nk_full; ++kt) slab(kt, std::false_type{});

@@ -126,6 +126,7 @@ int main(int argc, char** argv) {
         run("r1_regstage", [&] { k_gemm_dmma<<<g1, 256, G_SMEM>>>(dt, L, W, 3); });
         run("r2_tma", [&] { k_gemm_tma<<<g3, 256, G3_SMEM>>>(dt, dm, L, W, 3); });
         run("r2_tma_red", [&] { k_gemm_tma<<<g3, 256, G3_SMEM>>>(dt, dm, L, W, 7); });
+        run("r2_tma_red_freebars", [&] { k_gemm_tma<<<g3, 256, G3_SMEM>>>(dt, dm, L, W, 15); });
         cudaFree(L); cudaFree(W); cudaFree(W0); cudaFree(Wref); cudaFree(dmax); cudaFree(dt); cudaFree(dm);
     }
     return 0;
