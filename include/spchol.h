@@ -69,6 +69,18 @@ int spchol_triplet_to_csc_device_noalloc(int64_t nz, const int* d_ti, const int*
 int spchol_triplet_to_csc_gpu(int64_t nz, const int* ti, const int* tj, const double* tx, int n,
                               int* Ap, int* Ai, double* Ax, int64_t* nnz_out, double* device_ms);
 
+/* The Matrix Market parse on the GPU (the text half of SURVEY.md 8f-3; replaces the `file >> row >> col >> data` loop of
+ * load_matrix_market_to_csc, include/mtx_reader.hpp:41-56).  spchol_mtx_parse_device: d_text = the file's bytes from the
+ * size line on (leading '%' lines removed) in DEVICE memory; writes n, nnz and nnz 0-based triplets mirrored into the upper
+ * triangle to d_ti / d_tj / d_tx [nz_cap] -- the input of spchol_triplet_to_csc_device, so a matrix goes from text to the
+ * factorization without its triplets visiting the host.  Decimal -> double is exact (Eisel-Lemire, ties to even = strtod);
+ * the few tokens it does not decide (> 19 significant digits, inf / nan) are converted by the host's strtod, their count
+ * comes back in *host_converted (optional).  Errors as spchol_mtx_read; SPCHOL_ERANGE if the file holds more than nz_cap
+ * entries.  spchol_mtx_read_gpu: spchol_mtx_read's protocol and results with the parse on the device. */
+int spchol_mtx_parse_device(const char* d_text, int64_t nbytes, int64_t nz_cap, int* d_ti, int* d_tj, double* d_tx,
+                            int* n_out, int64_t* nz_out, int64_t* host_converted, void* stream);
+int spchol_mtx_read_gpu(const char* path, int* n_out, int64_t* nz_out, int* ti, int* tj, double* tx, double* device_ms);
+
 /* ---- orderings (host; additive: the reference has no ordering code) -------- */
 /* geometric nested dissection of an nx*ny*nz grid, the fixed permutation of the benchmark Laplacians
  * (SURVEY.md 8d): perm[new] = old grid id, id = x + nx*(y + ny*z) */

@@ -21,6 +21,8 @@ SIGNATURES = {
     "spchol_triplet_to_csc_device": (C.c_int, [C.c_int64, _VP, _VP, _VP, C.c_int, _VP, _VP, _VP, C.POINTER(C.c_int64), _VP]),
     "spchol_triplet_to_csc_device_noalloc": (C.c_int, [C.c_int64, _VP, _VP, _VP, C.c_int, _VP, _VP, _VP, C.POINTER(C.c_int64), _VP]),
     "spchol_triplet_to_csc_gpu": (C.c_int, [C.c_int64, _VP, _VP, _VP, C.c_int, _VP, _VP, _VP, C.POINTER(C.c_int64), C.POINTER(C.c_double)]),
+    "spchol_mtx_parse_device": (C.c_int, [_VP, C.c_int64, C.c_int64, _VP, _VP, _VP, C.POINTER(C.c_int), C.POINTER(C.c_int64), C.POINTER(C.c_int64), _VP]),
+    "spchol_mtx_read_gpu": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int64), _VP, _VP, _VP, C.POINTER(C.c_double)]),
     "spchol_mtx_read": (C.c_int, [C.c_char_p, C.POINTER(C.c_int), C.POINTER(C.c_int64), _VP, _VP, _VP]),
     "spchol_nd_perm_grid": (C.c_int, [C.c_int, C.c_int, C.c_int, _VP]),
     "spchol_order_amd": (C.c_int, [C.c_int, _VP, _VP, _VP]),

@@ -217,6 +217,22 @@ def load_matrix_market_to_csc(filename):
     return triplet_to_csc_matrix(ti, tj, tx, n.value)
 
 
+def load_matrix_market_to_csc_gpu(filename, return_ms=False):
+    """load_matrix_market_to_csc with both halves on the GPU: the text parse (spchol_mtx_read_gpu: one thread per 256-byte
+    chunk, exact decimal -> double) and the COO -> CSC conversion (spchol_triplet_to_csc_gpu).  Same result, bit for bit."""
+    L = lib()
+    n = C.c_int(0); nz = C.c_int64(0); ms = C.c_double(0)
+    rc = L.spchol_mtx_read_gpu(filename.encode(), C.byref(n), C.byref(nz), None, None, None, None)
+    if rc < 0:
+        raise RuntimeError(L.spchol_last_error().decode())      # std::runtime_error (mtx_reader.hpp:20)
+    ti = np.empty(nz.value, np.int32); tj = np.empty(nz.value, np.int32); tx = np.empty(nz.value, np.float64)
+    rc = L.spchol_mtx_read_gpu(filename.encode(), C.byref(n), C.byref(nz), ptr(ti), ptr(tj), ptr(tx), C.byref(ms))
+    if rc < 0:
+        raise RuntimeError(L.spchol_last_error().decode())
+    A = triplet_to_csc_matrix_gpu(ti, tj, tx, n.value)
+    return (A, ms.value, (ti, tj, tx)) if return_ms else A
+
+
 def order_amd(A):
     """Approximate-minimum-degree ordering of the pattern of A (upper CSC): perm[new] = old.  Additive:
     the reference has no ordering."""

@@ -20,6 +20,7 @@
 #include "kernels.cuh"
 #include "gemm_tma.cuh"
 #include "ingest.cuh"
+#include "mtx_parse.cuh"
 #include "tree_kernel.cuh"
 #include "residual.cuh"
 #include "solve.cuh"
@@ -1083,6 +1084,131 @@ int spchol_triplet_to_csc_gpu(int64_t nz, const int* ti, const int* tj, const do
     if (rc == 0) {
         cudaMemcpy(Ap, dAp, 4 * (static_cast<size_t>(n) + 1), cudaMemcpyDeviceToHost);
         if (*nnz_out > 0) { cudaMemcpy(Ai, dAi, 4 * static_cast<size_t>(*nnz_out), cudaMemcpyDeviceToHost); cudaMemcpy(Ax, dAx, 8 * static_cast<size_t>(*nnz_out), cudaMemcpyDeviceToHost); }
+    }
+    freeall();
+    return rc;
+}
+
+// ---- device-side Matrix Market parse (mtx_parse.cuh): text in device memory -> triplets in device memory ----
+// d_text / nbytes: the file from its size line on (the leading '%' comment lines removed -- spchol_mtx_read_gpu does that);
+// d_ti / d_tj / d_tx [nz_cap]: 0-based triplets mirrored into the upper triangle, as load_matrix_market_to_csc builds them
+// (include/mtx_reader.hpp:41-56) and spchol_triplet_to_csc_device takes them.  *host_converted (optional): values whose text
+// went to the host's strtod (more than 19 significant digits, inf / nan).  Synchronous on return.
+int spchol_mtx_parse_device(const char* d_text, int64_t nbytes, int64_t nz_cap, int* d_ti, int* d_tj, double* d_tx,
+                            int* n_out, int64_t* nz_out, int64_t* host_converted, void* stream) {
+    static const char* who = "spchol_mtx_parse_device";
+    if (!d_text || nbytes < 1 || nz_cap < 0 || !n_out || !nz_out || (nz_cap > 0 && (!d_ti || !d_tj || !d_tx))) { set_error(std::string(who) + ": bad argument"); return SPCHOL_EINVAL; }
+    if (nbytes >= (int64_t(1) << 32) || nz_cap > INT_MAX) { set_error(std::string(who) + ": text of 4 GiB or more / more than INT_MAX entries"); return SPCHOL_ERANGE; }
+    if (spchol_device_count() <= 0) { set_error(std::string(who) + ": no CUDA device"); return SPCHOL_ENOGPU; }
+    cudaStream_t st = static_cast<cudaStream_t>(stream);
+    const int64_t nchunks = (nbytes + MP_CHUNK - 1) / MP_CHUNK;
+    const int nbs = static_cast<int>((nchunks + IN_SCAN_BLOCK - 1) / IN_SCAN_BLOCK);
+    const unsigned fb_cap = static_cast<unsigned>(std::min<int64_t>(std::max<int64_t>(nz_cap, 1), int64_t(1) << 20));
+    auto up = [](size_t b) { return (b + 255) & ~size_t(255); };
+    const size_t bCnt = up(sizeof(unsigned) * nchunks), bSum = up(sizeof(unsigned) * nbs), bSmall = 256, bFe = up(sizeof(int) * fb_cap),
+                 bFv = up(sizeof(double) * fb_cap), bFt = up(static_cast<size_t>(MP_TOK_MAX) * fb_cap);
+    unsigned char* arena = nullptr;
+    if (cudaMalloc(&arena, bCnt + bSum + bSmall + bFe + bFv + bFt) != cudaSuccess) { cudaGetLastError(); set_error(std::string(who) + ": out of device memory"); return SPCHOL_ENOMEM; }
+    auto fail = [&](int code, const std::string& msg) { cudaFree(arena); set_error(std::string(who) + ": " + msg); return code; };
+    unsigned char* q = arena;
+    auto take = [&](size_t b) { unsigned char* r = q; q += b; return r; };
+    unsigned* counts = reinterpret_cast<unsigned*>(take(bCnt));
+    unsigned* sums = reinterpret_cast<unsigned*>(take(bSum));
+    unsigned char* small = take(bSmall);          // hdr[3] (0..23), ntok (24..31), fb_count (32..35), err_pos (40..47)
+    int* fb_e = reinterpret_cast<int*>(take(bFe));
+    double* fb_v = reinterpret_cast<double*>(take(bFv));
+    char* fb_text = reinterpret_cast<char*>(take(bFt));
+    MpOut o{reinterpret_cast<long long*>(small), d_ti, d_tj, d_tx, nz_cap, reinterpret_cast<unsigned long long*>(small + 40),
+            reinterpret_cast<unsigned long long*>(small + 24), reinterpret_cast<unsigned*>(small + 32), fb_cap, fb_e, fb_text};
+    if (cudaMemsetAsync(small, 0, 40, st) != cudaSuccess || cudaMemsetAsync(small + 40, 0xff, 8, st) != cudaSuccess) return fail(SPCHOL_ECUDA, "cudaMemsetAsync failed");
+    const unsigned gc = static_cast<unsigned>((nchunks + 127) / 128);
+    k_mp_count<<<gc, 128, 0, st>>>(d_text, nbytes, nchunks, counts);
+    ingest_scan(nchunks, counts, counts, sums, st);
+    k_mp_parse<<<gc, 128, 0, st>>>(d_text, nbytes, nchunks, counts, o);
+    unsigned char hs[48];
+    cudaMemcpyAsync(hs, small, 48, cudaMemcpyDeviceToHost, st);
+    if (cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) return fail(SPCHOL_ECUDA, "kernel failure");
+    long long hdr[3]; unsigned long long ntok = 0, err_pos = 0; unsigned fbn = 0;
+    std::memcpy(hdr, hs, 24); std::memcpy(&ntok, hs + 24, 8); std::memcpy(&fbn, hs + 32, 4); std::memcpy(&err_pos, hs + 40, 8);
+    if (ntok < 3 || hdr[0] <= 0 || hdr[0] != hdr[1] || hdr[2] < 0 || hdr[0] > INT_MAX) return fail(SPCHOL_EINVAL, "bad size line (matrix must be square)");
+    const long long nl = hdr[2];
+    if (nl > nz_cap) return fail(SPCHOL_ERANGE, "the file holds " + std::to_string(nl) + " entries, the buffers " + std::to_string(nz_cap));
+    if (ntok < 3ull + 3ull * static_cast<unsigned long long>(nl)) return fail(SPCHOL_EIO, "truncated file");
+    // a malformed token only matters among the 3 + 3 nl tokens the reference would read
+    if (err_pos < 3ull + 3ull * static_cast<unsigned long long>(nl))
+        return fail(SPCHOL_EIO, "token " + std::to_string(err_pos) + " of the data (" + (err_pos < 3 ? "size line" : "entry " + std::to_string((err_pos - 3) / 3)) + ") is not a number of the expected kind");
+    if (fbn > fb_cap) return fail(SPCHOL_ERANGE, std::to_string(fbn) + " values need the host's strtod (at most " + std::to_string(fb_cap) + "): use spchol_mtx_read");
+    if (fbn) {
+        std::vector<int> he(fbn); std::vector<char> ht(static_cast<size_t>(fbn) * MP_TOK_MAX); std::vector<double> hv(fbn);
+        if (cudaMemcpyAsync(he.data(), fb_e, sizeof(int) * fbn, cudaMemcpyDeviceToHost, st) != cudaSuccess ||
+            cudaMemcpyAsync(ht.data(), fb_text, ht.size(), cudaMemcpyDeviceToHost, st) != cudaSuccess || cudaStreamSynchronize(st) != cudaSuccess)
+            return fail(SPCHOL_ECUDA, "read-back of the tokens for the host failed");
+        for (unsigned k = 0; k < fbn; ++k) {
+            const char* t = ht.data() + static_cast<size_t>(k) * MP_TOK_MAX;
+            if (*t == '+') ++t;
+            char* endp = nullptr;
+            hv[k] = std::strtod(t, &endp);
+            if (endp == t || *endp != 0) return fail(SPCHOL_EIO, std::string("value '") + t + "' is not a number");
+        }
+        if (cudaMemcpyAsync(fb_v, hv.data(), sizeof(double) * fbn, cudaMemcpyHostToDevice, st) != cudaSuccess) return fail(SPCHOL_ECUDA, "cudaMemcpyAsync failed");
+        k_mp_scatter<<<(fbn + 255) / 256, 256, 0, st>>>(fbn, fb_e, fb_v, d_tx);
+    }
+    if (nl > 0) k_mp_mirror<<<static_cast<unsigned>((nl + 255) / 256), 256, 0, st>>>(nl, d_ti, d_tj);
+    if (cudaStreamSynchronize(st) != cudaSuccess || cudaGetLastError() != cudaSuccess) return fail(SPCHOL_ECUDA, "kernel failure");
+    cudaFree(arena);
+    *n_out = static_cast<int>(hdr[0]);
+    *nz_out = nl;
+    if (host_converted) *host_converted = fbn;
+    return SPCHOL_OK;
+}
+
+// load_matrix_market_to_csc's reading half (include/mtx_reader.hpp:17-56) with the parse on the GPU: same two-call protocol
+// and results as spchol_mtx_read (with ti == NULL only the sizes, from the host).  The file is read into host memory, the
+// leading '%' lines are dropped, the rest goes to the device in one copy.  *device_ms (optional): the device part alone.
+int spchol_mtx_read_gpu(const char* path, int* n_out, int64_t* nz_out, int* ti, int* tj, double* tx, double* device_ms) {
+    if (!path || !n_out || !nz_out) { set_error("spchol_mtx_read_gpu: null argument"); return SPCHOL_EINVAL; }
+    int rc = spchol_mtx_read(path, n_out, nz_out, nullptr, nullptr, nullptr);
+    if (rc || !ti) return rc;
+    if (!tj || !tx) { set_error("spchol_mtx_read_gpu: null argument"); return SPCHOL_EINVAL; }
+    if (spchol_device_count() <= 0) { set_error("spchol_mtx_read_gpu: no CUDA device"); return SPCHOL_ENOGPU; }
+    const int64_t nz = *nz_out;
+    std::FILE* f = std::fopen(path, "rb");
+    if (!f) { set_error(std::string("Could not open file ") + path); return SPCHOL_EIO; }
+    std::fseek(f, 0, SEEK_END);
+    const long sz = std::ftell(f);
+    std::fseek(f, 0, SEEK_SET);
+    std::vector<char> buf;
+    if (sz < 0) { std::fclose(f); set_error("spchol_mtx_read_gpu: cannot size the file"); return SPCHOL_EIO; }
+    try { buf.resize(static_cast<size_t>(sz)); } catch (const std::bad_alloc&) { std::fclose(f); set_error("out of host memory"); return SPCHOL_ENOMEM; }
+    buf.resize(std::fread(buf.data(), 1, buf.size(), f));
+    std::fclose(f);
+    size_t skip = 0;
+    while (skip < buf.size() && buf[skip] == '%') { while (skip < buf.size() && buf[skip] != '\n') ++skip; if (skip < buf.size()) ++skip; }
+    const int64_t nbytes = static_cast<int64_t>(buf.size() - skip);
+    if (nbytes < 1) { set_error("spchol_mtx_read_gpu: bad size line (matrix must be square)"); return SPCHOL_EINVAL; }
+    char* d_text = nullptr; int *d_ti = nullptr, *d_tj = nullptr; double* d_tx = nullptr;
+    const size_t z = static_cast<size_t>(std::max<int64_t>(nz, 1));
+    auto freeall = [&] { cudaFree(d_text); cudaFree(d_ti); cudaFree(d_tj); cudaFree(d_tx); };
+    if (cudaMalloc(&d_text, static_cast<size_t>(nbytes)) != cudaSuccess || cudaMalloc(&d_ti, 4 * z) != cudaSuccess ||
+        cudaMalloc(&d_tj, 4 * z) != cudaSuccess || cudaMalloc(&d_tx, 8 * z) != cudaSuccess) {
+        cudaGetLastError(); freeall(); set_error("spchol_mtx_read_gpu: out of device memory"); return SPCHOL_ENOMEM;
+    }
+    cudaMemcpy(d_text, buf.data() + skip, static_cast<size_t>(nbytes), cudaMemcpyHostToDevice);
+    cudaEvent_t e0, e1;
+    cudaEventCreate(&e0); cudaEventCreate(&e1);
+    cudaEventRecord(e0, nullptr);
+    int n2 = 0; int64_t nz2 = 0;
+    rc = spchol_mtx_parse_device(d_text, nbytes, nz, d_ti, d_tj, d_tx, &n2, &nz2, nullptr, nullptr);
+    cudaEventRecord(e1, nullptr);
+    cudaEventSynchronize(e1);
+    float ms = 0; cudaEventElapsedTime(&ms, e0, e1);
+    cudaEventDestroy(e0); cudaEventDestroy(e1);
+    if (device_ms) *device_ms = ms;
+    if (rc == 0 && (n2 != *n_out || nz2 != nz)) { rc = SPCHOL_EIO; set_error("spchol_mtx_read_gpu: size line read differently on the device"); }
+    if (rc == 0 && nz > 0) {
+        cudaMemcpy(ti, d_ti, 4 * static_cast<size_t>(nz), cudaMemcpyDeviceToHost);
+        cudaMemcpy(tj, d_tj, 4 * static_cast<size_t>(nz), cudaMemcpyDeviceToHost);
+        if (cudaMemcpy(tx, d_tx, 8 * static_cast<size_t>(nz), cudaMemcpyDeviceToHost) != cudaSuccess) { rc = SPCHOL_ECUDA; set_error("spchol_mtx_read_gpu: read-back failed"); }
     }
     freeall();
     return rc;
