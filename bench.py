@@ -210,6 +210,16 @@ def run_also():
             out[wl] = sm
         except Exception as exc:
             out[wl] = {"error": repr(exc)[:300]}
+    # the ingest in front of the path: COO -> CSC and the Matrix Market parse on the device, bench_ingest.py
+    t0 = time.time()
+    try:
+        r = subprocess.run([sys.executable, os.path.join(os.path.dirname(os.path.abspath(__file__)), "bench_ingest.py")],
+                           capture_output=True, text=True, timeout=300)
+        line = next((l for l in r.stdout.splitlines() if l.startswith("{")), None)
+        out["ingest"] = json.loads(line) if r.returncode == 0 and line else {"error": (r.stderr or r.stdout)[-300:]}
+        out["ingest"]["wall_seconds"] = round(time.time() - t0, 1)
+    except Exception as exc:
+        out["ingest"] = {"error": repr(exc)[:300]}
     return out
 
 
