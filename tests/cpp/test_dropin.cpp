@@ -164,6 +164,16 @@ int main(int argc, char** argv) {
             auto L = chol(A);
             CHECK(!L.has_value() && L.error() == "A is not positive definite.");
         }
+        for (const char* name : {"/bcsstk01.mtx", "/1138_bus.mtx"}) {   // the reader with parse and COO -> CSC on the GPU: same matrix, bit for bit
+            auto A = load_matrix_market_to_csc<double>(data + name);
+            auto B = load_matrix_market_to_csc_gpu<double>(data + name);
+            CHECK(B.size() == A.size() && B.p() == A.p() && B.i() == A.i() && B.x() == A.x());
+        }
+        {
+            bool threw = false;
+            try { load_matrix_market_to_csc_gpu<double>("/nonexistent.mtx"); } catch (const std::runtime_error&) { threw = true; }
+            CHECK(threw);
+        }
     } else {
         auto A = triplet_to_csc_matrix<double>({0, 0, 1}, {0, 1, 1}, {4.0, 1.0, 3.0}, 2);
         auto L = chol(A);
